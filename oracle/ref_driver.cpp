@@ -141,7 +141,9 @@ void orc_sort(orc_particle* first_, orc_particle* second_, uint32_t* cell_table,
   const SP parameters = sp(params);
   const unsigned n = parameters.particles_count;
   const int kBucketCount = 256, kRadixWidth = 8;
-  const int T = thread_count > 0 ? thread_count : 1024;
+  /* the reference needs T <= N (get_start_and_end underflows otherwise, sort.cl:10-16) */
+  int T = thread_count > 0 ? thread_count : 1024;
+  if ((unsigned)T > n) T = n > 0 ? (int)n : 1;
   P* cur_in = mp(first_);
   P* cur_out = mp(second_);
 
