@@ -1,0 +1,160 @@
+/* sphb — the extern "C" boundary of the B200 SPH step engine.
+ *
+ * The reference (ngromko/libclsph) has no plugin / FFI interface: its hot path is the
+ * private half of `class sph_simulation`, which talks to OpenCL through cl::Kernel and
+ * cl::Buffer members (libclsph/sph_simulation.h:29-72).  This header is what replaces
+ * that private half.  The C++11 `sph_simulation` in libclsph_b200/host/ keeps the
+ * reference's public surface (libclsph/sph_simulation.h:10-27) and calls ONLY these
+ * entry points; any other host language binds them the same way.
+ *
+ * Conventions
+ *   - plain C ABI: POD arguments, caller-owned host memory, engine-owned device memory,
+ *     no callbacks across the boundary, no torch / STL types in any signature;
+ *   - every call returns 0 on success; > 0 is a cudaError_t (or an ncclResult_t offset by
+ *     SPHB_ERR_NCCL_BASE), < 0 is one of the SPHB_ERR_* codes below; sphb_last_error()
+ *     gives the text with the file:line of the failing call (the C++ wrapper prints it and
+ *     exit(-1)s, the reference's EXIT_ON_CL_ERROR convention, util/cl_boilerplate.h:32-34);
+ *   - one engine = one GPU = one CUDA stream; an engine is not thread-safe;
+ *   - there is NO CPU fallback: without a CUDA device sphb_create() fails.
+ *
+ * Struct layouts are the reference's, byte for byte (OpenCL float3 = 16 bytes):
+ * libclsph/common/structures.h:16-65.
+ */
+#ifndef SPHB_H_
+#define SPHB_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SPHB_VERSION 1
+
+/* engine error codes (< 0) */
+#define SPHB_ERR_INVALID (-1)     /* bad argument / call order (e.g. step before upload) */
+#define SPHB_ERR_GRID (-2)        /* a grid dimension reached 1024: the reference asserts here
+                                     (libclsph/sph_simulation.cpp:722-724) */
+#define SPHB_ERR_NO_DEVICE (-3)   /* no usable CUDA device */
+#define SPHB_ERR_NO_SCENE (-4)    /* sphb_step before sphb_set_scene */
+#define SPHB_ERR_NCCL_MISSING (-5)/* multi-GPU entry point used but libnccl could not be loaded */
+#define SPHB_ERR_NCCL_BASE 100000 /* ncclResult_t r is returned as SPHB_ERR_NCCL_BASE + r */
+
+typedef struct { float s[4]; } sphb_float3; /* cl_float3 */
+
+/* libclsph/common/structures.h:40-44 — 80 bytes */
+typedef struct {
+  sphb_float3 position, velocity, intermediate_velocity, acceleration;
+  float density, pressure;
+  uint32_t grid_index;
+  uint32_t pad_;
+} sphb_particle;
+
+/* libclsph/common/structures.h:16-38 — 128 bytes */
+typedef struct {
+  uint32_t particles_count;
+  float fluid_density, total_mass, particle_mass, dynamic_viscosity;
+  float simulation_time, h, simulation_scale, target_fps;
+  float surface_tension_threshold, surface_tension, restitution, K;
+  uint32_t pad0_[3];
+  sphb_float3 constant_acceleration;
+  int32_t grid_size_x, grid_size_y, grid_size_z;
+  uint32_t grid_cell_count;
+  sphb_float3 min_point, max_point;
+} sphb_params;
+
+/* libclsph/common/structures.h:46-52 — 20 bytes */
+typedef struct {
+  float poly_6, poly_6_gradient, poly_6_laplacian, spiky, viscosity;
+} sphb_terms;
+
+/* libclsph/common/structures.h:54-65 — 56 bytes */
+typedef struct {
+  float maxx, maxy, maxz, minx, miny, minz;
+  size_t size_x, size_y, size_z, offset;
+} sphb_bb;
+
+typedef struct sphb_engine sphb_engine;
+
+/* Replaces init_cl_single_device + make_program + the make_kernel block + the buffer
+ * allocations of sph_simulation::simulate() (libclsph/sph_simulation.cpp:272-326).
+ * `device` is a CUDA ordinal (-1 = current device).  params->particles_count fixes the
+ * capacity; the physics constants are copied. */
+int sphb_create(const sphb_params* params, const sphb_terms* terms, int device,
+                sphb_engine** out);
+int sphb_destroy(sphb_engine* e);
+
+/* Replaces the bb_buffer_ upload (libclsph/sph_simulation.cpp:321-326) and
+ * sph_simulation::computeDistanceField() (:607-632 -> kernels/collisionsv2.cl:57-138):
+ * uploads the scene::load() products and builds the distance field on the device.
+ * transforms: 12 floats per face, rvertices: 4 floats per face. */
+int sphb_set_scene(sphb_engine* e, const sphb_bb* bbs, uint32_t face_count,
+                   const float* transforms, const float* rvertices,
+                   uint32_t total_grid_points);
+/* Copies the device distance field (total_grid_points floats) to `out` — for parity tests. */
+int sphb_get_distance_field(sphb_engine* e, float* out);
+
+/* Replaces the initial enqueueWriteBuffer (libclsph/sph_simulation.cpp:334-336) and the
+ * write-back after a pre/post-frame hook returned true (:743-745, :763-765).
+ * n must equal particles_count. */
+int sphb_upload(sphb_engine* e, const sphb_particle* aos, uint32_t n);
+
+/* Replaces sph_simulation::simulate_single_frame (libclsph/sph_simulation.cpp:200-263):
+ * bbox -> locate_in_grid -> sort_particles (+cell table) -> density_pressure -> forces ->
+ * { advection_collision(dt) ; computeTimeStep } until dt - computed <= 1e-5.
+ * *dt_out = the value the reference returns (time advanced and next step's dt). */
+int sphb_step(sphb_engine* e, float dt_in, float* dt_out);
+
+/* The engine's copy of `parameters` as the reference mutates it every step
+ * (min_point, max_point, grid_size_*, grid_cell_count; sph_simulation.cpp:670-727). */
+int sphb_get_parameters(sphb_engine* e, sphb_params* out);
+
+/* Replaces the enqueueReadBuffer of the whole state (libclsph/sph_simulation.cpp:415-417,
+ * :736-738): AoS, in the device's current (cell-sorted) order, exactly the order the
+ * reference would hold.  Padding lanes are written as 0. */
+int sphb_download(sphb_engine* e, sphb_particle* aos);
+
+/* Parity hooks for the last step (each pointer nullable):
+ *   keys[N]   sorted grid_index of every particle,
+ *   perm[N]   perm[k] = position BEFORE this step's sort of the particle now at k,
+ *   cell_table[min(cap, grid_cell_count)]  the reference's cell table (kernels/sort.cl:61-78),
+ *   attempts  how many times advection_collision was launched (>= 1). */
+int sphb_download_debug(sphb_engine* e, uint32_t* keys, uint32_t* perm, uint32_t* cell_table,
+                        uint32_t cell_table_cap, int* attempts);
+
+/* ---- measurement ------------------------------------------------------------------ */
+enum {
+  SPHB_PASS_BBOX = 0,    /* min/max of positions (only after an upload; otherwise fused in advect) */
+  SPHB_PASS_LOCATE,      /* Morton key per particle */
+  SPHB_PASS_SORT,        /* key/index radix sort, all passes */
+  SPHB_PASS_REORDER,     /* gather of pos / vel / v_half into sorted SoA */
+  SPHB_PASS_CELLTABLE,   /* cell start offsets */
+  SPHB_PASS_DENSITY,     /* density + pressure */
+  SPHB_PASS_FORCES,      /* forces -> acceleration */
+  SPHB_PASS_ADVECT,      /* advection + collision + max|v|^2, max|a|^2, bbox reductions */
+  SPHB_PASS_COUNT
+};
+/* When enabled, every pass of sphb_step is bracketed by CUDA events on the engine's
+ * stream; sphb_get_pass_times returns the accumulated milliseconds and launch counts
+ * since the last reset (this synchronises the stream). */
+int sphb_profile_enable(sphb_engine* e, int on);
+int sphb_profile_reset(sphb_engine* e);
+int sphb_get_pass_times(sphb_engine* e, float ms[SPHB_PASS_COUNT],
+                        uint32_t launches[SPHB_PASS_COUNT], uint32_t* steps);
+/* number of kernel launches issued by this engine since creation */
+uint64_t sphb_launch_count(sphb_engine* e);
+/* the engine's cudaStream_t (as void*), so a caller can record its own events on it */
+void* sphb_stream(sphb_engine* e);
+/* named integer options; unknown names return SPHB_ERR_INVALID.
+ *   "neighbor_kernel"  0 = per-particle 27-cell walk, 1 = cell-tile staged kernel (default) */
+int sphb_set_option(sphb_engine* e, const char* name, int value);
+
+const char* sphb_last_error(sphb_engine* e);
+/* text for a return code when no engine exists (sphb_create failed) */
+const char* sphb_error_string(int code);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SPHB_H_ */

@@ -1,0 +1,129 @@
+// Shared declarations of the sphb engine's translation units (internal; the public
+// boundary is include/sphb.h).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/sphb.h"
+
+namespace sphb {
+
+// Everything a kernel needs from `simulation_parameters` / `precomputed_kernel_values`
+// for one step, passed by value (the reference passes the whole 128-byte struct by value
+// to every kernel, libclsph/sph_simulation.cpp:205-206,224).
+struct StepConsts {
+  uint32_t n;                // particles_count
+  uint32_t grid_cell_count;  // Morton bound of the grid (cell table length)
+  float h, h2, cell;         // support radius, h*h, cell side = h*2
+  float minx, miny, minz;    // min_point
+  float mass, K, rho0, mu;   // particle_mass, K, fluid_density, dynamic_viscosity
+  float st_threshold, st;    // surface_tension_threshold, surface_tension
+  float gx, gy, gz;          // constant_acceleration
+  float c_poly6, c_poly6_grad, c_poly6_lap, c_spiky, c_visc;
+  float spiky_eps;           // -45 / (float)(M_PI * h^6): spiky_gradient's r < 1e-7 branch
+};
+
+// One face of the scene for the collision pass: inflated AABB + its distance-field grid
+// (libclsph/common/structures.h:54-65, integers pre-converted to fp32 because the
+// reference does its index arithmetic in fp32, kernels/collisionsv2.cl:152-156).
+struct Face {
+  float maxx, maxy, maxz, minx;  // one float4
+  float miny, minz, sx, sz;      // one float4: size_x, size_z as float
+  float sxm1, sym1, szm1, off;   // one float4: size-1 as float, offset as float
+};
+
+// Reduction cell shared by the bbox / time-step reductions.  Floats are stored in an
+// order-preserving unsigned encoding so that atomicMin/atomicMax work on them.
+struct Reduce {
+  unsigned min_enc[3];
+  unsigned max_enc[3];
+  unsigned max_v2;  // max |velocity|^2      (kernels/reduction.cl:66-94)
+  unsigned max_a2;  // max |acceleration|^2  (kernels/reduction.cl:96-124)
+};
+
+__host__ __device__ inline unsigned enc_float(float f) {
+#ifdef __CUDA_ARCH__
+  unsigned b = __float_as_uint(f);
+#else
+  unsigned b;
+  memcpy(&b, &f, 4);
+#endif
+  return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__host__ __device__ inline float dec_float(unsigned u) {
+  unsigned b = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u;
+#ifdef __CUDA_ARCH__
+  return __uint_as_float(b);
+#else
+  float f;
+  memcpy(&f, &b, 4);
+  return f;
+#endif
+}
+
+// 10-bit-per-axis Morton code (libclsph/common/util.h:41-62) and its inverse (:4-38).
+__host__ __device__ inline uint32_t spread10(uint32_t x) {
+  x = (x | (x << 16)) & 0x030000FFu;
+  x = (x | (x << 8)) & 0x0300F00Fu;
+  x = (x | (x << 4)) & 0x030C30C3u;
+  x = (x | (x << 2)) & 0x09249249u;
+  return x;
+}
+__host__ __device__ inline uint32_t morton3(uint32_t x, uint32_t y, uint32_t z) {
+  return spread10(x) | (spread10(y) << 1) | (spread10(z) << 2);
+}
+__host__ __device__ inline uint32_t compact10(uint32_t v) {
+  v &= 0x09249249u;
+  v = (v | (v >> 2)) & 0x030C30C3u;
+  v = (v | (v >> 4)) & 0x0300F00Fu;
+  v = (v | (v >> 8)) & 0x030000FFu;
+  v = (v | (v >> 16)) & 0x000003FFu;
+  return v;
+}
+
+// ---- launchers (each enqueues on `s` and returns the number of kernels launched) -------
+// kernels_exact.cu  (compiled with -fmad=false: results are those of the literal
+// expression trees, bit-identical to the CPU checker)
+int launch_reduce_init(Reduce* red, cudaStream_t s);
+int launch_bbox(const float4* pos, uint32_t n, Reduce* red, cudaStream_t s);
+int launch_locate(const float4* pos, uint32_t* keys, const StepConsts& c, cudaStream_t s);
+int launch_reorder(const uint32_t* perm, uint32_t n, const float4* pos_in, const float4* vel_in,
+                   const float4* vhf_in, float4* pos_out, float4* vel_out, float4* vhf_out,
+                   cudaStream_t s);
+int launch_cell_table(const uint32_t* sorted_keys, uint32_t n, uint32_t* table, uint32_t ncell,
+                      cudaStream_t s);
+int launch_advect(const float4* pos, const float4* vhf, const float4* acc, float4* pos_out,
+                  float4* vel_out, float4* vhf_out, uint32_t n, float dt, float restitution,
+                  const Face* faces, uint32_t face_count, const float* df, Reduce* red,
+                  cudaStream_t s);
+int launch_distance_field(float* df, const Face* faces, const uint32_t* face_offsets,
+                          const float* transforms, const float* rvertices, uint32_t face_count,
+                          uint32_t gridcount, cudaStream_t s);
+int launch_aos_to_soa(const sphb_particle* aos, uint32_t n, float4* pos, float4* vel, float4* vhf,
+                      float4* acc, float* rho, float* prs, uint32_t* keys, cudaStream_t s);
+int launch_soa_to_aos(sphb_particle* aos, uint32_t n, const float4* pos, const float4* vel,
+                      const float4* vhf, const float4* acc, const float* rho, const float* prs,
+                      const uint32_t* keys, cudaStream_t s);
+
+// kernels_sort.cu — stable LSD radix sort of (key, index) pairs, 8 bits per pass.
+struct SortBuffers {
+  uint32_t* keys[2];     // n each; the unsorted keys are in keys[0]
+  uint32_t* vals[2];     // n each
+  uint32_t* hist;        // sort_hist_entries(n)
+  uint32_t* block_sums;  // sort_block_sum_entries(n)
+};
+size_t sort_hist_entries(uint32_t n);
+size_t sort_block_sum_entries(uint32_t n);
+// Sorts over the low `key_bits` bits.  On return *result = r means: sorted keys are in
+// keys[r] and vals[r][k] = original index of the element now at k.  Returns launches.
+int launch_sort_pairs(const SortBuffers& b, uint32_t n, int key_bits, int* result,
+                      cudaStream_t s);
+
+// kernels_neighbors.cu (compiled with FMA contraction on; tolerance-checked)
+int launch_density(float4* pos, float4* vel, const uint32_t* keys, const uint32_t* table,
+                   float* rho, float* prs, const StepConsts& c, int variant, cudaStream_t s);
+int launch_forces(const float4* pos, const float4* vel, const uint32_t* keys,
+                  const uint32_t* table, const float* rho, float4* acc, const StepConsts& c,
+                  int variant, cudaStream_t s);
+
+}  // namespace sphb

@@ -1,0 +1,580 @@
+// sphb engine: host orchestration of one SPH step on one B200 + the extern "C" boundary
+// declared in include/sphb.h.  Restates libclsph/sph_simulation.cpp:200-263
+// (simulate_single_frame), :110-198 (sort_particles), :634-728 (findMinMaxPosition),
+// :536-605 (computeTimeStep) and :607-632 (computeDistanceField) as a sequence of CUDA
+// launches on one stream with ONE host read-back per step (32 bytes: max|v|^2, max|a|^2 and
+// the bbox of the advected positions, which is the next step's grid), instead of the
+// reference's four blocking reads and five buffer allocations per step.
+//
+// There is no CPU path in this file: every pass is a kernel from kernels_*.cu.
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "common.cuh"
+
+using namespace sphb;
+
+struct sphb_engine {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  uint32_t n = 0;
+  sphb_params params;   // the reference's `parameters`, mutated every step
+  sphb_terms terms;
+  float spiky_eps = 0.f;
+
+  // sorted SoA state; pos/vel/vhf are ping-pong pairs, cur[] says which half is live
+  float4* pos[2] = {nullptr, nullptr};
+  float4* vel[2] = {nullptr, nullptr};
+  float4* vhf[2] = {nullptr, nullptr};
+  int cur = 0;
+  float4* acc = nullptr;
+  float* rho = nullptr;
+  float* prs = nullptr;
+  SortBuffers sortb = {};
+  int sorted = 0;            // which half of sortb holds the last step's sorted keys / perm
+  uint32_t* cell_table = nullptr;
+  uint32_t cell_table_cap = 0;
+  sphb_particle* aos_stage = nullptr;  // device staging for upload / download
+
+  // scene
+  Face* faces = nullptr;
+  uint32_t* face_offsets = nullptr;
+  float* df = nullptr;
+  uint32_t face_count = 0, total_grid_points = 0;
+  bool have_scene = false;
+
+  // reductions
+  Reduce* red = nullptr;       // device
+  Reduce* red_host = nullptr;  // pinned
+  bool bbox_valid = false;     // red_host holds the bbox of the live positions
+  bool have_state = false;
+  int last_attempts = 0;
+  bool stepped = false;
+
+  // options / measurement
+  int neighbor_variant = 0;
+  bool profile = false;
+  cudaEvent_t ev[SPHB_PASS_COUNT + 1][2];
+  bool ev_created = false;
+  float pass_ms[SPHB_PASS_COUNT] = {};
+  uint32_t pass_launches[SPHB_PASS_COUNT] = {};
+  uint32_t prof_steps = 0;
+  uint64_t launches = 0;
+
+  std::string err;
+};
+
+namespace {
+
+thread_local std::string g_create_error;
+
+int fail(sphb_engine* e, int code, const char* file, int line, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  char full[640];
+  snprintf(full, sizeof full, "sphb error %d (%s:%d): %s", code, file, line, buf);
+  if (e) e->err = full; else g_create_error = full;
+  return code;
+}
+
+#define CUDA_TRY(e, call)                                                                   \
+  do {                                                                                      \
+    cudaError_t err__ = (call);                                                             \
+    if (err__ != cudaSuccess)                                                               \
+      return fail((e), (int)err__, __FILE__, __LINE__, "%s -> %s", #call,                   \
+                  cudaGetErrorString(err__));                                               \
+  } while (0)
+
+#define SPHB_FAIL(e, code, ...) return fail((e), (code), __FILE__, __LINE__, __VA_ARGS__)
+
+template <typename T>
+cudaError_t dev_alloc(T** p, size_t count) {
+  return cudaMalloc(reinterpret_cast<void**>(p), sizeof(T) * (count ? count : 1));
+}
+
+// libclsph/sph_simulation.cpp:668-727 — host fp32 arithmetic, same expressions.
+int grid_from_bbox(sphb_engine* e, const float mn[3], const float mx[3]) {
+  sphb_params& P = e->params;
+  const float side = (P.h * 2);
+  int32_t* gs[3] = {&P.grid_size_x, &P.grid_size_y, &P.grid_size_z};
+  for (int a = 0; a < 3; ++a) {
+    P.min_point.s[a] = mn[a] - 2 * side;
+    P.max_point.s[a] = mx[a] + 2 * side;
+    *gs[a] = (int32_t)static_cast<uint32_t>((P.max_point.s[a] - P.min_point.s[a]) / (side));
+  }
+  if (!(P.grid_size_x < 1024) || !(P.grid_size_y < 1024) || !(P.grid_size_z < 1024) ||
+      P.grid_size_x < 0 || P.grid_size_y < 0 || P.grid_size_z < 0)
+    SPHB_FAIL(e, SPHB_ERR_GRID, "grid %d x %d x %d: a dimension reached 1024 (the reference asserts, "
+              "sph_simulation.cpp:722-724)", P.grid_size_x, P.grid_size_y, P.grid_size_z);
+  P.grid_cell_count = morton3((uint32_t)P.grid_size_x, (uint32_t)P.grid_size_y, (uint32_t)P.grid_size_z);
+  return 0;
+}
+
+// libclsph/sph_simulation.cpp:598-602 — host fp32 arithmetic; comparisons against the
+// double literal 0.00001 as written.
+float dt_from_maxima(const sphb_params& P, float max_v2, float max_a2) {
+  float maxVel2 = max_v2;
+  float maxVel = std::sqrt(max_v2);
+  float maxAccel = std::sqrt(max_a2);
+  float dt = (std::sqrt(2 * maxAccel * P.h + maxVel2) - maxVel) / (2 * maxAccel);
+  if (dt < 0.00001) dt = 0.00001;
+  if (dt > 1.0f / (P.target_fps) * P.simulation_scale) dt = 1.0f / (P.target_fps) * P.simulation_scale;
+  return dt;
+}
+
+StepConsts make_consts(const sphb_engine* e) {
+  const sphb_params& P = e->params;
+  StepConsts c;
+  c.n = e->n;
+  c.grid_cell_count = P.grid_cell_count;
+  c.h = P.h;
+  c.h2 = P.h * P.h;
+  c.cell = (P.h * 2);
+  c.minx = P.min_point.s[0]; c.miny = P.min_point.s[1]; c.minz = P.min_point.s[2];
+  c.mass = P.particle_mass; c.K = P.K; c.rho0 = P.fluid_density; c.mu = P.dynamic_viscosity;
+  c.st_threshold = P.surface_tension_threshold; c.st = P.surface_tension;
+  c.gx = P.constant_acceleration.s[0]; c.gy = P.constant_acceleration.s[1];
+  c.gz = P.constant_acceleration.s[2];
+  c.c_poly6 = e->terms.poly_6; c.c_poly6_grad = e->terms.poly_6_gradient;
+  c.c_poly6_lap = e->terms.poly_6_laplacian; c.c_spiky = e->terms.spiky;
+  c.c_visc = e->terms.viscosity;
+  c.spiky_eps = e->spiky_eps;
+  return c;
+}
+
+struct PassTimer {
+  sphb_engine* e;
+  int pass;
+  PassTimer(sphb_engine* e_, int pass_) : e(e_), pass(pass_) {
+    if (e->profile) cudaEventRecord(e->ev[pass][0], e->stream);
+  }
+  void done(int launches) {
+    e->launches += launches;
+    if (e->profile) {
+      cudaEventRecord(e->ev[pass][1], e->stream);
+      e->pass_launches[pass] += launches;
+    }
+  }
+};
+
+}  // namespace
+
+extern "C" {
+
+const char* sphb_error_string(int code) {
+  if (!g_create_error.empty()) return g_create_error.c_str();
+  switch (code) {
+    case 0: return "ok";
+    case SPHB_ERR_INVALID: return "invalid argument or call order";
+    case SPHB_ERR_GRID: return "grid dimension reached 1024";
+    case SPHB_ERR_NO_DEVICE: return "no usable CUDA device";
+    case SPHB_ERR_NO_SCENE: return "no scene set";
+    case SPHB_ERR_NCCL_MISSING: return "libnccl could not be loaded";
+    default: return code > 0 ? cudaGetErrorString((cudaError_t)code) : "unknown sphb error";
+  }
+}
+
+const char* sphb_last_error(sphb_engine* e) { return e ? e->err.c_str() : g_create_error.c_str(); }
+
+int sphb_destroy(sphb_engine* e) {
+  if (!e) return 0;
+  cudaSetDevice(e->device);
+  if (e->stream) cudaStreamSynchronize(e->stream);
+  for (int k = 0; k < 2; ++k) {
+    cudaFree(e->pos[k]); cudaFree(e->vel[k]); cudaFree(e->vhf[k]);
+    cudaFree(e->sortb.keys[k]); cudaFree(e->sortb.vals[k]);
+  }
+  cudaFree(e->acc); cudaFree(e->rho); cudaFree(e->prs);
+  cudaFree(e->sortb.hist); cudaFree(e->sortb.block_sums);
+  cudaFree(e->cell_table); cudaFree(e->aos_stage);
+  cudaFree(e->faces); cudaFree(e->face_offsets); cudaFree(e->df);
+  cudaFree(e->red);
+  if (e->red_host) cudaFreeHost(e->red_host);
+  if (e->ev_created)
+    for (int p = 0; p <= SPHB_PASS_COUNT; ++p) {
+      cudaEventDestroy(e->ev[p][0]);
+      cudaEventDestroy(e->ev[p][1]);
+    }
+  if (e->stream) cudaStreamDestroy(e->stream);
+  delete e;
+  return 0;
+}
+
+int sphb_create(const sphb_params* params, const sphb_terms* terms, int device, sphb_engine** out) {
+  g_create_error.clear();
+  if (!params || !terms || !out) SPHB_FAIL(nullptr, SPHB_ERR_INVALID, "null argument");
+  *out = nullptr;
+  if (params->particles_count == 0) SPHB_FAIL(nullptr, SPHB_ERR_INVALID, "particles_count == 0");
+  int count = 0;
+  if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) {
+    cudaGetLastError();
+    SPHB_FAIL(nullptr, SPHB_ERR_NO_DEVICE, "no CUDA device (this engine has no CPU path)");
+  }
+  if (device < 0) {
+    if (cudaGetDevice(&device) != cudaSuccess) device = 0;
+  }
+  if (device >= count) SPHB_FAIL(nullptr, SPHB_ERR_NO_DEVICE, "device %d of %d", device, count);
+
+  sphb_engine* e = new sphb_engine();
+  e->device = device;
+  e->params = *params;
+  e->terms = *terms;
+  e->n = params->particles_count;
+  {  // smoothing.cl:24: -45.f / convert_float(M_PI * pown(h, 6))
+    float h6 = params->h;
+    for (int k = 1; k < 6; ++k) h6 = h6 * params->h;
+    e->spiky_eps = -45.f / (float)(M_PI * h6);
+  }
+  const uint32_t n = e->n;
+#define TRY_OR_DESTROY(call)                                                           \
+  do {                                                                                 \
+    cudaError_t err__ = (call);                                                        \
+    if (err__ != cudaSuccess) {                                                        \
+      int rc = fail(nullptr, (int)err__, __FILE__, __LINE__, "%s -> %s", #call,        \
+                    cudaGetErrorString(err__));                                        \
+      sphb_destroy(e);                                                                 \
+      return rc;                                                                       \
+    }                                                                                  \
+  } while (0)
+  TRY_OR_DESTROY(cudaSetDevice(device));
+  TRY_OR_DESTROY(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
+  for (int k = 0; k < 2; ++k) {
+    TRY_OR_DESTROY(dev_alloc(&e->pos[k], n));
+    TRY_OR_DESTROY(dev_alloc(&e->vel[k], n));
+    TRY_OR_DESTROY(dev_alloc(&e->vhf[k], n));
+    TRY_OR_DESTROY(dev_alloc(&e->sortb.keys[k], n));
+    TRY_OR_DESTROY(dev_alloc(&e->sortb.vals[k], n));
+  }
+  TRY_OR_DESTROY(dev_alloc(&e->acc, n));
+  TRY_OR_DESTROY(dev_alloc(&e->rho, n));
+  TRY_OR_DESTROY(dev_alloc(&e->prs, n));
+  TRY_OR_DESTROY(dev_alloc(&e->sortb.hist, sort_hist_entries(n)));
+  TRY_OR_DESTROY(dev_alloc(&e->sortb.block_sums, sort_block_sum_entries(n)));
+  TRY_OR_DESTROY(dev_alloc(&e->red, 1));
+  TRY_OR_DESTROY(cudaMallocHost(reinterpret_cast<void**>(&e->red_host), sizeof(Reduce)));
+  for (int p = 0; p <= SPHB_PASS_COUNT; ++p) {
+    TRY_OR_DESTROY(cudaEventCreate(&e->ev[p][0]));
+    TRY_OR_DESTROY(cudaEventCreate(&e->ev[p][1]));
+  }
+  e->ev_created = true;
+  // zero everything that a download-before-step may read
+  TRY_OR_DESTROY(cudaMemsetAsync(e->sortb.keys[0], 0, sizeof(uint32_t) * n, e->stream));
+  TRY_OR_DESTROY(cudaMemsetAsync(e->sortb.vals[0], 0, sizeof(uint32_t) * n, e->stream));
+  TRY_OR_DESTROY(cudaStreamSynchronize(e->stream));
+#undef TRY_OR_DESTROY
+  *out = e;
+  return 0;
+}
+
+int sphb_set_scene(sphb_engine* e, const sphb_bb* bbs, uint32_t face_count, const float* transforms,
+                   const float* rvertices, uint32_t total_grid_points) {
+  if (!e) return SPHB_ERR_INVALID;
+  if (face_count && (!bbs || !transforms || !rvertices))
+    SPHB_FAIL(e, SPHB_ERR_INVALID, "null scene arrays");
+  CUDA_TRY(e, cudaSetDevice(e->device));
+  CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+  cudaFree(e->faces); cudaFree(e->face_offsets); cudaFree(e->df);
+  e->faces = nullptr; e->face_offsets = nullptr; e->df = nullptr;
+  e->face_count = face_count;
+  e->total_grid_points = total_grid_points;
+
+  std::vector<Face> faces(face_count);
+  std::vector<uint32_t> offsets(face_count);
+  size_t pad = 2;
+  for (uint32_t i = 0; i < face_count; ++i) {
+    const sphb_bb& b = bbs[i];
+    Face& f = faces[i];
+    f.maxx = b.maxx; f.maxy = b.maxy; f.maxz = b.maxz;
+    f.minx = b.minx; f.miny = b.miny; f.minz = b.minz;
+    f.sx = (float)b.size_x; f.sz = (float)b.size_z;
+    f.sxm1 = (float)(b.size_x - 1); f.sym1 = (float)(b.size_y - 1); f.szm1 = (float)(b.size_z - 1);
+    f.off = (float)b.offset;
+    offsets[i] = (uint32_t)b.offset;
+    if (i && offsets[i] <= offsets[i - 1])
+      SPHB_FAIL(e, SPHB_ERR_INVALID, "BB offsets must be strictly increasing (face %u)", i);
+    const size_t reach = b.size_x * b.size_z + b.size_x + 2;
+    if (reach > pad) pad = reach;
+  }
+  // The reference samples df at (x+1, y+1, z+1) of the containing grid cell without a bound
+  // check (collisionsv2.cl:279-292): a position on a grid's upper face reads past that
+  // grid.  The field is padded with zeros so such reads stay inside the allocation.
+  const size_t df_len = (size_t)total_grid_points + pad;
+  CUDA_TRY(e, dev_alloc(&e->faces, face_count));
+  CUDA_TRY(e, dev_alloc(&e->face_offsets, face_count));
+  CUDA_TRY(e, dev_alloc(&e->df, df_len));
+  CUDA_TRY(e, cudaMemsetAsync(e->df, 0, sizeof(float) * df_len, e->stream));
+  float* d_tr = nullptr;
+  float* d_rv = nullptr;
+  if (face_count) {
+    CUDA_TRY(e, cudaMemcpyAsync(e->faces, faces.data(), sizeof(Face) * face_count,
+                                cudaMemcpyHostToDevice, e->stream));
+    CUDA_TRY(e, cudaMemcpyAsync(e->face_offsets, offsets.data(), sizeof(uint32_t) * face_count,
+                                cudaMemcpyHostToDevice, e->stream));
+    CUDA_TRY(e, dev_alloc(&d_tr, (size_t)face_count * 12));
+    CUDA_TRY(e, dev_alloc(&d_rv, (size_t)face_count * 4));
+    CUDA_TRY(e, cudaMemcpyAsync(d_tr, transforms, sizeof(float) * 12 * face_count,
+                                cudaMemcpyHostToDevice, e->stream));
+    CUDA_TRY(e, cudaMemcpyAsync(d_rv, rvertices, sizeof(float) * 4 * face_count,
+                                cudaMemcpyHostToDevice, e->stream));
+    e->launches += launch_distance_field(e->df, e->faces, e->face_offsets, d_tr, d_rv, face_count,
+                                         total_grid_points, e->stream);
+    CUDA_TRY(e, cudaGetLastError());
+  }
+  CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+  cudaFree(d_tr);
+  cudaFree(d_rv);
+  e->have_scene = true;
+  return 0;
+}
+
+int sphb_get_distance_field(sphb_engine* e, float* out) {
+  if (!e || !out) return SPHB_ERR_INVALID;
+  if (!e->have_scene) SPHB_FAIL(e, SPHB_ERR_NO_SCENE, "no scene");
+  CUDA_TRY(e, cudaSetDevice(e->device));
+  CUDA_TRY(e, cudaMemcpyAsync(out, e->df, sizeof(float) * e->total_grid_points,
+                              cudaMemcpyDeviceToHost, e->stream));
+  CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+  return 0;
+}
+
+int sphb_upload(sphb_engine* e, const sphb_particle* aos, uint32_t n) {
+  if (!e || !aos) return SPHB_ERR_INVALID;
+  if (n != e->n) SPHB_FAIL(e, SPHB_ERR_INVALID, "upload of %u particles into an engine of %u", n, e->n);
+  CUDA_TRY(e, cudaSetDevice(e->device));
+  if (!e->aos_stage) CUDA_TRY(e, dev_alloc(&e->aos_stage, n));
+  CUDA_TRY(e, cudaMemcpyAsync(e->aos_stage, aos, sizeof(sphb_particle) * n, cudaMemcpyHostToDevice,
+                              e->stream));
+  e->launches += launch_aos_to_soa(e->aos_stage, n, e->pos[e->cur], e->vel[e->cur], e->vhf[e->cur],
+                                   e->acc, e->rho, e->prs, e->sortb.keys[e->sorted], e->stream);
+  CUDA_TRY(e, cudaGetLastError());
+  CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+  e->bbox_valid = false;
+  e->have_state = true;
+  return 0;
+}
+
+namespace {
+
+// Reads the device reduction cell back (32 bytes) and waits for it: the one host
+// synchronisation of a step.
+int fetch_reduce(sphb_engine* e) {
+  CUDA_TRY(e, cudaMemcpyAsync(e->red_host, e->red, sizeof(Reduce), cudaMemcpyDeviceToHost, e->stream));
+  CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+  return 0;
+}
+
+void accumulate_pass(sphb_engine* e, int pass) {
+  float ms = 0.f;
+  if (cudaEventElapsedTime(&ms, e->ev[pass][0], e->ev[pass][1]) == cudaSuccess) e->pass_ms[pass] += ms;
+}
+
+int key_bits_for(uint32_t grid_cell_count) {
+  int bits = 0;
+  while (bits < 32 && (grid_cell_count >> bits) != 0) ++bits;
+  return bits < 1 ? 1 : bits;
+}
+
+}  // namespace
+
+int sphb_step(sphb_engine* e, float dt_in, float* dt_out) {
+  if (!e) return SPHB_ERR_INVALID;
+  if (!e->have_state) SPHB_FAIL(e, SPHB_ERR_INVALID, "sphb_step before sphb_upload");
+  if (!e->have_scene) SPHB_FAIL(e, SPHB_ERR_NO_SCENE, "sphb_step before sphb_set_scene");
+  CUDA_TRY(e, cudaSetDevice(e->device));
+  cudaStream_t s = e->stream;
+  const uint32_t n = e->n;
+  bool ran_bbox = false;
+
+  // 1. findMinMaxPosition (sph_simulation.cpp:634-728).  After the first step the bbox of
+  //    the live positions was already reduced by the advection kernel that wrote them.
+  if (!e->bbox_valid) {
+    PassTimer t(e, SPHB_PASS_BBOX);
+    int l = launch_reduce_init(e->red, s);
+    l += launch_bbox(e->pos[e->cur], n, e->red, s);
+    t.done(l);
+    CUDA_TRY(e, cudaGetLastError());
+    if (int rc = fetch_reduce(e)) return rc;
+    ran_bbox = true;
+  }
+  {
+    float mn[3], mx[3];
+    for (int a = 0; a < 3; ++a) {
+      mn[a] = dec_float(e->red_host->min_enc[a]);
+      mx[a] = dec_float(e->red_host->max_enc[a]);
+    }
+    if (int rc = grid_from_bbox(e, mn, mx)) return rc;
+  }
+  const uint32_t ncell = e->params.grid_cell_count;
+  if (ncell + 1 > e->cell_table_cap) {  // grows rarely: capacity is kept with 2x headroom
+    CUDA_TRY(e, cudaStreamSynchronize(s));
+    cudaFree(e->cell_table);
+    e->cell_table = nullptr;
+    uint32_t cap = 2 * (ncell + 1);
+    if (cap < 4096) cap = 4096;
+    CUDA_TRY(e, dev_alloc(&e->cell_table, cap));
+    e->cell_table_cap = cap;
+  }
+  const StepConsts c = make_consts(e);
+
+  // 2. locate_in_grid (kernels/grid.cl:40-64): keys only, no struct copy
+  {
+    PassTimer t(e, SPHB_PASS_LOCATE);
+    t.done(launch_locate(e->pos[e->cur], e->sortb.keys[0], c, s));
+  }
+  // 3. sort_particles (sph_simulation.cpp:110-198): (key, index) pairs, significant bits only
+  int r = 0;
+  {
+    PassTimer t(e, SPHB_PASS_SORT);
+    t.done(launch_sort_pairs(e->sortb, n, key_bits_for(ncell), &r, s));
+  }
+  e->sorted = r;
+  {
+    PassTimer t(e, SPHB_PASS_REORDER);
+    const int in = e->cur, out = in ^ 1;
+    t.done(launch_reorder(e->sortb.vals[r], n, e->pos[in], e->vel[in], e->vhf[in], e->pos[out],
+                          e->vel[out], e->vhf[out], s));
+    e->cur = out;
+  }
+  {
+    PassTimer t(e, SPHB_PASS_CELLTABLE);
+    t.done(launch_cell_table(e->sortb.keys[r], n, e->cell_table, ncell, s));
+  }
+  // 4. density_pressure (kernels/sphb.cl:3-35), 5. forces (:37-126)
+  {
+    PassTimer t(e, SPHB_PASS_DENSITY);
+    t.done(launch_density(e->pos[e->cur], e->vel[e->cur], e->sortb.keys[r], e->cell_table, e->rho,
+                          e->prs, c, e->neighbor_variant, s));
+  }
+  {
+    PassTimer t(e, SPHB_PASS_FORCES);
+    t.done(launch_forces(e->pos[e->cur], e->vel[e->cur], e->sortb.keys[r], e->cell_table, e->rho,
+                         e->acc, c, e->neighbor_variant, s));
+  }
+  CUDA_TRY(e, cudaGetLastError());
+
+  // 6. do { advection_collision(dt); computed = computeTimeStep } while (dt - computed > 1e-5)
+  //    (sph_simulation.cpp:246-260)
+  int attempts = 0;
+  float dt = dt_in, computed = dt_in;
+  const int in = e->cur, out = in ^ 1;
+  do {
+    dt = computed;
+    {
+      PassTimer t(e, SPHB_PASS_ADVECT);
+      int l = launch_reduce_init(e->red, s);
+      l += launch_advect(e->pos[in], e->vhf[in], e->acc, e->pos[out], e->vel[out], e->vhf[out], n,
+                         dt, e->params.restitution, e->faces, e->face_count, e->df, e->red, s);
+      t.done(l);
+    }
+    CUDA_TRY(e, cudaGetLastError());
+    if (int rc = fetch_reduce(e)) return rc;
+    if (e->profile) accumulate_pass(e, SPHB_PASS_ADVECT);
+    ++attempts;
+    computed = dt_from_maxima(e->params, dec_float(e->red_host->max_v2), dec_float(e->red_host->max_a2));
+  } while (dt - computed > 0.00001);
+  e->cur = out;
+  e->bbox_valid = true;
+  e->last_attempts = attempts;
+  e->stepped = true;
+  if (e->profile) {
+    if (ran_bbox) accumulate_pass(e, SPHB_PASS_BBOX);
+    for (int p = SPHB_PASS_LOCATE; p < SPHB_PASS_ADVECT; ++p) accumulate_pass(e, p);
+    e->prof_steps++;
+  }
+  if (dt_out) *dt_out = computed;
+  return 0;
+}
+
+int sphb_get_parameters(sphb_engine* e, sphb_params* out) {
+  if (!e || !out) return SPHB_ERR_INVALID;
+  *out = e->params;
+  return 0;
+}
+
+int sphb_download(sphb_engine* e, sphb_particle* aos) {
+  if (!e || !aos) return SPHB_ERR_INVALID;
+  if (!e->have_state) SPHB_FAIL(e, SPHB_ERR_INVALID, "sphb_download before sphb_upload");
+  CUDA_TRY(e, cudaSetDevice(e->device));
+  if (!e->aos_stage) CUDA_TRY(e, dev_alloc(&e->aos_stage, e->n));
+  e->launches += launch_soa_to_aos(e->aos_stage, e->n, e->pos[e->cur], e->vel[e->cur], e->vhf[e->cur],
+                                   e->acc, e->rho, e->prs, e->sortb.keys[e->sorted], e->stream);
+  CUDA_TRY(e, cudaGetLastError());
+  CUDA_TRY(e, cudaMemcpyAsync(aos, e->aos_stage, sizeof(sphb_particle) * e->n, cudaMemcpyDeviceToHost,
+                              e->stream));
+  CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+  return 0;
+}
+
+int sphb_download_debug(sphb_engine* e, uint32_t* keys, uint32_t* perm, uint32_t* cell_table,
+                        uint32_t cell_table_cap, int* attempts) {
+  if (!e) return SPHB_ERR_INVALID;
+  if (!e->stepped) SPHB_FAIL(e, SPHB_ERR_INVALID, "sphb_download_debug before the first sphb_step");
+  CUDA_TRY(e, cudaSetDevice(e->device));
+  if (keys)
+    CUDA_TRY(e, cudaMemcpyAsync(keys, e->sortb.keys[e->sorted], sizeof(uint32_t) * e->n,
+                                cudaMemcpyDeviceToHost, e->stream));
+  if (perm)
+    CUDA_TRY(e, cudaMemcpyAsync(perm, e->sortb.vals[e->sorted], sizeof(uint32_t) * e->n,
+                                cudaMemcpyDeviceToHost, e->stream));
+  if (cell_table) {
+    uint32_t cnt = e->params.grid_cell_count < cell_table_cap ? e->params.grid_cell_count : cell_table_cap;
+    if (cnt)
+      CUDA_TRY(e, cudaMemcpyAsync(cell_table, e->cell_table, sizeof(uint32_t) * cnt,
+                                  cudaMemcpyDeviceToHost, e->stream));
+  }
+  CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+  if (attempts) *attempts = e->last_attempts;
+  return 0;
+}
+
+int sphb_profile_enable(sphb_engine* e, int on) {
+  if (!e) return SPHB_ERR_INVALID;
+  e->profile = on != 0;
+  return 0;
+}
+
+int sphb_profile_reset(sphb_engine* e) {
+  if (!e) return SPHB_ERR_INVALID;
+  for (int p = 0; p < SPHB_PASS_COUNT; ++p) {
+    e->pass_ms[p] = 0.f;
+    e->pass_launches[p] = 0;
+  }
+  e->prof_steps = 0;
+  return 0;
+}
+
+int sphb_get_pass_times(sphb_engine* e, float ms[SPHB_PASS_COUNT], uint32_t launches[SPHB_PASS_COUNT],
+                        uint32_t* steps) {
+  if (!e) return SPHB_ERR_INVALID;
+  CUDA_TRY(e, cudaSetDevice(e->device));
+  CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+  for (int p = 0; p < SPHB_PASS_COUNT; ++p) {
+    if (ms) ms[p] = e->pass_ms[p];
+    if (launches) launches[p] = e->pass_launches[p];
+  }
+  if (steps) *steps = e->prof_steps;
+  return 0;
+}
+
+uint64_t sphb_launch_count(sphb_engine* e) { return e ? e->launches : 0; }
+
+void* sphb_stream(sphb_engine* e) { return e ? (void*)e->stream : nullptr; }
+
+int sphb_set_option(sphb_engine* e, const char* name, int value) {
+  if (!e || !name) return SPHB_ERR_INVALID;
+  if (!strcmp(name, "neighbor_kernel")) {
+    e->neighbor_variant = value;
+    return 0;
+  }
+  SPHB_FAIL(e, SPHB_ERR_INVALID, "unknown option '%s'", name);
+}
+
+}  // extern "C"

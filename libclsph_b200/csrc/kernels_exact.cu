@@ -1,0 +1,399 @@
+// Per-particle streaming kernels of the SPH step: bbox reduce, Morton locate, SoA reorder,
+// cell table, advection + distance-field collision, distance-field build, AoS<->SoA.
+//
+// This translation unit is compiled with -fmad=false (and CUDA's default IEEE '/' and
+// sqrt): every expression below evaluates exactly as the reference's expression tree does
+// without FMA contraction, so these passes are BIT-IDENTICAL to the CPU checker
+// (oracle/sph_oracle.c), not merely within tolerance.  They are all HBM-bound streaming
+// passes; the arithmetic is free.
+#include "common.cuh"
+
+namespace sphb {
+
+namespace {
+
+constexpr int kBlock = 256;
+
+__device__ __forceinline__ float warp_min(float v) {
+  for (int o = 16; o > 0; o >>= 1) v = fminf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// Block-level min/max of up to 8 values per thread, then one atomic per value per block.
+// vals[0..2] are minimised into red->min_enc, vals[3..5] maximised into red->max_enc,
+// vals[6], vals[7] maximised into max_v2 / max_a2.  `mask` selects which are live.
+__device__ __forceinline__ void block_reduce_to(Reduce* red, float (&vals)[8], unsigned mask) {
+  __shared__ float sh[8][kBlock / 32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    if (!(mask & (1u << k))) continue;
+    float v = (k < 3) ? warp_min(vals[k]) : warp_max(vals[k]);
+    if (lane == 0) sh[k][warp] = v;
+  }
+  __syncthreads();
+  if (warp == 0) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      if (!(mask & (1u << k))) continue;
+      float v = (lane < kBlock / 32) ? sh[k][lane] : (k < 3 ? INFINITY : -INFINITY);
+      v = (k < 3) ? warp_min(v) : warp_max(v);
+      if (lane == 0) {
+        if (k < 3) atomicMin(&red->min_enc[k], enc_float(v));
+        else if (k < 6) atomicMax(&red->max_enc[k - 3], enc_float(v));
+        else if (k == 6) atomicMax(&red->max_v2, enc_float(v));
+        else atomicMax(&red->max_a2, enc_float(v));
+      }
+    }
+  }
+}
+
+__global__ void k_reduce_init(Reduce* red) {
+  if (threadIdx.x == 0) {
+    for (int a = 0; a < 3; ++a) {
+      red->min_enc[a] = enc_float(INFINITY);
+      red->max_enc[a] = enc_float(-INFINITY);
+    }
+    red->max_v2 = enc_float(-INFINITY);
+    red->max_a2 = enc_float(-INFINITY);
+  }
+}
+
+// libclsph/kernels/reduction.cl:2-64 (minimum_pos + maximum_pos in one pass).
+__global__ void __launch_bounds__(kBlock) k_bbox(const float4* __restrict__ pos, uint32_t n,
+                                                 Reduce* red) {
+  float v[8] = {INFINITY, INFINITY, INFINITY, -INFINITY, -INFINITY, -INFINITY, 0.f, 0.f};
+  for (uint32_t i = blockIdx.x * kBlock + threadIdx.x; i < n; i += gridDim.x * kBlock) {
+    const float4 p = __ldg(pos + i);
+    v[0] = fminf(v[0], p.x); v[1] = fminf(v[1], p.y); v[2] = fminf(v[2], p.z);
+    v[3] = fmaxf(v[3], p.x); v[4] = fmaxf(v[4], p.y); v[5] = fmaxf(v[5], p.z);
+  }
+  block_reduce_to(red, v, 0x3f);
+}
+
+// libclsph/kernels/grid.cl:40-64: cell = (uint)((p - min) / (h*2)), key = Morton(cell).
+__global__ void __launch_bounds__(kBlock) k_locate(const float4* __restrict__ pos,
+                                                   uint32_t* __restrict__ keys, StepConsts c) {
+  const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
+  if (i >= c.n) return;
+  const float4 p = __ldg(pos + i);
+  const uint32_t cx = (uint32_t)((p.x - c.minx) / c.cell);
+  const uint32_t cy = (uint32_t)((p.y - c.miny) / c.cell);
+  const uint32_t cz = (uint32_t)((p.z - c.minz) / c.cell);
+  keys[i] = morton3(cx, cy, cz);
+}
+
+// The reference moves whole 80-byte structs in each of its 4 radix passes
+// (kernels/sort.cl:41-59); here only (key, index) pairs are sorted and the carried state
+// (position, velocity, intermediate_velocity: 36 of the 80 bytes) is gathered ONCE.
+__global__ void __launch_bounds__(kBlock)
+    k_reorder(const uint32_t* __restrict__ perm, uint32_t n, const float4* __restrict__ pos_in,
+              const float4* __restrict__ vel_in, const float4* __restrict__ vhf_in,
+              float4* __restrict__ pos_out, float4* __restrict__ vel_out,
+              float4* __restrict__ vhf_out) {
+  const uint32_t k = blockIdx.x * kBlock + threadIdx.x;
+  if (k >= n) return;
+  const uint32_t src = __ldg(perm + k);
+  float4 p = __ldg(pos_in + src), v = __ldg(vel_in + src), w = __ldg(vhf_in + src);
+  p.w = 0.f; v.w = 0.f; w.w = 0.f;
+  pos_out[k] = p;
+  vel_out[k] = v;
+  vhf_out[k] = w;
+}
+
+// libclsph/kernels/sort.cl:61-78 (+ the fillUintArray(cell_table, N) before it): entry c is
+// the index of the first sorted particle whose key is >= c.  One thread per CELL doing a
+// lower_bound, instead of one work-item per particle walking key gaps.  The reference's
+// quirk is kept: entries c <= key[0] are zeroed only by work-items that exist (c < N).
+__global__ void __launch_bounds__(kBlock)
+    k_cell_table(const uint32_t* __restrict__ keys, uint32_t n, uint32_t* __restrict__ table,
+                 uint32_t ncell) {
+  const uint32_t c = blockIdx.x * kBlock + threadIdx.x;
+  if (c >= ncell) return;
+  uint32_t lo = 0, hi = n;
+  while (lo < hi) {
+    const uint32_t mid = (lo + hi) >> 1;
+    if (__ldg(keys + mid) < c) lo = mid + 1; else hi = mid;
+  }
+  if (lo == 0 && c >= n) lo = n;
+  table[c] = lo;
+}
+
+// libclsph/kernels/collisionsv2.cl:140-156
+__device__ __forceinline__ float weighted_average(float x, float x1, float x2, float d1, float d2) {
+  return ((x2 - x) / (x2 - x1)) * d1 + ((x - x1) / (x2 - x1)) * d2;
+}
+__device__ __forceinline__ float bilinear(float x, float y, float xmin, float ymin, float xmax,
+                                          float ymax, float d00, float d01, float d10, float d11) {
+  const float R1 = weighted_average(x, xmin, xmax, d00, d10);
+  const float R2 = weighted_average(x, xmin, xmax, d01, d11);
+  return weighted_average(y, ymin, ymax, R1, R2);
+}
+__device__ __forceinline__ float len3(float x, float y, float z) {
+  return sqrtf((x * x + y * y) + z * z);
+}
+
+// libclsph/kernels/sphb.cl:177-223 (advection_collision) = advection.cl:6-18 (leapfrog) +
+// collisionsv2.cl:249-336 (handle_collisions) + :9-22 (respond), with the reductions of
+// computeTimeStep (reduction.cl:66-124) and of the NEXT step's findMinMaxPosition
+// (reduction.cl:2-64) fused in, so that a step ends with one 32-byte read-back.
+__global__ void __launch_bounds__(kBlock)
+    k_advect(const float4* __restrict__ pos, const float4* __restrict__ vhf,
+             const float4* __restrict__ acc, float4* __restrict__ pos_out,
+             float4* __restrict__ vel_out, float4* __restrict__ vhf_out, uint32_t n, float dt,
+             float restitution, const Face* __restrict__ faces, uint32_t face_count,
+             const float* __restrict__ df, Reduce* red) {
+  const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
+  float rv[8] = {INFINITY, INFINITY, INFINITY, -INFINITY, -INFINITY, -INFINITY, -INFINITY, -INFINITY};
+  if (i < n) {
+    const float4 x0 = __ldg(pos + i), vh = __ldg(vhf + i), a = __ldg(acc + i);
+    // leapfrog
+    const float nx = vh.x + a.x * dt, ny = vh.y + a.y * dt, nz = vh.z + a.z * dt;
+    const float px = x0.x + nx * dt, py = x0.y + ny * dt, pz = x0.z + nz * dt;
+
+    // LAST face whose inflated AABB contains the advected position
+    int indice = -1;
+    const float4* f4 = reinterpret_cast<const float4*>(faces);
+    for (int f = 0; f < (int)face_count; ++f) {
+      const float4 b0 = __ldg(f4 + 3 * f);
+      const float4 b1 = __ldg(f4 + 3 * f + 1);
+      if (px <= b0.x && px >= b0.w && py <= b0.y && py >= b1.x && pz <= b0.z && pz >= b1.y)
+        indice = f;
+    }
+    float rx = px, ry = py, rz = pz, wx = nx, wy = ny, wz = nz;
+    if (indice > -1) {
+      const Face F = faces[indice];
+      const float sidex = (F.maxx - F.minx) / F.sxm1;
+      const float sidey = (F.maxy - F.miny) / F.sym1;
+      const float sidez = (F.maxz - F.minz) / F.szm1;
+      const int x = (int)((px - F.minx) / sidex);
+      const int y = (int)((py - F.miny) / sidey);
+      const int z = (int)((pz - F.minz) / sidez);
+      const float bx = x * sidex + F.minx;
+      const float by = y * sidey + F.miny;
+      const float bz = z * sidez + F.minz;
+      const float xf = (float)x, yf = (float)y, zf = (float)z;
+      // getDFindex: fp32 index arithmetic, left to right (collisionsv2.cl:152-156)
+#define DFI(a_, b_, c_) \
+  __ldg(df + (int)(F.off + (yf + (float)(b_)) * F.sx * F.sz + F.sx * (zf + (float)(c_)) + xf + (float)(a_)))
+      const float d000 = DFI(0, 0, 0), d001 = DFI(0, 0, 1), d100 = DFI(1, 0, 0), d101 = DFI(1, 0, 1);
+      const float d010 = DFI(0, 1, 0), d011 = DFI(0, 1, 1), d110 = DFI(1, 1, 0), d111 = DFI(1, 1, 1);
+#undef DFI
+      const float facedown = bilinear(px, pz, bx, bz, bx + sidex, bz + sidez, d000, d001, d100, d101);
+      const float faceup = bilinear(px, pz, bx, bz, bx + sidex, bz + sidez, d010, d011, d110, d111);
+      const float d = weighted_average(py, by, by + sidey, facedown, faceup);
+      if ((double)d < 0.02) {  // compared in double, as the reference's literal makes it
+        const float faceright = bilinear(py, pz, by, bz, by + sidey, bz + sidez, d100, d101, d110, d111);
+        const float faceleft = bilinear(py, pz, by, bz, by + sidey, bz + sidez, d000, d001, d010, d011);
+        const float faceback = bilinear(px, py, bx, by, bx + sidex, by + sidey, d000, d010, d100, d110);
+        const float facefront = bilinear(px, py, bx, by, bx + sidex, by + sidey, d001, d011, d101, d111);
+        float mx = faceright - faceleft, my = faceup - facedown, mz = facefront - faceback;
+        const float lenn = len3(mx, my, mz);
+        mx = mx / lenn; my = my / lenn; mz = mz / lenn;
+        // respond()
+        const float ad = fabsf(d);
+        rx = px + ad * mx; ry = py + ad * my; rz = pz + ad * mz;
+        const float dotvn = (nx * mx + ny * my) + nz * mz;
+        const float f = (1.f + restitution * ad / (dt * len3(nx, ny, nz))) * dotvn;
+        wx = nx - f * mx; wy = ny - f * my; wz = nz - f * mz;
+      }
+    }
+    const float vx = (vh.x + wx) / 2.f, vy = (vh.y + wy) / 2.f, vz = (vh.z + wz) / 2.f;
+    pos_out[i] = make_float4(rx, ry, rz, 0.f);
+    vel_out[i] = make_float4(vx, vy, vz, 0.f);
+    vhf_out[i] = make_float4(wx, wy, wz, 0.f);
+    // fmin/fmax skip NaNs, as OpenCL's min/max do
+    rv[0] = rx; rv[1] = ry; rv[2] = rz; rv[3] = rx; rv[4] = ry; rv[5] = rz;
+    rv[6] = vx * vx + vy * vy + vz * vz;
+    rv[7] = a.x * a.x + a.y * a.y + a.z * a.z;
+    if (rx != rx) { rv[0] = INFINITY; rv[3] = -INFINITY; }
+    if (ry != ry) { rv[1] = INFINITY; rv[4] = -INFINITY; }
+    if (rz != rz) { rv[2] = INFINITY; rv[5] = -INFINITY; }
+    if (rv[6] != rv[6]) rv[6] = -INFINITY;
+    if (rv[7] != rv[7]) rv[7] = -INFINITY;
+  }
+  block_reduce_to(red, rv, 0xff);
+}
+
+// libclsph/kernels/collisionsv2.cl:24-55
+__device__ __forceinline__ float det2(float x1, float y1, float x2, float y2) {
+  return x1 * y2 - y1 * x2;
+}
+__device__ float dist_point_segment(float x, float y, float z, float x1, float y1, float x2,
+                                    float y2) {
+  const float A = y - x1, B = z - y1, C = x2 - x1, D = y2 - y1;
+  const float dot = A * C + B * D;
+  const float len_sq = C * C + D * D;
+  float param = -1;
+  if (len_sq != 0) param = dot / len_sq;
+  float xx, yy;
+  if (param < 0) {
+    xx = x1; yy = y1;
+  } else if (param > 1) {
+    xx = x2; yy = y2;
+  } else {
+    xx = x1 + param * C; yy = y1 + param * D;
+  }
+  const float dy = y - xx, dz = z - yy;
+  return sqrtf(x * x + dz * dz + dy * dy);
+}
+
+// libclsph/kernels/collisionsv2.cl:57-138 — one thread per distance-field grid point.
+// The reference finds the owning face by a linear walk down the offsets (:58-68); offsets
+// are strictly increasing, so an upper_bound gives the same face.
+__global__ void __launch_bounds__(kBlock)
+    k_distance_field(float* __restrict__ df, const Face* __restrict__ faces,
+                     const uint32_t* __restrict__ offsets, const float* __restrict__ tr,
+                     const float* __restrict__ rv, uint32_t face_count, uint32_t gridcount) {
+  const uint32_t g = blockIdx.x * kBlock + threadIdx.x;
+  if (g >= gridcount) return;
+  uint32_t lo = 0, hi = face_count;  // largest index with offsets[index] <= g (index 0 if none)
+  while (hi - lo > 1) {
+    const uint32_t mid = (lo + hi) >> 1;
+    if (__ldg(offsets + mid) <= g) lo = mid; else hi = mid;
+  }
+  const Face F = faces[lo];
+  const uint32_t rel = g - __ldg(offsets + lo);
+  const uint32_t sx = (uint32_t)F.sx, sz = (uint32_t)F.sz;
+  const int x = (int)((rel % (sx * sz)) % sx);
+  const int z = (int)((rel % (sx * sz)) / sx);
+  const int y = (int)(rel / (sx * sz));
+  const float px = x * (F.maxx - F.minx) / F.sxm1 + F.minx;
+  const float py = y * (F.maxy - F.miny) / F.sym1 + F.miny;
+  const float pz = z * (F.maxz - F.minz) / F.szm1 + F.minz;
+
+  float temd = 20;
+  const float4* f4 = reinterpret_cast<const float4*>(faces);
+  for (int i = 0; i < (int)face_count; ++i) {
+    const float4 b0 = __ldg(f4 + 3 * i);
+    const float4 b1 = __ldg(f4 + 3 * i + 1);
+    if (px <= b0.x && px >= b0.w && py <= b0.y && py >= b1.x && pz <= b0.z && pz >= b1.y) {
+      const float4 t0 = __ldg(reinterpret_cast<const float4*>(tr) + 3 * i);
+      const float4 t1 = __ldg(reinterpret_cast<const float4*>(tr) + 3 * i + 1);
+      const float4 t2 = __ldg(reinterpret_cast<const float4*>(tr) + 3 * i + 2);
+      const float4 R = __ldg(reinterpret_cast<const float4*>(rv) + i);
+      const float tpx = px + t0.w, tpy = py + t1.w, tpz = pz + t2.w;
+      const float rpx = t0.x * tpx + t0.y * tpy + t0.z * tpz;
+      const float rpy = t1.x * tpx + t1.y * tpy + t1.z * tpz;
+      const float rpz = t2.x * tpx + t2.y * tpy + t2.z * tpz;
+      const float v1y = R.y, v2x = R.z, v2y = R.w;
+      const float a = det2(rpy, rpz, 0, v1y) / det2(v2x, v2y, 0, v1y);
+      const float b = -det2(rpy, rpz, v2x, v2y) / det2(v2x, v2y, 0, v1y);
+      float d, td;
+      if (a > 0 && b > 0 && a + b < 1) {
+        d = fabsf(rpx);
+      } else {
+        d = dist_point_segment(rpx, rpy, rpz, 0, 0, R.x, R.y);
+        td = dist_point_segment(rpx, rpy, rpz, R.x, R.y, R.z, R.w);
+        if (td < d) d = td;
+        td = dist_point_segment(rpx, rpy, rpz, 0, 0, R.z, R.w);
+        if (td < d) d = td;
+      }
+      if (d < fabsf(temd)) temd = copysignf(d, rpx);
+    }
+  }
+  df[g] = temd;
+}
+
+// 80-byte AoS `particle` (libclsph/common/structures.h:40-44) <-> the engine's SoA.
+__global__ void __launch_bounds__(kBlock)
+    k_aos_to_soa(const sphb_particle* __restrict__ aos, uint32_t n, float4* pos, float4* vel,
+                 float4* vhf, float4* acc, float* rho, float* prs, uint32_t* keys) {
+  const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
+  if (i >= n) return;
+  const float4* src = reinterpret_cast<const float4*>(aos + i);
+  float4 p = src[0], v = src[1], w = src[2], a = src[3];
+  const float4 tail = src[4];
+  p.w = 0.f; v.w = 0.f; w.w = 0.f; a.w = 0.f;
+  pos[i] = p; vel[i] = v; vhf[i] = w; acc[i] = a;
+  rho[i] = tail.x;
+  prs[i] = tail.y;
+  keys[i] = __float_as_uint(tail.z);
+}
+
+__global__ void __launch_bounds__(kBlock)
+    k_soa_to_aos(sphb_particle* __restrict__ aos, uint32_t n, const float4* __restrict__ pos,
+                 const float4* __restrict__ vel, const float4* __restrict__ vhf,
+                 const float4* __restrict__ acc, const float* __restrict__ rho,
+                 const float* __restrict__ prs, const uint32_t* __restrict__ keys) {
+  const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
+  if (i >= n) return;
+  float4 p = pos[i], v = vel[i], w = vhf[i], a = acc[i];
+  p.w = 0.f; v.w = 0.f; w.w = 0.f; a.w = 0.f;
+  float4* dst = reinterpret_cast<float4*>(aos + i);
+  dst[0] = p; dst[1] = v; dst[2] = w; dst[3] = a;
+  dst[4] = make_float4(rho[i], prs[i], __uint_as_float(keys[i]), 0.f);
+}
+
+inline unsigned blocks_for(uint32_t n) { return (n + kBlock - 1) / kBlock; }
+
+}  // namespace
+
+int launch_reduce_init(Reduce* red, cudaStream_t s) {
+  k_reduce_init<<<1, 32, 0, s>>>(red);
+  return 1;
+}
+
+int launch_bbox(const float4* pos, uint32_t n, Reduce* red, cudaStream_t s) {
+  unsigned grid = blocks_for(n);
+  if (grid > 148 * 8) grid = 148 * 8;  // grid-stride: 8 resident CTAs of 256 on each of 148 SMs
+  k_bbox<<<grid, kBlock, 0, s>>>(pos, n, red);
+  return 1;
+}
+
+int launch_locate(const float4* pos, uint32_t* keys, const StepConsts& c, cudaStream_t s) {
+  k_locate<<<blocks_for(c.n), kBlock, 0, s>>>(pos, keys, c);
+  return 1;
+}
+
+int launch_reorder(const uint32_t* perm, uint32_t n, const float4* pos_in, const float4* vel_in,
+                   const float4* vhf_in, float4* pos_out, float4* vel_out, float4* vhf_out,
+                   cudaStream_t s) {
+  k_reorder<<<blocks_for(n), kBlock, 0, s>>>(perm, n, pos_in, vel_in, vhf_in, pos_out, vel_out,
+                                             vhf_out);
+  return 1;
+}
+
+int launch_cell_table(const uint32_t* sorted_keys, uint32_t n, uint32_t* table, uint32_t ncell,
+                      cudaStream_t s) {
+  if (ncell == 0) return 0;
+  k_cell_table<<<blocks_for(ncell), kBlock, 0, s>>>(sorted_keys, n, table, ncell);
+  return 1;
+}
+
+int launch_advect(const float4* pos, const float4* vhf, const float4* acc, float4* pos_out,
+                  float4* vel_out, float4* vhf_out, uint32_t n, float dt, float restitution,
+                  const Face* faces, uint32_t face_count, const float* df, Reduce* red,
+                  cudaStream_t s) {
+  k_advect<<<blocks_for(n), kBlock, 0, s>>>(pos, vhf, acc, pos_out, vel_out, vhf_out, n, dt,
+                                            restitution, faces, face_count, df, red);
+  return 1;
+}
+
+int launch_distance_field(float* df, const Face* faces, const uint32_t* face_offsets,
+                          const float* transforms, const float* rvertices, uint32_t face_count,
+                          uint32_t gridcount, cudaStream_t s) {
+  if (gridcount == 0 || face_count == 0) return 0;
+  k_distance_field<<<blocks_for(gridcount), kBlock, 0, s>>>(df, faces, face_offsets, transforms,
+                                                            rvertices, face_count, gridcount);
+  return 1;
+}
+
+int launch_aos_to_soa(const sphb_particle* aos, uint32_t n, float4* pos, float4* vel, float4* vhf,
+                      float4* acc, float* rho, float* prs, uint32_t* keys, cudaStream_t s) {
+  k_aos_to_soa<<<blocks_for(n), kBlock, 0, s>>>(aos, n, pos, vel, vhf, acc, rho, prs, keys);
+  return 1;
+}
+
+int launch_soa_to_aos(sphb_particle* aos, uint32_t n, const float4* pos, const float4* vel,
+                      const float4* vhf, const float4* acc, const float* rho, const float* prs,
+                      const uint32_t* keys, cudaStream_t s) {
+  k_soa_to_aos<<<blocks_for(n), kBlock, 0, s>>>(aos, n, pos, vel, vhf, acc, rho, prs, keys);
+  return 1;
+}
+
+}  // namespace sphb

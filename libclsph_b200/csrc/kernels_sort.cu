@@ -1,0 +1,207 @@
+// Stable least-significant-digit radix sort of (Morton key, particle index) pairs.
+//
+// Replaces the reference's sort_particles (libclsph/sph_simulation.cpp:110-198 with
+// kernels/sort.cl:23-59 and the Blelloch scans :108-200), which moves whole 80-byte
+// particles through 4 passes with at most 1024 work-items.  The observable contract is
+// "output = stable sort of the input order by grid_index"; it is independent of the
+// reference's thread count, so any stable sort reproduces its permutation bit for bit.
+//
+// Per 8-bit pass: (1) per-tile digit histogram, (2) exclusive scan of the
+// [digit][tile] table (two kernels; the third — adding the scanned block sums — is folded
+// into the scatter), (3) stable scatter: every warp owns a contiguous chunk of the tile,
+// ranks its elements with __match_any_sync, a 256-thread scan across warps turns per-warp
+// digit counts into offsets.  Only as many passes as the key has significant bits are run
+// (3 for grids up to 128 cells per axis, not 4).
+#include "common.cuh"
+
+namespace sphb {
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kWarps = kThreads / 32;
+constexpr int kRounds = 16;                       // 32-element rounds per warp
+constexpr int kWarpChunk = 32 * kRounds;          // 512
+constexpr int kTile = kWarps * kWarpChunk;        // 4096 elements per CTA
+constexpr int kScanTile = 2048;                   // entries per CTA in the table scan
+
+__global__ void __launch_bounds__(kThreads)
+    k_radix_hist(const uint32_t* __restrict__ keys, uint32_t n, int shift,
+                 uint32_t* __restrict__ hist, uint32_t ntiles) {
+  __shared__ uint32_t cnt[256];
+  cnt[threadIdx.x] = 0;
+  __syncthreads();
+  const uint32_t base = blockIdx.x * kTile;
+  const int lane = threadIdx.x & 31;
+#pragma unroll 4
+  for (int r = 0; r < kTile / kThreads; ++r) {
+    const uint32_t i = base + r * kThreads + threadIdx.x;
+    const bool valid = i < n;
+    const uint32_t d = valid ? ((__ldg(keys + i) >> shift) & 0xFFu) : 0x100u;
+    const unsigned peers = __match_any_sync(0xffffffffu, d);
+    if (valid && lane == __ffs(peers) - 1) atomicAdd(&cnt[d], __popc(peers));
+  }
+  __syncthreads();
+  hist[threadIdx.x * ntiles + blockIdx.x] = cnt[threadIdx.x];
+}
+
+// In-place exclusive scan of kScanTile entries per CTA; CTA totals go to sums[].
+__global__ void __launch_bounds__(kThreads)
+    k_scan_tiles(uint32_t* __restrict__ data, uint32_t len, uint32_t* __restrict__ sums) {
+  constexpr int kPer = kScanTile / kThreads;  // 8
+  __shared__ uint32_t warp_tot[kWarps];
+  const uint32_t base = blockIdx.x * kScanTile + threadIdx.x * kPer;
+  uint32_t v[kPer];
+  uint32_t t = 0;
+#pragma unroll
+  for (int k = 0; k < kPer; ++k) {
+    v[k] = (base + k < len) ? data[base + k] : 0u;
+    t += v[k];
+  }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  uint32_t incl = t;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t u = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += u;
+  }
+  if (lane == 31) warp_tot[warp] = incl;
+  __syncthreads();
+  uint32_t woff = 0;
+#pragma unroll
+  for (int w = 0; w < kWarps; ++w)
+    if (w < warp) woff += warp_tot[w];
+  uint32_t run = woff + incl - t;
+#pragma unroll
+  for (int k = 0; k < kPer; ++k) {
+    if (base + k < len) data[base + k] = run;
+    run += v[k];
+  }
+  if (threadIdx.x == kThreads - 1) sums[blockIdx.x] = run;
+}
+
+// Single-CTA exclusive scan of the per-tile totals (any length).
+__global__ void __launch_bounds__(kThreads) k_scan_sums(uint32_t* __restrict__ sums, uint32_t len) {
+  __shared__ uint32_t warp_tot[kWarps];
+  __shared__ uint32_t carry_s;
+  if (threadIdx.x == 0) carry_s = 0;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (uint32_t start = 0; start < len; start += kThreads) {
+    const uint32_t i = start + threadIdx.x;
+    const uint32_t v = i < len ? sums[i] : 0u;
+    uint32_t incl = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t u = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += u;
+    }
+    if (lane == 31) warp_tot[warp] = incl;
+    __syncthreads();
+    uint32_t woff = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < kWarps; ++w) {
+      if (w < warp) woff += warp_tot[w];
+      total += warp_tot[w];
+    }
+    const uint32_t carry = carry_s;
+    if (i < len) sums[i] = carry + woff + incl - v;
+    __syncthreads();
+    if (threadIdx.x == 0) carry_s = carry + total;
+    __syncthreads();
+  }
+}
+
+// Stable scatter of one tile.  vals_in == nullptr means "identity" (first pass).
+__global__ void __launch_bounds__(kThreads)
+    k_radix_scatter(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+                    uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, uint32_t n,
+                    int shift, const uint32_t* __restrict__ hist,
+                    const uint32_t* __restrict__ sums, uint32_t ntiles) {
+  __shared__ uint32_t warp_cnt[kWarps][256];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int w = 0; w < kWarps; ++w) warp_cnt[w][threadIdx.x] = 0;
+  __syncthreads();
+
+  const uint32_t chunk = blockIdx.x * kTile + warp * kWarpChunk;
+  uint32_t key[kRounds];
+  uint32_t rank[kRounds];  // rank of the element among equal digits inside this warp's chunk
+#pragma unroll
+  for (int r = 0; r < kRounds; ++r) {
+    const uint32_t i = chunk + r * 32 + lane;
+    const bool valid = i < n;
+    key[r] = valid ? __ldg(keys_in + i) : 0u;
+    const uint32_t d = valid ? ((key[r] >> shift) & 0xFFu) : 0x100u;
+    const unsigned peers = __match_any_sync(0xffffffffu, d);
+    const int leader = __ffs(peers) - 1;
+    uint32_t before = 0;
+    if (valid && lane == leader) {
+      before = warp_cnt[warp][d];
+      warp_cnt[warp][d] = before + __popc(peers);
+    }
+    before = __shfl_sync(0xffffffffu, before, leader);
+    rank[r] = before + __popc(peers & ((1u << lane) - 1u));
+    __syncwarp();
+  }
+  __syncthreads();
+
+  {  // digit `threadIdx.x`: global base of this tile, then offsets of each warp's run
+    const uint32_t d = threadIdx.x;
+    const uint32_t e = d * ntiles + blockIdx.x;
+    uint32_t run = __ldg(hist + e) + __ldg(sums + e / kScanTile);
+#pragma unroll
+    for (int w = 0; w < kWarps; ++w) {
+      const uint32_t c = warp_cnt[w][d];
+      warp_cnt[w][d] = run;
+      run += c;
+    }
+  }
+  __syncthreads();
+
+#pragma unroll
+  for (int r = 0; r < kRounds; ++r) {
+    const uint32_t i = chunk + r * 32 + lane;
+    if (i < n) {
+      const uint32_t d = (key[r] >> shift) & 0xFFu;
+      const uint32_t dst = warp_cnt[warp][d] + rank[r];
+      keys_out[dst] = key[r];
+      vals_out[dst] = vals_in ? __ldg(vals_in + i) : i;
+    }
+  }
+}
+
+inline uint32_t tiles_for(uint32_t n) { return (n + kTile - 1) / kTile; }
+
+}  // namespace
+
+size_t sort_hist_entries(uint32_t n) { return (size_t)256 * (tiles_for(n) ? tiles_for(n) : 1); }
+size_t sort_block_sum_entries(uint32_t n) {
+  return (sort_hist_entries(n) + kScanTile - 1) / kScanTile;
+}
+
+int launch_sort_pairs(const SortBuffers& b, uint32_t n, int key_bits, int* result, cudaStream_t s) {
+  *result = 0;
+  if (n == 0) return 0;
+  if (key_bits < 1) key_bits = 1;
+  if (key_bits > 32) key_bits = 32;
+  const int passes = (key_bits + 7) / 8;
+  const uint32_t ntiles = tiles_for(n);
+  const uint32_t hist_len = 256u * ntiles;
+  const uint32_t scan_tiles = (hist_len + kScanTile - 1) / kScanTile;
+  int launches = 0;
+  for (int p = 0; p < passes; ++p) {
+    const int in = p & 1, out = in ^ 1, shift = 8 * p;
+    k_radix_hist<<<ntiles, kThreads, 0, s>>>(b.keys[in], n, shift, b.hist, ntiles);
+    k_scan_tiles<<<scan_tiles, kThreads, 0, s>>>(b.hist, hist_len, b.block_sums);
+    k_scan_sums<<<1, kThreads, 0, s>>>(b.block_sums, scan_tiles);
+    k_radix_scatter<<<ntiles, kThreads, 0, s>>>(b.keys[in], p == 0 ? nullptr : b.vals[in],
+                                                b.keys[out], b.vals[out], n, shift, b.hist,
+                                                b.block_sums, ntiles);
+    launches += 4;
+  }
+  *result = passes & 1;
+  return launches;
+}
+
+}  // namespace sphb

@@ -1,0 +1,239 @@
+"""ctypes binding of include/sphb.h (one engine = one GPU = one stream)."""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+PARTICLE = np.dtype(
+    [
+        ("position", np.float32, 4),
+        ("velocity", np.float32, 4),
+        ("intermediate_velocity", np.float32, 4),
+        ("acceleration", np.float32, 4),
+        ("density", np.float32),
+        ("pressure", np.float32),
+        ("grid_index", np.uint32),
+        ("pad_", np.uint32),
+    ]
+)
+PARAMS = np.dtype(
+    [
+        ("particles_count", np.uint32),
+        ("fluid_density", np.float32),
+        ("total_mass", np.float32),
+        ("particle_mass", np.float32),
+        ("dynamic_viscosity", np.float32),
+        ("simulation_time", np.float32),
+        ("h", np.float32),
+        ("simulation_scale", np.float32),
+        ("target_fps", np.float32),
+        ("surface_tension_threshold", np.float32),
+        ("surface_tension", np.float32),
+        ("restitution", np.float32),
+        ("K", np.float32),
+        ("pad0_", np.uint32, 3),
+        ("constant_acceleration", np.float32, 4),
+        ("grid_size_x", np.int32),
+        ("grid_size_y", np.int32),
+        ("grid_size_z", np.int32),
+        ("grid_cell_count", np.uint32),
+        ("min_point", np.float32, 4),
+        ("max_point", np.float32, 4),
+    ]
+)
+TERMS = np.dtype(
+    [
+        ("poly_6", np.float32),
+        ("poly_6_gradient", np.float32),
+        ("poly_6_laplacian", np.float32),
+        ("spiky", np.float32),
+        ("viscosity", np.float32),
+    ]
+)
+BB = np.dtype(
+    [
+        ("maxx", np.float32),
+        ("maxy", np.float32),
+        ("maxz", np.float32),
+        ("minx", np.float32),
+        ("miny", np.float32),
+        ("minz", np.float32),
+        ("size_x", np.uint64),
+        ("size_y", np.uint64),
+        ("size_z", np.uint64),
+        ("offset", np.uint64),
+    ]
+)
+assert (PARTICLE.itemsize, PARAMS.itemsize, TERMS.itemsize, BB.itemsize) == (80, 128, 20, 56)
+
+PASS_NAMES = ["bbox", "locate", "sort", "reorder", "celltable", "density", "forces", "advect"]
+
+# every symbol include/sphb.h declares (tests check the library exports each one)
+SYMBOLS = [
+    "sphb_create", "sphb_destroy", "sphb_set_scene", "sphb_get_distance_field", "sphb_upload",
+    "sphb_step", "sphb_get_parameters", "sphb_download", "sphb_download_debug",
+    "sphb_profile_enable", "sphb_profile_reset", "sphb_get_pass_times", "sphb_launch_count",
+    "sphb_stream", "sphb_set_option", "sphb_last_error", "sphb_error_string",
+]
+
+
+class SphbError(RuntimeError):
+    def __init__(self, code, text):
+        super().__init__(f"[{code}] {text}")
+        self.code = code
+
+
+def lib_path():
+    return os.path.join(HERE, "libsphb.so")
+
+
+_lib = None
+
+
+def lib():
+    """Loads libsphb.so.  There is no fallback: a missing library is an error."""
+    global _lib
+    if _lib is None:
+        path = lib_path()
+        if not os.path.exists(path):
+            raise ImportError(
+                f"{path} is missing: build it with `python -m libclsph_b200.build` "
+                "(the sphb engine has no CPU or pure-Python path)")
+        L = C.CDLL(path)
+        vp, u32, i32, f32 = C.c_void_p, C.c_uint32, C.c_int, C.c_float
+        L.sphb_create.argtypes = [vp, vp, i32, C.POINTER(vp)]
+        L.sphb_destroy.argtypes = [vp]
+        L.sphb_set_scene.argtypes = [vp, vp, u32, vp, vp, u32]
+        L.sphb_get_distance_field.argtypes = [vp, vp]
+        L.sphb_upload.argtypes = [vp, vp, u32]
+        L.sphb_step.argtypes = [vp, f32, C.POINTER(f32)]
+        L.sphb_get_parameters.argtypes = [vp, vp]
+        L.sphb_download.argtypes = [vp, vp]
+        L.sphb_download_debug.argtypes = [vp, vp, vp, vp, u32, C.POINTER(i32)]
+        L.sphb_profile_enable.argtypes = [vp, i32]
+        L.sphb_profile_reset.argtypes = [vp]
+        L.sphb_get_pass_times.argtypes = [vp, vp, vp, C.POINTER(u32)]
+        L.sphb_launch_count.argtypes = [vp]
+        L.sphb_launch_count.restype = C.c_uint64
+        L.sphb_stream.argtypes = [vp]
+        L.sphb_stream.restype = vp
+        L.sphb_set_option.argtypes = [vp, C.c_char_p, i32]
+        L.sphb_last_error.argtypes = [vp]
+        L.sphb_last_error.restype = C.c_char_p
+        L.sphb_error_string.argtypes = [i32]
+        L.sphb_error_string.restype = C.c_char_p
+        _lib = L
+    return _lib
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+class Engine:
+    """One sphb_engine.  Arrays are numpy structured arrays of the dtypes above."""
+
+    def __init__(self, params, terms, device=-1):
+        self.L = lib()
+        self.h = C.c_void_p()
+        params = np.ascontiguousarray(params, PARAMS)
+        terms = np.ascontiguousarray(terms, TERMS)
+        rc = self.L.sphb_create(_ptr(params), _ptr(terms), device, C.byref(self.h))
+        if rc != 0:
+            self.h = None
+            raise SphbError(rc, self.L.sphb_error_string(rc).decode())
+        self.n = int(params.reshape(-1)[0]["particles_count"])
+
+    def _check(self, rc):
+        if rc != 0:
+            raise SphbError(rc, self.L.sphb_last_error(self.h).decode())
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.sphb_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def set_scene(self, bbs, transforms, rvertices, total_grid_points):
+        bbs = np.ascontiguousarray(bbs, BB)
+        transforms = np.ascontiguousarray(transforms, np.float32)
+        rvertices = np.ascontiguousarray(rvertices, np.float32)
+        self.total_grid_points = int(total_grid_points)
+        self._check(self.L.sphb_set_scene(self.h, _ptr(bbs), len(bbs), _ptr(transforms), _ptr(rvertices),
+                                          self.total_grid_points))
+
+    def distance_field(self):
+        out = np.zeros(self.total_grid_points, np.float32)
+        self._check(self.L.sphb_get_distance_field(self.h, _ptr(out)))
+        return out
+
+    def upload(self, particles):
+        particles = np.ascontiguousarray(particles, PARTICLE)
+        self._check(self.L.sphb_upload(self.h, _ptr(particles), len(particles)))
+
+    def upload_ptr(self, ptr, n):
+        """ptr: address of n 80-byte particles in (ideally pinned) host memory."""
+        self._check(self.L.sphb_upload(self.h, C.c_void_p(ptr), n))
+
+    def step(self, dt):
+        out = C.c_float()
+        self._check(self.L.sphb_step(self.h, dt, C.byref(out)))
+        return out.value
+
+    def parameters(self):
+        p = np.zeros(1, PARAMS)
+        self._check(self.L.sphb_get_parameters(self.h, _ptr(p)))
+        return p
+
+    def download(self, out=None):
+        if out is None:
+            out = np.zeros(self.n, PARTICLE)
+        self._check(self.L.sphb_download(self.h, _ptr(out)))
+        return out
+
+    def download_ptr(self, ptr):
+        self._check(self.L.sphb_download(self.h, C.c_void_p(ptr)))
+
+    def debug(self):
+        """dict(keys, perm, cell_table, attempts) of the last step."""
+        ncell = int(self.parameters()["grid_cell_count"][0])
+        keys = np.zeros(self.n, np.uint32)
+        perm = np.zeros(self.n, np.uint32)
+        table = np.zeros(ncell, np.uint32)
+        att = C.c_int()
+        self._check(self.L.sphb_download_debug(self.h, _ptr(keys), _ptr(perm), _ptr(table), ncell, C.byref(att)))
+        return dict(keys=keys, perm=perm, cell_table=table, attempts=att.value)
+
+    def profile(self, on=True):
+        self._check(self.L.sphb_profile_enable(self.h, int(on)))
+        self._check(self.L.sphb_profile_reset(self.h))
+
+    def pass_times(self):
+        """(dict pass -> ms accumulated, dict pass -> launches, steps) since profile()."""
+        ms = np.zeros(len(PASS_NAMES), np.float32)
+        ln = np.zeros(len(PASS_NAMES), np.uint32)
+        steps = C.c_uint32()
+        self._check(self.L.sphb_get_pass_times(self.h, _ptr(ms), _ptr(ln), C.byref(steps)))
+        return dict(zip(PASS_NAMES, ms.tolist())), dict(zip(PASS_NAMES, ln.tolist())), steps.value
+
+    def launch_count(self):
+        return int(self.L.sphb_launch_count(self.h))
+
+    def stream(self):
+        return self.L.sphb_stream(self.h)
+
+    def set_option(self, name, value):
+        self._check(self.L.sphb_set_option(self.h, name.encode(), int(value)))

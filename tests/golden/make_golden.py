@@ -1,0 +1,139 @@
+"""Generates the committed fixtures under tests/golden/ from the REFERENCE ITSELF.
+
+Run in the build container only (needs /root/reference and oracle/_ref/libsphref.so, the
+reference's own kernels/sph.cl + scene.cpp compiled as C++, see oracle/Makefile):
+
+    python tests/golden/make_golden.py
+
+Fixtures (all produced by the "reference" checker, never by the port or the CUDA engine):
+  scene_<name>.npz   scene::load products (bbs, transforms, rvertices, normals, total grid
+                     points) of a reference scene at a given distFieldThreshold, the triangle
+                     soup they came from, and a strided sample + checksum of the distance field
+  steps_<name>.npz   k successive simulate_single_frame results from the reference lattice:
+                     per step keys, permutation, cell table, rho, p, a, x, v, v_half, dt, attempts
+  advect_random.npz  one advection_collision over a seeded random state inside monkeybox
+"""
+import hashlib
+import os
+import sys
+import tempfile
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(HERE))
+from common import DEFAULT_SIM, FLUIDS, ROOT, box_mesh, dambreak_box, state_arrays, write_obj  # noqa: E402
+
+from oracle import pyorc  # noqa: E402
+
+REF = "/root/reference"
+
+
+def parse_obj_triangles(path):
+    """Triangle soup [nf,3,3] f32 in file order (fan triangulation, like tinyobj)."""
+    verts, tris = [], []
+    for line in open(path):
+        t = line.split()
+        if not t:
+            continue
+        if t[0] == "v":
+            verts.append([np.float32(x) for x in t[1:4]])
+        elif t[0] == "f":
+            idx = [int(tok.split("/")[0]) for tok in t[1:]]
+            idx = [i - 1 if i > 0 else len(verts) + i for i in idx]
+            for k in range(1, len(idx) - 1):
+                tris.append([verts[idx[0]], verts[idx[k]], verts[idx[k + 1]]])
+    return np.array(tris, np.float32)
+
+
+def scene_fixture(orc, name, root_dir, filename, threshold, soup, out):
+    sc = orc.ref_scene(root_dir, filename, threshold)
+    assert sc is not None, filename
+    df = orc.compute_df(sc["bbs"], sc["transforms"], sc["rvertices"], sc["total_gridpoints"])
+    np.savez_compressed(
+        out, threshold=np.float32(threshold), soup=soup, bbs=sc["bbs"], transforms=sc["transforms"],
+        rvertices=sc["rvertices"], face_normals=sc["face_normals"],
+        total_gridpoints=np.uint32(sc["total_gridpoints"]),
+        df_sample=df[::97].copy(), df_sha256=np.array(hashlib.sha256(df.tobytes()).hexdigest()))
+    print(name, "faces", sc["face_count"], "grid points", sc["total_gridpoints"])
+    return sc, df
+
+
+def steps_fixture(orc, fluid, n, sc, df, nsteps, out):
+    params, terms, vol = orc.settings(FLUIDS[fluid], DEFAULT_SIM, particles_count=n)
+    front = orc.init_particles(params, vol)
+    dt = np.float32(1.0) / params["target_fps"][0] * params["simulation_scale"][0]
+    rec = dict(n=np.uint32(n), fluid=np.array(fluid), initial=front.copy(), params0=params.copy(),
+               terms=terms.copy(), dt0=np.float32(dt))
+    for s in range(nsteps):
+        r = orc.step(front, params, terms, df, sc["bbs"], float(dt))
+        dt = r["dt"]
+        st = state_arrays(front)
+        for k, v in st.items():
+            rec[f"s{s}_{k}"] = v
+        rec[f"s{s}_perm"] = r["perm"]
+        rec[f"s{s}_cell_table"] = r["cell_table"]
+        rec[f"s{s}_dt"] = np.float32(r["dt"])
+        rec[f"s{s}_attempts"] = np.int32(r["attempts"])
+        rec[f"s{s}_params"] = params.copy()
+        print("  step", s, "dt", r["dt"], "attempts", r["attempts"], "grid",
+              params["grid_size_x"][0], params["grid_size_y"][0], params["grid_size_z"][0])
+    rec["nsteps"] = np.int32(nsteps)
+    np.savez_compressed(out, **rec)
+
+
+def main():
+    pyorc.build("reference")
+    orc = pyorc.load("reference")
+    hw = float(orc.settings(FLUIDS["water"], DEFAULT_SIM)[0]["h"][0])
+    hm = float(orc.settings(FLUIDS["mucus"], DEFAULT_SIM)[0]["h"][0])
+
+    # reference scenes
+    scenes = {}
+    for name, fn, h in [("box_water", "box.obj", hw), ("monkeybox_mucus", "monkeybox.obj", hm),
+                        ("cube_water", "cube.obj", hw), ("cone_water", "cone.obj", hw)]:
+        soup = parse_obj_triangles(os.path.join(REF, "scenes", fn))
+        scenes[name] = scene_fixture(orc, name, REF, fn, np.float32(h) * 2, soup,
+                                     os.path.join(HERE, f"scene_{name}.npz"))
+
+    # synthetic dam-break box (generated OBJ, loaded by the reference's scene.cpp)
+    n_dam = 4096
+    with tempfile.TemporaryDirectory() as tmp:
+        os.makedirs(os.path.join(tmp, "scenes"))
+        v, f = dambreak_box(n_dam)
+        write_obj(os.path.join(tmp, "scenes", "dam.obj"), [(v, f)])
+        soup = v[f]
+        scenes["dambreak_water"] = scene_fixture(orc, "dambreak_water", tmp, "dam.obj", np.float32(hw) * 2,
+                                                 soup, os.path.join(HERE, "scene_dambreak_water.npz"))
+
+    print("steps box_water")
+    steps_fixture(orc, "water", 4096, *scenes["box_water"], 3, os.path.join(HERE, "steps_box_water.npz"))
+    print("steps dambreak_water")
+    steps_fixture(orc, "water", n_dam, *scenes["dambreak_water"], 6, os.path.join(HERE, "steps_dambreak_water.npz"))
+    print("steps monkeybox_mucus")
+    steps_fixture(orc, "mucus", 2744, *scenes["monkeybox_mucus"], 3,
+                  os.path.join(HERE, "steps_monkeybox_mucus.npz"))
+
+    # advection + collision over a random state inside monkeybox (mucus: restitution 0.5)
+    sc, df = scenes["monkeybox_mucus"]
+    rng = np.random.default_rng(20261104)
+    n = 8192
+    p = np.zeros(n, pyorc.PARTICLE)
+    lo = np.array([-2.1, -2.1, -2.1], np.float32)
+    hi = np.array([2.1, 3.0, 2.1], np.float32)
+    p["position"][:, :3] = rng.uniform(lo, hi, (n, 3)).astype(np.float32)
+    p["intermediate_velocity"][:, :3] = rng.normal(0, 2.0, (n, 3)).astype(np.float32)
+    p["velocity"][:, :3] = p["intermediate_velocity"][:, :3]
+    p["acceleration"][:, :3] = rng.normal(0, 30.0, (n, 3)).astype(np.float32)
+    p["intermediate_velocity"][:16, :3] = 0  # |v| = 0 -> the reference's 0/0 in respond()
+    p["acceleration"][:16, :3] = 0
+    dt = np.float32(1.0 / 600.0)
+    out = orc.advect(p, 0.5, float(dt), df, sc["bbs"])
+    np.savez_compressed(os.path.join(HERE, "advect_random.npz"), input=p, output=out, dt=dt,
+                        restitution=np.float32(0.5))
+    moved = np.any(out["position"][:, :3] != (p["position"][:, :3] + (p["intermediate_velocity"][:, :3] + p["acceleration"][:, :3] * dt) * dt), axis=1)
+    print("advect_random: collided", int(moved.sum()), "of", n)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,100 @@
+"""CPU: pins the plain-C oracle (oracle/sph_oracle.c) against fixtures produced by the
+reference's own kernel source (tests/golden/make_golden.py).  Bit-exact everywhere: both are
+compiled with -ffp-contract=off and evaluate the same expression trees."""
+import hashlib
+import os
+
+import numpy as np
+import pytest
+
+from common import GOLDEN, state_arrays
+
+STEP_FIXTURES = [("steps_box_water", "scene_box_water"), ("steps_dambreak_water", "scene_dambreak_water"),
+                 ("steps_monkeybox_mucus", "scene_monkeybox_mucus")]
+
+
+def load_scene(name):
+    z = np.load(os.path.join(GOLDEN, name + ".npz"))
+    return z
+
+
+def bits(a):
+    a = np.ascontiguousarray(a)
+    return a.view(np.uint32) if a.dtype == np.float32 else a
+
+
+def test_struct_sizes(port_oracle):
+    assert port_oracle.kind == "port"
+
+
+@pytest.mark.parametrize("scene", ["scene_box_water", "scene_cube_water", "scene_cone_water",
+                                   "scene_dambreak_water", "scene_monkeybox_mucus"])
+def test_distance_field_matches_reference(port_oracle, scene):
+    z = load_scene(scene)
+    df = port_oracle.compute_df(z["bbs"], z["transforms"], z["rvertices"], int(z["total_gridpoints"]))
+    assert np.array_equal(bits(df[::97]), bits(z["df_sample"]))
+    assert hashlib.sha256(df.tobytes()).hexdigest() == str(z["df_sha256"])
+
+
+@pytest.mark.parametrize("steps,scene", STEP_FIXTURES)
+def test_steps_match_reference(port_oracle, steps, scene):
+    g = np.load(os.path.join(GOLDEN, steps + ".npz"))
+    sc = load_scene(scene)
+    orc = port_oracle
+    df = orc.compute_df(sc["bbs"], sc["transforms"], sc["rvertices"], int(sc["total_gridpoints"]))
+    params = g["params0"].copy()
+    terms = g["terms"].copy()
+    front = g["initial"].copy()
+    dt = float(g["dt0"])
+    for s in range(int(g["nsteps"])):
+        r = orc.step(front, params, terms, df, sc["bbs"], dt)
+        dt = r["dt"]
+        assert np.float32(dt).view(np.uint32) == g[f"s{s}_dt"].view(np.uint32)
+        assert r["attempts"] == int(g[f"s{s}_attempts"])
+        assert np.array_equal(r["perm"], g[f"s{s}_perm"])
+        assert np.array_equal(r["cell_table"], g[f"s{s}_cell_table"])
+        assert params.tobytes() == g[f"s{s}_params"].tobytes()
+        st = state_arrays(front)
+        for k, v in st.items():
+            assert np.array_equal(bits(v), bits(g[f"s{s}_{k}"])), (s, k)
+
+
+def test_settings_match_reference(port_oracle):
+    from common import DEFAULT_SIM, FLUIDS
+    for steps, fluid, n in [("steps_box_water", "water", 4096), ("steps_monkeybox_mucus", "mucus", 2744)]:
+        g = np.load(os.path.join(GOLDEN, steps + ".npz"))
+        p, t, vol = port_oracle.settings(FLUIDS[fluid], DEFAULT_SIM, particles_count=n)
+        assert p.tobytes() == g["params0"].tobytes()
+        assert t.tobytes() == g["terms"].tobytes()
+        init = port_oracle.init_particles(p, vol)
+        assert init.tobytes() == g["initial"].tobytes()
+
+
+def test_advect_random_matches_reference(port_oracle):
+    g = np.load(os.path.join(GOLDEN, "advect_random.npz"))
+    sc = load_scene("scene_monkeybox_mucus")
+    df = port_oracle.compute_df(sc["bbs"], sc["transforms"], sc["rvertices"], int(sc["total_gridpoints"]))
+    out = port_oracle.advect(g["input"], float(g["restitution"]), float(g["dt"]), df, sc["bbs"])
+    for f in ("position", "velocity", "intermediate_velocity"):
+        a, b = out[f][:, :3], g["output"][f][:, :3]
+        same = (bits(a) == bits(b)) | (np.isnan(a) & np.isnan(b))
+        assert same.all(), f
+
+
+def test_port_equals_reference_live(port_oracle, ref_oracle):
+    """When oracle/_ref is present (it travels to the GPU box as a built .so): one more config,
+    not in the fixtures, run through both checkers."""
+    from common import DEFAULT_SIM, FLUIDS
+    sc = load_scene("scene_dambreak_water")
+    outs = []
+    for orc in (port_oracle, ref_oracle):
+        p, t, vol = orc.settings(FLUIDS["water"], DEFAULT_SIM, particles_count=3375)
+        df = orc.compute_df(sc["bbs"], sc["transforms"], sc["rvertices"], int(sc["total_gridpoints"]))
+        front = orc.init_particles(p, vol)
+        dt = 1.0 / 600.0
+        for _ in range(4):
+            dt = orc.step(front, p, t, df, sc["bbs"], dt)["dt"]
+        outs.append((front.copy(), dt))
+    assert outs[0][1] == outs[1][1]
+    for f in ("position", "velocity", "intermediate_velocity", "acceleration", "density", "pressure", "grid_index"):
+        assert np.array_equal(bits(outs[0][0][f]), bits(outs[1][0][f])), f
