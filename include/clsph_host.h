@@ -1,0 +1,59 @@
+/* clsph_host — C entry points over the C++11 host classes that keep libclsph's API
+ * (libclsph_b200/host/: sph_simulation, scene, houdini_file_saver).  A C++ caller uses those
+ * classes directly, exactly as example/particles.cpp uses the reference's; these wrappers
+ * exist for callers that cannot (ctypes in tests/ and bench.py).  Built into
+ * libclsph_b200/libclsph_host.so, which links libsphb.so (include/sphb.h).
+ */
+#ifndef CLSPH_HOST_H_
+#define CLSPH_HOST_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#include "sphb.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct clsph_scene clsph_scene;
+
+/* scene::load (libclsph/scene.cpp:9-153) on an explicit OBJ path; NULL on failure. */
+clsph_scene* clsph_scene_load(const char* obj_path, float dist_field_threshold);
+uint32_t clsph_scene_face_count(const clsph_scene* s);
+uint32_t clsph_scene_total_grid_points(const clsph_scene* s);
+/* bbs[face_count], transforms[12*face_count], rvertices[4*face_count],
+ * face_normals[3*face_count]; each nullable */
+void clsph_scene_copy(const clsph_scene* s, sphb_bb* bbs, float* transforms, float* rvertices,
+                      float* face_normals);
+void clsph_scene_free(clsph_scene* s);
+
+/* sph_simulation::load_settings (libclsph/sph_simulation.cpp:434-532). 0 = ok, -1 = error
+ * (message in err). */
+int clsph_load_settings(const char* fluid_json, const char* sim_json, sphb_params* params,
+                        sphb_terms* terms, float* initial_volume, int* write_all_frames,
+                        int* serialize, char* err, size_t err_cap);
+
+/* The cube-lattice initial state of sph_simulation::init_particles (:75-96); every other
+ * field zero. */
+void clsph_lattice(sphb_particle* out, uint32_t count, float initial_volume);
+
+/* The PGEOMETRY V5 text houdini_file_saver::writeFrameToFile writes
+ * (util/houdini_geo/HoudiniFileDumpHelper.cpp:19-90).  Returns the length; copies it to `out`
+ * when cap is large enough. */
+size_t clsph_geo_text(const sphb_particle* particles, uint32_t count, float particle_mass,
+                      uint32_t threads, char* out, size_t cap);
+
+/* Headless sph_simulation::simulate() (:265-432) with a save_frame hook installed (frames are
+ * written as .geo under <frames_prefix>frames/ when frames_prefix is non-NULL).  Stops after
+ * max_steps sub-steps when max_steps > 0.  final_state / final_params receive what the last
+ * save_frame call saw. */
+int clsph_simulate(const char* fluid_json, const char* sim_json, const char* obj_path, int device,
+                   uint64_t max_steps, const char* frames_prefix, sphb_particle* final_state,
+                   sphb_params* final_params, uint64_t* steps_done, uint32_t* frames_saved,
+                   char* err, size_t err_cap);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CLSPH_HOST_H_ */

@@ -150,6 +150,12 @@ void* sphb_stream(sphb_engine* e);
  *   "neighbor_kernel"  0 = per-particle 27-cell walk, 1 = cell-tile staged kernel (default) */
 int sphb_set_option(sphb_engine* e, const char* name, int value);
 
+/* Page-locked host memory for the particle array (the reference asks OpenCL for
+ * CL_MEM_ALLOC_HOST_PTR buffers, libclsph/sph_simulation.cpp:311-316): uploads and downloads
+ * from such memory run at full PCIe rate.  Returns a cudaError_t. */
+int sphb_host_alloc(void** out, size_t bytes);
+int sphb_host_free(void* p);
+
 const char* sphb_last_error(sphb_engine* e);
 /* text for a return code when no engine exists (sphb_create failed) */
 const char* sphb_error_string(int code);

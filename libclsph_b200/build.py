@@ -1,9 +1,15 @@
-"""In-tree build of the sphb C-ABI library (libclsph_b200/libsphb.so) with nvcc for sm_100a.
+"""In-tree build of the product libraries.
 
-    python -m libclsph_b200.build [--force]
+    python -m libclsph_b200.build [--force] [-v]
 
-kernels_exact.cu is compiled with -fmad=false (bit-exact passes); everything else with
-nvcc's defaults.  No torch involvement: the library is plain CUDA runtime + C ABI.
+  libclsph_b200/libsphb.so        the CUDA step engine + its C ABI (include/sphb.h), nvcc, sm_100a.
+                                  kernels_exact.cu is compiled with -fmad=false (bit-exact
+                                  passes); everything else with nvcc's defaults.
+  libclsph_b200/libclsph_host.so  the C++11 host classes that keep libclsph's API (host/),
+                                  g++ -std=c++11, linked against libsphb.so, + include/clsph_host.h
+  libclsph_b200/clsphparticles    the command-line driver (host/example/particles.cpp)
+
+No torch involvement: plain CUDA runtime + C ABI.
 """
 import os
 import shutil
@@ -72,5 +78,54 @@ def build(force=False, verbose=False):
     return OUT
 
 
+HOST = os.path.join(HERE, "host")
+HOST_OUT = os.path.join(HERE, "libclsph_host.so")
+CLI_OUT = os.path.join(HERE, "clsphparticles")
+HOST_SOURCES = ["scene.cpp", "sph_simulation.cpp", "capi.cpp", "util/obj_reader.cpp",
+                "file_save_delegates/houdini_file_saver.cpp"]
+# -ffp-contract=off: scene preparation is compared bit for bit with the reference's
+HOST_FLAGS = ["-std=c++11", "-O2", "-ffp-contract=off", "-fPIC", "-Wall", "-pthread",
+              "-I", HOST, "-I", os.path.join(HERE, "..", "include")]
+
+
+def build_host(force=False, verbose=False):
+    """libclsph_host.so + clsphparticles (needs libsphb.so to link against)."""
+    gxx = shutil.which("g++") or "/usr/bin/g++"
+    os.makedirs(os.path.join(OBJDIR, "host"), exist_ok=True)
+    hdrs = []
+    for root, _, files in os.walk(HOST):
+        hdrs += [os.path.join(root, f) for f in files if f.endswith(".h")]
+    hdrs += [os.path.join(HERE, "..", "include", f) for f in ("sphb.h", "clsph_host.h")]
+    hdrs.append(os.path.abspath(__file__))
+    objs = []
+    for src in HOST_SOURCES:
+        path = os.path.join(HOST, src)
+        obj = os.path.join(OBJDIR, "host", src.replace("/", "_").replace(".cpp", ".o"))
+        objs.append(obj)
+        if force or _stale(obj, [path] + hdrs):
+            cmd = [gxx] + HOST_FLAGS + ["-c", path, "-o", obj]
+            if verbose:
+                print(" ".join(cmd), flush=True)
+            subprocess.check_call(cmd)
+    link = ["-L", HERE, "-lsphb", "-Wl,-rpath,$ORIGIN", "-pthread"]
+    if force or _stale(HOST_OUT, objs + [OUT]):
+        cmd = [gxx, "-shared", "-o", HOST_OUT] + objs + link
+        if verbose:
+            print(" ".join(cmd), flush=True)
+        subprocess.check_call(cmd)
+    cli_src = os.path.join(HOST, "example", "particles.cpp")
+    if force or _stale(CLI_OUT, [cli_src, HOST_OUT] + hdrs):
+        cmd = [gxx] + HOST_FLAGS + [cli_src, "-o", CLI_OUT, "-L", HERE, "-lclsph_host", "-lsphb",
+                                    "-Wl,-rpath,$ORIGIN", "-pthread"]
+        if verbose:
+            print(" ".join(cmd), flush=True)
+        subprocess.check_call(cmd)
+    return HOST_OUT
+
+
+def build_all(force=False, verbose=False):
+    return build(force, verbose), build_host(force, verbose)
+
+
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    print(build_all(force="--force" in sys.argv, verbose="-v" in sys.argv))

@@ -564,6 +564,24 @@ int sphb_get_pass_times(sphb_engine* e, float ms[SPHB_PASS_COUNT], uint32_t laun
   return 0;
 }
 
+int sphb_host_alloc(void** out, size_t bytes) {
+  if (!out) return SPHB_ERR_INVALID;
+  *out = nullptr;
+  g_create_error.clear();
+  cudaError_t err = cudaMallocHost(out, bytes ? bytes : 1);
+  if (err != cudaSuccess) {
+    cudaGetLastError();
+    return fail(nullptr, (int)err, __FILE__, __LINE__, "cudaMallocHost(%zu) -> %s", bytes,
+                cudaGetErrorString(err));
+  }
+  return 0;
+}
+
+int sphb_host_free(void* p) {
+  if (!p) return 0;
+  return (int)cudaFreeHost(p);
+}
+
 uint64_t sphb_launch_count(sphb_engine* e) { return e ? e->launches : 0; }
 
 void* sphb_stream(sphb_engine* e) { return e ? (void*)e->stream : nullptr; }

@@ -76,6 +76,7 @@ SYMBOLS = [
     "sphb_step", "sphb_get_parameters", "sphb_download", "sphb_download_debug",
     "sphb_profile_enable", "sphb_profile_reset", "sphb_get_pass_times", "sphb_launch_count",
     "sphb_stream", "sphb_set_option", "sphb_last_error", "sphb_error_string",
+    "sphb_host_alloc", "sphb_host_free",
 ]
 
 
@@ -124,6 +125,8 @@ def lib():
         L.sphb_last_error.restype = C.c_char_p
         L.sphb_error_string.argtypes = [i32]
         L.sphb_error_string.restype = C.c_char_p
+        L.sphb_host_alloc.argtypes = [C.POINTER(vp), C.c_size_t]
+        L.sphb_host_free.argtypes = [vp]
         _lib = L
     return _lib
 

@@ -1,0 +1,119 @@
+"""ctypes binding of include/clsph_host.h: the C++11 host classes (scene, sph_simulation,
+houdini_file_saver) behind C entry points.  No fallback: a missing library is an error."""
+import ctypes as C
+import os
+
+import numpy as np
+
+from .engine import BB, PARAMS, PARTICLE, TERMS, HERE, _ptr, lib as _engine_lib
+
+SYMBOLS = [
+    "clsph_scene_load", "clsph_scene_face_count", "clsph_scene_total_grid_points", "clsph_scene_copy",
+    "clsph_scene_free", "clsph_load_settings", "clsph_lattice", "clsph_geo_text", "clsph_simulate",
+]
+
+_lib = None
+
+
+def lib_path():
+    return os.path.join(HERE, "libclsph_host.so")
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        _engine_lib()  # libsphb.so first (the host library links it)
+        path = lib_path()
+        if not os.path.exists(path):
+            raise ImportError(f"{path} is missing: build it with `python -m libclsph_b200.build`")
+        L = C.CDLL(path)
+        vp, u32, i32, f32 = C.c_void_p, C.c_uint32, C.c_int, C.c_float
+        L.clsph_scene_load.argtypes = [C.c_char_p, f32]
+        L.clsph_scene_load.restype = vp
+        L.clsph_scene_face_count.argtypes = [vp]
+        L.clsph_scene_face_count.restype = u32
+        L.clsph_scene_total_grid_points.argtypes = [vp]
+        L.clsph_scene_total_grid_points.restype = u32
+        L.clsph_scene_copy.argtypes = [vp] * 5
+        L.clsph_scene_copy.restype = None
+        L.clsph_scene_free.argtypes = [vp]
+        L.clsph_scene_free.restype = None
+        L.clsph_load_settings.argtypes = [C.c_char_p, C.c_char_p, vp, vp, C.POINTER(f32), C.POINTER(i32),
+                                          C.POINTER(i32), C.c_char_p, C.c_size_t]
+        L.clsph_lattice.argtypes = [vp, u32, f32]
+        L.clsph_lattice.restype = None
+        L.clsph_geo_text.argtypes = [vp, u32, f32, u32, vp, C.c_size_t]
+        L.clsph_geo_text.restype = C.c_size_t
+        L.clsph_simulate.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, i32, C.c_uint64, C.c_char_p, vp, vp,
+                                     C.POINTER(C.c_uint64), C.POINTER(u32), C.c_char_p, C.c_size_t]
+        _lib = L
+    return _lib
+
+
+def load_scene(obj_path, threshold):
+    """scene::load on an OBJ path -> dict(face_count, total_gridpoints, bbs, transforms,
+    rvertices, face_normals), or None when the file cannot be loaded."""
+    L = lib()
+    h = L.clsph_scene_load(os.fsencode(obj_path), float(threshold))
+    if not h:
+        return None
+    try:
+        nf = L.clsph_scene_face_count(h)
+        sc = dict(face_count=nf, total_gridpoints=L.clsph_scene_total_grid_points(h),
+                  bbs=np.zeros(nf, BB), transforms=np.zeros(nf * 12, np.float32),
+                  rvertices=np.zeros(nf * 4, np.float32), face_normals=np.zeros(nf * 3, np.float32))
+        L.clsph_scene_copy(h, _ptr(sc["bbs"]), _ptr(sc["transforms"]), _ptr(sc["rvertices"]),
+                           _ptr(sc["face_normals"]))
+        return sc
+    finally:
+        L.clsph_scene_free(h)
+
+
+def load_settings(fluid_json, sim_json):
+    """sph_simulation::load_settings -> (params, terms, initial_volume, write_all_frames, serialize)"""
+    L = lib()
+    p = np.zeros(1, PARAMS)
+    t = np.zeros(1, TERMS)
+    vol = C.c_float()
+    w = C.c_int()
+    s = C.c_int()
+    err = C.create_string_buffer(512)
+    rc = L.clsph_load_settings(os.fsencode(fluid_json), os.fsencode(sim_json), _ptr(p), _ptr(t), C.byref(vol),
+                               C.byref(w), C.byref(s), err, len(err))
+    if rc != 0:
+        raise RuntimeError(err.value.decode())
+    return p, t, vol.value, bool(w.value), bool(s.value)
+
+
+def lattice(count, initial_volume, out=None):
+    if out is None:
+        out = np.zeros(count, PARTICLE)
+    lib().clsph_lattice(_ptr(out), count, initial_volume)
+    return out
+
+
+def geo_text(particles, particle_mass, threads=0):
+    particles = np.ascontiguousarray(particles, PARTICLE)
+    L = lib()
+    n = L.clsph_geo_text(_ptr(particles), len(particles), particle_mass, threads, None, 0)
+    buf = C.create_string_buffer(n)
+    L.clsph_geo_text(_ptr(particles), len(particles), particle_mass, threads, buf, n)
+    return buf.raw[:n]
+
+
+def simulate(fluid_json, sim_json, obj_path, device=-1, max_steps=0, frames_prefix=None, n=None):
+    """Headless sph_simulation::simulate(); returns dict(state, params, steps, frames)."""
+    L = lib()
+    if n is None:
+        n = int(load_settings(fluid_json, sim_json)[0]["particles_count"][0])
+    state = np.zeros(n, PARTICLE)
+    params = np.zeros(1, PARAMS)
+    steps = C.c_uint64()
+    frames = C.c_uint32()
+    err = C.create_string_buffer(512)
+    rc = L.clsph_simulate(os.fsencode(fluid_json), os.fsencode(sim_json), os.fsencode(obj_path), device,
+                          max_steps, os.fsencode(frames_prefix) if frames_prefix is not None else None,
+                          _ptr(state), _ptr(params), C.byref(steps), C.byref(frames), err, len(err))
+    if rc != 0:
+        raise RuntimeError(err.value.decode())
+    return dict(state=state, params=params, steps=steps.value, frames=frames.value)

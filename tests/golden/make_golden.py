@@ -135,5 +135,35 @@ def main():
     print("advect_random: collided", int(moved.sum()), "of", n)
 
 
+def geo_fixture(orc):
+    """One frame written by the reference's own houdini_file_saver (+ HoudiniFileDumpHelper)."""
+    import ctypes as C
+    rng = np.random.default_rng(7)
+    n = 257
+    p = np.zeros(n, pyorc.PARTICLE)
+    p["position"][:, :3] = rng.normal(0, 3.0, (n, 3)).astype(np.float32)
+    p["velocity"][:, :3] = (rng.normal(0, 1.0, (n, 3)) * 10.0 ** rng.integers(-8, 6, (n, 1))).astype(np.float32)
+    p["density"] = rng.uniform(-50, 2200, n).astype(np.float32)
+    p["density"][:6] = [0, 500, 1000, 1500, 2000, 999.99994]
+    p["position"][0, :3] = [0, -0.0, 1e-7]
+    p["position"][1, :3] = [123456.7, 1234567.0, 1e10]
+    p["velocity"][2, :3] = [np.nan, np.inf, -np.inf]
+    params, _, _ = orc.settings(FLUIDS["water"], DEFAULT_SIM, particles_count=n)
+    orc.lib.orcgeo_write.argtypes = [C.c_char_p, C.c_void_p, C.c_void_p, C.c_int]
+    with tempfile.TemporaryDirectory() as tmp:
+        os.makedirs(os.path.join(tmp, "frames"))
+        orc.lib.orcgeo_write((tmp + "/").encode(), p.ctypes.data, params.ctypes.data, 2)
+        names = sorted(os.listdir(os.path.join(tmp, "frames")))
+        text = open(os.path.join(tmp, "frames", names[0]), "rb").read()
+    np.savez_compressed(os.path.join(HERE, "geo_frame.npz"), particles=p, particle_mass=params["particle_mass"][0],
+                        names=np.array(names), text=np.frombuffer(text, np.uint8))
+    print("geo_frame:", names, len(text), "bytes")
+
+
 if __name__ == "__main__":
-    main()
+    if "--geo-only" in sys.argv:
+        pyorc.build("reference")
+        geo_fixture(pyorc.load("reference"))
+    else:
+        main()
+        geo_fixture(pyorc.load("reference"))
