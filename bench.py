@@ -1,0 +1,378 @@
+#!/usr/bin/env python
+"""bench.py — SPH particle-steps/s of the sphb step engine on B200 (BASELINE.json's metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--particles P]
+
+One "step" = one simulate_single_frame (libclsph/sph_simulation.cpp:200-263) over the whole
+particle set.  Workload at N = 1: BASELINE.json configs[3] on one GPU — the synthetic 16 777 216
+particle water box (256^3 reference lattice, water.json + default.json physics, open-top box
+x,z in [-4.8, 4.8], y in [-0.06, 12]); `config.secondary` adds configs[2] (1 M dam break).
+Prints ONE JSON line (rank 0).
+
+  value        particle-steps/s, state resident in HBM, CUDA events on the engine's stream
+  e2e          same metric through the C ABI with HOST buffers: every step uploads the 80-byte
+               AoS particles from pinned memory, steps, and downloads them again (the
+               write_all_frames + pre_frame-hook path of sph_simulation::simulate)
+  roofline     the dominant kernel (forces pass): algorithmic bytes (44 B/particle)
+               / its CUDA-event time, against MEASURED_PEAKS.json's HBM copy bandwidth
+  cpu_baseline the reference's own kernel source compiled as C++ (oracle/_ref) on the host
+               cores, on a bounded sample of the same workload
+--impl reference times only that CPU arm.
+"""
+import argparse
+import json
+import os
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WATER = dict(fluid_density=998.29, dynamic_viscosity=3.5, restitution=0, k=100,
+             surface_tension_threshold=7.065, surface_tension=0.0728,
+             particles_inside_influence_radius=20)
+SIM = dict(particles_count=64000, particle_mass=0.05, simulation_time=3, target_fps=60,
+           simulation_scale=0.1, write_all_frames=False, serialize=False,
+           constant_acceleration=dict(x=0, y=-9.8, z=0))
+# open-top box, vertex order / winding of scenes/box.obj (outward normals)
+BOX_FACES = [(1, 2, 3), (1, 5, 6), (2, 6, 3), (3, 7, 4), (5, 1, 4), (4, 1, 3), (2, 1, 6), (6, 7, 3),
+             (7, 8, 4), (8, 5, 4)]
+ALGO_BYTES = dict(bbox=12, locate=16, sort=None, reorder=76, celltable=5, density=20, forces=44,
+                  advect=72 + 24)  # advect carries the dt + bbox reductions
+STEP_BYTES_FUSED = {3: 285, 4: 301}  # per particle-step, by radix passes
+
+
+def write_box_obj(path, xmin, xmax, ymin, ymax, zmin, zmax):
+    v = [(xmax, ymin, zmin), (xmax, ymin, zmax), (xmin, ymin, zmax), (xmin, ymin, zmin),
+         (xmax, ymax, zmin), (xmax, ymax, zmax), (xmin, ymax, zmax), (xmin, ymax, zmin)]
+    with open(path, "w") as fh:
+        fh.write("o box\n")
+        for p in v:
+            fh.write("v %.9g %.9g %.9g\n" % p)
+        for f in BOX_FACES:
+            fh.write("f %d %d %d\n" % f)
+
+
+def lattice_side(n):
+    return float(np.cbrt(np.float32(n) * np.float32(SIM["particle_mass"]) / np.float32(WATER["fluid_density"])))
+
+
+def water_box_dims(n):
+    """configs[3]: the lattice block fills the box wall to wall (16.7 M: x,z in [-4.8, 4.8])."""
+    side = lattice_side(n)
+    half = side / 2 + 0.082  # 0.082 m clearance, as at 16.7 M
+    return (-half, half, -0.06, 1.27 * side, -half, half)
+
+
+def dam_break_dims(n):
+    """configs[2]: block against the -x wall, free to collapse along +x (1 M: x in [-1.9, 5.6])."""
+    side = lattice_side(n)
+    half = side / 2 + 0.057
+    return (-half, half + side, -0.06, 2.17 * side, -half, half)
+
+
+def write_json(path, d):
+    with open(path, "w") as fh:
+        fh.write(json.dumps(d, indent=4) + ";")
+
+
+def build_case(tmp, n, kind):
+    """Settings / lattice / scene through the PRODUCT's host layer (libclsph_b200.host)."""
+    from libclsph_b200 import host
+    write_json(os.path.join(tmp, "fluid.json"), WATER)
+    write_json(os.path.join(tmp, "sim.json"), dict(SIM, particles_count=int(n)))
+    params, terms, vol, _, _ = host.load_settings(os.path.join(tmp, "fluid.json"), os.path.join(tmp, "sim.json"))
+    dims = water_box_dims(n) if kind == "water_box" else dam_break_dims(n)
+    obj = os.path.join(tmp, f"{kind}_{n}.obj")
+    write_box_obj(obj, *dims)
+    sc = host.load_scene(obj, float(params["h"][0]) * 2)
+    if sc is None:
+        raise RuntimeError("scene load failed")
+    return dict(params=params, terms=terms, volume=vol, scene=sc, dims=dims, n=int(n))
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons of one GPU through NVML while the timed region runs."""
+
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown",
+               0x4: "sw_power_cap", 0x80: "hw_power_brake_slowdown"}
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.max_mhz = index, [], set(), None
+        self._stop_evt = threading.Event()
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if self.nv is None:
+            return
+        while not self._stop_evt.is_set():
+            try:
+                self.samples.append(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM))
+                r = self.nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                for bit, name in self.REASONS.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop_evt.wait(0.1)
+
+    def finish(self):
+        self._stop_evt.set()
+        self.join(timeout=2)
+        return dict(sm_mhz=float(np.median(self.samples)) if self.samples else None,
+                    sm_max_mhz=self.max_mhz, reasons=sorted(self.reasons), samples=len(self.samples))
+
+
+def physical_device(local_index):
+    vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+    if vis:
+        try:
+            return int(vis.split(",")[local_index])
+        except Exception:
+            return local_index
+    return local_index
+
+
+def measured_peak():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        try:
+            return float(json.load(open(path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def pinned_particles(n):
+    """n 80-byte particles in page-locked host memory (sphb_host_alloc) as a numpy view."""
+    import ctypes as C
+    from libclsph_b200 import PARTICLE, lib
+    ptr = C.c_void_p()
+    rc = lib().sphb_host_alloc(C.byref(ptr), n * PARTICLE.itemsize)
+    if rc != 0:
+        raise RuntimeError(f"sphb_host_alloc failed: {rc}")
+    buf = (C.c_char * (n * PARTICLE.itemsize)).from_address(ptr.value)
+    return np.frombuffer(buf, dtype=PARTICLE), ptr
+
+
+def run_gpu_case(case, steps, warmup, device, e2e_steps, sampler=None):
+    """Times `steps` resident steps (after `warmup`), then `e2e_steps` host-buffer steps."""
+    from libclsph_b200 import Engine, PASS_NAMES, host
+    n = case["n"]
+    sc = case["scene"]
+    stage, stage_ptr = pinned_particles(n)
+    host.lattice(n, case["volume"], out=stage)
+    e = Engine(case["params"], case["terms"], device)
+    e.set_scene(sc["bbs"], sc["transforms"], sc["rvertices"], sc["total_gridpoints"])
+    e.upload_ptr(stage_ptr.value, n)
+    dt = 1.0 / 600.0
+    for _ in range(warmup):
+        dt = e.step(dt)
+    e.profile(True)
+    l0 = e.launch_count()
+    if sampler:
+        sampler.start()
+    e.event_record(0)
+    for _ in range(steps):
+        dt = e.step(dt)
+    e.event_record(1)
+    ms = e.event_elapsed_ms(0, 1)
+    clocks = sampler.finish() if sampler else None
+    launches = e.launch_count() - l0
+    pass_ms, pass_launches, psteps = e.pass_times()
+    e.profile(False)
+    params_now = e.parameters()
+    res = dict(ms_total=ms, launches=launches, pass_ms=pass_ms, pass_launches=pass_launches,
+               clocks=clocks, dt=dt, grid=[int(params_now[k][0]) for k in ("grid_size_x", "grid_size_y", "grid_size_z")],
+               grid_cell_count=int(params_now["grid_cell_count"][0]))
+    # end to end: host buffers in, host buffers out, every step
+    if e2e_steps > 0:
+        e.download_ptr(stage_ptr.value)
+        for _ in range(1):  # one warm pass of the host path
+            e.upload_ptr(stage_ptr.value, n)
+            dt = e.step(dt)
+            e.download_ptr(stage_ptr.value)
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            e.upload_ptr(stage_ptr.value, n)
+            dt = e.step(dt)
+            e.download_ptr(stage_ptr.value)
+        res["e2e_s"] = time.perf_counter() - t0
+        res["e2e_steps"] = e2e_steps
+        res["finite"] = bool(np.isfinite(stage["position"][:: max(1, n // 4096), :3]).all())
+    e.close()
+    del stage
+    import ctypes as C
+    from libclsph_b200 import lib
+    lib().sphb_host_free(stage_ptr)
+    return res
+
+
+def cpu_arm(budget_s, steps, warmup, kind_pref="reference"):
+    """The reference's CPU implementation of the step (oracle/_ref = its own kernels/sph.cl +
+    scene.cpp compiled as C++, OpenMP over work-items; else the plain-C port) on a bounded
+    water-box sample sized so that (steps + warmup) steps take about budget_s seconds."""
+    from oracle import pyorc
+    kind = kind_pref if pyorc.available(kind_pref) else "port"
+    if kind == "port" and not pyorc.available("port"):
+        pyorc.build("port")
+    orc = pyorc.load(kind)
+    cores = orc.lib.orc_get_threads() or (os.cpu_count() or 1)
+
+    def prepare(n, tmp):
+        p, t, vol = orc.settings(WATER, dict(SIM, particles_count=int(n)))
+        dims = water_box_dims(n)
+        os.makedirs(os.path.join(tmp, "scenes"), exist_ok=True)
+        write_box_obj(os.path.join(tmp, "scenes", f"box_{n}.obj"), *dims)
+        if kind == "reference":
+            sc = orc.ref_scene(tmp, f"box_{n}.obj", float(p["h"][0]) * 2)
+        else:
+            from libclsph_b200 import host
+            sc = host.load_scene(os.path.join(tmp, "scenes", f"box_{n}.obj"), float(p["h"][0]) * 2)
+        df = orc.compute_df(sc["bbs"], sc["transforms"], sc["rvertices"], int(sc["total_gridpoints"]))
+        return p, t, orc.init_particles(p, vol), sc, df
+
+    def run(n, k, w, tmp):
+        p, t, front, sc, df = prepare(n, tmp)
+        dt = 1.0 / 600.0
+        for _ in range(w):
+            dt = orc.step(front, p, t, df, sc["bbs"], dt)["dt"]
+        t0 = time.perf_counter()
+        for _ in range(k):
+            dt = orc.step(front, p, t, df, sc["bbs"], dt)["dt"]
+        return time.perf_counter() - t0
+
+    with tempfile.TemporaryDirectory() as tmp:
+        probe_n = 32 ** 3
+        rate = probe_n / max(run(probe_n, 1, 1, tmp), 1e-6)  # particle-steps/s, calibration
+        want = rate * budget_s / max(1, steps + warmup)
+        side = int(max(32, min(160, np.floor(np.cbrt(want)))))
+        n = side ** 3
+        secs = run(n, steps, warmup, tmp)
+    return dict(value=n * steps / secs, unit="particle-steps/s", cores=int(cores), kind=kind,
+                sample=f"{n} particle ({side}^3) water box, {steps} steps after {warmup} warm-up, "
+                       f"{secs:.1f} s; same physics and scene family as the GPU workload",
+                n=n, seconds=secs)
+
+
+def emit(line):
+    """The ONE JSON line, on the real stdout (fd 1 is pointed at stderr while the run is going,
+    because native code on the path prints progress lines)."""
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
+
+_REAL_STDOUT = 1
+
+
+def main():
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--particles", type=int, default=16777216)
+    ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--cpu-budget", type=float, default=20.0, help="seconds of CPU baseline work")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-secondary", action="store_true", help="skip the 1 M dam-break leg")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    workload = f"synthetic {args.particles}-particle water box (water.json + default.json physics, " \
+               f"reference lattice, open-top box), BASELINE.json configs[3]"
+
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        cb = cpu_arm(max(30.0, 12.0 * (args.steps + args.warmup)), args.steps, args.warmup)
+        line = dict(metric="SPH particle-steps/sec", value=cb["value"], unit="particle-steps/s", impl="reference",
+                    n_gpus=args.gpus, steps=args.steps, warmup=args.warmup,
+                    ms_per_step=1e3 * cb["seconds"] / args.steps, higher_is_better=True, scaling="weak",
+                    vs_baseline=None, dtype="f32", data="synthetic",
+                    config=dict(workload=workload, timed_sample=cb["sample"]),
+                    cpu_baseline=dict(value=cb["value"], unit=cb["unit"], cores=cb["cores"], kind=cb["kind"],
+                                      sample=cb["sample"]),
+                    e2e=dict(value=cb["value"], unit="particle-steps/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0))
+        emit(line)
+        return 0
+
+    if world > 1 or args.gpus > 1:
+        from bench_multi import main_multi
+        return main_multi(args, rank, world, local, workload)
+
+    from libclsph_b200 import build
+    build.build_all()
+    with tempfile.TemporaryDirectory() as tmp:
+        case = build_case(tmp, args.particles, "water_box")
+        sampler = ClockSampler(physical_device(local))
+        r = run_gpu_case(case, args.steps, warmup, local, args.e2e_steps, sampler)
+        secondary = None
+        if not args.no_secondary:
+            c2 = build_case(tmp, 1000000, "dam_break")
+            r2 = run_gpu_case(c2, max(args.steps, 20), warmup, local, 0)
+            secondary = dict(workload="synthetic 1000000-particle water dam break, BASELINE.json configs[2]",
+                             value=c2["n"] * max(args.steps, 20) / (r2["ms_total"] * 1e-3), unit="particle-steps/s",
+                             ms_per_step=r2["ms_total"] / max(args.steps, 20),
+                             pass_ms_per_step={k: v / max(args.steps, 20) for k, v in r2["pass_ms"].items()})
+    n = case["n"]
+    ms_step = r["ms_total"] / args.steps
+    value = n * args.steps / (r["ms_total"] * 1e-3)
+    peak, peak_src = measured_peak()
+    # dominant kernel: the forces pass (one launch per step)
+    f_ms = r["pass_ms"]["forces"] / max(1, r["pass_launches"]["forces"])
+    achieved = ALGO_BYTES["forces"] * n / (f_ms * 1e-3) / 1e9
+    radix_passes = (max(1, r["grid_cell_count"].bit_length()) + 7) // 8
+    step_bytes = STEP_BYTES_FUSED.get(radix_passes, 301)
+    per_pass = {}
+    for k, v in r["pass_ms"].items():
+        per_pass[k] = dict(ms_per_step=v / args.steps, launches_per_step=r["pass_launches"][k] / args.steps)
+        ab = ALGO_BYTES.get(k) if k != "sort" else 16 * radix_passes + 4
+        if ab and v > 0:
+            per_pass[k]["algo_gbs"] = ab * n / (v / args.steps * 1e-3) / 1e9
+    line = dict(
+        metric="SPH particle-steps/sec", value=value, unit="particle-steps/s", n_gpus=1, steps=args.steps,
+        warmup=warmup, ms_per_step=ms_step, higher_is_better=True, scaling="weak", vs_baseline=None,
+        dtype="f32", data="synthetic",
+        config=dict(workload=workload, particles=n, box=[round(x, 4) for x in case["dims"]], grid=r["grid"],
+                    radix_passes=radix_passes, l2="inputs exceed L2 (positions alone are %d MB)" % (16 * n >> 20),
+                    parallelism="1 GPU", secondary=secondary),
+        clocks=r["clocks"], gpu_launches=r["launches"],
+        roofline=dict(bound="hbm", kernel="forces pass (k_forces_*)", achieved=achieved, peak=peak, unit="GB/s",
+                      frac=achieved / peak, traffic=None, peak_source=peak_src,
+                      algorithmic_bytes_per_particle=ALGO_BYTES["forces"], launch_ms=f_ms,
+                      whole_step=dict(algorithmic_bytes_per_particle=step_bytes,
+                                      achieved=step_bytes * n / (ms_step * 1e-3) / 1e9,
+                                      frac=step_bytes * n / (ms_step * 1e-3) / 1e9 / peak)),
+        passes=per_pass)
+    if "e2e_s" in r:
+        line["e2e"] = dict(value=n * r["e2e_steps"] / r["e2e_s"], unit="particle-steps/s",
+                           h2d_bytes_per_step=80 * n, d2h_bytes_per_step=80 * n + 32, steps=r["e2e_steps"],
+                           finite=r["finite"])
+    if not args.no_cpu:
+        cb = cpu_arm(args.cpu_budget, 2, 1)
+        line["cpu_baseline"] = dict(value=cb["value"], unit=cb["unit"], cores=cb["cores"], kind=cb["kind"],
+                                    sample=cb["sample"])
+    emit(line)
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

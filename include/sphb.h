@@ -123,6 +123,10 @@ int sphb_download(sphb_engine* e, sphb_particle* aos);
 int sphb_download_debug(sphb_engine* e, uint32_t* keys, uint32_t* perm, uint32_t* cell_table,
                         uint32_t cell_table_cap, int* attempts);
 
+/* Parity hook: runs ONLY advection_collision (kernels/sphb.cl:177-223) with time step dt over
+ * the uploaded state (uploaded accelerations included), in place of a full step. */
+int sphb_debug_advect(sphb_engine* e, float dt);
+
 /* ---- measurement ------------------------------------------------------------------ */
 enum {
   SPHB_PASS_BBOX = 0,    /* min/max of positions (only after an upload; otherwise fused in advect) */
@@ -142,6 +146,10 @@ int sphb_profile_enable(sphb_engine* e, int on);
 int sphb_profile_reset(sphb_engine* e);
 int sphb_get_pass_times(sphb_engine* e, float ms[SPHB_PASS_COUNT],
                         uint32_t launches[SPHB_PASS_COUNT], uint32_t* steps);
+/* Caller-side timing on the engine's stream: record one of 4 event slots, then read the
+ * milliseconds between two recorded slots (synchronises on the later one). */
+int sphb_event_record(sphb_engine* e, int slot);
+int sphb_event_elapsed_ms(sphb_engine* e, int from_slot, int to_slot, float* ms);
 /* number of kernel launches issued by this engine since creation */
 uint64_t sphb_launch_count(sphb_engine* e);
 /* the engine's cudaStream_t (as void*), so a caller can record its own events on it */

@@ -60,6 +60,7 @@ struct sphb_engine {
   int neighbor_variant = 0;
   bool profile = false;
   cudaEvent_t ev[SPHB_PASS_COUNT + 1][2];
+  cudaEvent_t user_ev[4];
   bool ev_created = false;
   float pass_ms[SPHB_PASS_COUNT] = {};
   uint32_t pass_launches[SPHB_PASS_COUNT] = {};
@@ -202,6 +203,7 @@ int sphb_destroy(sphb_engine* e) {
     for (int p = 0; p <= SPHB_PASS_COUNT; ++p) {
       cudaEventDestroy(e->ev[p][0]);
       cudaEventDestroy(e->ev[p][1]);
+      if (p < 4) cudaEventDestroy(e->user_ev[p]);
     }
   if (e->stream) cudaStreamDestroy(e->stream);
   delete e;
@@ -264,6 +266,7 @@ int sphb_create(const sphb_params* params, const sphb_terms* terms, int device, 
     TRY_OR_DESTROY(cudaEventCreate(&e->ev[p][0]));
     TRY_OR_DESTROY(cudaEventCreate(&e->ev[p][1]));
   }
+  for (int k = 0; k < 4; ++k) TRY_OR_DESTROY(cudaEventCreate(&e->user_ev[k]));
   e->ev_created = true;
   // zero everything that a download-before-step may read
   TRY_OR_DESTROY(cudaMemsetAsync(e->sortb.keys[0], 0, sizeof(uint32_t) * n, e->stream));
@@ -535,6 +538,23 @@ int sphb_download_debug(sphb_engine* e, uint32_t* keys, uint32_t* perm, uint32_t
   return 0;
 }
 
+int sphb_debug_advect(sphb_engine* e, float dt) {
+  if (!e) return SPHB_ERR_INVALID;
+  if (!e->have_state) SPHB_FAIL(e, SPHB_ERR_INVALID, "sphb_debug_advect before sphb_upload");
+  if (!e->have_scene) SPHB_FAIL(e, SPHB_ERR_NO_SCENE, "sphb_debug_advect before sphb_set_scene");
+  CUDA_TRY(e, cudaSetDevice(e->device));
+  const int in = e->cur, out = in ^ 1;
+  e->launches += launch_reduce_init(e->red, e->stream);
+  e->launches += launch_advect(e->pos[in], e->vhf[in], e->acc, e->pos[out], e->vel[out], e->vhf[out],
+                               e->n, dt, e->params.restitution, e->faces, e->face_count, e->df, e->red,
+                               e->stream);
+  CUDA_TRY(e, cudaGetLastError());
+  if (int rc = fetch_reduce(e)) return rc;
+  e->cur = out;
+  e->bbox_valid = true;
+  return 0;
+}
+
 int sphb_profile_enable(sphb_engine* e, int on) {
   if (!e) return SPHB_ERR_INVALID;
   e->profile = on != 0;
@@ -580,6 +600,21 @@ int sphb_host_alloc(void** out, size_t bytes) {
 int sphb_host_free(void* p) {
   if (!p) return 0;
   return (int)cudaFreeHost(p);
+}
+
+int sphb_event_record(sphb_engine* e, int slot) {
+  if (!e || slot < 0 || slot >= 4) return SPHB_ERR_INVALID;
+  CUDA_TRY(e, cudaSetDevice(e->device));
+  CUDA_TRY(e, cudaEventRecord(e->user_ev[slot], e->stream));
+  return 0;
+}
+
+int sphb_event_elapsed_ms(sphb_engine* e, int from_slot, int to_slot, float* ms) {
+  if (!e || !ms || from_slot < 0 || from_slot >= 4 || to_slot < 0 || to_slot >= 4) return SPHB_ERR_INVALID;
+  CUDA_TRY(e, cudaSetDevice(e->device));
+  CUDA_TRY(e, cudaEventSynchronize(e->user_ev[to_slot]));
+  CUDA_TRY(e, cudaEventElapsedTime(ms, e->user_ev[from_slot], e->user_ev[to_slot]));
+  return 0;
 }
 
 uint64_t sphb_launch_count(sphb_engine* e) { return e ? e->launches : 0; }

@@ -76,7 +76,7 @@ SYMBOLS = [
     "sphb_step", "sphb_get_parameters", "sphb_download", "sphb_download_debug",
     "sphb_profile_enable", "sphb_profile_reset", "sphb_get_pass_times", "sphb_launch_count",
     "sphb_stream", "sphb_set_option", "sphb_last_error", "sphb_error_string",
-    "sphb_host_alloc", "sphb_host_free",
+    "sphb_host_alloc", "sphb_host_free", "sphb_debug_advect", "sphb_event_record", "sphb_event_elapsed_ms",
 ]
 
 
@@ -125,6 +125,9 @@ def lib():
         L.sphb_last_error.restype = C.c_char_p
         L.sphb_error_string.argtypes = [i32]
         L.sphb_error_string.restype = C.c_char_p
+        L.sphb_debug_advect.argtypes = [vp, f32]
+        L.sphb_event_record.argtypes = [vp, i32]
+        L.sphb_event_elapsed_ms.argtypes = [vp, i32, i32, C.POINTER(f32)]
         L.sphb_host_alloc.argtypes = [C.POINTER(vp), C.c_size_t]
         L.sphb_host_free.argtypes = [vp]
         _lib = L
@@ -220,6 +223,9 @@ class Engine:
         self._check(self.L.sphb_download_debug(self.h, _ptr(keys), _ptr(perm), _ptr(table), ncell, C.byref(att)))
         return dict(keys=keys, perm=perm, cell_table=table, attempts=att.value)
 
+    def debug_advect(self, dt):
+        self._check(self.L.sphb_debug_advect(self.h, dt))
+
     def profile(self, on=True):
         self._check(self.L.sphb_profile_enable(self.h, int(on)))
         self._check(self.L.sphb_profile_reset(self.h))
@@ -231,6 +237,14 @@ class Engine:
         steps = C.c_uint32()
         self._check(self.L.sphb_get_pass_times(self.h, _ptr(ms), _ptr(ln), C.byref(steps)))
         return dict(zip(PASS_NAMES, ms.tolist())), dict(zip(PASS_NAMES, ln.tolist())), steps.value
+
+    def event_record(self, slot):
+        self._check(self.L.sphb_event_record(self.h, slot))
+
+    def event_elapsed_ms(self, a, b):
+        ms = C.c_float()
+        self._check(self.L.sphb_event_elapsed_ms(self.h, a, b, C.byref(ms)))
+        return ms.value
 
     def launch_count(self):
         return int(self.L.sphb_launch_count(self.h))

@@ -83,3 +83,43 @@ def state_arrays(particles):
         vhf=xyz(particles["intermediate_velocity"]), acc=xyz(particles["acceleration"]),
         rho=particles["density"].copy(), prs=particles["pressure"].copy(),
         key=particles["grid_index"].copy())
+
+
+def write_json(path, d):
+    import json
+    with open(path, "w") as fh:
+        fh.write(json.dumps(d, indent=4) + ";")  # the reference's property files end in '};'
+
+
+def make_case(tmpdir, fluid="water", n=4096, box=None, particle_mass=None):
+    """A synthetic case built with the PRODUCT's host code (libclsph_b200.host): settings from
+    temporary JSON files, the reference lattice, and an open-top box scene (default: the
+    dam-break box scaled to n).  Returns dict(params, terms, particles, scene)."""
+    from libclsph_b200 import host
+    tmpdir = str(tmpdir)
+    sim = dict(DEFAULT_SIM, particles_count=int(n))
+    if particle_mass is not None:
+        sim["particle_mass"] = particle_mass
+    write_json(os.path.join(tmpdir, "fluid.json"), FLUIDS[fluid])
+    write_json(os.path.join(tmpdir, "sim.json"), sim)
+    params, terms, vol, _, _ = host.load_settings(os.path.join(tmpdir, "fluid.json"), os.path.join(tmpdir, "sim.json"))
+    if box is None:
+        side = float(np.cbrt(vol))
+        half = side / 2
+        box = (-half - 0.06, half + 1.0 * side, -0.06, 2.2 * side, -half - 0.06, half + 0.06)
+    v, f = box_mesh(*box)
+    obj = os.path.join(tmpdir, "scene.obj")
+    write_obj(obj, [(v, f)])
+    sc = host.load_scene(obj, float(params["h"][0]) * 2)
+    assert sc is not None
+    return dict(params=params, terms=terms, particles=host.lattice(int(n), vol), scene=sc, volume=vol,
+                fluid_json=os.path.join(tmpdir, "fluid.json"), sim_json=os.path.join(tmpdir, "sim.json"),
+                obj=obj)
+
+
+def new_engine(case, device=-1):
+    from libclsph_b200 import Engine
+    e = Engine(case["params"], case["terms"], device)
+    sc = case["scene"]
+    e.set_scene(sc["bbs"], sc["transforms"], sc["rvertices"], sc["total_gridpoints"])
+    return e

@@ -1,0 +1,162 @@
+"""GPU parity: the sphb CUDA engine (through its C ABI) against the CPU oracle and against the
+fixtures the reference's own kernel source produced (tests/golden/).
+
+Bar (BASELINE.json north_star): cell indices, sorted order (permutation) and cell table
+BIT-EXACT; density, pressure, acceleration, position, velocity within a relative tolerance of
+1e-5 per step from an identical input state (SPH trajectories are chaotic, so the strict check
+re-seeds the engine from the oracle's state every step; free runs are short).
+
+Tolerances, as written below:
+  TOL = 1e-5
+  rho   : max|d rho| <= TOL * max|rho|
+  p     : |dp_i|     <= TOL * 7 K (rho_i/rho0)^7  + TOL * max|p|   (Tait cancels near rho0)
+  a     : max|da|    <= TOL * max|a|     (per array, not per component)
+  x,v,v_half : max|d| <= TOL * max|.|
+  dt    : |d dt|     <= TOL * dt
+"""
+import os
+
+import numpy as np
+import pytest
+
+from common import GOLDEN, box_mesh, make_case, new_engine, rel_err, state_arrays, xyz
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-5
+
+
+def aos_from(g, prefix, n):
+    """AoS particle array from the golden per-step arrays `<prefix>_{pos,vel,vhf,...}`."""
+    from libclsph_b200 import PARTICLE
+    p = np.zeros(n, PARTICLE)
+    p["position"][:, :3] = g[prefix + "_pos"]
+    p["velocity"][:, :3] = g[prefix + "_vel"]
+    p["intermediate_velocity"][:, :3] = g[prefix + "_vhf"]
+    p["acceleration"][:, :3] = g[prefix + "_acc"]
+    p["density"] = g[prefix + "_rho"]
+    p["pressure"] = g[prefix + "_prs"]
+    p["grid_index"] = g[prefix + "_key"]
+    return p
+
+
+def check_floats(got, want, K, rho0, where=""):
+    """got / want: dicts from state_arrays()."""
+    errs = {}
+    errs["rho"] = rel_err(got["rho"], want["rho"])
+    q = (want["rho"].astype(np.float64) / rho0) ** 7
+    bound = TOL * 7 * K * q + TOL * np.max(np.abs(want["prs"]))
+    dp = np.abs(got["prs"].astype(np.float64) - want["prs"])
+    errs["prs"] = float(np.max(dp / bound)) * TOL
+    for k in ("acc", "pos", "vel", "vhf"):
+        errs[k] = rel_err(got[k], want[k])
+    for k, v in errs.items():
+        assert v <= TOL, f"{where}: {k} error {v:.3e} > {TOL}"
+    return errs
+
+
+def check_exact(dbg, state_key, want_perm, want_table, want_key, where=""):
+    assert np.array_equal(dbg["keys"], want_key), f"{where}: sorted keys differ"
+    assert np.array_equal(state_key, want_key), f"{where}: grid_index differs"
+    assert np.array_equal(dbg["perm"], want_perm), f"{where}: permutation differs"
+    assert np.array_equal(dbg["cell_table"], want_table), f"{where}: cell table differs"
+
+
+FIXTURES = [("steps_box_water", "scene_box_water"), ("steps_dambreak_water", "scene_dambreak_water"),
+            ("steps_monkeybox_mucus", "scene_monkeybox_mucus")]
+
+
+@pytest.mark.parametrize("steps,scene", FIXTURES)
+def test_reseeded_steps_match_reference_fixtures(steps, scene):
+    """Every step of every fixture, each from the reference's own input state."""
+    from libclsph_b200 import Engine
+    g = np.load(os.path.join(GOLDEN, steps + ".npz"))
+    sc = np.load(os.path.join(GOLDEN, scene + ".npz"))
+    n = int(g["n"])
+    params = g["params0"].copy()
+    K, rho0 = float(params["K"][0]), float(params["fluid_density"][0])
+    with Engine(params, g["terms"]) as e:
+        e.set_scene(sc["bbs"], sc["transforms"], sc["rvertices"], int(sc["total_gridpoints"]))
+        for s in range(int(g["nsteps"])):
+            state = g["initial"] if s == 0 else aos_from(g, f"s{s-1}", n)
+            dt_in = float(g["dt0"]) if s == 0 else float(g[f"s{s-1}_dt"])
+            e.upload(state)
+            dt = e.step(dt_in)
+            out = e.download()
+            dbg = e.debug()
+            where = f"{steps} step {s}"
+            check_exact(dbg, out["grid_index"], g[f"s{s}_perm"], g[f"s{s}_cell_table"], g[f"s{s}_key"], where)
+            assert e.parameters().tobytes() == g[f"s{s}_params"].tobytes(), where
+            want = {k: g[f"s{s}_{k}"] for k in ("pos", "vel", "vhf", "acc", "rho", "prs")}
+            check_floats(state_arrays(out), want, K, rho0, where)
+            assert abs(dt - float(g[f"s{s}_dt"])) <= TOL * float(g[f"s{s}_dt"]), where
+            assert dbg["attempts"] == int(g[f"s{s}_attempts"]), where
+
+
+def test_distance_field_bit_exact_vs_fixtures():
+    """computeDistanceField on the device == the reference's, bit for bit (sample + sha256)."""
+    import hashlib
+    from libclsph_b200 import Engine
+    for scene, steps in [("scene_box_water", "steps_box_water"), ("scene_cube_water", "steps_box_water"),
+                         ("scene_cone_water", "steps_box_water"), ("scene_dambreak_water", "steps_box_water"),
+                         ("scene_monkeybox_mucus", "steps_monkeybox_mucus")]:
+        g = np.load(os.path.join(GOLDEN, steps + ".npz"))
+        sc = np.load(os.path.join(GOLDEN, scene + ".npz"))
+        with Engine(g["params0"], g["terms"]) as e:
+            e.set_scene(sc["bbs"], sc["transforms"], sc["rvertices"], int(sc["total_gridpoints"]))
+            df = e.distance_field()
+        assert np.array_equal(df[::97].view(np.uint32), sc["df_sample"].view(np.uint32)), scene
+        assert hashlib.sha256(df.tobytes()).hexdigest() == str(sc["df_sha256"]), scene
+
+
+def test_advect_collide_bit_exact_vs_fixture():
+    """advection_collision alone over a seeded random state inside monkeybox (restitution 0.5,
+    978 faces, including the |v| = 0 -> NaN case of respond()): the streaming passes are
+    compiled without FMA contraction and must equal the reference bit for bit."""
+    from libclsph_b200 import Engine
+    g = np.load(os.path.join(GOLDEN, "advect_random.npz"))
+    sc = np.load(os.path.join(GOLDEN, "scene_monkeybox_mucus.npz"))
+    st = np.load(os.path.join(GOLDEN, "steps_monkeybox_mucus.npz"))
+    params = st["params0"].copy()
+    params["particles_count"] = len(g["input"])
+    params["restitution"] = float(g["restitution"])
+    with Engine(params, st["terms"]) as e:
+        e.set_scene(sc["bbs"], sc["transforms"], sc["rvertices"], int(sc["total_gridpoints"]))
+        e.upload(g["input"])
+        e.debug_advect(float(g["dt"]))
+        out = e.download()
+    for f in ("position", "velocity", "intermediate_velocity"):
+        a, b = xyz(out[f]), xyz(g["output"][f])
+        same = (a.view(np.uint32) == b.view(np.uint32)) | (np.isnan(a) & np.isnan(b))
+        assert same.all(), (f, int((~same).sum()))
+
+
+def test_free_run_matches_reference(port_oracle):
+    """6 free-running steps (no re-upload): exercises the bbox fused into the advection kernel.
+    Floats drift (chaos) so they are held to 50*TOL; the sorted order is checked bit-exact
+    against the oracle run from the ENGINE's own previous state."""
+    from libclsph_b200 import Engine
+    g = np.load(os.path.join(GOLDEN, "steps_dambreak_water.npz"))
+    sc = np.load(os.path.join(GOLDEN, "scene_dambreak_water.npz"))
+    orc = port_oracle
+    df = orc.compute_df(sc["bbs"], sc["transforms"], sc["rvertices"], int(sc["total_gridpoints"]))
+    with Engine(g["params0"], g["terms"]) as e:
+        e.set_scene(sc["bbs"], sc["transforms"], sc["rvertices"], int(sc["total_gridpoints"]))
+        e.upload(g["initial"])
+        dt = float(g["dt0"])
+        for s in range(int(g["nsteps"])):
+            prev = e.download()
+            prev_dt = dt
+            dt = e.step(dt)
+            out = e.download()
+            dbg = e.debug()
+            # oracle from the engine's previous state
+            front = prev.copy()
+            p = e.parameters().copy()
+            r = orc.step(front, p, g["terms"].copy(), df, sc["bbs"], prev_dt)
+            check_exact(dbg, out["grid_index"], r["perm"], r["cell_table"], front["grid_index"], f"free step {s}")
+            assert e.parameters().tobytes() == p.tobytes()
+            got = state_arrays(out)
+            for k in ("pos", "vel", "vhf", "acc", "rho"):
+                assert rel_err(got[k], g[f"s{s}_{k}"]) <= 50 * TOL, (s, k)
+            assert abs(dt - float(g[f"s{s}_dt"])) <= 50 * TOL * float(g[f"s{s}_dt"])
