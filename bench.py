@@ -42,7 +42,7 @@ SIM = dict(particles_count=64000, particle_mass=0.05, simulation_time=3, target_
 BOX_FACES = [(1, 2, 3), (1, 5, 6), (2, 6, 3), (3, 7, 4), (5, 1, 4), (4, 1, 3), (2, 1, 6), (6, 7, 3),
              (7, 8, 4), (8, 5, 4)]
 ALGO_BYTES = dict(bbox=12, locate=16, sort=None, reorder=76, celltable=5, density=20, forces=44,
-                  advect=72 + 24)  # advect carries the dt + bbox reductions
+                  advect=72 + 24, refrank=None)  # advect carries the dt + bbox reductions
 STEP_BYTES_FUSED = {3: 285, 4: 301}  # per particle-step, by radix passes
 
 

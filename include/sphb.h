@@ -130,13 +130,14 @@ int sphb_debug_advect(sphb_engine* e, float dt);
 /* ---- measurement ------------------------------------------------------------------ */
 enum {
   SPHB_PASS_BBOX = 0,    /* min/max of positions (only after an upload; otherwise fused in advect) */
-  SPHB_PASS_LOCATE,      /* Morton key per particle */
+  SPHB_PASS_LOCATE,      /* cell key per particle */
   SPHB_PASS_SORT,        /* key/index radix sort, all passes */
   SPHB_PASS_REORDER,     /* gather of pos / vel / v_half into sorted SoA */
-  SPHB_PASS_CELLTABLE,   /* cell start offsets */
+  SPHB_PASS_CELLTABLE,   /* cell start offsets of the search grid */
   SPHB_PASS_DENSITY,     /* density + pressure */
   SPHB_PASS_FORCES,      /* forces -> acceleration */
   SPHB_PASS_ADVECT,      /* advection + collision + max|v|^2, max|a|^2, bbox reductions */
+  SPHB_PASS_REFRANK,     /* the reference's cell table + every particle's place in its sorted array */
   SPHB_PASS_COUNT
 };
 /* When enabled, every pass of sphb_step is bracketed by CUDA events on the engine's

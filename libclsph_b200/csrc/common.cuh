@@ -21,6 +21,10 @@ struct StepConsts {
   float gx, gy, gz;          // constant_acceleration
   float c_poly6, c_poly6_grad, c_poly6_lap, c_spiky, c_visc;
   float spiky_eps;           // -45 / (float)(M_PI * h^6): spiky_gradient's r < 1e-7 branch
+  // The engine's own search grid: cells of side h (half a reference cell), row-major
+  // (x fastest).  fine coordinate = 2 * reference coordinate + (upper half ? 1 : 0).
+  uint32_t fnx, fny, fnz;    // fine grid dimensions = 2 * grid_size_{x,y,z}
+  uint32_t nfine;            // fnx * fny * fnz
 };
 
 // One face of the scene for the collision pass: inflated AABB + its distance-field grid
@@ -88,10 +92,23 @@ int launch_reduce_init(Reduce* red, cudaStream_t s);
 int launch_bbox(const float4* pos, uint32_t n, Reduce* red, cudaStream_t s);
 int launch_locate(const float4* pos, uint32_t* keys, const StepConsts& c, cudaStream_t s);
 int launch_reorder(const uint32_t* perm, uint32_t n, const float4* pos_in, const float4* vel_in,
-                   const float4* vhf_in, float4* pos_out, float4* vel_out, float4* vhf_out,
-                   cudaStream_t s);
-int launch_cell_table(const uint32_t* sorted_keys, uint32_t n, uint32_t* table, uint32_t ncell,
-                      cudaStream_t s);
+                   const float4* vhf_in, const uint32_t* rank_in, float4* pos_out, float4* vel_out,
+                   float4* vhf_out, uint32_t* rank_out, cudaStream_t s);
+// fine cell table: ftable[f] = index of the first sorted particle whose fine key is >= f,
+// for f in [0, nfine]; ftable must hold nfine + 1 entries.  scratch: scan_scratch_entries().
+int launch_fine_table(const uint32_t* sorted_keys, uint32_t n, uint32_t* ftable, uint32_t nfine,
+                      uint32_t* scratch, cudaStream_t s);
+// The reference's order.  Given the compute-ordered fine keys, the fine table and every
+// particle's PREVIOUS reference rank (rank_prev, compute order), produces the reference's
+// cell table (ref_table[c] = number of particles whose Morton key is < c, ncell entries), the
+// Morton key of every particle (ckey) and every particle's NEW reference rank
+// (= position in the array the reference would hold after its stable sort by Morton key).
+int launch_reference_rank(const uint32_t* fine_keys, const uint32_t* ftable, const uint32_t* rank_prev,
+                          uint32_t* ref_table, uint32_t* ckey, uint32_t* rank_new, const StepConsts& c,
+                          uint32_t* scratch, cudaStream_t s);
+// keys_ref[rank[i]] = ckey[i], perm_ref[rank[i]] = rank_prev[i]
+int launch_reference_debug(const uint32_t* rank, const uint32_t* rank_prev, const uint32_t* ckey,
+                           uint32_t n, uint32_t* keys_ref, uint32_t* perm_ref, cudaStream_t s);
 int launch_advect(const float4* pos, const float4* vhf, const float4* acc, float4* pos_out,
                   float4* vel_out, float4* vhf_out, uint32_t n, float dt, float restitution,
                   const Face* faces, uint32_t face_count, const float* df, Reduce* red,
@@ -99,11 +116,14 @@ int launch_advect(const float4* pos, const float4* vhf, const float4* acc, float
 int launch_distance_field(float* df, const Face* faces, const uint32_t* face_offsets,
                           const float* transforms, const float* rvertices, uint32_t face_count,
                           uint32_t gridcount, cudaStream_t s);
+// upload: particle i of the AoS array gets reference rank i
 int launch_aos_to_soa(const sphb_particle* aos, uint32_t n, float4* pos, float4* vel, float4* vhf,
-                      float4* acc, float* rho, float* prs, uint32_t* keys, cudaStream_t s);
+                      float4* acc, float* rho, float* prs, uint32_t* ckey, uint32_t* rank,
+                      cudaStream_t s);
+// download: particle i is written to aos[rank[i]] (the reference's order)
 int launch_soa_to_aos(sphb_particle* aos, uint32_t n, const float4* pos, const float4* vel,
                       const float4* vhf, const float4* acc, const float* rho, const float* prs,
-                      const uint32_t* keys, cudaStream_t s);
+                      const uint32_t* ckey, const uint32_t* rank, cudaStream_t s);
 
 // kernels_sort.cu — stable LSD radix sort of (key, index) pairs, 8 bits per pass.
 struct SortBuffers {
@@ -118,12 +138,18 @@ size_t sort_block_sum_entries(uint32_t n);
 // keys[r] and vals[r][k] = original index of the element now at k.  Returns launches.
 int launch_sort_pairs(const SortBuffers& b, uint32_t n, int key_bits, int* result,
                       cudaStream_t s);
+// In-place exclusive scans of `len` u32 entries (sum, or running maximum with identity 0).
+// scratch must hold scan_scratch_entries(len) entries.
+size_t scan_scratch_entries(size_t len);
+int launch_exclusive_sum(uint32_t* data, uint32_t len, uint32_t* scratch, cudaStream_t s);
+int launch_exclusive_max(uint32_t* data, uint32_t len, uint32_t* scratch, cudaStream_t s);
 
 // kernels_neighbors.cu (compiled with FMA contraction on; tolerance-checked)
-int launch_density(float4* pos, float4* vel, const uint32_t* keys, const uint32_t* table,
+// keys = compute-ordered fine keys, ftable = fine cell table (nfine + 1 entries)
+int launch_density(float4* pos, float4* vel, const uint32_t* keys, const uint32_t* ftable,
                    float* rho, float* prs, const StepConsts& c, int variant, cudaStream_t s);
 int launch_forces(const float4* pos, const float4* vel, const uint32_t* keys,
-                  const uint32_t* table, const float* rho, float4* acc, const StepConsts& c,
+                  const uint32_t* ftable, const float* rho, float4* acc, const StepConsts& c,
                   int variant, cudaStream_t s);
 
 }  // namespace sphb

@@ -37,8 +37,18 @@ struct sphb_engine {
   float* prs = nullptr;
   SortBuffers sortb = {};
   int sorted = 0;            // which half of sortb holds the last step's sorted keys / perm
-  uint32_t* cell_table = nullptr;
-  uint32_t cell_table_cap = 0;
+  // The compute order is the engine's own (fine row-major cells); rank_cur[i] is the position
+  // of particle i in the REFERENCE's order, rank_prev[i] its position one step earlier
+  // (= the permutation the reference's sort applied), ckey[i] its Morton key (grid_index).
+  uint32_t* rank_cur = nullptr;
+  uint32_t* rank_prev = nullptr;
+  uint32_t* ckey = nullptr;
+  uint32_t* ftable = nullptr;     // fine cell table, nfine + 1 entries
+  size_t ftable_cap = 0;
+  uint32_t* ref_table = nullptr;  // the reference's cell table, grid_cell_count (+1) entries
+  size_t ref_table_cap = 0;
+  uint32_t* scan_scratch = nullptr;
+  size_t scan_scratch_cap = 0;
   sphb_particle* aos_stage = nullptr;  // device staging for upload / download
 
   // scene
@@ -148,6 +158,10 @@ StepConsts make_consts(const sphb_engine* e) {
   c.c_poly6_lap = e->terms.poly_6_laplacian; c.c_spiky = e->terms.spiky;
   c.c_visc = e->terms.viscosity;
   c.spiky_eps = e->spiky_eps;
+  c.fnx = 2u * (uint32_t)P.grid_size_x;
+  c.fny = 2u * (uint32_t)P.grid_size_y;
+  c.fnz = 2u * (uint32_t)P.grid_size_z;
+  c.nfine = c.fnx * c.fny * c.fnz;
   return c;
 }
 
@@ -195,7 +209,8 @@ int sphb_destroy(sphb_engine* e) {
   }
   cudaFree(e->acc); cudaFree(e->rho); cudaFree(e->prs);
   cudaFree(e->sortb.hist); cudaFree(e->sortb.block_sums);
-  cudaFree(e->cell_table); cudaFree(e->aos_stage);
+  cudaFree(e->rank_cur); cudaFree(e->rank_prev); cudaFree(e->ckey);
+  cudaFree(e->ftable); cudaFree(e->ref_table); cudaFree(e->scan_scratch); cudaFree(e->aos_stage);
   cudaFree(e->faces); cudaFree(e->face_offsets); cudaFree(e->df);
   cudaFree(e->red);
   if (e->red_host) cudaFreeHost(e->red_host);
@@ -255,6 +270,9 @@ int sphb_create(const sphb_params* params, const sphb_terms* terms, int device, 
     TRY_OR_DESTROY(dev_alloc(&e->sortb.keys[k], n));
     TRY_OR_DESTROY(dev_alloc(&e->sortb.vals[k], n));
   }
+  TRY_OR_DESTROY(dev_alloc(&e->rank_cur, n));
+  TRY_OR_DESTROY(dev_alloc(&e->rank_prev, n));
+  TRY_OR_DESTROY(dev_alloc(&e->ckey, n));
   TRY_OR_DESTROY(dev_alloc(&e->acc, n));
   TRY_OR_DESTROY(dev_alloc(&e->rho, n));
   TRY_OR_DESTROY(dev_alloc(&e->prs, n));
@@ -269,8 +287,8 @@ int sphb_create(const sphb_params* params, const sphb_terms* terms, int device, 
   for (int k = 0; k < 4; ++k) TRY_OR_DESTROY(cudaEventCreate(&e->user_ev[k]));
   e->ev_created = true;
   // zero everything that a download-before-step may read
-  TRY_OR_DESTROY(cudaMemsetAsync(e->sortb.keys[0], 0, sizeof(uint32_t) * n, e->stream));
-  TRY_OR_DESTROY(cudaMemsetAsync(e->sortb.vals[0], 0, sizeof(uint32_t) * n, e->stream));
+  TRY_OR_DESTROY(cudaMemsetAsync(e->ckey, 0, sizeof(uint32_t) * n, e->stream));
+  TRY_OR_DESTROY(cudaMemsetAsync(e->rank_prev, 0, sizeof(uint32_t) * n, e->stream));
   TRY_OR_DESTROY(cudaStreamSynchronize(e->stream));
 #undef TRY_OR_DESTROY
   *out = e;
@@ -356,7 +374,7 @@ int sphb_upload(sphb_engine* e, const sphb_particle* aos, uint32_t n) {
   CUDA_TRY(e, cudaMemcpyAsync(e->aos_stage, aos, sizeof(sphb_particle) * n, cudaMemcpyHostToDevice,
                               e->stream));
   e->launches += launch_aos_to_soa(e->aos_stage, n, e->pos[e->cur], e->vel[e->cur], e->vhf[e->cur],
-                                   e->acc, e->rho, e->prs, e->sortb.keys[e->sorted], e->stream);
+                                   e->acc, e->rho, e->prs, e->ckey, e->rank_cur, e->stream);
   CUDA_TRY(e, cudaGetLastError());
   CUDA_TRY(e, cudaStreamSynchronize(e->stream));
   e->bbox_valid = false;
@@ -377,6 +395,33 @@ int fetch_reduce(sphb_engine* e) {
 void accumulate_pass(sphb_engine* e, int pass) {
   float ms = 0.f;
   if (cudaEventElapsedTime(&ms, e->ev[pass][0], e->ev[pass][1]) == cudaSuccess) e->pass_ms[pass] += ms;
+}
+
+int ensure_tables(sphb_engine* e, size_t fine_entries, size_t ref_entries) {
+  // grow rarely: capacities are kept with 1.5x headroom
+  const bool grow_f = fine_entries > e->ftable_cap, grow_r = ref_entries > e->ref_table_cap;
+  if (!grow_f && !grow_r) return 0;
+  CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+  if (grow_f) {
+    cudaFree(e->ftable);
+    e->ftable = nullptr;
+    e->ftable_cap = fine_entries + fine_entries / 2 + 1024;
+    CUDA_TRY(e, dev_alloc(&e->ftable, e->ftable_cap));
+  }
+  if (grow_r) {
+    cudaFree(e->ref_table);
+    e->ref_table = nullptr;
+    e->ref_table_cap = ref_entries + ref_entries / 2 + 1024;
+    CUDA_TRY(e, dev_alloc(&e->ref_table, e->ref_table_cap));
+  }
+  const size_t need = scan_scratch_entries(e->ftable_cap > e->ref_table_cap ? e->ftable_cap : e->ref_table_cap);
+  if (need > e->scan_scratch_cap) {
+    cudaFree(e->scan_scratch);
+    e->scan_scratch = nullptr;
+    e->scan_scratch_cap = need;
+    CUDA_TRY(e, dev_alloc(&e->scan_scratch, need));
+  }
+  return 0;
 }
 
 int key_bits_for(uint32_t grid_cell_count) {
@@ -416,16 +461,8 @@ int sphb_step(sphb_engine* e, float dt_in, float* dt_out) {
     if (int rc = grid_from_bbox(e, mn, mx)) return rc;
   }
   const uint32_t ncell = e->params.grid_cell_count;
-  if (ncell + 1 > e->cell_table_cap) {  // grows rarely: capacity is kept with 2x headroom
-    CUDA_TRY(e, cudaStreamSynchronize(s));
-    cudaFree(e->cell_table);
-    e->cell_table = nullptr;
-    uint32_t cap = 2 * (ncell + 1);
-    if (cap < 4096) cap = 4096;
-    CUDA_TRY(e, dev_alloc(&e->cell_table, cap));
-    e->cell_table_cap = cap;
-  }
   const StepConsts c = make_consts(e);
+  if (int rc = ensure_tables(e, (size_t)c.nfine + 1, (size_t)ncell + 1)) return rc;
 
   // 2. locate_in_grid (kernels/grid.cl:40-64): keys only, no struct copy
   {
@@ -436,29 +473,36 @@ int sphb_step(sphb_engine* e, float dt_in, float* dt_out) {
   int r = 0;
   {
     PassTimer t(e, SPHB_PASS_SORT);
-    t.done(launch_sort_pairs(e->sortb, n, key_bits_for(ncell), &r, s));
+    t.done(launch_sort_pairs(e->sortb, n, key_bits_for(c.nfine), &r, s));
   }
   e->sorted = r;
   {
     PassTimer t(e, SPHB_PASS_REORDER);
     const int in = e->cur, out = in ^ 1;
-    t.done(launch_reorder(e->sortb.vals[r], n, e->pos[in], e->vel[in], e->vhf[in], e->pos[out],
-                          e->vel[out], e->vhf[out], s));
+    t.done(launch_reorder(e->sortb.vals[r], n, e->pos[in], e->vel[in], e->vhf[in], e->rank_cur,
+                          e->pos[out], e->vel[out], e->vhf[out], e->rank_prev, s));
     e->cur = out;
   }
   {
     PassTimer t(e, SPHB_PASS_CELLTABLE);
-    t.done(launch_cell_table(e->sortb.keys[r], n, e->cell_table, ncell, s));
+    t.done(launch_fine_table(e->sortb.keys[r], n, e->ftable, c.nfine, e->scan_scratch, s));
+  }
+  // the reference's cell table (kernels/sort.cl:61-78) and every particle's place in the
+  // reference's sorted array
+  {
+    PassTimer t(e, SPHB_PASS_REFRANK);
+    t.done(launch_reference_rank(e->sortb.keys[r], e->ftable, e->rank_prev, e->ref_table, e->ckey,
+                                 e->rank_cur, c, e->scan_scratch, s));
   }
   // 4. density_pressure (kernels/sphb.cl:3-35), 5. forces (:37-126)
   {
     PassTimer t(e, SPHB_PASS_DENSITY);
-    t.done(launch_density(e->pos[e->cur], e->vel[e->cur], e->sortb.keys[r], e->cell_table, e->rho,
+    t.done(launch_density(e->pos[e->cur], e->vel[e->cur], e->sortb.keys[r], e->ftable, e->rho,
                           e->prs, c, e->neighbor_variant, s));
   }
   {
     PassTimer t(e, SPHB_PASS_FORCES);
-    t.done(launch_forces(e->pos[e->cur], e->vel[e->cur], e->sortb.keys[r], e->cell_table, e->rho,
+    t.done(launch_forces(e->pos[e->cur], e->vel[e->cur], e->sortb.keys[r], e->ftable, e->rho,
                          e->acc, c, e->neighbor_variant, s));
   }
   CUDA_TRY(e, cudaGetLastError());
@@ -489,7 +533,8 @@ int sphb_step(sphb_engine* e, float dt_in, float* dt_out) {
   e->stepped = true;
   if (e->profile) {
     if (ran_bbox) accumulate_pass(e, SPHB_PASS_BBOX);
-    for (int p = SPHB_PASS_LOCATE; p < SPHB_PASS_ADVECT; ++p) accumulate_pass(e, p);
+    for (int p = SPHB_PASS_LOCATE; p < SPHB_PASS_COUNT; ++p)
+      if (p != SPHB_PASS_ADVECT) accumulate_pass(e, p);
     e->prof_steps++;
   }
   if (dt_out) *dt_out = computed;
@@ -508,7 +553,7 @@ int sphb_download(sphb_engine* e, sphb_particle* aos) {
   CUDA_TRY(e, cudaSetDevice(e->device));
   if (!e->aos_stage) CUDA_TRY(e, dev_alloc(&e->aos_stage, e->n));
   e->launches += launch_soa_to_aos(e->aos_stage, e->n, e->pos[e->cur], e->vel[e->cur], e->vhf[e->cur],
-                                   e->acc, e->rho, e->prs, e->sortb.keys[e->sorted], e->stream);
+                                   e->acc, e->rho, e->prs, e->ckey, e->rank_cur, e->stream);
   CUDA_TRY(e, cudaGetLastError());
   CUDA_TRY(e, cudaMemcpyAsync(aos, e->aos_stage, sizeof(sphb_particle) * e->n, cudaMemcpyDeviceToHost,
                               e->stream));
@@ -521,19 +566,31 @@ int sphb_download_debug(sphb_engine* e, uint32_t* keys, uint32_t* perm, uint32_t
   if (!e) return SPHB_ERR_INVALID;
   if (!e->stepped) SPHB_FAIL(e, SPHB_ERR_INVALID, "sphb_download_debug before the first sphb_step");
   CUDA_TRY(e, cudaSetDevice(e->device));
+  // the sort buffers are free between steps: use the half that does not hold the fine keys
+  const int scratch = e->sorted ^ 1;
+  e->launches += launch_reference_debug(e->rank_cur, e->rank_prev, e->ckey, e->n, e->sortb.keys[scratch],
+                                        e->sortb.vals[scratch], e->stream);
+  CUDA_TRY(e, cudaGetLastError());
   if (keys)
-    CUDA_TRY(e, cudaMemcpyAsync(keys, e->sortb.keys[e->sorted], sizeof(uint32_t) * e->n,
+    CUDA_TRY(e, cudaMemcpyAsync(keys, e->sortb.keys[scratch], sizeof(uint32_t) * e->n,
                                 cudaMemcpyDeviceToHost, e->stream));
   if (perm)
-    CUDA_TRY(e, cudaMemcpyAsync(perm, e->sortb.vals[e->sorted], sizeof(uint32_t) * e->n,
+    CUDA_TRY(e, cudaMemcpyAsync(perm, e->sortb.vals[scratch], sizeof(uint32_t) * e->n,
                                 cudaMemcpyDeviceToHost, e->stream));
+  uint32_t cnt = 0;
+  uint32_t first_key = 0;
   if (cell_table) {
-    uint32_t cnt = e->params.grid_cell_count < cell_table_cap ? e->params.grid_cell_count : cell_table_cap;
+    cnt = e->params.grid_cell_count < cell_table_cap ? e->params.grid_cell_count : cell_table_cap;
     if (cnt)
-      CUDA_TRY(e, cudaMemcpyAsync(cell_table, e->cell_table, sizeof(uint32_t) * cnt,
+      CUDA_TRY(e, cudaMemcpyAsync(cell_table, e->ref_table, sizeof(uint32_t) * cnt,
                                   cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(e, cudaMemcpyAsync(&first_key, e->sortb.keys[scratch], sizeof(uint32_t),
+                                cudaMemcpyDeviceToHost, e->stream));
   }
   CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+  // kernels/sort.cl:61-78 quirk: the table is pre-filled with N, and entries c <= key[0] are
+  // zeroed by work-item c — which exists only when c < N.
+  for (uint32_t cidx = e->n; cell_table && cidx <= first_key && cidx < cnt; ++cidx) cell_table[cidx] = e->n;
   if (attempts) *attempts = e->last_attempts;
   return 0;
 }

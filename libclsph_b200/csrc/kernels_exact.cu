@@ -75,26 +75,44 @@ __global__ void __launch_bounds__(kBlock) k_bbox(const float4* __restrict__ pos,
   block_reduce_to(red, v, 0x3f);
 }
 
-// libclsph/kernels/grid.cl:40-64: cell = (uint)((p - min) / (h*2)), key = Morton(cell).
+// libclsph/kernels/grid.cl:40-64 computes cell = (uint)((p - min) / (h*2)) per axis — that
+// expression is evaluated here exactly (IEEE subtract and divide, truncation), because the
+// reference's sorted order and cell table are functions of it.  The engine's own search grid
+// halves the cell: fine = 2*cell + (the particle lies in the upper half of the cell), and the
+// sort key is the ROW-MAJOR index of the fine cell, so that three x-adjacent cells are one
+// contiguous run of particles.  (The upper-half test may be off by an ulp at the mid-plane;
+// pairs that could be missed because of it have |r| within an ulp of h, where every
+// smoothing kernel is zero.)
+__device__ __forceinline__ uint32_t fine_coord(float p, float mn, float cell, float h) {
+  const float rel = p - mn;
+  const uint32_t c = (uint32_t)(rel / cell);
+  const float within = rel - (float)c * cell;
+  return 2u * c + (within >= h ? 1u : 0u);
+}
+
 __global__ void __launch_bounds__(kBlock) k_locate(const float4* __restrict__ pos,
                                                    uint32_t* __restrict__ keys, StepConsts c) {
   const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
   if (i >= c.n) return;
   const float4 p = __ldg(pos + i);
-  const uint32_t cx = (uint32_t)((p.x - c.minx) / c.cell);
-  const uint32_t cy = (uint32_t)((p.y - c.miny) / c.cell);
-  const uint32_t cz = (uint32_t)((p.z - c.minz) / c.cell);
-  keys[i] = morton3(cx, cy, cz);
+  uint32_t fx = fine_coord(p.x, c.minx, c.cell, c.h);
+  uint32_t fy = fine_coord(p.y, c.miny, c.cell, c.h);
+  uint32_t fz = fine_coord(p.z, c.minz, c.cell, c.h);
+  // NaN / runaway positions: park them in the last cell instead of indexing out of bounds
+  fx = min(fx, c.fnx - 1); fy = min(fy, c.fny - 1); fz = min(fz, c.fnz - 1);
+  keys[i] = (fz * c.fny + fy) * c.fnx + fx;
 }
 
 // The reference moves whole 80-byte structs in each of its 4 radix passes
 // (kernels/sort.cl:41-59); here only (key, index) pairs are sorted and the carried state
-// (position, velocity, intermediate_velocity: 36 of the 80 bytes) is gathered ONCE.
+// (position, velocity, intermediate_velocity: 36 of the 80 bytes, + the 4-byte reference
+// rank) is gathered ONCE.
 __global__ void __launch_bounds__(kBlock)
     k_reorder(const uint32_t* __restrict__ perm, uint32_t n, const float4* __restrict__ pos_in,
               const float4* __restrict__ vel_in, const float4* __restrict__ vhf_in,
-              float4* __restrict__ pos_out, float4* __restrict__ vel_out,
-              float4* __restrict__ vhf_out) {
+              const uint32_t* __restrict__ rank_in, float4* __restrict__ pos_out,
+              float4* __restrict__ vel_out, float4* __restrict__ vhf_out,
+              uint32_t* __restrict__ rank_out) {
   const uint32_t k = blockIdx.x * kBlock + threadIdx.x;
   if (k >= n) return;
   const uint32_t src = __ldg(perm + k);
@@ -103,24 +121,85 @@ __global__ void __launch_bounds__(kBlock)
   pos_out[k] = p;
   vel_out[k] = v;
   vhf_out[k] = w;
+  rank_out[k] = __ldg(rank_in + src);
 }
 
-// libclsph/kernels/sort.cl:61-78 (+ the fillUintArray(cell_table, N) before it): entry c is
-// the index of the first sorted particle whose key is >= c.  One thread per CELL doing a
-// lower_bound, instead of one work-item per particle walking key gaps.  The reference's
-// quirk is kept: entries c <= key[0] are zeroed only by work-items that exist (c < N).
+// Fine cell table, step 1: ends[f] = (index of the last particle of fine cell f) + 1 (else 0).
+// An exclusive running maximum then turns `ends` into ftable[f] = first particle with key >= f.
 __global__ void __launch_bounds__(kBlock)
-    k_cell_table(const uint32_t* __restrict__ keys, uint32_t n, uint32_t* __restrict__ table,
-                 uint32_t ncell) {
-  const uint32_t c = blockIdx.x * kBlock + threadIdx.x;
-  if (c >= ncell) return;
-  uint32_t lo = 0, hi = n;
-  while (lo < hi) {
-    const uint32_t mid = (lo + hi) >> 1;
-    if (__ldg(keys + mid) < c) lo = mid + 1; else hi = mid;
+    k_mark_cell_ends(const uint32_t* __restrict__ keys, uint32_t n, uint32_t* __restrict__ ends) {
+  const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
+  if (i >= n) return;
+  const uint32_t k = __ldg(keys + i);
+  if (i + 1 == n || __ldg(keys + i + 1) != k) ends[k] = i + 1;
+}
+
+// ---- the reference's order ---------------------------------------------------------------
+// The reference keeps its particle array stably sorted by the Morton key of the 2h cell
+// (sph_simulation.cpp:110-198): position of a particle = (number of particles in cells with a
+// smaller key) + (number of particles of its own cell that preceded it in the previous array).
+// The engine computes exactly that number for every particle — its "reference rank" — without
+// moving any data: downloads scatter through it, and the parity hooks report it.
+__device__ __forceinline__ void fine_coords_of(uint32_t key, const StepConsts& c, uint32_t& fx,
+                                               uint32_t& fy, uint32_t& fz) {
+  fx = key % c.fnx;
+  const uint32_t t = key / c.fnx;
+  fy = t % c.fny;
+  fz = t / c.fny;
+}
+
+// histogram over Morton cells; lanes of a warp that share a cell add once
+__global__ void __launch_bounds__(kBlock)
+    k_morton_hist(const uint32_t* __restrict__ fine_keys, uint32_t* __restrict__ hist,
+                  uint32_t* __restrict__ ckey, StepConsts c) {
+  const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
+  const bool valid = i < c.n;
+  uint32_t m = 0xFFFFFFFFu;
+  if (valid) {
+    uint32_t fx, fy, fz;
+    fine_coords_of(__ldg(fine_keys + i), c, fx, fy, fz);
+    m = morton3(fx >> 1, fy >> 1, fz >> 1);
+    ckey[i] = m;
   }
-  if (lo == 0 && c >= n) lo = n;
-  table[c] = lo;
+  const unsigned peers = __match_any_sync(0xffffffffu, m);
+  const int lane = threadIdx.x & 31;
+  if (valid && lane == __ffs(peers) - 1 && m < c.grid_cell_count) atomicAdd(hist + m, __popc(peers));
+}
+
+__global__ void __launch_bounds__(kBlock)
+    k_reference_rank(const uint32_t* __restrict__ fine_keys, const uint32_t* __restrict__ ftable,
+                     const uint32_t* __restrict__ rank_prev, const uint32_t* __restrict__ ref_table,
+                     uint32_t* __restrict__ rank_new, StepConsts c) {
+  const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
+  if (i >= c.n) return;
+  uint32_t fx, fy, fz;
+  fine_coords_of(__ldg(fine_keys + i), c, fx, fy, fz);
+  const uint32_t m = morton3(fx >> 1, fy >> 1, fz >> 1);
+  const uint32_t mine = __ldg(rank_prev + i);
+  const uint32_t x0 = fx & ~1u, y0 = fy & ~1u, z0 = fz & ~1u;
+  uint32_t before = 0;
+#pragma unroll
+  for (uint32_t dz = 0; dz < 2; ++dz)
+#pragma unroll
+    for (uint32_t dy = 0; dy < 2; ++dy) {
+      const uint32_t row = ((z0 + dz) * c.fny + (y0 + dy)) * c.fnx + x0;
+      const uint32_t s = __ldg(ftable + row), e = __ldg(ftable + row + 2);
+      for (uint32_t j = s; j < e; ++j) before += (__ldg(rank_prev + j) < mine) ? 1u : 0u;
+    }
+  rank_new[i] = (m < c.grid_cell_count ? __ldg(ref_table + m) : 0u) + before;
+}
+
+__global__ void __launch_bounds__(kBlock)
+    k_reference_debug(const uint32_t* __restrict__ rank, const uint32_t* __restrict__ rank_prev,
+                      const uint32_t* __restrict__ ckey, uint32_t n, uint32_t* __restrict__ keys_ref,
+                      uint32_t* __restrict__ perm_ref) {
+  const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
+  if (i >= n) return;
+  const uint32_t r = __ldg(rank + i);
+  if (r < n) {
+    keys_ref[r] = __ldg(ckey + i);
+    perm_ref[r] = __ldg(rank_prev + i);
+  }
 }
 
 // libclsph/kernels/collisionsv2.cl:140-156
@@ -299,10 +378,12 @@ __global__ void __launch_bounds__(kBlock)
   df[g] = temd;
 }
 
-// 80-byte AoS `particle` (libclsph/common/structures.h:40-44) <-> the engine's SoA.
+// 80-byte AoS `particle` (libclsph/common/structures.h:40-44) <-> the engine's SoA.  The AoS
+// array is in the reference's order; the SoA is in the engine's compute order, and rank[i] is
+// where particle i sits in the reference's order.
 __global__ void __launch_bounds__(kBlock)
     k_aos_to_soa(const sphb_particle* __restrict__ aos, uint32_t n, float4* pos, float4* vel,
-                 float4* vhf, float4* acc, float* rho, float* prs, uint32_t* keys) {
+                 float4* vhf, float4* acc, float* rho, float* prs, uint32_t* ckey, uint32_t* rank) {
   const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
   if (i >= n) return;
   const float4* src = reinterpret_cast<const float4*>(aos + i);
@@ -312,21 +393,25 @@ __global__ void __launch_bounds__(kBlock)
   pos[i] = p; vel[i] = v; vhf[i] = w; acc[i] = a;
   rho[i] = tail.x;
   prs[i] = tail.y;
-  keys[i] = __float_as_uint(tail.z);
+  ckey[i] = __float_as_uint(tail.z);
+  rank[i] = i;
 }
 
 __global__ void __launch_bounds__(kBlock)
     k_soa_to_aos(sphb_particle* __restrict__ aos, uint32_t n, const float4* __restrict__ pos,
                  const float4* __restrict__ vel, const float4* __restrict__ vhf,
                  const float4* __restrict__ acc, const float* __restrict__ rho,
-                 const float* __restrict__ prs, const uint32_t* __restrict__ keys) {
+                 const float* __restrict__ prs, const uint32_t* __restrict__ ckey,
+                 const uint32_t* __restrict__ rank) {
   const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
   if (i >= n) return;
+  const uint32_t r = __ldg(rank + i);
+  if (r >= n) return;
   float4 p = pos[i], v = vel[i], w = vhf[i], a = acc[i];
   p.w = 0.f; v.w = 0.f; w.w = 0.f; a.w = 0.f;
-  float4* dst = reinterpret_cast<float4*>(aos + i);
+  float4* dst = reinterpret_cast<float4*>(aos + r);
   dst[0] = p; dst[1] = v; dst[2] = w; dst[3] = a;
-  dst[4] = make_float4(rho[i], prs[i], __uint_as_float(keys[i]), 0.f);
+  dst[4] = make_float4(rho[i], prs[i], __uint_as_float(ckey[i]), 0.f);
 }
 
 inline unsigned blocks_for(uint32_t n) { return (n + kBlock - 1) / kBlock; }
@@ -351,17 +436,33 @@ int launch_locate(const float4* pos, uint32_t* keys, const StepConsts& c, cudaSt
 }
 
 int launch_reorder(const uint32_t* perm, uint32_t n, const float4* pos_in, const float4* vel_in,
-                   const float4* vhf_in, float4* pos_out, float4* vel_out, float4* vhf_out,
-                   cudaStream_t s) {
-  k_reorder<<<blocks_for(n), kBlock, 0, s>>>(perm, n, pos_in, vel_in, vhf_in, pos_out, vel_out,
-                                             vhf_out);
+                   const float4* vhf_in, const uint32_t* rank_in, float4* pos_out, float4* vel_out,
+                   float4* vhf_out, uint32_t* rank_out, cudaStream_t s) {
+  k_reorder<<<blocks_for(n), kBlock, 0, s>>>(perm, n, pos_in, vel_in, vhf_in, rank_in, pos_out,
+                                             vel_out, vhf_out, rank_out);
   return 1;
 }
 
-int launch_cell_table(const uint32_t* sorted_keys, uint32_t n, uint32_t* table, uint32_t ncell,
-                      cudaStream_t s) {
-  if (ncell == 0) return 0;
-  k_cell_table<<<blocks_for(ncell), kBlock, 0, s>>>(sorted_keys, n, table, ncell);
+int launch_fine_table(const uint32_t* sorted_keys, uint32_t n, uint32_t* ftable, uint32_t nfine,
+                      uint32_t* scratch, cudaStream_t s) {
+  cudaMemsetAsync(ftable, 0, sizeof(uint32_t) * ((size_t)nfine + 1), s);
+  k_mark_cell_ends<<<blocks_for(n), kBlock, 0, s>>>(sorted_keys, n, ftable);
+  return 1 + launch_exclusive_max(ftable, nfine + 1, scratch, s);
+}
+
+int launch_reference_rank(const uint32_t* fine_keys, const uint32_t* ftable, const uint32_t* rank_prev,
+                          uint32_t* ref_table, uint32_t* ckey, uint32_t* rank_new, const StepConsts& c,
+                          uint32_t* scratch, cudaStream_t s) {
+  cudaMemsetAsync(ref_table, 0, sizeof(uint32_t) * ((size_t)c.grid_cell_count + 1), s);
+  k_morton_hist<<<blocks_for(c.n), kBlock, 0, s>>>(fine_keys, ref_table, ckey, c);
+  int l = 1 + launch_exclusive_sum(ref_table, c.grid_cell_count + 1, scratch, s);
+  k_reference_rank<<<blocks_for(c.n), kBlock, 0, s>>>(fine_keys, ftable, rank_prev, ref_table, rank_new, c);
+  return l + 1;
+}
+
+int launch_reference_debug(const uint32_t* rank, const uint32_t* rank_prev, const uint32_t* ckey,
+                           uint32_t n, uint32_t* keys_ref, uint32_t* perm_ref, cudaStream_t s) {
+  k_reference_debug<<<blocks_for(n), kBlock, 0, s>>>(rank, rank_prev, ckey, n, keys_ref, perm_ref);
   return 1;
 }
 
@@ -384,15 +485,16 @@ int launch_distance_field(float* df, const Face* faces, const uint32_t* face_off
 }
 
 int launch_aos_to_soa(const sphb_particle* aos, uint32_t n, float4* pos, float4* vel, float4* vhf,
-                      float4* acc, float* rho, float* prs, uint32_t* keys, cudaStream_t s) {
-  k_aos_to_soa<<<blocks_for(n), kBlock, 0, s>>>(aos, n, pos, vel, vhf, acc, rho, prs, keys);
+                      float4* acc, float* rho, float* prs, uint32_t* ckey, uint32_t* rank,
+                      cudaStream_t s) {
+  k_aos_to_soa<<<blocks_for(n), kBlock, 0, s>>>(aos, n, pos, vel, vhf, acc, rho, prs, ckey, rank);
   return 1;
 }
 
 int launch_soa_to_aos(sphb_particle* aos, uint32_t n, const float4* pos, const float4* vel,
                       const float4* vhf, const float4* acc, const float* rho, const float* prs,
-                      const uint32_t* keys, cudaStream_t s) {
-  k_soa_to_aos<<<blocks_for(n), kBlock, 0, s>>>(aos, n, pos, vel, vhf, acc, rho, prs, keys);
+                      const uint32_t* ckey, const uint32_t* rank, cudaStream_t s) {
+  k_soa_to_aos<<<blocks_for(n), kBlock, 0, s>>>(aos, n, pos, vel, vhf, acc, rho, prs, ckey, rank);
   return 1;
 }
 

@@ -4,8 +4,12 @@
 // smoothing.cl:1-4) and sphb.cl:37-126 (forces, with smoothing.cl:6-34).  Both visit, for
 // every particle, the 27 cells of side 2h around its own cell, although the smoothing
 // kernels vanish beyond h: ~1000 candidate pairs per particle for ~20-40 true neighbours.
-// A pair with r >= h contributes exactly zero to every sum, so the kernels here skip such
-// pairs before doing any work on them; results are unchanged up to summation order.
+// A pair with r >= h contributes exactly zero to every sum, so the kernels here (a) search a
+// grid of side h instead — 27 cells of side h hold ~130 candidates — and (b) skip pairs with
+// r >= h before doing any work on them; results are unchanged up to summation order.
+//
+// Particles are sorted by the row-major index of their fine cell, so the three x-adjacent
+// cells of each of the 9 (dy, dz) rows are ONE contiguous run [ftable[row], ftable[row + 3]).
 //
 // This translation unit is compiled with FMA contraction ON and uses rsqrt for 1/r; it is
 // checked against the CPU oracle to a stated tolerance (tests/test_gpu_parity.py), unlike
@@ -22,13 +26,6 @@ namespace {
 
 constexpr int kBlock = 128;
 
-__device__ __forceinline__ void cell_range(uint32_t cell, const uint32_t* __restrict__ table,
-                                           const StepConsts& c, uint32_t& start, uint32_t& end) {
-  // libclsph/kernels/grid.cl:19-29
-  start = __ldg(table + cell);
-  end = (c.grid_cell_count > cell + 1) ? __ldg(table + cell + 1) : c.n;
-}
-
 // Tait equation, sphb.cl:32-34: K * ((rho/rho0)^7 - 1), pown as repeated multiplication
 __device__ __forceinline__ float tait_pressure(float rho, const StepConsts& c) {
   const float q = rho / c.rho0;
@@ -38,33 +35,54 @@ __device__ __forceinline__ float tait_pressure(float rho, const StepConsts& c) {
   return c.K * (q7 - 1.f);
 }
 
-// ---- variant 0: one thread per particle walking the 27 cells ---------------------------
+__device__ __forceinline__ void fine_coords_of(uint32_t key, const StepConsts& c, uint32_t& fx,
+                                               uint32_t& fy, uint32_t& fz) {
+  fx = key % c.fnx;
+  const uint32_t t = key / c.fnx;
+  fy = t % c.fny;
+  fz = t / c.fny;
+}
+
+// first / one-past-last particle of the 3-cell row centred on fine cell (fx, fy + dy, fz + dz);
+// an empty range when the row lies outside the grid
+__device__ __forceinline__ void row_range(const uint32_t* __restrict__ ftable, const StepConsts& c,
+                                          uint32_t fx, uint32_t fy, uint32_t fz, int dy, int dz,
+                                          uint32_t& s, uint32_t& e) {
+  const uint32_t y = fy + dy, z = fz + dz;  // wraps to a huge value below 0
+  if (y >= c.fny || z >= c.fnz) {
+    s = e = 0;
+    return;
+  }
+  const uint32_t x0 = fx > 0 ? fx - 1 : 0, x1 = min(fx + 2, c.fnx);
+  const uint32_t row = (z * c.fny + y) * c.fnx;
+  s = __ldg(ftable + row + x0);
+  e = __ldg(ftable + row + x1);
+}
+
+// ---- one thread per particle walking the 9 rows ------------------------------------------
 __global__ void __launch_bounds__(kBlock)
     k_density_walk(float4* pos, float4* vel, const uint32_t* __restrict__ keys,
-                   const uint32_t* __restrict__ table, float* __restrict__ rho,
+                   const uint32_t* __restrict__ ftable, float* __restrict__ rho,
                    float* __restrict__ prs, StepConsts c) {
   const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
   if (i >= c.n) return;
   const float4 pi = pos[i];
-  const uint32_t key = __ldg(keys + i);
-  const uint32_t cx = compact10(key), cy = compact10(key >> 1), cz = compact10(key >> 2);
+  uint32_t fx, fy, fz;
+  fine_coords_of(__ldg(keys + i), c, fx, fy, fz);
   float sum = 0.f;
-  // unsigned loop bounds exactly as forces.cl:25-27 (a coordinate of 0 would wrap and skip
-  // everything; the 2-cell padding of min_point keeps coordinates >= 2)
-  for (uint32_t z = cz - 1; z <= cz + 1; ++z)
-    for (uint32_t y = cy - 1; y <= cy + 1; ++y)
-      for (uint32_t x = cx - 1; x <= cx + 1; ++x) {
-        const uint32_t cell = morton3(x, y, z);
-        if (cell >= c.grid_cell_count) continue;
-        uint32_t s, e;
-        cell_range(cell, table, c, s, e);
-        for (uint32_t j = s; j < e; ++j) {
-          const float4 pj = __ldg(reinterpret_cast<const float4*>(pos) + j);
-          const float dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
-          const float t = c.h2 - (dx * dx + dy * dy + dz * dz);
-          if (t > 0.f) sum += t * t * t;
-        }
+#pragma unroll 1
+  for (int dz = -1; dz <= 1; ++dz)
+#pragma unroll 1
+    for (int dy = -1; dy <= 1; ++dy) {
+      uint32_t s, e;
+      row_range(ftable, c, fx, fy, fz, dy, dz, s, e);
+      for (uint32_t j = s; j < e; ++j) {
+        const float4 pj = __ldg(reinterpret_cast<const float4*>(pos) + j);
+        const float dx = pi.x - pj.x, dy_ = pi.y - pj.y, dz_ = pi.z - pj.z;
+        const float t = c.h2 - (dx * dx + dy_ * dy_ + dz_ * dz_);
+        if (t > 0.f) sum += t * t * t;
       }
+    }
   const float density = (c.mass * c.c_poly6) * sum;
   const float pressure = tait_pressure(density, c);
   rho[i] = density;
@@ -134,28 +152,27 @@ __device__ __forceinline__ float4 force_finish(const ForceAcc& A, float rho_i, f
 
 __global__ void __launch_bounds__(kBlock)
     k_forces_walk(const float4* __restrict__ pos, const float4* __restrict__ vel,
-                  const uint32_t* __restrict__ keys, const uint32_t* __restrict__ table,
+                  const uint32_t* __restrict__ keys, const uint32_t* __restrict__ ftable,
                   const float* __restrict__ rho, float4* __restrict__ acc, StepConsts c) {
   const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
   if (i >= c.n) return;
   const float4 pi = __ldg(pos + i), vi = __ldg(vel + i);
-  const uint32_t key = __ldg(keys + i);
-  const uint32_t cx = compact10(key), cy = compact10(key >> 1), cz = compact10(key >> 2);
+  uint32_t fx, fy, fz;
+  fine_coords_of(__ldg(keys + i), c, fx, fy, fz);
   ForceAcc A = {};
-  for (uint32_t z = cz - 1; z <= cz + 1; ++z)
-    for (uint32_t y = cy - 1; y <= cy + 1; ++y)
-      for (uint32_t x = cx - 1; x <= cx + 1; ++x) {
-        const uint32_t cell = morton3(x, y, z);
-        if (cell >= c.grid_cell_count) continue;
-        uint32_t s, e;
-        cell_range(cell, table, c, s, e);
-        for (uint32_t j = s; j < e; ++j) {
-          const float4 pj = __ldg(pos + j);
-          const float dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
-          const float r2 = dx * dx + dy * dy + dz * dz;
-          if (r2 < c.h2 && j != i) force_pair(A, pi, vi, pj, __ldg(vel + j), dx, dy, dz, r2, c);
-        }
+#pragma unroll 1
+  for (int dz = -1; dz <= 1; ++dz)
+#pragma unroll 1
+    for (int dy = -1; dy <= 1; ++dy) {
+      uint32_t s, e;
+      row_range(ftable, c, fx, fy, fz, dy, dz, s, e);
+      for (uint32_t j = s; j < e; ++j) {
+        const float4 pj = __ldg(pos + j);
+        const float dx = pi.x - pj.x, dy_ = pi.y - pj.y, dz_ = pi.z - pj.z;
+        const float r2 = dx * dx + dy_ * dy_ + dz_ * dz_;
+        if (r2 < c.h2 && j != i) force_pair(A, pi, vi, pj, __ldg(vel + j), dx, dy_, dz_, r2, c);
       }
+    }
   acc[i] = force_finish(A, __ldg(rho + i), vi.w, c);
 }
 
@@ -163,18 +180,18 @@ inline unsigned blocks_for(uint32_t n) { return (n + kBlock - 1) / kBlock; }
 
 }  // namespace
 
-int launch_density(float4* pos, float4* vel, const uint32_t* keys, const uint32_t* table,
+int launch_density(float4* pos, float4* vel, const uint32_t* keys, const uint32_t* ftable,
                    float* rho, float* prs, const StepConsts& c, int variant, cudaStream_t s) {
   (void)variant;
-  k_density_walk<<<blocks_for(c.n), kBlock, 0, s>>>(pos, vel, keys, table, rho, prs, c);
+  k_density_walk<<<blocks_for(c.n), kBlock, 0, s>>>(pos, vel, keys, ftable, rho, prs, c);
   return 1;
 }
 
 int launch_forces(const float4* pos, const float4* vel, const uint32_t* keys,
-                  const uint32_t* table, const float* rho, float4* acc, const StepConsts& c,
+                  const uint32_t* ftable, const float* rho, float4* acc, const StepConsts& c,
                   int variant, cudaStream_t s) {
   (void)variant;
-  k_forces_walk<<<blocks_for(c.n), kBlock, 0, s>>>(pos, vel, keys, table, rho, acc, c);
+  k_forces_walk<<<blocks_for(c.n), kBlock, 0, s>>>(pos, vel, keys, ftable, rho, acc, c);
   return 1;
 }
 

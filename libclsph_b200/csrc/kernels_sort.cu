@@ -171,6 +171,108 @@ __global__ void __launch_bounds__(kThreads)
   }
 }
 
+// ---- generic in-place exclusive scans (sum / running maximum) ---------------------------
+struct OpSum {
+  __device__ static uint32_t apply(uint32_t a, uint32_t b) { return a + b; }
+};
+struct OpMax {
+  __device__ static uint32_t apply(uint32_t a, uint32_t b) { return a > b ? a : b; }
+};
+
+template <typename Op>
+__device__ __forceinline__ uint32_t warp_inclusive(uint32_t v, int lane) {
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t u = __shfl_up_sync(0xffffffffu, v, o);
+    if (lane >= o) v = Op::apply(v, u);
+  }
+  return v;
+}
+
+// exclusive scan of kScanTile entries per CTA; CTA totals go to sums[]
+template <typename Op>
+__global__ void __launch_bounds__(kThreads)
+    k_xscan_tiles(uint32_t* __restrict__ data, uint32_t len, uint32_t* __restrict__ sums) {
+  constexpr int kPer = kScanTile / kThreads;
+  __shared__ uint32_t warp_tot[kWarps];
+  const uint32_t base = blockIdx.x * kScanTile + threadIdx.x * kPer;
+  uint32_t v[kPer];
+  uint32_t t = 0;
+#pragma unroll
+  for (int k = 0; k < kPer; ++k) {
+    v[k] = (base + k < len) ? data[base + k] : 0u;
+    t = Op::apply(t, v[k]);
+  }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t incl = warp_inclusive<Op>(t, lane);
+  if (lane == 31) warp_tot[warp] = incl;
+  __syncthreads();
+  uint32_t run = 0;
+#pragma unroll
+  for (int w = 0; w < kWarps; ++w)
+    if (w < warp) run = Op::apply(run, warp_tot[w]);
+  const uint32_t prev_lane = __shfl_up_sync(0xffffffffu, incl, 1);
+  if (lane > 0) run = Op::apply(run, prev_lane);
+#pragma unroll
+  for (int k = 0; k < kPer; ++k) {
+    if (base + k < len) data[base + k] = run;
+    run = Op::apply(run, v[k]);
+  }
+  if (threadIdx.x == kThreads - 1) sums[blockIdx.x] = run;
+}
+
+// single-CTA exclusive scan of the CTA totals (any length)
+template <typename Op>
+__global__ void __launch_bounds__(kThreads) k_xscan_sums(uint32_t* __restrict__ sums, uint32_t len) {
+  __shared__ uint32_t warp_tot[kWarps];
+  __shared__ uint32_t carry_s;
+  if (threadIdx.x == 0) carry_s = 0;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (uint32_t start = 0; start < len; start += kThreads) {
+    const uint32_t i = start + threadIdx.x;
+    const uint32_t v = i < len ? sums[i] : 0u;
+    const uint32_t incl = warp_inclusive<Op>(v, lane);
+    if (lane == 31) warp_tot[warp] = incl;
+    __syncthreads();
+    uint32_t run = carry_s, total = carry_s;
+#pragma unroll
+    for (int w = 0; w < kWarps; ++w) {
+      if (w < warp) run = Op::apply(run, warp_tot[w]);
+      total = Op::apply(total, warp_tot[w]);
+    }
+    const uint32_t prev_lane = __shfl_up_sync(0xffffffffu, incl, 1);
+    if (lane > 0) run = Op::apply(run, prev_lane);
+    if (i < len) sums[i] = run;
+    __syncthreads();
+    if (threadIdx.x == 0) carry_s = total;
+    __syncthreads();
+  }
+}
+
+template <typename Op>
+__global__ void __launch_bounds__(kThreads)
+    k_xscan_apply(uint32_t* __restrict__ data, uint32_t len, const uint32_t* __restrict__ sums) {
+  const uint32_t off = __ldg(sums + blockIdx.x);
+  const uint32_t base = blockIdx.x * kScanTile;
+#pragma unroll
+  for (int k = 0; k < kScanTile / kThreads; ++k) {
+    const uint32_t i = base + k * kThreads + threadIdx.x;
+    if (i < len) data[i] = Op::apply(data[i], off);
+  }
+}
+
+template <typename Op>
+int exclusive_scan(uint32_t* data, uint32_t len, uint32_t* scratch, cudaStream_t s) {
+  if (len == 0) return 0;
+  const uint32_t tiles = (len + kScanTile - 1) / kScanTile;
+  k_xscan_tiles<Op><<<tiles, kThreads, 0, s>>>(data, len, scratch);
+  if (tiles == 1) return 1;
+  k_xscan_sums<Op><<<1, kThreads, 0, s>>>(scratch, tiles);
+  k_xscan_apply<Op><<<tiles, kThreads, 0, s>>>(data, len, scratch);
+  return 3;
+}
+
 inline uint32_t tiles_for(uint32_t n) { return (n + kTile - 1) / kTile; }
 
 }  // namespace
@@ -178,6 +280,14 @@ inline uint32_t tiles_for(uint32_t n) { return (n + kTile - 1) / kTile; }
 size_t sort_hist_entries(uint32_t n) { return (size_t)256 * (tiles_for(n) ? tiles_for(n) : 1); }
 size_t sort_block_sum_entries(uint32_t n) {
   return (sort_hist_entries(n) + kScanTile - 1) / kScanTile;
+}
+
+size_t scan_scratch_entries(size_t len) { return (len + kScanTile - 1) / kScanTile + 1; }
+int launch_exclusive_sum(uint32_t* data, uint32_t len, uint32_t* scratch, cudaStream_t s) {
+  return exclusive_scan<OpSum>(data, len, scratch, s);
+}
+int launch_exclusive_max(uint32_t* data, uint32_t len, uint32_t* scratch, cudaStream_t s) {
+  return exclusive_scan<OpMax>(data, len, scratch, s);
 }
 
 int launch_sort_pairs(const SortBuffers& b, uint32_t n, int key_bits, int* result, cudaStream_t s) {

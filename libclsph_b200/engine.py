@@ -68,7 +68,7 @@ BB = np.dtype(
 )
 assert (PARTICLE.itemsize, PARAMS.itemsize, TERMS.itemsize, BB.itemsize) == (80, 128, 20, 56)
 
-PASS_NAMES = ["bbox", "locate", "sort", "reorder", "celltable", "density", "forces", "advect"]
+PASS_NAMES = ["bbox", "locate", "sort", "reorder", "celltable", "density", "forces", "advect", "refrank"]
 
 # every symbol include/sphb.h declares (tests check the library exports each one)
 SYMBOLS = [
