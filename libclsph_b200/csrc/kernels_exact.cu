@@ -226,9 +226,10 @@ __global__ void __launch_bounds__(kBlock)
              float4* __restrict__ vel_out, float4* __restrict__ vhf_out, uint32_t n, float dt,
              float restitution, const Face* __restrict__ faces, uint32_t face_count,
              const float* __restrict__ df, Reduce* red) {
-  const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
+  // grid-stride over a grid sized to the machine: one set of 8 atomics per CTA, not per 256
+  // particles (65 536 CTAs hammering the same 8 words serialise in L2)
   float rv[8] = {INFINITY, INFINITY, INFINITY, -INFINITY, -INFINITY, -INFINITY, -INFINITY, -INFINITY};
-  if (i < n) {
+  for (uint32_t i = blockIdx.x * kBlock + threadIdx.x; i < n; i += gridDim.x * kBlock) {
     const float4 x0 = __ldg(pos + i), vh = __ldg(vhf + i), a = __ldg(acc + i);
     // leapfrog
     const float nx = vh.x + a.x * dt, ny = vh.y + a.y * dt, nz = vh.z + a.z * dt;
@@ -285,15 +286,11 @@ __global__ void __launch_bounds__(kBlock)
     pos_out[i] = make_float4(rx, ry, rz, 0.f);
     vel_out[i] = make_float4(vx, vy, vz, 0.f);
     vhf_out[i] = make_float4(wx, wy, wz, 0.f);
-    // fmin/fmax skip NaNs, as OpenCL's min/max do
-    rv[0] = rx; rv[1] = ry; rv[2] = rz; rv[3] = rx; rv[4] = ry; rv[5] = rz;
-    rv[6] = vx * vx + vy * vy + vz * vz;
-    rv[7] = a.x * a.x + a.y * a.y + a.z * a.z;
-    if (rx != rx) { rv[0] = INFINITY; rv[3] = -INFINITY; }
-    if (ry != ry) { rv[1] = INFINITY; rv[4] = -INFINITY; }
-    if (rz != rz) { rv[2] = INFINITY; rv[5] = -INFINITY; }
-    if (rv[6] != rv[6]) rv[6] = -INFINITY;
-    if (rv[7] != rv[7]) rv[7] = -INFINITY;
+    // fminf / fmaxf return the non-NaN operand: NaNs are skipped, as OpenCL's min/max do
+    rv[0] = fminf(rv[0], rx); rv[1] = fminf(rv[1], ry); rv[2] = fminf(rv[2], rz);
+    rv[3] = fmaxf(rv[3], rx); rv[4] = fmaxf(rv[4], ry); rv[5] = fmaxf(rv[5], rz);
+    rv[6] = fmaxf(rv[6], vx * vx + vy * vy + vz * vz);
+    rv[7] = fmaxf(rv[7], a.x * a.x + a.y * a.y + a.z * a.z);
   }
   block_reduce_to(red, rv, 0xff);
 }
@@ -470,7 +467,9 @@ int launch_advect(const float4* pos, const float4* vhf, const float4* acc, float
                   float4* vel_out, float4* vhf_out, uint32_t n, float dt, float restitution,
                   const Face* faces, uint32_t face_count, const float* df, Reduce* red,
                   cudaStream_t s) {
-  k_advect<<<blocks_for(n), kBlock, 0, s>>>(pos, vhf, acc, pos_out, vel_out, vhf_out, n, dt,
+  unsigned grid = blocks_for(n);
+  if (grid > 148 * 8) grid = 148 * 8;  // 8 resident CTAs of 256 threads on each of 148 SMs
+  k_advect<<<grid, kBlock, 0, s>>>(pos, vhf, acc, pos_out, vel_out, vhf_out, n, dt,
                                             restitution, faces, face_count, df, red);
   return 1;
 }

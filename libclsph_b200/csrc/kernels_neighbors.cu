@@ -43,20 +43,44 @@ __device__ __forceinline__ void fine_coords_of(uint32_t key, const StepConsts& c
   fz = t / c.fny;
 }
 
-// first / one-past-last particle of the 3-cell row centred on fine cell (fx, fy + dy, fz + dz);
-// an empty range when the row lies outside the grid
-__device__ __forceinline__ void row_range(const uint32_t* __restrict__ ftable, const StepConsts& c,
-                                          uint32_t fx, uint32_t fy, uint32_t fz, int dy, int dz,
-                                          uint32_t& s, uint32_t& e) {
-  const uint32_t y = fy + dy, z = fz + dz;  // wraps to a huge value below 0
-  if (y >= c.fny || z >= c.fnz) {
-    s = e = 0;
-    return;
+// Where a particle sits inside its fine cell, in units of h: lo = distance to the cell's lower
+// face, hi = distance to its upper face (both clamped to [0, 1]).
+struct CellFrac {
+  float lo[3], hi[3];
+};
+__device__ __forceinline__ CellFrac cell_frac(const float4& p, uint32_t fx, uint32_t fy, uint32_t fz,
+                                              const StepConsts& c) {
+  CellFrac f;
+  const float inv_h = 1.f / c.h;
+  const float u[3] = {(p.x - c.minx) * inv_h - (float)fx, (p.y - c.miny) * inv_h - (float)fy,
+                      (p.z - c.minz) * inv_h - (float)fz};
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {
+    f.lo[a] = fminf(fmaxf(u[a], 0.f), 1.f);
+    f.hi[a] = 1.f - f.lo[a];
   }
-  const uint32_t x0 = fx > 0 ? fx - 1 : 0, x1 = min(fx + 2, c.fnx);
-  const uint32_t row = (z * c.fny + y) * c.fnx;
-  s = __ldg(ftable + row + x0);
-  e = __ldg(ftable + row + x1);
+  return f;
+}
+
+// First / one-past-last particle of the x-run of row (fy + dy, fz + dz) that can hold a
+// neighbour of a particle at `f` inside cell (fx, fy, fz): a neighbouring cell is visited only
+// if its nearest point is closer than h.  An empty range when nothing in the row can be.
+constexpr float kReach2 = 1.0f + 1.0e-3f;  // (h * (1 + slack))^2 in units of h^2
+__device__ __forceinline__ void row_range(const uint32_t* __restrict__ ftable, const StepConsts& c,
+                                          uint32_t fx, uint32_t fy, uint32_t fz, const CellFrac& f,
+                                          int dy, int dz, uint32_t& s, uint32_t& e) {
+  s = e = 0;
+  const uint32_t y = fy + dy, z = fz + dz;  // wraps to a huge value below 0
+  if (y >= c.fny || z >= c.fnz) return;
+  const float gy = dy < 0 ? f.lo[1] : (dy > 0 ? f.hi[1] : 0.f);
+  const float gz = dz < 0 ? f.lo[2] : (dz > 0 ? f.hi[2] : 0.f);
+  const float q = gy * gy + gz * gz;
+  if (q >= kReach2) return;
+  const bool left = fx > 0 && q + f.lo[0] * f.lo[0] < kReach2;
+  const bool right = fx + 1 < c.fnx && q + f.hi[0] * f.hi[0] < kReach2;
+  const uint32_t row = (z * c.fny + y) * c.fnx + fx;
+  s = __ldg(ftable + row - (left ? 1u : 0u));
+  e = __ldg(ftable + row + (right ? 2u : 1u));
 }
 
 // ---- one thread per particle walking the 9 rows ------------------------------------------
@@ -69,13 +93,14 @@ __global__ void __launch_bounds__(kBlock)
   const float4 pi = pos[i];
   uint32_t fx, fy, fz;
   fine_coords_of(__ldg(keys + i), c, fx, fy, fz);
+  const CellFrac f = cell_frac(pi, fx, fy, fz, c);
   float sum = 0.f;
 #pragma unroll 1
   for (int dz = -1; dz <= 1; ++dz)
 #pragma unroll 1
     for (int dy = -1; dy <= 1; ++dy) {
       uint32_t s, e;
-      row_range(ftable, c, fx, fy, fz, dy, dz, s, e);
+      row_range(ftable, c, fx, fy, fz, f, dy, dz, s, e);
       for (uint32_t j = s; j < e; ++j) {
         const float4 pj = __ldg(reinterpret_cast<const float4*>(pos) + j);
         const float dx = pi.x - pj.x, dy_ = pi.y - pj.y, dz_ = pi.z - pj.z;
@@ -150,29 +175,53 @@ __device__ __forceinline__ float4 force_finish(const ForceAcc& A, float rho_i, f
   return make_float4(sx / rho_i + c.gx, sy / rho_i + c.gy, sz / rho_i + c.gz, 0.f);
 }
 
+// Forces in two loops per particle.  Loop A tests the ~100 candidates and only RECORDS the
+// ~20-40 with r < h in a per-thread column of shared memory; loop B then evaluates the pair
+// terms for recorded neighbours only.  In a single loop nearly every iteration has at least
+// one of the 32 lanes inside h, so the whole warp would pay for the ~45-instruction pair
+// evaluation on every candidate.
+constexpr int kHitCap = 40;
 __global__ void __launch_bounds__(kBlock)
-    k_forces_walk(const float4* __restrict__ pos, const float4* __restrict__ vel,
+    k_forces_list(const float4* __restrict__ pos, const float4* __restrict__ vel,
                   const uint32_t* __restrict__ keys, const uint32_t* __restrict__ ftable,
                   const float* __restrict__ rho, float4* __restrict__ acc, StepConsts c) {
+  __shared__ uint32_t hit[kHitCap][kBlock];
   const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
   if (i >= c.n) return;
   const float4 pi = __ldg(pos + i), vi = __ldg(vel + i);
   uint32_t fx, fy, fz;
   fine_coords_of(__ldg(keys + i), c, fx, fy, fz);
+  const CellFrac f = cell_frac(pi, fx, fy, fz, c);
   ForceAcc A = {};
+  int cnt = 0;
+  auto drain = [&]() {
+    for (int k = 0; k < cnt; ++k) {
+      const uint32_t j = hit[k][threadIdx.x];
+      const float4 pj = __ldg(pos + j);
+      const float4 vj = __ldg(vel + j);
+      const float dx = pi.x - pj.x, dy_ = pi.y - pj.y, dz_ = pi.z - pj.z;
+      const float r2 = dx * dx + dy_ * dy_ + dz_ * dz_;
+      force_pair(A, pi, vi, pj, vj, dx, dy_, dz_, r2, c);
+    }
+    cnt = 0;
+  };
 #pragma unroll 1
   for (int dz = -1; dz <= 1; ++dz)
 #pragma unroll 1
     for (int dy = -1; dy <= 1; ++dy) {
       uint32_t s, e;
-      row_range(ftable, c, fx, fy, fz, dy, dz, s, e);
+      row_range(ftable, c, fx, fy, fz, f, dy, dz, s, e);
       for (uint32_t j = s; j < e; ++j) {
         const float4 pj = __ldg(pos + j);
         const float dx = pi.x - pj.x, dy_ = pi.y - pj.y, dz_ = pi.z - pj.z;
         const float r2 = dx * dx + dy_ * dy_ + dz_ * dz_;
-        if (r2 < c.h2 && j != i) force_pair(A, pi, vi, pj, __ldg(vel + j), dx, dy_, dz_, r2, c);
+        if (r2 < c.h2 && j != i) {
+          hit[cnt][threadIdx.x] = j;
+          if (++cnt == kHitCap) drain();
+        }
       }
     }
+  drain();
   acc[i] = force_finish(A, __ldg(rho + i), vi.w, c);
 }
 
@@ -191,7 +240,7 @@ int launch_forces(const float4* pos, const float4* vel, const uint32_t* keys,
                   const uint32_t* ftable, const float* rho, float4* acc, const StepConsts& c,
                   int variant, cudaStream_t s) {
   (void)variant;
-  k_forces_walk<<<blocks_for(c.n), kBlock, 0, s>>>(pos, vel, keys, ftable, rho, acc, c);
+  k_forces_list<<<blocks_for(c.n), kBlock, 0, s>>>(pos, vel, keys, ftable, rho, acc, c);
   return 1;
 }
 
