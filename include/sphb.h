@@ -156,7 +156,8 @@ uint64_t sphb_launch_count(sphb_engine* e);
 /* the engine's cudaStream_t (as void*), so a caller can record its own events on it */
 void* sphb_stream(sphb_engine* e);
 /* named integer options; unknown names return SPHB_ERR_INVALID.
- *   "neighbor_kernel"  0 = per-particle 27-cell walk, 1 = cell-tile staged kernel (default) */
+ *   "neighbor_kernel"  0 (default) = the density pass records a neighbour list that the forces
+ *                      pass consumes; 1 = both passes search the grid on their own */
 int sphb_set_option(sphb_engine* e, const char* name, int value);
 
 /* Page-locked host memory for the particle array (the reference asks OpenCL for

@@ -145,11 +145,16 @@ int launch_exclusive_sum(uint32_t* data, uint32_t len, uint32_t* scratch, cudaSt
 int launch_exclusive_max(uint32_t* data, uint32_t len, uint32_t* scratch, cudaStream_t s);
 
 // kernels_neighbors.cu (compiled with FMA contraction on; tolerance-checked)
-// keys = compute-ordered fine keys, ftable = fine cell table (nfine + 1 entries)
+// keys = compute-ordered fine keys, ftable = fine cell table (nfine + 1 entries).
+// variant 0: the density pass records a neighbour list (nlist: neighbor_list_entries(n) u16,
+// ncount: n u8) that the forces pass consumes; variant 1: both passes search on their own.
+size_t neighbor_list_entries(uint32_t n);
 int launch_density(float4* pos, float4* vel, const uint32_t* keys, const uint32_t* ftable,
-                   float* rho, float* prs, const StepConsts& c, int variant, cudaStream_t s);
+                   float* rho, float* prs, uint16_t* nlist, uint8_t* ncount, const StepConsts& c,
+                   int variant, cudaStream_t s);
 int launch_forces(const float4* pos, const float4* vel, const uint32_t* keys,
-                  const uint32_t* ftable, const float* rho, float4* acc, const StepConsts& c,
-                  int variant, cudaStream_t s);
+                  const uint32_t* ftable, const float* rho, const uint16_t* nlist,
+                  const uint8_t* ncount, float4* acc, const StepConsts& c, int variant,
+                  cudaStream_t s);
 
 }  // namespace sphb

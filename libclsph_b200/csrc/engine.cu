@@ -43,6 +43,8 @@ struct sphb_engine {
   uint32_t* rank_cur = nullptr;
   uint32_t* rank_prev = nullptr;
   uint32_t* ckey = nullptr;
+  uint16_t* nlist = nullptr;  // neighbour codes recorded by the density pass, k-major
+  uint8_t* ncount = nullptr;
   uint32_t* ftable = nullptr;     // fine cell table, nfine + 1 entries
   size_t ftable_cap = 0;
   uint32_t* ref_table = nullptr;  // the reference's cell table, grid_cell_count (+1) entries
@@ -210,6 +212,7 @@ int sphb_destroy(sphb_engine* e) {
   cudaFree(e->acc); cudaFree(e->rho); cudaFree(e->prs);
   cudaFree(e->sortb.hist); cudaFree(e->sortb.block_sums);
   cudaFree(e->rank_cur); cudaFree(e->rank_prev); cudaFree(e->ckey);
+  cudaFree(e->nlist); cudaFree(e->ncount);
   cudaFree(e->ftable); cudaFree(e->ref_table); cudaFree(e->scan_scratch); cudaFree(e->aos_stage);
   cudaFree(e->faces); cudaFree(e->face_offsets); cudaFree(e->df);
   cudaFree(e->red);
@@ -273,6 +276,8 @@ int sphb_create(const sphb_params* params, const sphb_terms* terms, int device, 
   TRY_OR_DESTROY(dev_alloc(&e->rank_cur, n));
   TRY_OR_DESTROY(dev_alloc(&e->rank_prev, n));
   TRY_OR_DESTROY(dev_alloc(&e->ckey, n));
+  TRY_OR_DESTROY(dev_alloc(&e->nlist, neighbor_list_entries(n)));
+  TRY_OR_DESTROY(dev_alloc(&e->ncount, n));
   TRY_OR_DESTROY(dev_alloc(&e->acc, n));
   TRY_OR_DESTROY(dev_alloc(&e->rho, n));
   TRY_OR_DESTROY(dev_alloc(&e->prs, n));
@@ -498,12 +503,12 @@ int sphb_step(sphb_engine* e, float dt_in, float* dt_out) {
   {
     PassTimer t(e, SPHB_PASS_DENSITY);
     t.done(launch_density(e->pos[e->cur], e->vel[e->cur], e->sortb.keys[r], e->ftable, e->rho,
-                          e->prs, c, e->neighbor_variant, s));
+                          e->prs, e->nlist, e->ncount, c, e->neighbor_variant, s));
   }
   {
     PassTimer t(e, SPHB_PASS_FORCES);
     t.done(launch_forces(e->pos[e->cur], e->vel[e->cur], e->sortb.keys[r], e->ftable, e->rho,
-                         e->acc, c, e->neighbor_variant, s));
+                         e->nlist, e->ncount, e->acc, c, e->neighbor_variant, s));
   }
   CUDA_TRY(e, cudaGetLastError());
 

@@ -83,11 +83,22 @@ __device__ __forceinline__ void row_range(const uint32_t* __restrict__ ftable, c
   e = __ldg(ftable + row + (right ? 2u : 1u));
 }
 
-// ---- one thread per particle walking the 9 rows ------------------------------------------
+// ---- density + pressure: one thread per particle walking the 9 rows -----------------------
+// Besides the density sum, the pass RECORDS which candidates were inside h, so that the forces
+// pass does not have to search again: a neighbour is stored as a 16-bit code
+// (row 0..8) << 12 | (offset of the neighbour inside that row's run), staged per thread in
+// shared memory and flushed k-major (nlist[k * n + i]) so that the stores — and the forces
+// pass's loads — are coalesced across the warp.  count 255 = "list unusable" (more than
+// kListCap neighbours, or a row run longer than 4096): the forces pass then searches itself.
+constexpr int kListCap = 64;
+constexpr uint32_t kListOverflow = 255;
+
 __global__ void __launch_bounds__(kBlock)
-    k_density_walk(float4* pos, float4* vel, const uint32_t* __restrict__ keys,
+    k_density_list(float4* pos, float4* vel, const uint32_t* __restrict__ keys,
                    const uint32_t* __restrict__ ftable, float* __restrict__ rho,
-                   float* __restrict__ prs, StepConsts c) {
+                   float* __restrict__ prs, uint16_t* __restrict__ nlist,
+                   uint8_t* __restrict__ ncount, StepConsts c) {
+  __shared__ uint16_t hit[kListCap][kBlock];
   const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
   if (i >= c.n) return;
   const float4 pi = pos[i];
@@ -95,17 +106,28 @@ __global__ void __launch_bounds__(kBlock)
   fine_coords_of(__ldg(keys + i), c, fx, fy, fz);
   const CellFrac f = cell_frac(pi, fx, fy, fz, c);
   float sum = 0.f;
+  uint32_t cnt = 0;
+  bool overflow = false;
+  int row = 0;
 #pragma unroll 1
   for (int dz = -1; dz <= 1; ++dz)
 #pragma unroll 1
-    for (int dy = -1; dy <= 1; ++dy) {
+    for (int dy = -1; dy <= 1; ++dy, ++row) {
       uint32_t s, e;
       row_range(ftable, c, fx, fy, fz, f, dy, dz, s, e);
+      if (e - s > 4096u) overflow = true;
+      const uint32_t tag = (uint32_t)row << 12;
       for (uint32_t j = s; j < e; ++j) {
         const float4 pj = __ldg(reinterpret_cast<const float4*>(pos) + j);
         const float dx = pi.x - pj.x, dy_ = pi.y - pj.y, dz_ = pi.z - pj.z;
         const float t = c.h2 - (dx * dx + dy_ * dy_ + dz_ * dz_);
-        if (t > 0.f) sum += t * t * t;
+        if (t > 0.f) {
+          sum += t * t * t;
+          if (j != i) {
+            if (cnt < (uint32_t)kListCap) hit[cnt][threadIdx.x] = (uint16_t)(tag | ((j - s) & 4095u));
+            ++cnt;
+          }
+        }
       }
     }
   const float density = (c.mass * c.c_poly6) * sum;
@@ -115,6 +137,10 @@ __global__ void __launch_bounds__(kBlock)
   // derived per-particle factors for the forces pass (only the w lanes are written)
   reinterpret_cast<float*>(pos + i)[3] = pressure / (density * density);
   reinterpret_cast<float*>(vel + i)[3] = c.mass / density;
+  if (cnt > (uint32_t)kListCap) overflow = true;
+  ncount[i] = overflow ? (uint8_t)kListOverflow : (uint8_t)cnt;
+  if (!overflow)
+    for (uint32_t k = 0; k < cnt; ++k) nlist[(size_t)k * c.n + i] = hit[k][threadIdx.x];
 }
 
 struct ForceAcc {
@@ -225,22 +251,80 @@ __global__ void __launch_bounds__(kBlock)
   acc[i] = force_finish(A, __ldg(rho + i), vi.w, c);
 }
 
+// Forces from the neighbour list the density pass recorded.
+__global__ void __launch_bounds__(kBlock)
+    k_forces_nlist(const float4* __restrict__ pos, const float4* __restrict__ vel,
+                   const uint32_t* __restrict__ keys, const uint32_t* __restrict__ ftable,
+                   const float* __restrict__ rho, const uint16_t* __restrict__ nlist,
+                   const uint8_t* __restrict__ ncount, float4* __restrict__ acc, StepConsts c) {
+  __shared__ uint32_t row_start[9][kBlock];
+  const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
+  if (i >= c.n) return;
+  const float4 pi = __ldg(pos + i), vi = __ldg(vel + i);
+  uint32_t fx, fy, fz;
+  fine_coords_of(__ldg(keys + i), c, fx, fy, fz);
+  const CellFrac f = cell_frac(pi, fx, fy, fz, c);
+  const uint32_t cnt = ncount[i];
+  ForceAcc A = {};
+  if (cnt != kListOverflow) {
+    int row = 0;
+#pragma unroll
+    for (int dz = -1; dz <= 1; ++dz)
+#pragma unroll
+      for (int dy = -1; dy <= 1; ++dy, ++row) {
+        uint32_t s, e;
+        row_range(ftable, c, fx, fy, fz, f, dy, dz, s, e);
+        row_start[row][threadIdx.x] = s;
+      }
+    for (uint32_t k = 0; k < cnt; ++k) {
+      const uint32_t code = nlist[(size_t)k * c.n + i];
+      const uint32_t j = row_start[code >> 12][threadIdx.x] + (code & 4095u);
+      const float4 pj = __ldg(pos + j);
+      const float4 vj = __ldg(vel + j);
+      const float dx = pi.x - pj.x, dy_ = pi.y - pj.y, dz_ = pi.z - pj.z;
+      const float r2 = dx * dx + dy_ * dy_ + dz_ * dz_;
+      force_pair(A, pi, vi, pj, vj, dx, dy_, dz_, r2, c);
+    }
+  } else {  // the list overflowed: search again
+#pragma unroll 1
+    for (int dz = -1; dz <= 1; ++dz)
+#pragma unroll 1
+      for (int dy = -1; dy <= 1; ++dy) {
+        uint32_t s, e;
+        row_range(ftable, c, fx, fy, fz, f, dy, dz, s, e);
+        for (uint32_t j = s; j < e; ++j) {
+          const float4 pj = __ldg(pos + j);
+          const float dx = pi.x - pj.x, dy_ = pi.y - pj.y, dz_ = pi.z - pj.z;
+          const float r2 = dx * dx + dy_ * dy_ + dz_ * dz_;
+          if (r2 < c.h2 && j != i) force_pair(A, pi, vi, pj, __ldg(vel + j), dx, dy_, dz_, r2, c);
+        }
+      }
+  }
+  acc[i] = force_finish(A, __ldg(rho + i), vi.w, c);
+}
+
 inline unsigned blocks_for(uint32_t n) { return (n + kBlock - 1) / kBlock; }
 
 }  // namespace
 
+size_t neighbor_list_entries(uint32_t n) { return (size_t)kListCap * n; }
+
 int launch_density(float4* pos, float4* vel, const uint32_t* keys, const uint32_t* ftable,
-                   float* rho, float* prs, const StepConsts& c, int variant, cudaStream_t s) {
-  (void)variant;
-  k_density_walk<<<blocks_for(c.n), kBlock, 0, s>>>(pos, vel, keys, ftable, rho, prs, c);
+                   float* rho, float* prs, uint16_t* nlist, uint8_t* ncount, const StepConsts& c,
+                   int variant, cudaStream_t s) {
+  (void)variant;  // the list is recorded either way; variant 1 just does not use it
+  k_density_list<<<blocks_for(c.n), kBlock, 0, s>>>(pos, vel, keys, ftable, rho, prs, nlist, ncount, c);
   return 1;
 }
 
 int launch_forces(const float4* pos, const float4* vel, const uint32_t* keys,
-                  const uint32_t* ftable, const float* rho, float4* acc, const StepConsts& c,
-                  int variant, cudaStream_t s) {
-  (void)variant;
-  k_forces_list<<<blocks_for(c.n), kBlock, 0, s>>>(pos, vel, keys, ftable, rho, acc, c);
+                  const uint32_t* ftable, const float* rho, const uint16_t* nlist,
+                  const uint8_t* ncount, float4* acc, const StepConsts& c, int variant,
+                  cudaStream_t s) {
+  if (variant == 1)
+    k_forces_list<<<blocks_for(c.n), kBlock, 0, s>>>(pos, vel, keys, ftable, rho, acc, c);
+  else
+    k_forces_nlist<<<blocks_for(c.n), kBlock, 0, s>>>(pos, vel, keys, ftable, rho, nlist, ncount, acc, c);
   return 1;
 }
 

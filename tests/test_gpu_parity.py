@@ -160,3 +160,42 @@ def test_free_run_matches_reference(port_oracle):
             for k in ("pos", "vel", "vhf", "acc", "rho"):
                 assert rel_err(got[k], g[f"s{s}_{k}"]) <= 50 * TOL, (s, k)
             assert abs(dt - float(g[f"s{s}_dt"])) <= 50 * TOL * float(g[f"s{s}_dt"])
+
+
+@pytest.mark.parametrize("variant", [0, 1])
+def test_neighbor_kernel_variants(variant):
+    """Both neighbour-pass variants (recorded list / independent search) against the fixture."""
+    from libclsph_b200 import Engine
+    g = np.load(os.path.join(GOLDEN, "steps_monkeybox_mucus.npz"))
+    sc = np.load(os.path.join(GOLDEN, "scene_monkeybox_mucus.npz"))
+    params = g["params0"].copy()
+    with Engine(params, g["terms"]) as e:
+        e.set_option("neighbor_kernel", variant)
+        e.set_scene(sc["bbs"], sc["transforms"], sc["rvertices"], int(sc["total_gridpoints"]))
+        e.upload(g["initial"])
+        e.step(float(g["dt0"]))
+        out = e.download()
+    want = {k: g[f"s0_{k}"] for k in ("pos", "vel", "vhf", "acc", "rho", "prs")}
+    check_floats(state_arrays(out), want, float(params["K"][0]), float(params["fluid_density"][0]), f"variant {variant}")
+
+
+def test_neighbor_list_overflow_falls_back(tmp_path, port_oracle):
+    """A block compressed to ~5x rest density: more than 64 neighbours per particle, so the
+    recorded list overflows and the forces pass must search on its own."""
+    case = make_case(tmp_path, "water", 4096)
+    p = case["particles"]
+    p["position"][:, :3] *= np.float32(0.6)
+    orc = port_oracle
+    sc = case["scene"]
+    df = orc.compute_df(sc["bbs"], sc["transforms"], sc["rvertices"], int(sc["total_gridpoints"]))
+    front, params = p.copy(), case["params"].copy()
+    with new_engine(case) as e:
+        e.upload(p)
+        e.step(1.0 / 600.0)
+        out = e.download()
+        dbg = e.debug()
+    r = orc.step(front, params, case["terms"].copy(), df, sc["bbs"], 1.0 / 600.0)
+    check_exact(dbg, out["grid_index"], r["perm"], r["cell_table"], front["grid_index"], "overflow")
+    got, want = state_arrays(out), state_arrays(front)
+    assert rel_err(got["rho"], want["rho"]) <= TOL
+    assert rel_err(got["acc"], want["acc"]) <= TOL
