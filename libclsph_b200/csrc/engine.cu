@@ -22,6 +22,8 @@ using namespace sphb;
 struct sphb_engine {
   int device = 0;
   cudaStream_t stream = nullptr;
+  cudaStream_t side = nullptr;  // the reference-order bookkeeping runs beside the neighbour passes
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   uint32_t n = 0;
   sphb_params params;   // the reference's `parameters`, mutated every step
   sphb_terms terms;
@@ -170,13 +172,15 @@ StepConsts make_consts(const sphb_engine* e) {
 struct PassTimer {
   sphb_engine* e;
   int pass;
-  PassTimer(sphb_engine* e_, int pass_) : e(e_), pass(pass_) {
-    if (e->profile) cudaEventRecord(e->ev[pass][0], e->stream);
+  cudaStream_t st;
+  PassTimer(sphb_engine* e_, int pass_, cudaStream_t st_ = nullptr)
+      : e(e_), pass(pass_), st(st_ ? st_ : e_->stream) {
+    if (e->profile) cudaEventRecord(e->ev[pass][0], st);
   }
   void done(int launches) {
     e->launches += launches;
     if (e->profile) {
-      cudaEventRecord(e->ev[pass][1], e->stream);
+      cudaEventRecord(e->ev[pass][1], st);
       e->pass_launches[pass] += launches;
     }
   }
@@ -223,6 +227,9 @@ int sphb_destroy(sphb_engine* e) {
       cudaEventDestroy(e->ev[p][1]);
       if (p < 4) cudaEventDestroy(e->user_ev[p]);
     }
+  if (e->ev_fork) cudaEventDestroy(e->ev_fork);
+  if (e->ev_join) cudaEventDestroy(e->ev_join);
+  if (e->side) cudaStreamDestroy(e->side);
   if (e->stream) cudaStreamDestroy(e->stream);
   delete e;
   return 0;
@@ -266,6 +273,13 @@ int sphb_create(const sphb_params* params, const sphb_terms* terms, int device, 
   } while (0)
   TRY_OR_DESTROY(cudaSetDevice(device));
   TRY_OR_DESTROY(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
+  {  // highest priority: its small kernels must slot in between the neighbour passes' CTAs
+    int lo = 0, hi = 0;
+    TRY_OR_DESTROY(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+    TRY_OR_DESTROY(cudaStreamCreateWithPriority(&e->side, cudaStreamNonBlocking, hi));
+  }
+  TRY_OR_DESTROY(cudaEventCreateWithFlags(&e->ev_fork, cudaEventDisableTiming));
+  TRY_OR_DESTROY(cudaEventCreateWithFlags(&e->ev_join, cudaEventDisableTiming));
   for (int k = 0; k < 2; ++k) {
     TRY_OR_DESTROY(dev_alloc(&e->pos[k], n));
     TRY_OR_DESTROY(dev_alloc(&e->vel[k], n));
@@ -493,12 +507,16 @@ int sphb_step(sphb_engine* e, float dt_in, float* dt_out) {
     t.done(launch_fine_table(e->sortb.keys[r], n, e->ftable, c.nfine, e->scan_scratch, s));
   }
   // the reference's cell table (kernels/sort.cl:61-78) and every particle's place in the
-  // reference's sorted array
+  // reference's sorted array: nothing in the step depends on it, so it runs on the side
+  // stream while the (compute-bound) neighbour passes run, and is joined before the step ends
+  CUDA_TRY(e, cudaEventRecord(e->ev_fork, s));
+  CUDA_TRY(e, cudaStreamWaitEvent(e->side, e->ev_fork, 0));
   {
-    PassTimer t(e, SPHB_PASS_REFRANK);
+    PassTimer t(e, SPHB_PASS_REFRANK, e->side);
     t.done(launch_reference_rank(e->sortb.keys[r], e->ftable, e->rank_prev, e->ref_table, e->ckey,
-                                 e->rank_cur, c, e->scan_scratch, s));
+                                 e->rank_cur, c, e->scan_scratch, e->side));
   }
+  CUDA_TRY(e, cudaEventRecord(e->ev_join, e->side));
   // 4. density_pressure (kernels/sphb.cl:3-35), 5. forces (:37-126)
   {
     PassTimer t(e, SPHB_PASS_DENSITY);
@@ -510,6 +528,7 @@ int sphb_step(sphb_engine* e, float dt_in, float* dt_out) {
     t.done(launch_forces(e->pos[e->cur], e->vel[e->cur], e->sortb.keys[r], e->ftable, e->rho,
                          e->nlist, e->ncount, e->acc, c, e->neighbor_variant, s));
   }
+  CUDA_TRY(e, cudaStreamWaitEvent(s, e->ev_join, 0));
   CUDA_TRY(e, cudaGetLastError());
 
   // 6. do { advection_collision(dt); computed = computeTimeStep } while (dt - computed > 1e-5)

@@ -98,7 +98,8 @@ __global__ void __launch_bounds__(kBlock)
                    const uint32_t* __restrict__ ftable, float* __restrict__ rho,
                    float* __restrict__ prs, uint16_t* __restrict__ nlist,
                    uint8_t* __restrict__ ncount, StepConsts c) {
-  __shared__ uint16_t hit[kListCap][kBlock];
+  // one column per thread; row kListCap is a dump row that absorbs writes past the capacity
+  __shared__ uint16_t hit[(kListCap + 1) * kBlock];
   const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
   if (i >= c.n) return;
   const float4 pi = pos[i];
@@ -106,28 +107,34 @@ __global__ void __launch_bounds__(kBlock)
   fine_coords_of(__ldg(keys + i), c, fx, fy, fz);
   const CellFrac f = cell_frac(pi, fx, fy, fz, c);
   float sum = 0.f;
-  uint32_t cnt = 0;
+  // The inner loop is branch-free: the cubic term is clamped instead of skipped, and a hit
+  // (the particle itself included — the forces pass skips it) is recorded with a predicated
+  // store at a cursor that advances only on hits.
+  // (shared-window byte addresses, so that the store is one predicated STS)
+  const uint32_t hit_base = (uint32_t)__cvta_generic_to_shared(hit) + 2u * threadIdx.x;
+  uint32_t cursor = hit_base;
+  const uint32_t cursor_end = hit_base + 2u * kListCap * kBlock;
   bool overflow = false;
-  int row = 0;
+  uint32_t tag = 0;
 #pragma unroll 1
   for (int dz = -1; dz <= 1; ++dz)
 #pragma unroll 1
-    for (int dy = -1; dy <= 1; ++dy, ++row) {
+    for (int dy = -1; dy <= 1; ++dy, tag += 4096u) {
       uint32_t s, e;
       row_range(ftable, c, fx, fy, fz, f, dy, dz, s, e);
       if (e - s > 4096u) overflow = true;
-      const uint32_t tag = (uint32_t)row << 12;
-      for (uint32_t j = s; j < e; ++j) {
+      uint32_t code = tag;
+#pragma unroll 4
+      for (uint32_t j = s; j < e; ++j, ++code) {
         const float4 pj = __ldg(reinterpret_cast<const float4*>(pos) + j);
         const float dx = pi.x - pj.x, dy_ = pi.y - pj.y, dz_ = pi.z - pj.z;
         const float t = c.h2 - (dx * dx + dy_ * dy_ + dz_ * dz_);
-        if (t > 0.f) {
-          sum += t * t * t;
-          if (j != i) {
-            if (cnt < (uint32_t)kListCap) hit[cnt][threadIdx.x] = (uint16_t)(tag | ((j - s) & 4095u));
-            ++cnt;
-          }
-        }
+        const bool inside = t > 0.f;
+        const float tt = fmaxf(t, 0.f);
+        sum = fmaf(tt * tt, tt, sum);
+        asm volatile("{ .reg .pred p; setp.ne.u32 p, %2, 0; @p st.shared.u16 [%0], %1; }"
+                     :: "r"(cursor), "h"((uint16_t)code), "r"((uint32_t)inside) : "memory");
+        cursor = min(cursor + (inside ? 2u * kBlock : 0u), cursor_end);
       }
     }
   const float density = (c.mass * c.c_poly6) * sum;
@@ -137,10 +144,11 @@ __global__ void __launch_bounds__(kBlock)
   // derived per-particle factors for the forces pass (only the w lanes are written)
   reinterpret_cast<float*>(pos + i)[3] = pressure / (density * density);
   reinterpret_cast<float*>(vel + i)[3] = c.mass / density;
-  if (cnt > (uint32_t)kListCap) overflow = true;
+  const uint32_t cnt = (cursor - hit_base) / (2u * kBlock);
+  if (cnt >= (uint32_t)kListCap) overflow = true;  // the dump row was reached
   ncount[i] = overflow ? (uint8_t)kListOverflow : (uint8_t)cnt;
   if (!overflow)
-    for (uint32_t k = 0; k < cnt; ++k) nlist[(size_t)k * c.n + i] = hit[k][threadIdx.x];
+    for (uint32_t k = 0; k < cnt; ++k) nlist[(size_t)k * c.n + i] = hit[k * kBlock + threadIdx.x];
 }
 
 struct ForceAcc {
@@ -279,6 +287,7 @@ __global__ void __launch_bounds__(kBlock)
     for (uint32_t k = 0; k < cnt; ++k) {
       const uint32_t code = nlist[(size_t)k * c.n + i];
       const uint32_t j = row_start[code >> 12][threadIdx.x] + (code & 4095u);
+      if (j == i) continue;  // the list holds the particle itself
       const float4 pj = __ldg(pos + j);
       const float4 vj = __ldg(vel + j);
       const float dx = pi.x - pj.x, dy_ = pi.y - pj.y, dz_ = pi.z - pj.z;
