@@ -39,6 +39,7 @@ extern "C" {
 #define SPHB_ERR_NO_DEVICE (-3)   /* no usable CUDA device */
 #define SPHB_ERR_NO_SCENE (-4)    /* sphb_step before sphb_set_scene */
 #define SPHB_ERR_NCCL_MISSING (-5)/* multi-GPU entry point used but libnccl could not be loaded */
+#define SPHB_ERR_CAPACITY (-6)    /* slab engine: more particles / halo records than allocated */
 #define SPHB_ERR_NCCL_BASE 100000 /* ncclResult_t r is returned as SPHB_ERR_NCCL_BASE + r */
 
 typedef struct { float s[4]; } sphb_float3; /* cl_float3 */
@@ -126,6 +127,46 @@ int sphb_download_debug(sphb_engine* e, uint32_t* keys, uint32_t* perm, uint32_t
 /* Parity hook: runs ONLY advection_collision (kernels/sphb.cl:177-223) with time step dt over
  * the uploaded state (uploaded accelerations included), in place of a full step. */
 int sphb_debug_advect(sphb_engine* e, float dt);
+
+/* ---- slab engines: the step partitioned over the GPUs of one box ---------------------------
+ * The reference is single-device (libclsph/sph_simulation.cpp:273-275); this section is new.
+ * One process per GPU creates ONE slab engine that owns the particles with x in [xlo, xhi).
+ * Per step the caller moves two fixed-size messages to / from its slab neighbours (NCCL send /
+ * recv over NVLink) and all-reduces 8 floats per advection attempt; the engine does the rest:
+ *
+ *   sphb_slab_pack(e, send_left, send_right)      owned particles -> migrants + 2h ghost layer
+ *   [send/recv sphb_slab_message_bytes(e) bytes with each neighbour]
+ *   sphb_slab_unpack(e, recv_left, recv_right, &n_owned, &n_ghost)
+ *   sphb_slab_forces(e, global_min, global_max)   grid of the GLOBAL bbox, density over owned +
+ *                                                 ghosts, forces over owned
+ *   do { sphb_slab_advect(e, dt, red8); [all-reduce MAX red8]; dt' = sphb_compute_dt(...); }
+ *   while (dt - dt' > 1e-5)                       (sph_simulation.cpp:246-260)
+ *   sphb_slab_commit(e)                           drop the ghosts; red8 = the next global bbox
+ *
+ * red8 (device floats): -min x, -min y, -min z, max x, max y, max z, max |v|^2, max |a|^2 over
+ * the owned particles, so that ONE all-reduce(MAX) serves computeTimeStep and the next step's
+ * findMinMaxPosition.  All message / red8 pointers are DEVICE pointers owned by the caller;
+ * every call is enqueued on sphb_stream(e).  Particles carry a caller-chosen 31-bit id; there
+ * is no global sorted order across slabs: downloads return (particle, id) pairs, with
+ * grid_index the reference's Morton key under the global grid. */
+int sphb_slab_create(const sphb_params* params /* particles_count = GLOBAL count */,
+                     const sphb_terms* terms, int device, uint32_t capacity /* local particle slots */,
+                     uint32_t exchange_capacity /* records per message */, sphb_engine** out);
+size_t sphb_slab_message_bytes(sphb_engine* e); /* 16 + 48 * exchange_capacity */
+int sphb_slab_configure(sphb_engine* e, float xlo, float xhi, int has_left, int has_right);
+int sphb_slab_upload(sphb_engine* e, const sphb_particle* aos, const uint32_t* ids, uint32_t n_owned);
+int sphb_slab_bbox(sphb_engine* e, float* red8_dev); /* bbox of the owned positions only */
+int sphb_slab_pack(sphb_engine* e, void* send_left_dev, void* send_right_dev);
+int sphb_slab_unpack(sphb_engine* e, const void* recv_left_dev, const void* recv_right_dev,
+                     uint32_t* n_owned, uint32_t* n_ghost); /* synchronises: the host learns the counts */
+int sphb_slab_forces(sphb_engine* e, const float global_min[3], const float global_max[3]);
+int sphb_slab_advect(sphb_engine* e, float dt, float* red8_dev);
+int sphb_slab_commit(sphb_engine* e);
+/* owned particles in local order + their ids (aos / ids nullable: just the count) */
+int sphb_slab_download(sphb_engine* e, sphb_particle* aos, uint32_t* ids, uint32_t capacity,
+                       uint32_t* n_owned);
+/* computeTimeStep's host arithmetic (libclsph/sph_simulation.cpp:598-602) */
+float sphb_compute_dt(const sphb_params* params, float max_v2, float max_a2);
 
 /* ---- measurement ------------------------------------------------------------------ */
 enum {

@@ -30,7 +30,8 @@ SOURCES = {
     "kernels_exact.cu": ["-fmad=false"],
     "kernels_sort.cu": [],
     "kernels_neighbors.cu": [],
-    "multi.cu": [],
+    "kernels_slab.cu": ["-fmad=false"],
+    "slab.cu": [],
 }
 
 

@@ -112,7 +112,7 @@ int launch_reference_debug(const uint32_t* rank, const uint32_t* rank_prev, cons
 int launch_advect(const float4* pos, const float4* vhf, const float4* acc, float4* pos_out,
                   float4* vel_out, float4* vhf_out, uint32_t n, float dt, float restitution,
                   const Face* faces, uint32_t face_count, const float* df, Reduce* red,
-                  cudaStream_t s);
+                  cudaStream_t s, const uint32_t* ghost_ids = nullptr);
 int launch_distance_field(float* df, const Face* faces, const uint32_t* face_offsets,
                           const float* transforms, const float* rvertices, uint32_t face_count,
                           uint32_t gridcount, cudaStream_t s);
@@ -155,6 +155,27 @@ int launch_density(float4* pos, float4* vel, const uint32_t* keys, const uint32_
 int launch_forces(const float4* pos, const float4* vel, const uint32_t* keys,
                   const uint32_t* ftable, const float* rho, const uint16_t* nlist,
                   const uint8_t* ncount, float4* acc, const StepConsts& c, int variant,
-                  cudaStream_t s);
+                  cudaStream_t s, const uint32_t* ghost_ids = nullptr);
+
+// kernels_slab.cu — the slab-decomposed (multi-GPU) step
+size_t slab_message_bytes(uint32_t record_capacity);
+int launch_slab_pack(const float4* pos, const float4* vel, const float4* vhf, uint32_t* ids,
+                     const uint32_t* n_owned_dev, uint32_t n_upper, float xlo, float xhi, float halo,
+                     int has_left, int has_right, void* msg_left, void* msg_right, uint32_t cap,
+                     uint32_t* counters, cudaStream_t s);
+int launch_slab_unpack(const void* msg, uint32_t count, uint32_t offset, float4* pos, float4* vel,
+                       float4* vhf, uint32_t* ids, cudaStream_t s);
+int launch_slab_compact(const float4* pos, const float4* vel, const float4* vhf, const uint32_t* ids,
+                        uint32_t n, float4* pos_out, float4* vel_out, float4* vhf_out, uint32_t* ids_out,
+                        uint32_t* src_of, uint32_t* n_owned_out, cudaStream_t s);
+int launch_slab_to_aos(sphb_particle* aos, uint32_t* ids_out, const uint32_t* n_owned_dev, uint32_t n_upper,
+                       const float4* pos, const float4* vel, const float4* vhf, const uint32_t* ids,
+                       const uint32_t* src_of, const float4* acc, const float* rho, const float* prs,
+                       const uint32_t* ckey, cudaStream_t s);
+int launch_slab_ckey(const float4* pos, uint32_t n, const float gmin[3], float cell, uint32_t* ckey,
+                     cudaStream_t s);
+int launch_slab_reduce_floats(const Reduce* red, float* out, cudaStream_t s);
+int launch_slab_bbox(const float4* pos, const uint32_t* n_owned_dev, uint32_t n_upper, Reduce* red,
+                     cudaStream_t s);
 
 }  // namespace sphb

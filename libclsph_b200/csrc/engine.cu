@@ -7,186 +7,15 @@
 // reference's four blocking reads and five buffer allocations per step.
 //
 // There is no CPU path in this file: every pass is a kernel from kernels_*.cu.
-#include <cmath>
-#include <cstdarg>
-#include <cstdio>
-#include <cstdlib>
-#include <cstring>
-#include <string>
-#include <vector>
 
-#include "common.cuh"
 
-using namespace sphb;
 
-struct sphb_engine {
-  int device = 0;
-  cudaStream_t stream = nullptr;
-  cudaStream_t side = nullptr;  // the reference-order bookkeeping runs beside the neighbour passes
-  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
-  uint32_t n = 0;
-  sphb_params params;   // the reference's `parameters`, mutated every step
-  sphb_terms terms;
-  float spiky_eps = 0.f;
+#include "engine_internal.cuh"
 
-  // sorted SoA state; pos/vel/vhf are ping-pong pairs, cur[] says which half is live
-  float4* pos[2] = {nullptr, nullptr};
-  float4* vel[2] = {nullptr, nullptr};
-  float4* vhf[2] = {nullptr, nullptr};
-  int cur = 0;
-  float4* acc = nullptr;
-  float* rho = nullptr;
-  float* prs = nullptr;
-  SortBuffers sortb = {};
-  int sorted = 0;            // which half of sortb holds the last step's sorted keys / perm
-  // The compute order is the engine's own (fine row-major cells); rank_cur[i] is the position
-  // of particle i in the REFERENCE's order, rank_prev[i] its position one step earlier
-  // (= the permutation the reference's sort applied), ckey[i] its Morton key (grid_index).
-  uint32_t* rank_cur = nullptr;
-  uint32_t* rank_prev = nullptr;
-  uint32_t* ckey = nullptr;
-  uint16_t* nlist = nullptr;  // neighbour codes recorded by the density pass, k-major
-  uint8_t* ncount = nullptr;
-  uint32_t* ftable = nullptr;     // fine cell table, nfine + 1 entries
-  size_t ftable_cap = 0;
-  uint32_t* ref_table = nullptr;  // the reference's cell table, grid_cell_count (+1) entries
-  size_t ref_table_cap = 0;
-  uint32_t* scan_scratch = nullptr;
-  size_t scan_scratch_cap = 0;
-  sphb_particle* aos_stage = nullptr;  // device staging for upload / download
-
-  // scene
-  Face* faces = nullptr;
-  uint32_t* face_offsets = nullptr;
-  float* df = nullptr;
-  uint32_t face_count = 0, total_grid_points = 0;
-  bool have_scene = false;
-
-  // reductions
-  Reduce* red = nullptr;       // device
-  Reduce* red_host = nullptr;  // pinned
-  bool bbox_valid = false;     // red_host holds the bbox of the live positions
-  bool have_state = false;
-  int last_attempts = 0;
-  bool stepped = false;
-
-  // options / measurement
-  int neighbor_variant = 0;
-  bool profile = false;
-  cudaEvent_t ev[SPHB_PASS_COUNT + 1][2];
-  cudaEvent_t user_ev[4];
-  bool ev_created = false;
-  float pass_ms[SPHB_PASS_COUNT] = {};
-  uint32_t pass_launches[SPHB_PASS_COUNT] = {};
-  uint32_t prof_steps = 0;
-  uint64_t launches = 0;
-
-  std::string err;
-};
-
-namespace {
-
-thread_local std::string g_create_error;
-
-int fail(sphb_engine* e, int code, const char* file, int line, const char* fmt, ...) {
-  char buf[512];
-  va_list ap;
-  va_start(ap, fmt);
-  vsnprintf(buf, sizeof buf, fmt, ap);
-  va_end(ap);
-  char full[640];
-  snprintf(full, sizeof full, "sphb error %d (%s:%d): %s", code, file, line, buf);
-  if (e) e->err = full; else g_create_error = full;
-  return code;
+std::string& sphb_create_error_slot() {
+  static thread_local std::string slot;
+  return slot;
 }
-
-#define CUDA_TRY(e, call)                                                                   \
-  do {                                                                                      \
-    cudaError_t err__ = (call);                                                             \
-    if (err__ != cudaSuccess)                                                               \
-      return fail((e), (int)err__, __FILE__, __LINE__, "%s -> %s", #call,                   \
-                  cudaGetErrorString(err__));                                               \
-  } while (0)
-
-#define SPHB_FAIL(e, code, ...) return fail((e), (code), __FILE__, __LINE__, __VA_ARGS__)
-
-template <typename T>
-cudaError_t dev_alloc(T** p, size_t count) {
-  return cudaMalloc(reinterpret_cast<void**>(p), sizeof(T) * (count ? count : 1));
-}
-
-// libclsph/sph_simulation.cpp:668-727 — host fp32 arithmetic, same expressions.
-int grid_from_bbox(sphb_engine* e, const float mn[3], const float mx[3]) {
-  sphb_params& P = e->params;
-  const float side = (P.h * 2);
-  int32_t* gs[3] = {&P.grid_size_x, &P.grid_size_y, &P.grid_size_z};
-  for (int a = 0; a < 3; ++a) {
-    P.min_point.s[a] = mn[a] - 2 * side;
-    P.max_point.s[a] = mx[a] + 2 * side;
-    *gs[a] = (int32_t)static_cast<uint32_t>((P.max_point.s[a] - P.min_point.s[a]) / (side));
-  }
-  if (!(P.grid_size_x < 1024) || !(P.grid_size_y < 1024) || !(P.grid_size_z < 1024) ||
-      P.grid_size_x < 0 || P.grid_size_y < 0 || P.grid_size_z < 0)
-    SPHB_FAIL(e, SPHB_ERR_GRID, "grid %d x %d x %d: a dimension reached 1024 (the reference asserts, "
-              "sph_simulation.cpp:722-724)", P.grid_size_x, P.grid_size_y, P.grid_size_z);
-  P.grid_cell_count = morton3((uint32_t)P.grid_size_x, (uint32_t)P.grid_size_y, (uint32_t)P.grid_size_z);
-  return 0;
-}
-
-// libclsph/sph_simulation.cpp:598-602 — host fp32 arithmetic; comparisons against the
-// double literal 0.00001 as written.
-float dt_from_maxima(const sphb_params& P, float max_v2, float max_a2) {
-  float maxVel2 = max_v2;
-  float maxVel = std::sqrt(max_v2);
-  float maxAccel = std::sqrt(max_a2);
-  float dt = (std::sqrt(2 * maxAccel * P.h + maxVel2) - maxVel) / (2 * maxAccel);
-  if (dt < 0.00001) dt = 0.00001;
-  if (dt > 1.0f / (P.target_fps) * P.simulation_scale) dt = 1.0f / (P.target_fps) * P.simulation_scale;
-  return dt;
-}
-
-StepConsts make_consts(const sphb_engine* e) {
-  const sphb_params& P = e->params;
-  StepConsts c;
-  c.n = e->n;
-  c.grid_cell_count = P.grid_cell_count;
-  c.h = P.h;
-  c.h2 = P.h * P.h;
-  c.cell = (P.h * 2);
-  c.minx = P.min_point.s[0]; c.miny = P.min_point.s[1]; c.minz = P.min_point.s[2];
-  c.mass = P.particle_mass; c.K = P.K; c.rho0 = P.fluid_density; c.mu = P.dynamic_viscosity;
-  c.st_threshold = P.surface_tension_threshold; c.st = P.surface_tension;
-  c.gx = P.constant_acceleration.s[0]; c.gy = P.constant_acceleration.s[1];
-  c.gz = P.constant_acceleration.s[2];
-  c.c_poly6 = e->terms.poly_6; c.c_poly6_grad = e->terms.poly_6_gradient;
-  c.c_poly6_lap = e->terms.poly_6_laplacian; c.c_spiky = e->terms.spiky;
-  c.c_visc = e->terms.viscosity;
-  c.spiky_eps = e->spiky_eps;
-  c.fnx = 2u * (uint32_t)P.grid_size_x;
-  c.fny = 2u * (uint32_t)P.grid_size_y;
-  c.fnz = 2u * (uint32_t)P.grid_size_z;
-  c.nfine = c.fnx * c.fny * c.fnz;
-  return c;
-}
-
-struct PassTimer {
-  sphb_engine* e;
-  int pass;
-  cudaStream_t st;
-  PassTimer(sphb_engine* e_, int pass_, cudaStream_t st_ = nullptr)
-      : e(e_), pass(pass_), st(st_ ? st_ : e_->stream) {
-    if (e->profile) cudaEventRecord(e->ev[pass][0], st);
-  }
-  void done(int launches) {
-    e->launches += launches;
-    if (e->profile) {
-      cudaEventRecord(e->ev[pass][1], st);
-      e->pass_launches[pass] += launches;
-    }
-  }
-};
-
-}  // namespace
 
 extern "C" {
 
@@ -217,6 +46,8 @@ int sphb_destroy(sphb_engine* e) {
   cudaFree(e->sortb.hist); cudaFree(e->sortb.block_sums);
   cudaFree(e->rank_cur); cudaFree(e->rank_prev); cudaFree(e->ckey);
   cudaFree(e->nlist); cudaFree(e->ncount);
+  cudaFree(e->n_owned_dev); cudaFree(e->counters); cudaFree(e->src_of);
+  if (e->host_counts) cudaFreeHost(e->host_counts);
   cudaFree(e->ftable); cudaFree(e->ref_table); cudaFree(e->scan_scratch); cudaFree(e->aos_stage);
   cudaFree(e->faces); cudaFree(e->face_offsets); cudaFree(e->df);
   cudaFree(e->red);
@@ -236,6 +67,11 @@ int sphb_destroy(sphb_engine* e) {
 }
 
 int sphb_create(const sphb_params* params, const sphb_terms* terms, int device, sphb_engine** out) {
+  return sphb_create_with_capacity(params, terms, device, params ? params->particles_count : 0, out);
+}
+
+int sphb_create_with_capacity(const sphb_params* params, const sphb_terms* terms, int device,
+                              uint32_t capacity, sphb_engine** out) {
   g_create_error.clear();
   if (!params || !terms || !out) SPHB_FAIL(nullptr, SPHB_ERR_INVALID, "null argument");
   *out = nullptr;
@@ -255,12 +91,13 @@ int sphb_create(const sphb_params* params, const sphb_terms* terms, int device, 
   e->params = *params;
   e->terms = *terms;
   e->n = params->particles_count;
+  e->cap = capacity ? capacity : e->n;
   {  // smoothing.cl:24: -45.f / convert_float(M_PI * pown(h, 6))
     float h6 = params->h;
     for (int k = 1; k < 6; ++k) h6 = h6 * params->h;
     e->spiky_eps = -45.f / (float)(M_PI * h6);
   }
-  const uint32_t n = e->n;
+  const uint32_t n = e->cap;
 #define TRY_OR_DESTROY(call)                                                           \
   do {                                                                                 \
     cudaError_t err__ = (call);                                                        \
@@ -401,55 +238,6 @@ int sphb_upload(sphb_engine* e, const sphb_particle* aos, uint32_t n) {
   return 0;
 }
 
-namespace {
-
-// Reads the device reduction cell back (32 bytes) and waits for it: the one host
-// synchronisation of a step.
-int fetch_reduce(sphb_engine* e) {
-  CUDA_TRY(e, cudaMemcpyAsync(e->red_host, e->red, sizeof(Reduce), cudaMemcpyDeviceToHost, e->stream));
-  CUDA_TRY(e, cudaStreamSynchronize(e->stream));
-  return 0;
-}
-
-void accumulate_pass(sphb_engine* e, int pass) {
-  float ms = 0.f;
-  if (cudaEventElapsedTime(&ms, e->ev[pass][0], e->ev[pass][1]) == cudaSuccess) e->pass_ms[pass] += ms;
-}
-
-int ensure_tables(sphb_engine* e, size_t fine_entries, size_t ref_entries) {
-  // grow rarely: capacities are kept with 1.5x headroom
-  const bool grow_f = fine_entries > e->ftable_cap, grow_r = ref_entries > e->ref_table_cap;
-  if (!grow_f && !grow_r) return 0;
-  CUDA_TRY(e, cudaStreamSynchronize(e->stream));
-  if (grow_f) {
-    cudaFree(e->ftable);
-    e->ftable = nullptr;
-    e->ftable_cap = fine_entries + fine_entries / 2 + 1024;
-    CUDA_TRY(e, dev_alloc(&e->ftable, e->ftable_cap));
-  }
-  if (grow_r) {
-    cudaFree(e->ref_table);
-    e->ref_table = nullptr;
-    e->ref_table_cap = ref_entries + ref_entries / 2 + 1024;
-    CUDA_TRY(e, dev_alloc(&e->ref_table, e->ref_table_cap));
-  }
-  const size_t need = scan_scratch_entries(e->ftable_cap > e->ref_table_cap ? e->ftable_cap : e->ref_table_cap);
-  if (need > e->scan_scratch_cap) {
-    cudaFree(e->scan_scratch);
-    e->scan_scratch = nullptr;
-    e->scan_scratch_cap = need;
-    CUDA_TRY(e, dev_alloc(&e->scan_scratch, need));
-  }
-  return 0;
-}
-
-int key_bits_for(uint32_t grid_cell_count) {
-  int bits = 0;
-  while (bits < 32 && (grid_cell_count >> bits) != 0) ++bits;
-  return bits < 1 ? 1 : bits;
-}
-
-}  // namespace
 
 int sphb_step(sphb_engine* e, float dt_in, float* dt_out) {
   if (!e) return SPHB_ERR_INVALID;

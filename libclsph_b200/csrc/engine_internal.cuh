@@ -1,0 +1,252 @@
+// Internal definitions shared by the engine's host translation units (engine.cu, slab.cu):
+// the engine object and its small host helpers.  Not part of the public boundary.
+#pragma once
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "common.cuh"
+
+using namespace sphb;
+
+struct sphb_engine {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  cudaStream_t side = nullptr;  // the reference-order bookkeeping runs beside the neighbour passes
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  uint32_t n = 0;    // particles the kernels run over (slab mode: owned + ghosts of this step)
+  uint32_t cap = 0;  // allocated particle slots (== n outside slab mode)
+  // slab mode (multi-GPU, slab.cu): this engine owns the particles with x in [xlo, xhi)
+  bool slab = false;
+  float xlo = 0.f, xhi = 0.f;
+  int has_left = 0, has_right = 0;
+  uint32_t exch_cap = 0;           // records per halo / migration message
+  uint32_t n_owned = 0;            // host copy (valid after unpack / upload)
+  uint32_t n_upper = 0;            // host upper bound of *n_owned_dev between syncs
+  uint32_t* n_owned_dev = nullptr; // device count of owned particles (written by compaction)
+  uint32_t* counters = nullptr;    // 4 pack counters (device)
+  uint32_t* src_of = nullptr;      // compaction map of the last commit
+  uint32_t* host_counts = nullptr; // pinned, 16 words
+  bool committed = false;          // src_of / acc / rho / prs describe the live owned particles
+  int slab_in = 0;                 // ping-pong half holding the pre-advect state of this step
+  sphb_params params;   // the reference's `parameters`, mutated every step
+  sphb_terms terms;
+  float spiky_eps = 0.f;
+
+  // sorted SoA state; pos/vel/vhf are ping-pong pairs, cur[] says which half is live
+  float4* pos[2] = {nullptr, nullptr};
+  float4* vel[2] = {nullptr, nullptr};
+  float4* vhf[2] = {nullptr, nullptr};
+  int cur = 0;
+  float4* acc = nullptr;
+  float* rho = nullptr;
+  float* prs = nullptr;
+  SortBuffers sortb = {};
+  int sorted = 0;            // which half of sortb holds the last step's sorted keys / perm
+  // The compute order is the engine's own (fine row-major cells); rank_cur[i] is the position
+  // of particle i in the REFERENCE's order, rank_prev[i] its position one step earlier
+  // (= the permutation the reference's sort applied), ckey[i] its Morton key (grid_index).
+  uint32_t* rank_cur = nullptr;
+  uint32_t* rank_prev = nullptr;
+  uint32_t* ckey = nullptr;
+  uint16_t* nlist = nullptr;  // neighbour codes recorded by the density pass, k-major
+  uint8_t* ncount = nullptr;
+  uint32_t* ftable = nullptr;     // fine cell table, nfine + 1 entries
+  size_t ftable_cap = 0;
+  uint32_t* ref_table = nullptr;  // the reference's cell table, grid_cell_count (+1) entries
+  size_t ref_table_cap = 0;
+  uint32_t* scan_scratch = nullptr;
+  size_t scan_scratch_cap = 0;
+  sphb_particle* aos_stage = nullptr;  // device staging for upload / download
+
+  // scene
+  Face* faces = nullptr;
+  uint32_t* face_offsets = nullptr;
+  float* df = nullptr;
+  uint32_t face_count = 0, total_grid_points = 0;
+  bool have_scene = false;
+
+  // reductions
+  Reduce* red = nullptr;       // device
+  Reduce* red_host = nullptr;  // pinned
+  bool bbox_valid = false;     // red_host holds the bbox of the live positions
+  bool have_state = false;
+  int last_attempts = 0;
+  bool stepped = false;
+
+  // options / measurement
+  int neighbor_variant = 0;
+  bool profile = false;
+  cudaEvent_t ev[SPHB_PASS_COUNT + 1][2];
+  cudaEvent_t user_ev[4];
+  bool ev_created = false;
+  float pass_ms[SPHB_PASS_COUNT] = {};
+  uint32_t pass_launches[SPHB_PASS_COUNT] = {};
+  uint32_t prof_steps = 0;
+  uint64_t launches = 0;
+
+  std::string err;
+};
+
+std::string& sphb_create_error_slot();
+extern "C" int sphb_create_with_capacity(const sphb_params* params, const sphb_terms* terms, int device,
+                                         uint32_t capacity, sphb_engine** out);
+
+namespace {
+
+// text of the last failure that happened without an engine (one slot per thread, engine.cu)
+#define g_create_error (::sphb_create_error_slot())
+
+int fail(sphb_engine* e, int code, const char* file, int line, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  char full[640];
+  snprintf(full, sizeof full, "sphb error %d (%s:%d): %s", code, file, line, buf);
+  if (e) e->err = full; else g_create_error = full;
+  return code;
+}
+
+#define CUDA_TRY(e, call)                                                                   \
+  do {                                                                                      \
+    cudaError_t err__ = (call);                                                             \
+    if (err__ != cudaSuccess)                                                               \
+      return fail((e), (int)err__, __FILE__, __LINE__, "%s -> %s", #call,                   \
+                  cudaGetErrorString(err__));                                               \
+  } while (0)
+
+#define SPHB_FAIL(e, code, ...) return fail((e), (code), __FILE__, __LINE__, __VA_ARGS__)
+
+template <typename T>
+cudaError_t dev_alloc(T** p, size_t count) {
+  return cudaMalloc(reinterpret_cast<void**>(p), sizeof(T) * (count ? count : 1));
+}
+
+// libclsph/sph_simulation.cpp:668-727 — host fp32 arithmetic, same expressions.
+int grid_from_bbox(sphb_engine* e, const float mn[3], const float mx[3]) {
+  sphb_params& P = e->params;
+  const float side = (P.h * 2);
+  int32_t* gs[3] = {&P.grid_size_x, &P.grid_size_y, &P.grid_size_z};
+  for (int a = 0; a < 3; ++a) {
+    P.min_point.s[a] = mn[a] - 2 * side;
+    P.max_point.s[a] = mx[a] + 2 * side;
+    *gs[a] = (int32_t)static_cast<uint32_t>((P.max_point.s[a] - P.min_point.s[a]) / (side));
+  }
+  if (!(P.grid_size_x < 1024) || !(P.grid_size_y < 1024) || !(P.grid_size_z < 1024) ||
+      P.grid_size_x < 0 || P.grid_size_y < 0 || P.grid_size_z < 0)
+    SPHB_FAIL(e, SPHB_ERR_GRID, "grid %d x %d x %d: a dimension reached 1024 (the reference asserts, "
+              "sph_simulation.cpp:722-724)", P.grid_size_x, P.grid_size_y, P.grid_size_z);
+  P.grid_cell_count = morton3((uint32_t)P.grid_size_x, (uint32_t)P.grid_size_y, (uint32_t)P.grid_size_z);
+  return 0;
+}
+
+// libclsph/sph_simulation.cpp:598-602 — host fp32 arithmetic; comparisons against the
+// double literal 0.00001 as written.
+float dt_from_maxima(const sphb_params& P, float max_v2, float max_a2) {
+  float maxVel2 = max_v2;
+  float maxVel = std::sqrt(max_v2);
+  float maxAccel = std::sqrt(max_a2);
+  float dt = (std::sqrt(2 * maxAccel * P.h + maxVel2) - maxVel) / (2 * maxAccel);
+  if (dt < 0.00001) dt = 0.00001;
+  if (dt > 1.0f / (P.target_fps) * P.simulation_scale) dt = 1.0f / (P.target_fps) * P.simulation_scale;
+  return dt;
+}
+
+StepConsts make_consts(const sphb_engine* e) {
+  const sphb_params& P = e->params;
+  StepConsts c;
+  c.n = e->n;
+  c.grid_cell_count = P.grid_cell_count;
+  c.h = P.h;
+  c.h2 = P.h * P.h;
+  c.cell = (P.h * 2);
+  c.minx = P.min_point.s[0]; c.miny = P.min_point.s[1]; c.minz = P.min_point.s[2];
+  c.mass = P.particle_mass; c.K = P.K; c.rho0 = P.fluid_density; c.mu = P.dynamic_viscosity;
+  c.st_threshold = P.surface_tension_threshold; c.st = P.surface_tension;
+  c.gx = P.constant_acceleration.s[0]; c.gy = P.constant_acceleration.s[1];
+  c.gz = P.constant_acceleration.s[2];
+  c.c_poly6 = e->terms.poly_6; c.c_poly6_grad = e->terms.poly_6_gradient;
+  c.c_poly6_lap = e->terms.poly_6_laplacian; c.c_spiky = e->terms.spiky;
+  c.c_visc = e->terms.viscosity;
+  c.spiky_eps = e->spiky_eps;
+  c.fnx = 2u * (uint32_t)P.grid_size_x;
+  c.fny = 2u * (uint32_t)P.grid_size_y;
+  c.fnz = 2u * (uint32_t)P.grid_size_z;
+  c.nfine = c.fnx * c.fny * c.fnz;
+  return c;
+}
+
+struct PassTimer {
+  sphb_engine* e;
+  int pass;
+  cudaStream_t st;
+  PassTimer(sphb_engine* e_, int pass_, cudaStream_t st_ = nullptr)
+      : e(e_), pass(pass_), st(st_ ? st_ : e_->stream) {
+    if (e->profile) cudaEventRecord(e->ev[pass][0], st);
+  }
+  void done(int launches) {
+    e->launches += launches;
+    if (e->profile) {
+      cudaEventRecord(e->ev[pass][1], st);
+      e->pass_launches[pass] += launches;
+    }
+  }
+};
+
+}  // namespace
+
+namespace {
+
+// Reads the device reduction cell back (32 bytes) and waits for it: the one host
+// synchronisation of a step.
+int fetch_reduce(sphb_engine* e) {
+  CUDA_TRY(e, cudaMemcpyAsync(e->red_host, e->red, sizeof(Reduce), cudaMemcpyDeviceToHost, e->stream));
+  CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+  return 0;
+}
+
+void accumulate_pass(sphb_engine* e, int pass) {
+  float ms = 0.f;
+  if (cudaEventElapsedTime(&ms, e->ev[pass][0], e->ev[pass][1]) == cudaSuccess) e->pass_ms[pass] += ms;
+}
+
+int ensure_tables(sphb_engine* e, size_t fine_entries, size_t ref_entries) {
+  // grow rarely: capacities are kept with 1.5x headroom
+  const bool grow_f = fine_entries > e->ftable_cap, grow_r = ref_entries > e->ref_table_cap;
+  if (!grow_f && !grow_r) return 0;
+  CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+  if (grow_f) {
+    cudaFree(e->ftable);
+    e->ftable = nullptr;
+    e->ftable_cap = fine_entries + fine_entries / 2 + 1024;
+    CUDA_TRY(e, dev_alloc(&e->ftable, e->ftable_cap));
+  }
+  if (grow_r) {
+    cudaFree(e->ref_table);
+    e->ref_table = nullptr;
+    e->ref_table_cap = ref_entries + ref_entries / 2 + 1024;
+    CUDA_TRY(e, dev_alloc(&e->ref_table, e->ref_table_cap));
+  }
+  const size_t need = scan_scratch_entries(e->ftable_cap > e->ref_table_cap ? e->ftable_cap : e->ref_table_cap);
+  if (need > e->scan_scratch_cap) {
+    cudaFree(e->scan_scratch);
+    e->scan_scratch = nullptr;
+    e->scan_scratch_cap = need;
+    CUDA_TRY(e, dev_alloc(&e->scan_scratch, need));
+  }
+  return 0;
+}
+
+int key_bits_for(uint32_t grid_cell_count) {
+  int bits = 0;
+  while (bits < 32 && (grid_cell_count >> bits) != 0) ++bits;
+  return bits < 1 ? 1 : bits;
+}
+
+}  // namespace

@@ -225,12 +225,19 @@ __global__ void __launch_bounds__(kBlock)
              const float4* __restrict__ acc, float4* __restrict__ pos_out,
              float4* __restrict__ vel_out, float4* __restrict__ vhf_out, uint32_t n, float dt,
              float restitution, const Face* __restrict__ faces, uint32_t face_count,
-             const float* __restrict__ df, Reduce* red) {
+             const float* __restrict__ df, Reduce* red, const uint32_t* __restrict__ ghost_ids) {
   // grid-stride over a grid sized to the machine: one set of 8 atomics per CTA, not per 256
   // particles (65 536 CTAs hammering the same 8 words serialise in L2)
   float rv[8] = {INFINITY, INFINITY, INFINITY, -INFINITY, -INFINITY, -INFINITY, -INFINITY, -INFINITY};
   for (uint32_t i = blockIdx.x * kBlock + threadIdx.x; i < n; i += gridDim.x * kBlock) {
     const float4 x0 = __ldg(pos + i), vh = __ldg(vhf + i), a = __ldg(acc + i);
+    if (ghost_ids && (__ldg(ghost_ids + i) & 0x80000000u)) {
+      // slab mode: a ghost belongs to another rank, which advects it; here it is carried
+      // through unchanged and kept out of the reductions
+      pos_out[i] = x0;
+      vhf_out[i] = vh;
+      continue;
+    }
     // leapfrog
     const float nx = vh.x + a.x * dt, ny = vh.y + a.y * dt, nz = vh.z + a.z * dt;
     const float px = x0.x + nx * dt, py = x0.y + ny * dt, pz = x0.z + nz * dt;
@@ -466,11 +473,11 @@ int launch_reference_debug(const uint32_t* rank, const uint32_t* rank_prev, cons
 int launch_advect(const float4* pos, const float4* vhf, const float4* acc, float4* pos_out,
                   float4* vel_out, float4* vhf_out, uint32_t n, float dt, float restitution,
                   const Face* faces, uint32_t face_count, const float* df, Reduce* red,
-                  cudaStream_t s) {
+                  cudaStream_t s, const uint32_t* ghost_ids) {
   unsigned grid = blocks_for(n);
   if (grid > 148 * 8) grid = 148 * 8;  // 8 resident CTAs of 256 threads on each of 148 SMs
   k_advect<<<grid, kBlock, 0, s>>>(pos, vhf, acc, pos_out, vel_out, vhf_out, n, dt,
-                                            restitution, faces, face_count, df, red);
+                                            restitution, faces, face_count, df, red, ghost_ids);
   return 1;
 }
 

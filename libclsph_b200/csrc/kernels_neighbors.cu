@@ -264,10 +264,15 @@ __global__ void __launch_bounds__(kBlock)
     k_forces_nlist(const float4* __restrict__ pos, const float4* __restrict__ vel,
                    const uint32_t* __restrict__ keys, const uint32_t* __restrict__ ftable,
                    const float* __restrict__ rho, const uint16_t* __restrict__ nlist,
-                   const uint8_t* __restrict__ ncount, float4* __restrict__ acc, StepConsts c) {
+                   const uint8_t* __restrict__ ncount, float4* __restrict__ acc, StepConsts c,
+                   const uint32_t* __restrict__ ghost_ids) {
   __shared__ uint32_t row_start[9][kBlock];
   const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
   if (i >= c.n) return;
+  if (ghost_ids && (__ldg(ghost_ids + i) & 0x80000000u)) {  // slab mode: another rank's particle
+    acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    return;
+  }
   const float4 pi = __ldg(pos + i), vi = __ldg(vel + i);
   uint32_t fx, fy, fz;
   fine_coords_of(__ldg(keys + i), c, fx, fy, fz);
@@ -329,11 +334,11 @@ int launch_density(float4* pos, float4* vel, const uint32_t* keys, const uint32_
 int launch_forces(const float4* pos, const float4* vel, const uint32_t* keys,
                   const uint32_t* ftable, const float* rho, const uint16_t* nlist,
                   const uint8_t* ncount, float4* acc, const StepConsts& c, int variant,
-                  cudaStream_t s) {
-  if (variant == 1)
+                  cudaStream_t s, const uint32_t* ghost_ids) {
+  if (variant == 1 && !ghost_ids)
     k_forces_list<<<blocks_for(c.n), kBlock, 0, s>>>(pos, vel, keys, ftable, rho, acc, c);
   else
-    k_forces_nlist<<<blocks_for(c.n), kBlock, 0, s>>>(pos, vel, keys, ftable, rho, nlist, ncount, acc, c);
+    k_forces_nlist<<<blocks_for(c.n), kBlock, 0, s>>>(pos, vel, keys, ftable, rho, nlist, ncount, acc, c, ghost_ids);
   return 1;
 }
 

@@ -77,6 +77,9 @@ SYMBOLS = [
     "sphb_profile_enable", "sphb_profile_reset", "sphb_get_pass_times", "sphb_launch_count",
     "sphb_stream", "sphb_set_option", "sphb_last_error", "sphb_error_string",
     "sphb_host_alloc", "sphb_host_free", "sphb_debug_advect", "sphb_event_record", "sphb_event_elapsed_ms",
+    "sphb_slab_create", "sphb_slab_message_bytes", "sphb_slab_configure", "sphb_slab_upload", "sphb_slab_bbox",
+    "sphb_slab_pack", "sphb_slab_unpack", "sphb_slab_forces", "sphb_slab_advect", "sphb_slab_commit",
+    "sphb_slab_download", "sphb_compute_dt",
 ]
 
 
@@ -125,6 +128,20 @@ def lib():
         L.sphb_last_error.restype = C.c_char_p
         L.sphb_error_string.argtypes = [i32]
         L.sphb_error_string.restype = C.c_char_p
+        L.sphb_slab_create.argtypes = [vp, vp, i32, u32, u32, C.POINTER(vp)]
+        L.sphb_slab_message_bytes.argtypes = [vp]
+        L.sphb_slab_message_bytes.restype = C.c_size_t
+        L.sphb_slab_configure.argtypes = [vp, f32, f32, i32, i32]
+        L.sphb_slab_upload.argtypes = [vp, vp, vp, u32]
+        L.sphb_slab_bbox.argtypes = [vp, vp]
+        L.sphb_slab_pack.argtypes = [vp, vp, vp]
+        L.sphb_slab_unpack.argtypes = [vp, vp, vp, C.POINTER(u32), C.POINTER(u32)]
+        L.sphb_slab_forces.argtypes = [vp, vp, vp]
+        L.sphb_slab_advect.argtypes = [vp, f32, vp]
+        L.sphb_slab_commit.argtypes = [vp]
+        L.sphb_slab_download.argtypes = [vp, vp, vp, u32, C.POINTER(u32)]
+        L.sphb_compute_dt.argtypes = [vp, f32, f32]
+        L.sphb_compute_dt.restype = f32
         L.sphb_debug_advect.argtypes = [vp, f32]
         L.sphb_event_record.argtypes = [vp, i32]
         L.sphb_event_elapsed_ms.argtypes = [vp, i32, i32, C.POINTER(f32)]
@@ -141,12 +158,19 @@ def _ptr(a):
 class Engine:
     """One sphb_engine.  Arrays are numpy structured arrays of the dtypes above."""
 
-    def __init__(self, params, terms, device=-1):
+    def __init__(self, params, terms, device=-1, slab_capacity=None, exchange_capacity=0):
+        """slab_capacity=None: a whole-domain engine (sphb_create); else a slab engine
+        (sphb_slab_create) with that many local particle slots."""
         self.L = lib()
         self.h = C.c_void_p()
         params = np.ascontiguousarray(params, PARAMS)
         terms = np.ascontiguousarray(terms, TERMS)
-        rc = self.L.sphb_create(_ptr(params), _ptr(terms), device, C.byref(self.h))
+        if slab_capacity is None:
+            rc = self.L.sphb_create(_ptr(params), _ptr(terms), device, C.byref(self.h))
+        else:
+            rc = self.L.sphb_slab_create(_ptr(params), _ptr(terms), device, int(slab_capacity),
+                                         int(exchange_capacity), C.byref(self.h))
+        self.params0 = params.copy()
         if rc != 0:
             self.h = None
             raise SphbError(rc, self.L.sphb_error_string(rc).decode())

@@ -1,0 +1,281 @@
+"""Slab-decomposed stepping: one process per GPU, `torch.distributed` for the plumbing.
+
+The reference is single-device (libclsph/sph_simulation.cpp:273-275); this is the layer that
+spreads its step over the GPUs of one box.  Rank r owns the particles with x in
+[cuts[r], cuts[r+1]).  Per step (include/sphb.h, "slab engines"):
+
+    pack -> send/recv one fixed-size message with each slab neighbour (NCCL over NVLink)
+         -> unpack -> forces -> { advect(dt) -> all-reduce MAX of 8 floats -> dt' } -> commit
+
+`SlabDriver` holds only the protocol; the per-rank work is behind a small local-engine
+interface, implemented by `CudaSlab` (the sphb C ABI) here and by a numpy stand-in in
+tests/ (world_size-2 gloo tests of the protocol on CPU).
+"""
+import ctypes as C
+
+import numpy as np
+
+RECORD_BYTES = 48
+HEADER_BYTES = 16
+
+
+def message_bytes(exchange_capacity):
+    return HEADER_BYTES + RECORD_BYTES * int(exchange_capacity)
+
+
+def needs_retry(dt, computed):
+    """`dt - computed > 0.00001` as the reference evaluates it: a float subtraction compared
+    with a double literal (libclsph/sph_simulation.cpp:260)."""
+    return float(np.float32(dt) - np.float32(computed)) > 0.00001
+
+
+class CudaSlab:
+    """Local-engine interface over the sphb C ABI (one slab engine on one GPU)."""
+
+    def __init__(self, params, terms, scene, device, capacity, exchange_capacity):
+        import torch
+        from .engine import Engine
+        self.torch = torch
+        self.device = torch.device("cuda", device)
+        torch.cuda.set_device(self.device)
+        self.e = Engine(params, terms, device, slab_capacity=capacity, exchange_capacity=exchange_capacity)
+        self.e.set_scene(scene["bbs"], scene["transforms"], scene["rvertices"], scene["total_gridpoints"])
+        self.params = np.ascontiguousarray(params).copy()
+        self.exchange_capacity = int(exchange_capacity)
+        self.capacity = int(capacity)
+        self.stream = torch.cuda.ExternalStream(self.e.stream(), device=self.device)
+
+    # -- buffers the driver communicates with ------------------------------------------------
+    def new_message(self):
+        return self.torch.zeros(message_bytes(self.exchange_capacity), dtype=self.torch.uint8, device=self.device)
+
+    def new_red8(self):
+        return self.torch.zeros(8, dtype=self.torch.float32, device=self.device)
+
+    def red8_to_host(self, red8):
+        return red8.cpu().numpy()  # synchronises the current (= the engine's) stream
+
+    def stream_context(self):
+        return self.torch.cuda.stream(self.stream)
+
+    # -- the engine ---------------------------------------------------------------------------
+    def _chk(self, rc):
+        self.e._check(rc)
+
+    def configure(self, xlo, xhi, has_left, has_right):
+        self._chk(self.e.L.sphb_slab_configure(self.e.h, xlo, xhi, int(has_left), int(has_right)))
+
+    def upload(self, particles, ids):
+        from .engine import PARTICLE, _ptr
+        particles = np.ascontiguousarray(particles, PARTICLE)
+        ids = np.ascontiguousarray(ids, np.uint32)
+        assert len(particles) == len(ids)
+        self._chk(self.e.L.sphb_slab_upload(self.e.h, _ptr(particles), _ptr(ids), len(ids)))
+
+    def bbox(self, red8):
+        self._chk(self.e.L.sphb_slab_bbox(self.e.h, red8.data_ptr()))
+
+    def pack(self, send_left, send_right):
+        self._chk(self.e.L.sphb_slab_pack(self.e.h, send_left.data_ptr() if send_left is not None else None,
+                                          send_right.data_ptr() if send_right is not None else None))
+
+    def unpack(self, recv_left, recv_right):
+        no, ng = C.c_uint32(), C.c_uint32()
+        self._chk(self.e.L.sphb_slab_unpack(self.e.h, recv_left.data_ptr() if recv_left is not None else None,
+                                            recv_right.data_ptr() if recv_right is not None else None,
+                                            C.byref(no), C.byref(ng)))
+        return no.value, ng.value
+
+    def forces(self, gmin, gmax):
+        gmin = np.ascontiguousarray(gmin, np.float32)
+        gmax = np.ascontiguousarray(gmax, np.float32)
+        self._chk(self.e.L.sphb_slab_forces(self.e.h, gmin.ctypes.data, gmax.ctypes.data))
+
+    def advect(self, dt, red8):
+        self._chk(self.e.L.sphb_slab_advect(self.e.h, dt, red8.data_ptr()))
+
+    def commit(self):
+        self._chk(self.e.L.sphb_slab_commit(self.e.h))
+
+    def compute_dt(self, max_v2, max_a2):
+        return float(self.e.L.sphb_compute_dt(self.params.ctypes.data, float(max_v2), float(max_a2)))
+
+    def download(self):
+        """(owned particles in local order, their ids)"""
+        from .engine import PARTICLE, _ptr
+        n = C.c_uint32()
+        self._chk(self.e.L.sphb_slab_download(self.e.h, None, None, 0, C.byref(n)))
+        out = np.zeros(n.value, PARTICLE)
+        ids = np.zeros(n.value, np.uint32)
+        if n.value:
+            self._chk(self.e.L.sphb_slab_download(self.e.h, _ptr(out), _ptr(ids), n.value, C.byref(n)))
+        return out, ids
+
+    def close(self):
+        self.e.close()
+
+
+class SlabDriver:
+    """The per-step exchange protocol of one rank.  `local` implements the local-engine
+    interface (CudaSlab, or a CPU stand-in); `dist` is torch.distributed (any backend)."""
+
+    def __init__(self, local, cuts, rank, world, dist=None, group=None):
+        assert len(cuts) == world + 1
+        self.local, self.rank, self.world, self.dist, self.group = local, rank, world, dist, group
+        self.left = rank - 1 if rank > 0 else None
+        self.right = rank + 1 if rank + 1 < world else None
+        self.cuts = [float(np.float32(c)) for c in cuts]
+        local.configure(self.cuts[rank], self.cuts[rank + 1], self.left is not None, self.right is not None)
+        self.send_l = local.new_message() if self.left is not None else None
+        self.recv_l = local.new_message() if self.left is not None else None
+        self.send_r = local.new_message() if self.right is not None else None
+        self.recv_r = local.new_message() if self.right is not None else None
+        self.red8 = local.new_red8()
+        self.gmin = self.gmax = None
+        self.n_owned = self.n_ghost = 0
+        self.attempts = 0
+        self.bytes_sent = 0
+
+    # -- collectives ---------------------------------------------------------------------------
+    def _allreduce_max(self, t):
+        if self.world > 1:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX, group=self.group)
+
+    def _exchange(self):
+        if self.world == 1:
+            return
+        d = self.dist
+        ops = []
+        # a fixed order (left pair, then right pair) on every rank keeps the pairs matched
+        if self.left is not None:
+            ops.append(d.P2POp(d.isend, self.send_l, self.left, self.group))
+            ops.append(d.P2POp(d.irecv, self.recv_l, self.left, self.group))
+        if self.right is not None:
+            ops.append(d.P2POp(d.isend, self.send_r, self.right, self.group))
+            ops.append(d.P2POp(d.irecv, self.recv_r, self.right, self.group))
+        for req in d.batch_isend_irecv(ops):
+            req.wait()
+        self.bytes_sent += sum(int(t.numel()) for t in (self.send_l, self.send_r) if t is not None)
+
+    def _set_bbox(self, r):
+        self.gmin = np.array([-r[0], -r[1], -r[2]], np.float32)
+        self.gmax = np.array([r[3], r[4], r[5]], np.float32)
+
+    # -- life cycle ----------------------------------------------------------------------------
+    def start(self, particles, ids):
+        """Uploads this rank's particles and agrees on the initial global bbox."""
+        with self.local.stream_context():
+            self.local.upload(particles, ids)
+            self.local.bbox(self.red8)
+            self._allreduce_max(self.red8)
+            self._set_bbox(self.local.red8_to_host(self.red8))
+
+    def step(self, dt):
+        """One simulate_single_frame over all slabs; returns the computed dt (identical on
+        every rank)."""
+        loc = self.local
+        with loc.stream_context():
+            loc.pack(self.send_l, self.send_r)
+            self._exchange()
+            self.n_owned, self.n_ghost = loc.unpack(self.recv_l, self.recv_r)
+            loc.forces(self.gmin, self.gmax)
+            computed = dt
+            self.attempts = 0
+            while True:
+                dt = computed
+                loc.advect(dt, self.red8)
+                self._allreduce_max(self.red8)
+                r = loc.red8_to_host(self.red8)
+                computed = loc.compute_dt(r[6], r[7])
+                self.attempts += 1
+                if not needs_retry(dt, computed):
+                    break
+            loc.commit()
+            self._set_bbox(r)
+        return computed
+
+
+class LoopbackWorld:
+    """All ranks of a slab decomposition inside ONE process (one GPU, or the CPU stand-in):
+    the same per-rank calls as SlabDriver.step, run phase by phase over the ranks, with the
+    messages moved by a copy and the all-reduce done by hand.  For tests, and for running a
+    domain larger than one engine's capacity on a single device."""
+
+    def __init__(self, locals_, cuts):
+        self.world = len(locals_)
+        self.ranks = [SlabDriver(loc, cuts, r, self.world) for r, loc in enumerate(locals_)]
+        self.attempts = 0
+
+    def _allreduce(self):
+        hosts = [d.local.red8_to_host(d.red8) for d in self.ranks]
+        return np.maximum.reduce(hosts).astype(np.float32)
+
+    def start(self, parts):
+        """parts: per rank (particles, ids)"""
+        for d, (p, ids) in zip(self.ranks, parts):
+            with d.local.stream_context():
+                d.local.upload(p, ids)
+                d.local.bbox(d.red8)
+        r = self._allreduce()
+        for d in self.ranks:
+            d._set_bbox(r)
+
+    def step(self, dt):
+        R = self.ranks
+        for d in R:
+            with d.local.stream_context():
+                d.local.pack(d.send_l, d.send_r)
+        for k, d in enumerate(R):  # my right message is my right neighbour's left inbox
+            with d.local.stream_context():
+                if d.right is not None:
+                    _sync(d.local)
+                    R[k + 1].recv_l.copy_(d.send_r)
+                if d.left is not None:
+                    _sync(d.local)
+                    R[k - 1].recv_r.copy_(d.send_l)
+        for d in R:
+            _sync(d.local)
+        for d in R:
+            with d.local.stream_context():
+                d.n_owned, d.n_ghost = d.local.unpack(d.recv_l, d.recv_r)
+                d.local.forces(d.gmin, d.gmax)
+        computed = dt
+        self.attempts = 0
+        while True:
+            dt = computed
+            for d in R:
+                with d.local.stream_context():
+                    d.local.advect(dt, d.red8)
+            r = self._allreduce()
+            computed = R[0].local.compute_dt(r[6], r[7])
+            self.attempts += 1
+            if not needs_retry(dt, computed):
+                break
+        for d in R:
+            with d.local.stream_context():
+                d.local.commit()
+            d._set_bbox(r)
+            d.attempts = self.attempts
+        return computed
+
+
+def _sync(local):
+    t = getattr(local, "torch", None)
+    if t is not None:
+        t.cuda.synchronize()
+
+
+def equal_count_cuts(x, world):
+    """Slab faces for `world` ranks with (nearly) equal particle counts: faces lie midway
+    between neighbouring distinct x values; the outer faces are -inf / +inf."""
+    xs = np.sort(np.asarray(x, np.float32))
+    cuts = [-np.inf]
+    for r in range(1, world):
+        k = (len(xs) * r) // world
+        lo = xs[k - 1] if k > 0 else xs[0]
+        # first value strictly greater than xs[k-1], so that a lattice plane is never split
+        j = np.searchsorted(xs, lo, side="right")
+        hi = xs[j] if j < len(xs) else lo
+        cuts.append(float(np.float32((np.float64(lo) + np.float64(hi)) / 2)))
+    cuts.append(np.inf)
+    return cuts
