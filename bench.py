@@ -289,6 +289,8 @@ def main():
     ap.add_argument("--particles", type=int, default=16777216)
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--cpu-budget", type=float, default=20.0, help="seconds of CPU baseline work")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="N > 1: one --particles block per GPU (weak) or the N = 1 workload cut in N (strong)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-secondary", action="store_true", help="skip the 1 M dam-break leg")
     args = ap.parse_args()

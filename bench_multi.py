@@ -1,0 +1,158 @@
+"""bench.py's N > 1 arm: the slab-decomposed step, one process per GPU over NCCL.
+
+Weak scaling (default): every rank owns one reference lattice block of `--particles` particles
+(the N = 1 workload); the blocks stand side by side along x in one open-top box, so the whole
+job is an N-times longer water box of N * particles particles.  `--scaling strong` instead
+cuts the single N = 1 workload (BASELINE.json configs[3]: the 16.7 M box) into N slabs.
+Timing: barrier + synchronize on both sides, CUDA events on each engine's stream, MAX over
+ranks; `value` = all particles of all ranks * steps / that time.
+"""
+import json
+import os
+import tempfile
+import time
+
+import numpy as np
+
+
+def main_multi(args, rank, world, local, workload):
+    import torch
+    import torch.distributed as dist
+    import __main__ as B  # bench.py itself (it owns the real stdout)
+    if not hasattr(B, "emit"):
+        import bench as B
+    from libclsph_b200 import PARTICLE, build, host
+    from libclsph_b200.slab import CudaSlab, SlabDriver, equal_count_cuts
+
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    if rank == 0:
+        build.build_all()
+    dist.barrier()
+    strong = getattr(args, "scaling", "weak") == "strong"
+    n0 = int(args.particles)
+    n_total = n0 if strong else n0 * world
+    warmup = max(args.warmup, 3)
+
+    with tempfile.TemporaryDirectory() as tmp:
+        B.write_json(os.path.join(tmp, "fluid.json"), B.WATER)
+        B.write_json(os.path.join(tmp, "sim.json"), dict(B.SIM, particles_count=n0))
+        params, terms, vol, _, _ = host.load_settings(os.path.join(tmp, "fluid.json"), os.path.join(tmp, "sim.json"))
+        params["particles_count"] = n_total
+        params["total_mass"] = np.float32(n_total) * params["particle_mass"]
+        side = float(np.cbrt(np.float32(vol)))
+        per_side = int(np.ceil(np.cbrt(np.float32(n0))))
+        spacing = float(np.float32(side) / np.float32(per_side))
+        block = host.lattice(n0, vol)  # the reference lattice of one block
+        if strong:
+            x = block["position"][:, 0]
+            cuts = equal_count_cuts(x, world)
+            mine = (x >= np.float32(cuts[rank])) & (x < np.float32(cuts[rank + 1]))
+            mine_p = block[mine]
+            ids = np.nonzero(mine)[0].astype(np.uint32)
+            dims = B.water_box_dims(n0)
+        else:
+            pitch = np.float32(per_side * spacing)
+            block["position"][:, 0] += np.float32(rank) * pitch
+            mine_p = block
+            ids = (np.arange(n0, dtype=np.uint64) + np.uint64(rank) * np.uint64(n0)).astype(np.uint32)
+            x0 = -np.float32(side) / np.float32(2)
+            cuts = [-np.inf] + [float(x0 + np.float32(r) * pitch - np.float32(spacing) / 2) for r in range(1, world)] + [np.inf]
+            d = B.water_box_dims(n0)
+            dims = (d[0], float(d[1] + np.float32(world - 1) * pitch), d[2], d[3], d[4], d[5])
+        obj = os.path.join(tmp, f"box_rank{rank}.obj")
+        B.write_box_obj(obj, *dims)
+        sc = host.load_scene(obj, float(params["h"][0]) * 2)
+    n_mine = len(mine_p)
+    # ghost layer: 2 layers of thickness 2h across the slab's cross-section, with head-room
+    planes = 2 * float(params["h"][0]) / spacing + 1  # lattice planes inside a 2h layer
+    exch = int(1.5 * per_side * per_side * planes) + 65536
+    cap = int(n_mine * 1.25) + 2 * exch
+    loc = CudaSlab(params, terms, sc, local, cap, exch)
+    drv = SlabDriver(loc, cuts, rank, world, dist)
+    drv.start(mine_p, ids)
+    del block, mine_p
+    e = loc.e
+    dt = 1.0 / 600.0
+    for _ in range(warmup):
+        dt = drv.step(dt)
+    e.profile(True)
+    l0 = e.launch_count()
+    sampler = B.ClockSampler(B.physical_device(local)) if rank == 0 else None
+    torch.cuda.synchronize()
+    dist.barrier()
+    torch.cuda.synchronize()
+    if sampler:
+        sampler.start()
+    bytes0 = drv.bytes_sent
+    t0 = time.perf_counter()
+    e.event_record(0)
+    for _ in range(args.steps):
+        dt = drv.step(dt)
+    e.event_record(1)
+    ms = e.event_elapsed_ms(0, 1)
+    torch.cuda.synchronize()
+    wall = time.perf_counter() - t0
+    dist.barrier()
+    clocks = sampler.finish() if sampler else None
+    launches = e.launch_count() - l0
+    pass_ms, pass_launches, _ = e.pass_times()
+    stats = torch.tensor([ms, wall * 1e3, float(launches), float(drv.n_owned), float(drv.n_ghost),
+                          float(drv.bytes_sent - bytes0)] + [pass_ms[k] for k in sorted(pass_ms)],
+                         dtype=torch.float64, device="cuda")
+    allstats = [torch.zeros_like(stats) for _ in range(world)]
+    dist.all_gather(allstats, stats)
+    owned_total = sum(int(s[3]) for s in allstats)
+    # end to end: every rank downloads its slab to the host and uploads it again, every step
+    e2e = None
+    if args.e2e_steps > 0:
+        t0 = time.perf_counter()
+        for _ in range(args.e2e_steps):
+            part, pid = loc.download()
+            drv.start(part, pid)
+            dt = drv.step(dt)
+        torch.cuda.synchronize()
+        e2e_s = time.perf_counter() - t0
+        t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e = dict(value=n_total * args.e2e_steps / float(t[0]), unit="particle-steps/s",
+                   h2d_bytes_per_step=84 * n_total, d2h_bytes_per_step=84 * n_total + 32 * world,
+                   steps=args.e2e_steps)
+    if rank == 0:
+        ms_max = max(float(s[0]) for s in allstats)
+        ms_step = ms_max / args.steps
+        peak, peak_src = B.measured_peak()
+        names = sorted(pass_ms)
+        per_rank = []
+        for r, s in enumerate(allstats):
+            per_rank.append(dict(rank=r, ms_per_step=float(s[0]) / args.steps, owned=int(s[3]), ghosts=int(s[4]),
+                                 halo_bytes_per_step=float(s[5]) / args.steps,
+                                 pass_ms_per_step={k: float(s[6 + i]) / args.steps for i, k in enumerate(names)}))
+        slow = max(per_rank, key=lambda d: d["ms_per_step"])
+        f_ms = slow["pass_ms_per_step"]["forces"]
+        n_loc = slow["owned"]
+        achieved = B.ALGO_BYTES["forces"] * n_loc / (f_ms * 1e-3) / 1e9 if f_ms > 0 else 0.0
+        line = dict(
+            metric="SPH particle-steps/sec", value=n_total * args.steps / (ms_max * 1e-3), unit="particle-steps/s",
+            n_gpus=world, steps=args.steps, warmup=warmup, ms_per_step=ms_step, higher_is_better=True,
+            scaling="strong" if strong else "weak", vs_baseline=None, dtype="f32", data="synthetic",
+            config=dict(workload=workload if strong else
+                        f"{world} x ({n0}-particle reference lattice block) side by side along x in one open-top "
+                        f"water box (water.json + default.json physics): BASELINE.json configs[3]'s block per GPU",
+                        particles=n_total, particles_per_gpu=n0 if not strong else n_total // world,
+                        box=[round(float(v), 4) for v in dims],
+                        parallelism=f"{world} x-slabs, 2h ghost layer + migration by NCCL send/recv, "
+                                    f"1 all-reduce(8 floats) per advection attempt",
+                        l2="inputs exceed L2", exchange_capacity_records=exch, owned_total=owned_total),
+            clocks=clocks, gpu_launches=int(sum(float(s[2]) for s in allstats)),
+            roofline=dict(bound="hbm", kernel="forces pass (k_forces_nlist), slowest rank", achieved=achieved,
+                          peak=peak, unit="GB/s", frac=achieved / peak, traffic=None, peak_source=peak_src,
+                          algorithmic_bytes_per_particle=B.ALGO_BYTES["forces"], launch_ms=f_ms),
+            ranks=per_rank)
+        if e2e:
+            line["e2e"] = e2e
+        B.emit(line)
+    loc.close()
+    dist.barrier()
+    dist.destroy_process_group()
+    return 0

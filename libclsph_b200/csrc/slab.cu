@@ -255,6 +255,10 @@ int sphb_slab_commit(sphb_engine* e) {
   CUDA_TRY(e, cudaGetLastError());
   std::swap(e->rank_cur, e->rank_prev);
   e->cur = in;
+  if (e->profile) {  // the accepted advection attempt
+    CUDA_TRY(e, cudaStreamSynchronize(s));
+    accumulate_pass(e, SPHB_PASS_ADVECT);
+  }
   e->n_upper = e->n;  // the exact count is on the device; the host reads it at the next unpack
   e->committed = true;
   return 0;
