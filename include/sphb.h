@@ -198,7 +198,10 @@ uint64_t sphb_launch_count(sphb_engine* e);
 void* sphb_stream(sphb_engine* e);
 /* named integer options; unknown names return SPHB_ERR_INVALID.
  *   "neighbor_kernel"  0 (default) = the density pass records a neighbour list that the forces
- *                      pass consumes; 1 = both passes search the grid on their own */
+ *                      pass consumes; 1 = both passes search the grid on their own
+ *   "triangle_bin"     1 (default) = scenes of 17+ faces get a uniform-grid triangle bin for the
+ *                      collision pass; 0 = every particle tests every face (set before
+ *                      sphb_set_scene) */
 int sphb_set_option(sphb_engine* e, const char* name, int value);
 
 /* Page-locked host memory for the particle array (the reference asks OpenCL for

@@ -36,6 +36,20 @@ struct Face {
   float sxm1, sym1, szm1, off;   // one float4: size-1 as float, offset as float
 };
 
+// Uniform-grid triangle bin over the union of the faces' inflated AABBs.  Bin cell c lists, in
+// DESCENDING order, every face whose AABB (grown by one bin cell, so that rounding in the
+// particle's bin coordinate can never hide a face) touches it: the collision pass walks that
+// list and stops at the first face whose AABB really contains the point — which is the
+// reference's "last face containing the point" (kernels/collisionsv2.cl:255-261) without
+// its loop over ALL faces.
+struct FaceBin {
+  const uint32_t* start;  // nx*ny*nz + 1 entries (nullptr: bin not built, scan all faces)
+  const uint32_t* faces;  // face indices
+  float ox, oy, oz;       // origin
+  float inv;              // 1 / bin cell side
+  uint32_t nx, ny, nz;
+};
+
 // Reduction cell shared by the bbox / time-step reductions.  Floats are stored in an
 // order-preserving unsigned encoding so that atomicMin/atomicMax work on them.
 struct Reduce {
@@ -112,7 +126,7 @@ int launch_reference_debug(const uint32_t* rank, const uint32_t* rank_prev, cons
 int launch_advect(const float4* pos, const float4* vhf, const float4* acc, float4* pos_out,
                   float4* vel_out, float4* vhf_out, uint32_t n, float dt, float restitution,
                   const Face* faces, uint32_t face_count, const float* df, Reduce* red,
-                  cudaStream_t s, const uint32_t* ghost_ids = nullptr);
+                  cudaStream_t s, const uint32_t* ghost_ids = nullptr, const FaceBin* bin = nullptr);
 int launch_distance_field(float* df, const Face* faces, const uint32_t* face_offsets,
                           const float* transforms, const float* rvertices, uint32_t face_count,
                           uint32_t gridcount, cudaStream_t s);

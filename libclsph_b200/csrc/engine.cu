@@ -50,6 +50,7 @@ int sphb_destroy(sphb_engine* e) {
   if (e->host_counts) cudaFreeHost(e->host_counts);
   cudaFree(e->ftable); cudaFree(e->ref_table); cudaFree(e->scan_scratch); cudaFree(e->aos_stage);
   cudaFree(e->faces); cudaFree(e->face_offsets); cudaFree(e->df);
+  cudaFree(e->bin_start); cudaFree(e->bin_faces);
   cudaFree(e->red);
   if (e->red_host) cudaFreeHost(e->red_host);
   if (e->ev_created)
@@ -151,6 +152,83 @@ int sphb_create_with_capacity(const sphb_params* params, const sphb_terms* terms
   return 0;
 }
 
+namespace {
+// Uniform-grid triangle bin (common.cuh: FaceBin), built on the host once per scene: a few
+// thousand faces at most.  Bin cell side = the largest of (scene extent / 96) per axis, so the
+// grid has at most ~96^3 cells; each face is entered into every bin cell its inflated AABB
+// touches, grown by one cell on every side.
+int build_face_bin(sphb_engine* e, const sphb_bb* bbs, uint32_t face_count) {
+  cudaFree(e->bin_start); cudaFree(e->bin_faces);
+  e->bin_start = e->bin_faces = nullptr;
+  e->bin = FaceBin();
+  if ((int)face_count < e->bin_min_faces || face_count == 0) return 0;
+  float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+  for (uint32_t f = 0; f < face_count; ++f) {
+    const float mn[3] = {bbs[f].minx, bbs[f].miny, bbs[f].minz}, mx[3] = {bbs[f].maxx, bbs[f].maxy, bbs[f].maxz};
+    for (int a = 0; a < 3; ++a) {
+      if (mn[a] < lo[a]) lo[a] = mn[a];
+      if (mx[a] > hi[a]) hi[a] = mx[a];
+    }
+  }
+  float side = 0.f;
+  for (int a = 0; a < 3; ++a) side = fmaxf(side, (hi[a] - lo[a]) / 96.f);
+  if (!(side > 0.f) || !std::isfinite(side)) return 0;
+  FaceBin b = FaceBin();
+  b.inv = 1.f / side;
+  b.ox = lo[0] - side; b.oy = lo[1] - side; b.oz = lo[2] - side;  // one spare cell below
+  uint32_t dims[3];
+  for (int a = 0; a < 3; ++a) dims[a] = (uint32_t)((hi[a] - lo[a]) * b.inv) + 4u;
+  b.nx = dims[0]; b.ny = dims[1]; b.nz = dims[2];
+  const size_t ncell = (size_t)b.nx * b.ny * b.nz;
+  const float org[3] = {b.ox, b.oy, b.oz};
+  auto cell_range = [&](const sphb_bb& bb, int a, uint32_t& c0, uint32_t& c1) {
+    const float mn = a == 0 ? bb.minx : a == 1 ? bb.miny : bb.minz;
+    const float mx = a == 0 ? bb.maxx : a == 1 ? bb.maxy : bb.maxz;
+    const long first = (long)floorf((mn - org[a]) * b.inv) - 1, last = (long)floorf((mx - org[a]) * b.inv) + 1;
+    c0 = (uint32_t)(first < 0 ? 0 : first);
+    c1 = (uint32_t)(last >= (long)dims[a] ? (long)dims[a] - 1 : last);
+  };
+  std::vector<uint32_t> start(ncell + 1, 0);
+  for (int pass = 0; pass < 2; ++pass) {
+    std::vector<uint32_t> cursor;
+    std::vector<uint32_t> ids;
+    if (pass == 1) {
+      uint32_t run = 0;
+      for (size_t c = 0; c <= ncell; ++c) {
+        const uint32_t cnt = start[c];
+        start[c] = run;
+        run += cnt;
+      }
+      cursor.assign(start.begin(), start.end() - 1);
+      ids.resize(start[ncell]);
+    }
+    // descending face order: the first containing face found is the reference's LAST one
+    for (uint32_t k = 0; k < face_count; ++k) {
+      const uint32_t f = face_count - 1 - k;
+      uint32_t x0, x1, y0, y1, z0, z1;
+      cell_range(bbs[f], 0, x0, x1); cell_range(bbs[f], 1, y0, y1); cell_range(bbs[f], 2, z0, z1);
+      for (uint32_t z = z0; z <= z1; ++z)
+        for (uint32_t y = y0; y <= y1; ++y)
+          for (uint32_t x = x0; x <= x1; ++x) {
+            const size_t c = ((size_t)z * b.ny + y) * b.nx + x;
+            if (pass == 0) ++start[c]; else ids[cursor[c]++] = f;
+          }
+    }
+    if (pass == 1) {
+      CUDA_TRY(e, dev_alloc(&e->bin_start, ncell + 1));
+      CUDA_TRY(e, dev_alloc(&e->bin_faces, ids.size()));
+      CUDA_TRY(e, cudaMemcpy(e->bin_start, start.data(), sizeof(uint32_t) * (ncell + 1), cudaMemcpyHostToDevice));
+      if (!ids.empty())
+        CUDA_TRY(e, cudaMemcpy(e->bin_faces, ids.data(), sizeof(uint32_t) * ids.size(), cudaMemcpyHostToDevice));
+    }
+  }
+  b.start = e->bin_start;
+  b.faces = e->bin_faces;
+  e->bin = b;
+  return 0;
+}
+}  // namespace
+
 int sphb_set_scene(sphb_engine* e, const sphb_bb* bbs, uint32_t face_count, const float* transforms,
                    const float* rvertices, uint32_t total_grid_points) {
   if (!e) return SPHB_ERR_INVALID;
@@ -208,6 +286,7 @@ int sphb_set_scene(sphb_engine* e, const sphb_bb* bbs, uint32_t face_count, cons
   CUDA_TRY(e, cudaStreamSynchronize(e->stream));
   cudaFree(d_tr);
   cudaFree(d_rv);
+  if (int rc = build_face_bin(e, bbs, face_count)) return rc;
   e->have_scene = true;
   return 0;
 }
@@ -330,7 +409,7 @@ int sphb_step(sphb_engine* e, float dt_in, float* dt_out) {
       PassTimer t(e, SPHB_PASS_ADVECT);
       int l = launch_reduce_init(e->red, s);
       l += launch_advect(e->pos[in], e->vhf[in], e->acc, e->pos[out], e->vel[out], e->vhf[out], n,
-                         dt, e->params.restitution, e->faces, e->face_count, e->df, e->red, s);
+                         dt, e->params.restitution, e->faces, e->face_count, e->df, e->red, s, nullptr, &e->bin);
       t.done(l);
     }
     CUDA_TRY(e, cudaGetLastError());
@@ -416,7 +495,7 @@ int sphb_debug_advect(sphb_engine* e, float dt) {
   e->launches += launch_reduce_init(e->red, e->stream);
   e->launches += launch_advect(e->pos[in], e->vhf[in], e->acc, e->pos[out], e->vel[out], e->vhf[out],
                                e->n, dt, e->params.restitution, e->faces, e->face_count, e->df, e->red,
-                               e->stream);
+                               e->stream, nullptr, &e->bin);
   CUDA_TRY(e, cudaGetLastError());
   if (int rc = fetch_reduce(e)) return rc;
   e->cur = out;
@@ -492,6 +571,10 @@ void* sphb_stream(sphb_engine* e) { return e ? (void*)e->stream : nullptr; }
 
 int sphb_set_option(sphb_engine* e, const char* name, int value) {
   if (!e || !name) return SPHB_ERR_INVALID;
+  if (!strcmp(name, "triangle_bin")) {  // takes effect at the next sphb_set_scene
+    e->bin_min_faces = value ? 17 : 0x7fffffff;
+    return 0;
+  }
   if (!strcmp(name, "neighbor_kernel")) {
     e->neighbor_variant = value;
     return 0;

@@ -69,6 +69,10 @@ struct sphb_engine {
   float* df = nullptr;
   uint32_t face_count = 0, total_grid_points = 0;
   bool have_scene = false;
+  FaceBin bin = {};               // uniform-grid triangle bin (start == nullptr: not built)
+  uint32_t* bin_start = nullptr;  // device storage behind `bin`
+  uint32_t* bin_faces = nullptr;
+  int bin_min_faces = 17;         // scenes with fewer faces scan them all (option "triangle_bin")
 
   // reductions
   Reduce* red = nullptr;       // device

@@ -225,7 +225,8 @@ __global__ void __launch_bounds__(kBlock)
              const float4* __restrict__ acc, float4* __restrict__ pos_out,
              float4* __restrict__ vel_out, float4* __restrict__ vhf_out, uint32_t n, float dt,
              float restitution, const Face* __restrict__ faces, uint32_t face_count,
-             const float* __restrict__ df, Reduce* red, const uint32_t* __restrict__ ghost_ids) {
+             const float* __restrict__ df, Reduce* red, const uint32_t* __restrict__ ghost_ids,
+             FaceBin bin) {
   // grid-stride over a grid sized to the machine: one set of 8 atomics per CTA, not per 256
   // particles (65 536 CTAs hammering the same 8 words serialise in L2)
   float rv[8] = {INFINITY, INFINITY, INFINITY, -INFINITY, -INFINITY, -INFINITY, -INFINITY, -INFINITY};
@@ -245,11 +246,32 @@ __global__ void __launch_bounds__(kBlock)
     // LAST face whose inflated AABB contains the advected position
     int indice = -1;
     const float4* f4 = reinterpret_cast<const float4*>(faces);
-    for (int f = 0; f < (int)face_count; ++f) {
-      const float4 b0 = __ldg(f4 + 3 * f);
-      const float4 b1 = __ldg(f4 + 3 * f + 1);
-      if (px <= b0.x && px >= b0.w && py <= b0.y && py >= b1.x && pz <= b0.z && pz >= b1.y)
-        indice = f;
+    if (bin.start) {
+      // candidates of the point's bin cell, highest face index first
+      const float bx_ = (px - bin.ox) * bin.inv, by_ = (py - bin.oy) * bin.inv, bz_ = (pz - bin.oz) * bin.inv;
+      if (bx_ >= 0.f && by_ >= 0.f && bz_ >= 0.f) {
+        const uint32_t cx = (uint32_t)bx_, cy = (uint32_t)by_, cz = (uint32_t)bz_;
+        if (cx < bin.nx && cy < bin.ny && cz < bin.nz) {
+          const uint32_t cell = (cz * bin.ny + cy) * bin.nx + cx;
+          const uint32_t k1 = __ldg(bin.start + cell + 1);
+          for (uint32_t k = __ldg(bin.start + cell); k < k1; ++k) {
+            const int f = (int)__ldg(bin.faces + k);
+            const float4 b0 = __ldg(f4 + 3 * f);
+            const float4 b1 = __ldg(f4 + 3 * f + 1);
+            if (px <= b0.x && px >= b0.w && py <= b0.y && py >= b1.x && pz <= b0.z && pz >= b1.y) {
+              indice = f;
+              break;
+            }
+          }
+        }
+      }
+    } else {
+      for (int f = 0; f < (int)face_count; ++f) {
+        const float4 b0 = __ldg(f4 + 3 * f);
+        const float4 b1 = __ldg(f4 + 3 * f + 1);
+        if (px <= b0.x && px >= b0.w && py <= b0.y && py >= b1.x && pz <= b0.z && pz >= b1.y)
+          indice = f;
+      }
     }
     float rx = px, ry = py, rz = pz, wx = nx, wy = ny, wz = nz;
     if (indice > -1) {
@@ -473,11 +495,13 @@ int launch_reference_debug(const uint32_t* rank, const uint32_t* rank_prev, cons
 int launch_advect(const float4* pos, const float4* vhf, const float4* acc, float4* pos_out,
                   float4* vel_out, float4* vhf_out, uint32_t n, float dt, float restitution,
                   const Face* faces, uint32_t face_count, const float* df, Reduce* red,
-                  cudaStream_t s, const uint32_t* ghost_ids) {
+                  cudaStream_t s, const uint32_t* ghost_ids, const FaceBin* bin) {
+  FaceBin b = {};
+  if (bin) b = *bin;
   unsigned grid = blocks_for(n);
   if (grid > 148 * 8) grid = 148 * 8;  // 8 resident CTAs of 256 threads on each of 148 SMs
   k_advect<<<grid, kBlock, 0, s>>>(pos, vhf, acc, pos_out, vel_out, vhf_out, n, dt,
-                                            restitution, faces, face_count, df, red, ghost_ids);
+                                            restitution, faces, face_count, df, red, ghost_ids, b);
   return 1;
 }
 

@@ -236,7 +236,7 @@ int sphb_slab_advect(sphb_engine* e, float dt, float* out8_dev) {
     int l = launch_reduce_init(e->red, s);
     if (e->n)
       l += launch_advect(e->pos[in], e->vhf[in], e->acc, e->pos[out], e->vel[out], e->vhf[out], e->n, dt,
-                         e->params.restitution, e->faces, e->face_count, e->df, e->red, s, e->rank_cur);
+                         e->params.restitution, e->faces, e->face_count, e->df, e->red, s, e->rank_cur, &e->bin);
     l += launch_slab_reduce_floats(e->red, out8_dev, s);
     t.done(l);
   }

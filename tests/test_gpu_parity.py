@@ -109,8 +109,10 @@ def test_distance_field_bit_exact_vs_fixtures():
         assert hashlib.sha256(df.tobytes()).hexdigest() == str(sc["df_sha256"]), scene
 
 
-def test_advect_collide_bit_exact_vs_fixture():
-    """advection_collision alone over a seeded random state inside monkeybox (restitution 0.5,
+@pytest.mark.parametrize("triangle_bin", [1, 0])
+def test_advect_collide_bit_exact_vs_fixture(triangle_bin):
+    """(with the uniform-grid triangle bin, and with the reference's loop over all faces)
+    advection_collision alone over a seeded random state inside monkeybox (restitution 0.5,
     978 faces, including the |v| = 0 -> NaN case of respond()): the streaming passes are
     compiled without FMA contraction and must equal the reference bit for bit."""
     from libclsph_b200 import Engine
@@ -121,6 +123,7 @@ def test_advect_collide_bit_exact_vs_fixture():
     params["particles_count"] = len(g["input"])
     params["restitution"] = float(g["restitution"])
     with Engine(params, st["terms"]) as e:
+        e.set_option("triangle_bin", triangle_bin)
         e.set_scene(sc["bbs"], sc["transforms"], sc["rvertices"], int(sc["total_gridpoints"]))
         e.upload(g["input"])
         e.debug_advect(float(g["dt"]))
