@@ -199,6 +199,9 @@ void* sphb_stream(sphb_engine* e);
 /* named integer options; unknown names return SPHB_ERR_INVALID.
  *   "neighbor_kernel"  0 (default) = the density pass records a neighbour list that the forces
  *                      pass consumes; 1 = both passes search the grid on their own
+ *   "sort"             0 (default) = counting sort by search cell (the scan of the counts is the
+ *                      cell table), made stable by a per-cell canonical order; 1 = LSD radix
+ *                      sort of (key, index) pairs.  Both give the same order.
  *   "triangle_bin"     1 (default) = scenes of 17+ faces get a uniform-grid triangle bin for the
  *                      collision pass; 0 = every particle tests every face (set before
  *                      sphb_set_scene) */

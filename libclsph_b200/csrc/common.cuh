@@ -105,6 +105,13 @@ __host__ __device__ inline uint32_t compact10(uint32_t v) {
 int launch_reduce_init(Reduce* red, cudaStream_t s);
 int launch_bbox(const float4* pos, uint32_t n, Reduce* red, cudaStream_t s);
 int launch_locate(const float4* pos, uint32_t* keys, const StepConsts& c, cudaStream_t s);
+// Counting sort by search cell (locate fused in): on return keys_sorted[d] = cell key of the
+// particle at sorted position d, perm[d] = its index before the sort (stable: ascending inside a
+// cell), ftable[f] = first sorted position of cell f (nfine + 1 entries).  keys_tmp, slot_tmp,
+// src_tmp: n-entry scratch.
+int launch_cell_sort(const float4* pos, const StepConsts& c, uint32_t* keys_tmp, uint32_t* slot_tmp,
+                     uint32_t* ftable, uint32_t* scan_scratch, uint32_t* keys_sorted, uint32_t* src_tmp,
+                     uint32_t* perm, cudaStream_t s);
 int launch_reorder(const uint32_t* perm, uint32_t n, const float4* pos_in, const float4* vel_in,
                    const float4* vhf_in, const uint32_t* rank_in, float4* pos_out, float4* vel_out,
                    float4* vhf_out, uint32_t* rank_out, cudaStream_t s);

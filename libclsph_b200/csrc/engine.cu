@@ -350,28 +350,17 @@ int sphb_step(sphb_engine* e, float dt_in, float* dt_out) {
   const StepConsts c = make_consts(e);
   if (int rc = ensure_tables(e, (size_t)c.nfine + 1, (size_t)ncell + 1)) return rc;
 
-  // 2. locate_in_grid (kernels/grid.cl:40-64): keys only, no struct copy
-  {
-    PassTimer t(e, SPHB_PASS_LOCATE);
-    t.done(launch_locate(e->pos[e->cur], e->sortb.keys[0], c, s));
-  }
-  // 3. sort_particles (sph_simulation.cpp:110-198): (key, index) pairs, significant bits only
-  int r = 0;
-  {
-    PassTimer t(e, SPHB_PASS_SORT);
-    t.done(launch_sort_pairs(e->sortb, n, key_bits_for(c.nfine), &r, s));
-  }
-  e->sorted = r;
+  // 2. locate_in_grid (kernels/grid.cl:40-64) + 3. sort_particles (sph_simulation.cpp:110-198):
+  //    keys only, no struct copies; then ONE gather of the carried state
+  const uint32_t* skeys = nullptr;
+  const uint32_t* perm = nullptr;
+  if (int rc = order_by_cell(e, c, &skeys, &perm)) return rc;
   {
     PassTimer t(e, SPHB_PASS_REORDER);
     const int in = e->cur, out = in ^ 1;
-    t.done(launch_reorder(e->sortb.vals[r], n, e->pos[in], e->vel[in], e->vhf[in], e->rank_cur,
+    t.done(launch_reorder(perm, n, e->pos[in], e->vel[in], e->vhf[in], e->rank_cur,
                           e->pos[out], e->vel[out], e->vhf[out], e->rank_prev, s));
     e->cur = out;
-  }
-  {
-    PassTimer t(e, SPHB_PASS_CELLTABLE);
-    t.done(launch_fine_table(e->sortb.keys[r], n, e->ftable, c.nfine, e->scan_scratch, s));
   }
   // the reference's cell table (kernels/sort.cl:61-78) and every particle's place in the
   // reference's sorted array: nothing in the step depends on it, so it runs on the side
@@ -380,19 +369,19 @@ int sphb_step(sphb_engine* e, float dt_in, float* dt_out) {
   CUDA_TRY(e, cudaStreamWaitEvent(e->side, e->ev_fork, 0));
   {
     PassTimer t(e, SPHB_PASS_REFRANK, e->side);
-    t.done(launch_reference_rank(e->sortb.keys[r], e->ftable, e->rank_prev, e->ref_table, e->ckey,
+    t.done(launch_reference_rank(skeys, e->ftable, e->rank_prev, e->ref_table, e->ckey,
                                  e->rank_cur, c, e->scan_scratch, e->side));
   }
   CUDA_TRY(e, cudaEventRecord(e->ev_join, e->side));
   // 4. density_pressure (kernels/sphb.cl:3-35), 5. forces (:37-126)
   {
     PassTimer t(e, SPHB_PASS_DENSITY);
-    t.done(launch_density(e->pos[e->cur], e->vel[e->cur], e->sortb.keys[r], e->ftable, e->rho,
+    t.done(launch_density(e->pos[e->cur], e->vel[e->cur], skeys, e->ftable, e->rho,
                           e->prs, e->nlist, e->ncount, c, e->neighbor_variant, s));
   }
   {
     PassTimer t(e, SPHB_PASS_FORCES);
-    t.done(launch_forces(e->pos[e->cur], e->vel[e->cur], e->sortb.keys[r], e->ftable, e->rho,
+    t.done(launch_forces(e->pos[e->cur], e->vel[e->cur], skeys, e->ftable, e->rho,
                          e->nlist, e->ncount, e->acc, c, e->neighbor_variant, s));
   }
   CUDA_TRY(e, cudaStreamWaitEvent(s, e->ev_join, 0));
@@ -458,15 +447,16 @@ int sphb_download_debug(sphb_engine* e, uint32_t* keys, uint32_t* perm, uint32_t
   if (!e->stepped) SPHB_FAIL(e, SPHB_ERR_INVALID, "sphb_download_debug before the first sphb_step");
   CUDA_TRY(e, cudaSetDevice(e->device));
   // the sort buffers are free between steps: use the half that does not hold the fine keys
-  const int scratch = e->sorted ^ 1;
-  e->launches += launch_reference_debug(e->rank_cur, e->rank_prev, e->ckey, e->n, e->sortb.keys[scratch],
-                                        e->sortb.vals[scratch], e->stream);
+  uint32_t* const scratch_k = e->free_keys;
+  uint32_t* const scratch_v = e->free_vals;
+  e->launches += launch_reference_debug(e->rank_cur, e->rank_prev, e->ckey, e->n, scratch_k, scratch_v,
+                                        e->stream);
   CUDA_TRY(e, cudaGetLastError());
   if (keys)
-    CUDA_TRY(e, cudaMemcpyAsync(keys, e->sortb.keys[scratch], sizeof(uint32_t) * e->n,
+    CUDA_TRY(e, cudaMemcpyAsync(keys, scratch_k, sizeof(uint32_t) * e->n,
                                 cudaMemcpyDeviceToHost, e->stream));
   if (perm)
-    CUDA_TRY(e, cudaMemcpyAsync(perm, e->sortb.vals[scratch], sizeof(uint32_t) * e->n,
+    CUDA_TRY(e, cudaMemcpyAsync(perm, scratch_v, sizeof(uint32_t) * e->n,
                                 cudaMemcpyDeviceToHost, e->stream));
   uint32_t cnt = 0;
   uint32_t first_key = 0;
@@ -475,7 +465,7 @@ int sphb_download_debug(sphb_engine* e, uint32_t* keys, uint32_t* perm, uint32_t
     if (cnt)
       CUDA_TRY(e, cudaMemcpyAsync(cell_table, e->ref_table, sizeof(uint32_t) * cnt,
                                   cudaMemcpyDeviceToHost, e->stream));
-    CUDA_TRY(e, cudaMemcpyAsync(&first_key, e->sortb.keys[scratch], sizeof(uint32_t),
+    CUDA_TRY(e, cudaMemcpyAsync(&first_key, scratch_k, sizeof(uint32_t),
                                 cudaMemcpyDeviceToHost, e->stream));
   }
   CUDA_TRY(e, cudaStreamSynchronize(e->stream));
@@ -573,6 +563,10 @@ int sphb_set_option(sphb_engine* e, const char* name, int value) {
   if (!e || !name) return SPHB_ERR_INVALID;
   if (!strcmp(name, "triangle_bin")) {  // takes effect at the next sphb_set_scene
     e->bin_min_faces = value ? 17 : 0x7fffffff;
+    return 0;
+  }
+  if (!strcmp(name, "sort")) {
+    e->sort_variant = value ? 1 : 0;
     return 0;
   }
   if (!strcmp(name, "neighbor_kernel")) {

@@ -46,7 +46,10 @@ struct sphb_engine {
   float* rho = nullptr;
   float* prs = nullptr;
   SortBuffers sortb = {};
-  int sorted = 0;            // which half of sortb holds the last step's sorted keys / perm
+  int sorted = 0;            // which half of sortb holds the last step's sorted keys
+  int sort_variant = 0;      // 0 = counting sort by search cell, 1 = LSD radix sort
+  uint32_t* free_keys = nullptr;  // sort buffers that are free between steps (download scratch)
+  uint32_t* free_vals = nullptr;
   // The compute order is the engine's own (fine row-major cells); rank_cur[i] is the position
   // of particle i in the REFERENCE's order, rank_prev[i] its position one step earlier
   // (= the permutation the reference's sort applied), ckey[i] its Morton key (grid_index).
@@ -85,6 +88,7 @@ struct sphb_engine {
   // options / measurement
   int neighbor_variant = 0;
   bool profile = false;
+  uint32_t recorded = 0;  // bit p: pass p's event pair was recorded and not yet accumulated
   cudaEvent_t ev[SPHB_PASS_COUNT + 1][2];
   cudaEvent_t user_ev[4];
   bool ev_created = false;
@@ -198,6 +202,7 @@ struct PassTimer {
     e->launches += launches;
     if (e->profile) {
       cudaEventRecord(e->ev[pass][1], st);
+      e->recorded |= 1u << pass;
       e->pass_launches[pass] += launches;
     }
   }
@@ -216,6 +221,8 @@ int fetch_reduce(sphb_engine* e) {
 }
 
 void accumulate_pass(sphb_engine* e, int pass) {
+  if (!(e->recorded & (1u << pass))) return;
+  e->recorded &= ~(1u << pass);
   float ms = 0.f;
   if (cudaEventElapsedTime(&ms, e->ev[pass][0], e->ev[pass][1]) == cudaSuccess) e->pass_ms[pass] += ms;
 }
@@ -244,6 +251,45 @@ int ensure_tables(sphb_engine* e, size_t fine_entries, size_t ref_entries) {
     e->scan_scratch_cap = need;
     CUDA_TRY(e, dev_alloc(&e->scan_scratch, need));
   }
+  return 0;
+}
+
+int key_bits_for(uint32_t grid_cell_count);
+
+// locate + sort + search-cell table, by either variant.  On return: *skeys = sorted search keys,
+// *perm = previous index of every sorted particle, e->ftable built.
+int order_by_cell(sphb_engine* e, const StepConsts& c, const uint32_t** skeys, const uint32_t** perm) {
+  cudaStream_t s = e->stream;
+  SortBuffers& b = e->sortb;
+  if (e->sort_variant == 0) {
+    PassTimer t(e, SPHB_PASS_SORT);
+    t.done(launch_cell_sort(e->pos[e->cur], c, b.keys[0], b.vals[0], e->ftable, e->scan_scratch, b.keys[1],
+                            b.vals[1], b.vals[0], s));
+    e->sorted = 1;
+    *skeys = b.keys[1];
+    *perm = b.vals[0];
+    e->free_keys = b.keys[0];
+    e->free_vals = b.vals[1];
+    return 0;
+  }
+  {
+    PassTimer t(e, SPHB_PASS_LOCATE);
+    t.done(launch_locate(e->pos[e->cur], b.keys[0], c, s));
+  }
+  int r = 0;
+  {
+    PassTimer t(e, SPHB_PASS_SORT);
+    t.done(launch_sort_pairs(b, c.n, key_bits_for(c.nfine), &r, s));
+  }
+  e->sorted = r;
+  {
+    PassTimer t(e, SPHB_PASS_CELLTABLE);
+    t.done(launch_fine_table(b.keys[r], c.n, e->ftable, c.nfine, e->scan_scratch, s));
+  }
+  *skeys = b.keys[r];
+  *perm = b.vals[r];
+  e->free_keys = b.keys[r ^ 1];
+  e->free_vals = b.vals[r ^ 1];
   return 0;
 }
 

@@ -90,17 +90,70 @@ __device__ __forceinline__ uint32_t fine_coord(float p, float mn, float cell, fl
   return 2u * c + (within >= h ? 1u : 0u);
 }
 
-__global__ void __launch_bounds__(kBlock) k_locate(const float4* __restrict__ pos,
-                                                   uint32_t* __restrict__ keys, StepConsts c) {
-  const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
-  if (i >= c.n) return;
-  const float4 p = __ldg(pos + i);
+__device__ __forceinline__ uint32_t fine_key_of(const float4& p, const StepConsts& c) {
   uint32_t fx = fine_coord(p.x, c.minx, c.cell, c.h);
   uint32_t fy = fine_coord(p.y, c.miny, c.cell, c.h);
   uint32_t fz = fine_coord(p.z, c.minz, c.cell, c.h);
   // NaN / runaway positions: park them in the last cell instead of indexing out of bounds
   fx = min(fx, c.fnx - 1); fy = min(fy, c.fny - 1); fz = min(fz, c.fnz - 1);
-  keys[i] = (fz * c.fny + fy) * c.fnx + fx;
+  return (fz * c.fny + fy) * c.fnx + fx;
+}
+
+__global__ void __launch_bounds__(kBlock) k_locate(const float4* __restrict__ pos,
+                                                   uint32_t* __restrict__ keys, StepConsts c) {
+  const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
+  if (i >= c.n) return;
+  keys[i] = fine_key_of(__ldg(pos + i), c);
+}
+
+// ---- counting sort by search cell ------------------------------------------------------------
+// The search grid has about as many cells as there are particles / 4, so ordering particles by
+// cell is a COUNTING sort: (1) key + a slot inside the cell from one atomic per (warp, cell),
+// (2) exclusive scan of the counts — which IS the cell table —, (3) placement, (4) a
+// canonicalisation that orders each cell's members by their previous index, so that the
+// result is exactly the stable sort a radix sort would give (atomics decide the slots, so
+// without it the order inside a cell would vary from run to run).
+__global__ void __launch_bounds__(kBlock)
+    k_locate_count(const float4* __restrict__ pos, uint32_t* __restrict__ keys, uint32_t* __restrict__ slot,
+                   uint32_t* __restrict__ count, StepConsts c) {
+  const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
+  const bool valid = i < c.n;
+  const uint32_t key = valid ? fine_key_of(__ldg(pos + i), c) : 0xFFFFFFFFu;
+  const unsigned peers = __match_any_sync(0xffffffffu, key);
+  const int lane = threadIdx.x & 31;
+  const int leader = __ffs(peers) - 1;
+  uint32_t base = 0;
+  if (valid && lane == leader) base = atomicAdd(count + key, __popc(peers));
+  base = __shfl_sync(0xffffffffu, base, leader);
+  if (valid) {
+    keys[i] = key;
+    slot[i] = base + __popc(peers & ((1u << lane) - 1u));
+  }
+}
+
+__global__ void __launch_bounds__(kBlock)
+    k_place(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ slot,
+            const uint32_t* __restrict__ start, uint32_t n, uint32_t* __restrict__ keys_sorted,
+            uint32_t* __restrict__ src_tmp) {
+  const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
+  if (i >= n) return;
+  const uint32_t key = __ldg(keys + i);
+  const uint32_t d = __ldg(start + key) + __ldg(slot + i);
+  keys_sorted[d] = key;
+  src_tmp[d] = i;
+}
+
+__global__ void __launch_bounds__(kBlock)
+    k_canonical_order(const uint32_t* __restrict__ keys_sorted, const uint32_t* __restrict__ src_tmp,
+                      const uint32_t* __restrict__ start, uint32_t n, uint32_t* __restrict__ perm) {
+  const uint32_t d = blockIdx.x * kBlock + threadIdx.x;
+  if (d >= n) return;
+  const uint32_t key = __ldg(keys_sorted + d);
+  const uint32_t s = __ldg(start + key), e = __ldg(start + key + 1);
+  const uint32_t mine = __ldg(src_tmp + d);
+  uint32_t before = 0;
+  for (uint32_t j = s; j < e; ++j) before += (__ldg(src_tmp + j) < mine) ? 1u : 0u;
+  perm[s + before] = mine;
 }
 
 // The reference moves whole 80-byte structs in each of its 4 radix passes
@@ -459,6 +512,17 @@ int launch_bbox(const float4* pos, uint32_t n, Reduce* red, cudaStream_t s) {
 int launch_locate(const float4* pos, uint32_t* keys, const StepConsts& c, cudaStream_t s) {
   k_locate<<<blocks_for(c.n), kBlock, 0, s>>>(pos, keys, c);
   return 1;
+}
+
+int launch_cell_sort(const float4* pos, const StepConsts& c, uint32_t* keys_tmp, uint32_t* slot_tmp,
+                     uint32_t* ftable, uint32_t* scan_scratch, uint32_t* keys_sorted, uint32_t* src_tmp,
+                     uint32_t* perm, cudaStream_t s) {
+  cudaMemsetAsync(ftable, 0, sizeof(uint32_t) * ((size_t)c.nfine + 1), s);
+  k_locate_count<<<blocks_for(c.n), kBlock, 0, s>>>(pos, keys_tmp, slot_tmp, ftable, c);
+  int l = 1 + launch_exclusive_sum(ftable, c.nfine + 1, scan_scratch, s);
+  k_place<<<blocks_for(c.n), kBlock, 0, s>>>(keys_tmp, slot_tmp, ftable, c.n, keys_sorted, src_tmp);
+  k_canonical_order<<<blocks_for(c.n), kBlock, 0, s>>>(keys_sorted, src_tmp, ftable, c.n, perm);
+  return l + 2;
 }
 
 int launch_reorder(const uint32_t* perm, uint32_t n, const float4* pos_in, const float4* vel_in,

@@ -180,20 +180,13 @@ int sphb_slab_forces(sphb_engine* e, const float gmin[3], const float gmax[3]) {
     e->slab_in = e->cur;
     return 0;
   }
-  {
-    PassTimer t(e, SPHB_PASS_LOCATE);
-    t.done(launch_locate(e->pos[e->cur], e->sortb.keys[0], c, s));
-  }
-  int r = 0;
-  {
-    PassTimer t(e, SPHB_PASS_SORT);
-    t.done(launch_sort_pairs(e->sortb, n, key_bits_for(c.nfine), &r, s));
-  }
-  e->sorted = r;
+  const uint32_t* skeys = nullptr;
+  const uint32_t* perm = nullptr;
+  if (int rc = order_by_cell(e, c, &skeys, &perm)) return rc;
   {
     PassTimer t(e, SPHB_PASS_REORDER);
     const int in = e->cur, out = in ^ 1;
-    int l = launch_reorder(e->sortb.vals[r], n, e->pos[in], e->vel[in], e->vhf[in], e->rank_cur, e->pos[out],
+    int l = launch_reorder(perm, n, e->pos[in], e->vel[in], e->vhf[in], e->rank_cur, e->pos[out],
                            e->vel[out], e->vhf[out], e->rank_prev, s);
     std::swap(e->rank_cur, e->rank_prev);  // ids (+ ghost bit) now in compute order
     e->cur = out;
@@ -201,17 +194,13 @@ int sphb_slab_forces(sphb_engine* e, const float gmin[3], const float gmax[3]) {
     t.done(l);
   }
   {
-    PassTimer t(e, SPHB_PASS_CELLTABLE);
-    t.done(launch_fine_table(e->sortb.keys[r], n, e->ftable, c.nfine, e->scan_scratch, s));
-  }
-  {
     PassTimer t(e, SPHB_PASS_DENSITY);
-    t.done(launch_density(e->pos[e->cur], e->vel[e->cur], e->sortb.keys[r], e->ftable, e->rho, e->prs,
+    t.done(launch_density(e->pos[e->cur], e->vel[e->cur], skeys, e->ftable, e->rho, e->prs,
                           e->nlist, e->ncount, c, 0, s));
   }
   {
     PassTimer t(e, SPHB_PASS_FORCES);
-    t.done(launch_forces(e->pos[e->cur], e->vel[e->cur], e->sortb.keys[r], e->ftable, e->rho, e->nlist,
+    t.done(launch_forces(e->pos[e->cur], e->vel[e->cur], skeys, e->ftable, e->rho, e->nlist,
                          e->ncount, e->acc, c, 0, s, e->rank_cur));
   }
   CUDA_TRY(e, cudaGetLastError());
@@ -277,7 +266,7 @@ int sphb_slab_download(sphb_engine* e, sphb_particle* aos, uint32_t* ids, uint32
   if (!aos || !ids) return 0;
   if (n > capacity) SPHB_FAIL(e, SPHB_ERR_CAPACITY, "download of %u particles into %u slots", n, capacity);
   if (n == 0) return 0;
-  uint32_t* ids_dev = e->sortb.vals[e->sorted ^ 1];  // free between steps
+  uint32_t* ids_dev = e->free_vals ? e->free_vals : e->sortb.vals[1];  // free between steps
   const int cur = e->cur;
   e->launches += launch_slab_to_aos(e->aos_stage, ids_dev, e->n_owned_dev, n, e->pos[cur], e->vel[cur],
                                     e->vhf[cur], e->rank_cur, e->committed ? e->src_of : nullptr, e->acc,
