@@ -50,6 +50,20 @@ struct FaceBin {
   uint32_t nx, ny, nz;
 };
 
+// Slab mode of the advection pass: ghosts (bit 31 of the id) are skipped, and the owned
+// particles are written DENSELY at dst[i] (an exclusive scan of the owned flags), so that the
+// step ends with the owned particles compacted without a separate pass.  Besides the state,
+// the pass writes the id, the compute-order index (src_of, to find acceleration / density /
+// pressure later) and the reference's Morton grid_index under the global grid origin.
+struct SlabAdvect {
+  const uint32_t* ids;  // nullptr: not in slab mode
+  const uint32_t* dst;
+  uint32_t* ids_out;
+  uint32_t* src_of;
+  uint32_t* ckey_out;
+  float gminx, gminy, gminz, cell;
+};
+
 // Reduction cell shared by the bbox / time-step reductions.  Floats are stored in an
 // order-preserving unsigned encoding so that atomicMin/atomicMax work on them.
 struct Reduce {
@@ -133,7 +147,7 @@ int launch_reference_debug(const uint32_t* rank, const uint32_t* rank_prev, cons
 int launch_advect(const float4* pos, const float4* vhf, const float4* acc, float4* pos_out,
                   float4* vel_out, float4* vhf_out, uint32_t n, float dt, float restitution,
                   const Face* faces, uint32_t face_count, const float* df, Reduce* red,
-                  cudaStream_t s, const uint32_t* ghost_ids = nullptr, const FaceBin* bin = nullptr);
+                  cudaStream_t s, const SlabAdvect* slab = nullptr, const FaceBin* bin = nullptr);
 int launch_distance_field(float* df, const Face* faces, const uint32_t* face_offsets,
                           const float* transforms, const float* rvertices, uint32_t face_count,
                           uint32_t gridcount, cudaStream_t s);
@@ -186,15 +200,13 @@ int launch_slab_pack(const float4* pos, const float4* vel, const float4* vhf, ui
                      uint32_t* counters, cudaStream_t s);
 int launch_slab_unpack(const void* msg, uint32_t count, uint32_t offset, float4* pos, float4* vel,
                        float4* vhf, uint32_t* ids, cudaStream_t s);
-int launch_slab_compact(const float4* pos, const float4* vel, const float4* vhf, const uint32_t* ids,
-                        uint32_t n, float4* pos_out, float4* vel_out, float4* vhf_out, uint32_t* ids_out,
-                        uint32_t* src_of, uint32_t* n_owned_out, cudaStream_t s);
+// dst[i] = number of owned particles before i (compute order); *n_owned_out = their total
+int launch_slab_owned_scan(const uint32_t* ids, uint32_t n, uint32_t* dst, uint32_t* scan_scratch,
+                           uint32_t* n_owned_out, cudaStream_t s);
 int launch_slab_to_aos(sphb_particle* aos, uint32_t* ids_out, const uint32_t* n_owned_dev, uint32_t n_upper,
                        const float4* pos, const float4* vel, const float4* vhf, const uint32_t* ids,
                        const uint32_t* src_of, const float4* acc, const float* rho, const float* prs,
                        const uint32_t* ckey, cudaStream_t s);
-int launch_slab_ckey(const float4* pos, uint32_t n, const float gmin[3], float cell, uint32_t* ckey,
-                     cudaStream_t s);
 int launch_slab_reduce_floats(const Reduce* red, float* out, cudaStream_t s);
 int launch_slab_bbox(const float4* pos, const uint32_t* n_owned_dev, uint32_t n_upper, Reduce* red,
                      cudaStream_t s);

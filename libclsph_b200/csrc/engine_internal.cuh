@@ -230,7 +230,7 @@ void accumulate_pass(sphb_engine* e, int pass) {
 int ensure_tables(sphb_engine* e, size_t fine_entries, size_t ref_entries) {
   // grow rarely: capacities are kept with 1.5x headroom
   const bool grow_f = fine_entries > e->ftable_cap, grow_r = ref_entries > e->ref_table_cap;
-  if (!grow_f && !grow_r) return 0;
+  if (!grow_f && !grow_r && e->scan_scratch) return 0;
   CUDA_TRY(e, cudaStreamSynchronize(e->stream));
   if (grow_f) {
     cudaFree(e->ftable);
@@ -244,7 +244,9 @@ int ensure_tables(sphb_engine* e, size_t fine_entries, size_t ref_entries) {
     e->ref_table_cap = ref_entries + ref_entries / 2 + 1024;
     CUDA_TRY(e, dev_alloc(&e->ref_table, e->ref_table_cap));
   }
-  const size_t need = scan_scratch_entries(e->ftable_cap > e->ref_table_cap ? e->ftable_cap : e->ref_table_cap);
+  size_t longest = e->ftable_cap > e->ref_table_cap ? e->ftable_cap : e->ref_table_cap;
+  if (e->cap > longest) longest = e->cap;  // slab mode scans one flag per particle
+  const size_t need = scan_scratch_entries(longest);
   if (need > e->scan_scratch_cap) {
     cudaFree(e->scan_scratch);
     e->scan_scratch = nullptr;

@@ -278,19 +278,24 @@ __global__ void __launch_bounds__(kBlock)
              const float4* __restrict__ acc, float4* __restrict__ pos_out,
              float4* __restrict__ vel_out, float4* __restrict__ vhf_out, uint32_t n, float dt,
              float restitution, const Face* __restrict__ faces, uint32_t face_count,
-             const float* __restrict__ df, Reduce* red, const uint32_t* __restrict__ ghost_ids,
-             FaceBin bin) {
+             const float* __restrict__ df, Reduce* red, SlabAdvect slab, FaceBin bin) {
   // grid-stride over a grid sized to the machine: one set of 8 atomics per CTA, not per 256
   // particles (65 536 CTAs hammering the same 8 words serialise in L2)
   float rv[8] = {INFINITY, INFINITY, INFINITY, -INFINITY, -INFINITY, -INFINITY, -INFINITY, -INFINITY};
   for (uint32_t i = blockIdx.x * kBlock + threadIdx.x; i < n; i += gridDim.x * kBlock) {
     const float4 x0 = __ldg(pos + i), vh = __ldg(vhf + i), a = __ldg(acc + i);
-    if (ghost_ids && (__ldg(ghost_ids + i) & 0x80000000u)) {
-      // slab mode: a ghost belongs to another rank, which advects it; here it is carried
-      // through unchanged and kept out of the reductions
-      pos_out[i] = x0;
-      vhf_out[i] = vh;
-      continue;
+    uint32_t o = i;  // where the result goes
+    if (slab.ids) {
+      // slab mode: a ghost belongs to another rank, which advects it; owned particles are
+      // written densely (dst = exclusive scan of the owned flags)
+      const uint32_t id = __ldg(slab.ids + i);
+      if (id & 0x80000000u) continue;
+      o = __ldg(slab.dst + i);
+      slab.ids_out[o] = id;
+      slab.src_of[o] = i;
+      slab.ckey_out[o] = morton3((uint32_t)((x0.x - slab.gminx) / slab.cell),
+                                 (uint32_t)((x0.y - slab.gminy) / slab.cell),
+                                 (uint32_t)((x0.z - slab.gminz) / slab.cell));
     }
     // leapfrog
     const float nx = vh.x + a.x * dt, ny = vh.y + a.y * dt, nz = vh.z + a.z * dt;
@@ -365,9 +370,9 @@ __global__ void __launch_bounds__(kBlock)
       }
     }
     const float vx = (vh.x + wx) / 2.f, vy = (vh.y + wy) / 2.f, vz = (vh.z + wz) / 2.f;
-    pos_out[i] = make_float4(rx, ry, rz, 0.f);
-    vel_out[i] = make_float4(vx, vy, vz, 0.f);
-    vhf_out[i] = make_float4(wx, wy, wz, 0.f);
+    pos_out[o] = make_float4(rx, ry, rz, 0.f);
+    vel_out[o] = make_float4(vx, vy, vz, 0.f);
+    vhf_out[o] = make_float4(wx, wy, wz, 0.f);
     // fminf / fmaxf return the non-NaN operand: NaNs are skipped, as OpenCL's min/max do
     rv[0] = fminf(rv[0], rx); rv[1] = fminf(rv[1], ry); rv[2] = fminf(rv[2], rz);
     rv[3] = fmaxf(rv[3], rx); rv[4] = fmaxf(rv[4], ry); rv[5] = fmaxf(rv[5], rz);
@@ -559,13 +564,15 @@ int launch_reference_debug(const uint32_t* rank, const uint32_t* rank_prev, cons
 int launch_advect(const float4* pos, const float4* vhf, const float4* acc, float4* pos_out,
                   float4* vel_out, float4* vhf_out, uint32_t n, float dt, float restitution,
                   const Face* faces, uint32_t face_count, const float* df, Reduce* red,
-                  cudaStream_t s, const uint32_t* ghost_ids, const FaceBin* bin) {
+                  cudaStream_t s, const SlabAdvect* slab, const FaceBin* bin) {
   FaceBin b = {};
   if (bin) b = *bin;
+  SlabAdvect sa = {};
+  if (slab) sa = *slab;
   unsigned grid = blocks_for(n);
   if (grid > 148 * 8) grid = 148 * 8;  // 8 resident CTAs of 256 threads on each of 148 SMs
   k_advect<<<grid, kBlock, 0, s>>>(pos, vhf, acc, pos_out, vel_out, vhf_out, n, dt,
-                                            restitution, faces, face_count, df, red, ghost_ids, b);
+                                            restitution, faces, face_count, df, red, sa, b);
   return 1;
 }
 

@@ -59,10 +59,10 @@ __global__ void __launch_bounds__(kBlock)
   if (base >= n) return;
   const uint32_t i = base + threadIdx.x;
   const bool live = i < n;
-  float4 p = make_float4(0, 0, 0, 0), v = p, w = p;
+  float4 p = make_float4(0, 0, 0, 0);
   uint32_t id = 0;
   if (live) {
-    p = __ldg(pos + i); v = __ldg(vel + i); w = __ldg(vhf + i);
+    p = __ldg(pos + i);
     id = ids[i] & ~kGhostBit;
   }
   const bool mig_r = live && has_right && p.x >= xhi;
@@ -73,10 +73,13 @@ __global__ void __launch_bounds__(kBlock)
   const uint32_t sl = warp_append(counters + 0, to_l);
   warp_append(counters + 3, mig_r);
   warp_append(counters + 1, mig_l);
-  if (to_r && sr < cap) write_record(msg_right, sr, p, v, w, id, mig_r);
-  if (to_l && sl < cap) write_record(msg_left, sl, p, v, w, id, mig_l);
+  if (to_r || to_l) {  // few particles are near a face: only they read the rest of their state
+    const float4 v = __ldg(vel + i), w = __ldg(vhf + i);
+    if (to_r && sr < cap) write_record(msg_right, sr, p, v, w, id, mig_r);
+    if (to_l && sl < cap) write_record(msg_left, sl, p, v, w, id, mig_l);
+  }
   // a particle that left stays here as a ghost of its new owner
-  if (live) ids[i] = (mig_r || mig_l) ? (id | kGhostBit) : id;
+  if (mig_r || mig_l) ids[i] = id | kGhostBit;
 }
 
 __global__ void k_slab_headers(const uint32_t* __restrict__ counters, float4* msg_left, float4* msg_right) {
@@ -101,24 +104,16 @@ __global__ void __launch_bounds__(kBlock)
   ids[offset + k] = b.w != 0.f ? id : (id | kGhostBit);
 }
 
-// Keeps the owned particles of [0, n): dst arrays get them densely, src_of[dst] = source index
-// (so that acceleration / density / pressure, which are not moved, can still be found), and
-// *n_owned_out = how many.
+// owned flags (1 = not a ghost) for the exclusive scan that gives every owned particle its
+// dense output slot
 __global__ void __launch_bounds__(kBlock)
-    k_slab_compact(const float4* __restrict__ pos, const float4* __restrict__ vel,
-                   const float4* __restrict__ vhf, const uint32_t* __restrict__ ids, uint32_t n,
-                   float4* __restrict__ pos_out, float4* __restrict__ vel_out, float4* __restrict__ vhf_out,
-                   uint32_t* __restrict__ ids_out, uint32_t* __restrict__ src_of,
-                   uint32_t* __restrict__ n_owned_out) {
+    k_slab_owned_flags(const uint32_t* __restrict__ ids, uint32_t n, uint32_t* __restrict__ flags) {
   const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
-  const bool keep = i < n && !(ids[i] & kGhostBit);
-  const uint32_t dst = warp_append(n_owned_out, keep);
-  if (!keep) return;
-  float4 p = __ldg(pos + i), v = __ldg(vel + i), w = __ldg(vhf + i);
-  p.w = 0.f; v.w = 0.f; w.w = 0.f;
-  pos_out[dst] = p; vel_out[dst] = v; vhf_out[dst] = w;
-  ids_out[dst] = ids[i];
-  src_of[dst] = i;
+  if (i < n) flags[i] = (__ldg(ids + i) & kGhostBit) ? 0u : 1u;
+}
+__global__ void k_slab_owned_count(const uint32_t* __restrict__ ids, const uint32_t* __restrict__ dst,
+                                   uint32_t n, uint32_t* __restrict__ n_owned_out) {
+  if (threadIdx.x == 0) *n_owned_out = n ? dst[n - 1] + ((ids[n - 1] & kGhostBit) ? 0u : 1u) : 0u;
 }
 
 // Owned particles -> 80-byte AoS (local order) + their ids.  grid_index is the reference's
@@ -141,23 +136,12 @@ __global__ void __launch_bounds__(kBlock)
     const uint32_t s = src_of[i];
     a = acc[s]; a.w = 0.f;
     d = rho[s]; pr = prs[s];
-    key = ckey[s];
+    key = ckey[i];  // written densely by the advection pass
   }
   float4* dst = reinterpret_cast<float4*>(aos + i);
   dst[0] = p; dst[1] = v; dst[2] = w; dst[3] = a;
   dst[4] = make_float4(d, pr, __uint_as_float(key), 0.f);
   ids_out[i] = ids[i] & ~kGhostBit;
-}
-
-// grid_index of every local particle: kernels/grid.cl:40-64 with the GLOBAL grid origin
-__global__ void __launch_bounds__(kBlock)
-    k_slab_ckey(const float4* __restrict__ pos, uint32_t n, float gminx, float gminy, float gminz,
-                float cell, uint32_t* __restrict__ ckey) {
-  const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
-  if (i >= n) return;
-  const float4 q = __ldg(pos + i);
-  ckey[i] = morton3((uint32_t)((q.x - gminx) / cell), (uint32_t)((q.y - gminy) / cell),
-                    (uint32_t)((q.z - gminz) / cell));
 }
 
 // local reduction cell (order-preserving encodings) -> floats the ranks can all-reduce with
@@ -220,14 +204,16 @@ int launch_slab_unpack(const void* msg, uint32_t count, uint32_t offset, float4*
   return 1;
 }
 
-int launch_slab_compact(const float4* pos, const float4* vel, const float4* vhf, const uint32_t* ids,
-                        uint32_t n, float4* pos_out, float4* vel_out, float4* vhf_out, uint32_t* ids_out,
-                        uint32_t* src_of, uint32_t* n_owned_out, cudaStream_t s) {
-  cudaMemsetAsync(n_owned_out, 0, sizeof(uint32_t), s);
-  if (n == 0) return 0;
-  k_slab_compact<<<blocks_for(n), kBlock, 0, s>>>(pos, vel, vhf, ids, n, pos_out, vel_out, vhf_out, ids_out,
-                                                 src_of, n_owned_out);
-  return 1;
+int launch_slab_owned_scan(const uint32_t* ids, uint32_t n, uint32_t* dst, uint32_t* scan_scratch,
+                           uint32_t* n_owned_out, cudaStream_t s) {
+  if (n == 0) {
+    cudaMemsetAsync(n_owned_out, 0, sizeof(uint32_t), s);
+    return 0;
+  }
+  k_slab_owned_flags<<<blocks_for(n), kBlock, 0, s>>>(ids, n, dst);
+  int l = 1 + launch_exclusive_sum(dst, n, scan_scratch, s);
+  k_slab_owned_count<<<1, 32, 0, s>>>(ids, dst, n, n_owned_out);
+  return l + 1;
 }
 
 int launch_slab_to_aos(sphb_particle* aos, uint32_t* ids_out, const uint32_t* n_owned_dev, uint32_t n_upper,
@@ -237,13 +223,6 @@ int launch_slab_to_aos(sphb_particle* aos, uint32_t* ids_out, const uint32_t* n_
   if (n_upper == 0) return 0;
   k_slab_to_aos<<<blocks_for(n_upper), kBlock, 0, s>>>(aos, ids_out, n_owned_dev, pos, vel, vhf, ids, src_of,
                                                       acc, rho, prs, ckey);
-  return 1;
-}
-
-int launch_slab_ckey(const float4* pos, uint32_t n, const float gmin[3], float cell, uint32_t* ckey,
-                     cudaStream_t s) {
-  if (n == 0) return 0;
-  k_slab_ckey<<<blocks_for(n), kBlock, 0, s>>>(pos, n, gmin[0], gmin[1], gmin[2], cell, ckey);
   return 1;
 }
 

@@ -190,7 +190,6 @@ int sphb_slab_forces(sphb_engine* e, const float gmin[3], const float gmax[3]) {
                            e->vel[out], e->vhf[out], e->rank_prev, s);
     std::swap(e->rank_cur, e->rank_prev);  // ids (+ ghost bit) now in compute order
     e->cur = out;
-    l += launch_slab_ckey(e->pos[out], n, P.min_point.s, c.cell, e->ckey, s);
     t.done(l);
   }
   {
@@ -203,6 +202,8 @@ int sphb_slab_forces(sphb_engine* e, const float gmin[3], const float gmax[3]) {
     t.done(launch_forces(e->pos[e->cur], e->vel[e->cur], skeys, e->ftable, e->rho, e->nlist,
                          e->ncount, e->acc, c, 0, s, e->rank_cur));
   }
+  // every owned particle's dense slot in the advected arrays (ghosts are dropped there)
+  e->launches += launch_slab_owned_scan(e->rank_cur, n, e->free_keys, e->scan_scratch, e->n_owned_dev, s);
   CUDA_TRY(e, cudaGetLastError());
   e->slab_in = e->cur;
   e->stepped = true;
@@ -223,9 +224,19 @@ int sphb_slab_advect(sphb_engine* e, float dt, float* out8_dev) {
   {
     PassTimer t(e, SPHB_PASS_ADVECT);
     int l = launch_reduce_init(e->red, s);
-    if (e->n)
+    if (e->n) {
+      SlabAdvect sa;
+      sa.ids = e->rank_cur;
+      sa.dst = e->free_keys;
+      sa.ids_out = e->rank_prev;
+      sa.src_of = e->src_of;
+      sa.ckey_out = e->ckey;
+      sa.gminx = e->params.min_point.s[0]; sa.gminy = e->params.min_point.s[1];
+      sa.gminz = e->params.min_point.s[2];
+      sa.cell = e->params.h * 2;
       l += launch_advect(e->pos[in], e->vhf[in], e->acc, e->pos[out], e->vel[out], e->vhf[out], e->n, dt,
-                         e->params.restitution, e->faces, e->face_count, e->df, e->red, s, e->rank_cur, &e->bin);
+                         e->params.restitution, e->faces, e->face_count, e->df, e->red, s, &sa, &e->bin);
+    }
     l += launch_slab_reduce_floats(e->red, out8_dev, s);
     t.done(l);
   }
@@ -238,12 +249,11 @@ int sphb_slab_commit(sphb_engine* e) {
   CUDA_TRY(e, cudaSetDevice(e->device));
   cudaStream_t s = e->stream;
   const int in = e->slab_in, out = in ^ 1;
-  // advected state (out) -> compacted owned particles (in); ids: rank_cur -> rank_prev
-  e->launches += launch_slab_compact(e->pos[out], e->vel[out], e->vhf[out], e->rank_cur, e->n, e->pos[in],
-                                     e->vel[in], e->vhf[in], e->rank_prev, e->src_of, e->n_owned_dev, s);
-  CUDA_TRY(e, cudaGetLastError());
+  // the advection pass already wrote the owned particles densely into the `out` half (ids into
+  // rank_prev): committing is a pointer swap
+  (void)in;
   std::swap(e->rank_cur, e->rank_prev);
-  e->cur = in;
+  e->cur = out;
   if (e->profile) {  // the accepted advection attempt
     CUDA_TRY(e, cudaStreamSynchronize(s));
     accumulate_pass(e, SPHB_PASS_ADVECT);
