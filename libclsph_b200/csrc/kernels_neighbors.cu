@@ -289,15 +289,31 @@ __global__ void __launch_bounds__(kBlock)
         row_range(ftable, c, fx, fy, fz, f, dy, dz, s, e);
         row_start[row][threadIdx.x] = s;
       }
-    for (uint32_t k = 0; k < cnt; ++k) {
-      const uint32_t code = nlist[(size_t)k * c.n + i];
-      const uint32_t j = row_start[code >> 12][threadIdx.x] + (code & 4095u);
-      if (j == i) continue;  // the list holds the particle itself
-      const float4 pj = __ldg(pos + j);
-      const float4 vj = __ldg(vel + j);
-      const float dx = pi.x - pj.x, dy_ = pi.y - pj.y, dz_ = pi.z - pj.z;
-      const float r2 = dx * dx + dy_ * dy_ + dz_ * dz_;
-      force_pair(A, pi, vi, pj, vj, dx, dy_, dz_, r2, c);
+    // four neighbours per trip: their codes, then their eight float4 loads, are issued together
+    // (each is a dependent chain code -> row start -> position / velocity -> ~45 flops)
+    const uint16_t* mine = nlist + i;
+    for (uint32_t k = 0; k < cnt; k += 4) {
+      uint32_t j[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const bool live = k + u < cnt;
+        const uint32_t code = live ? mine[(size_t)(k + u) * c.n] : 0u;
+        // a dead slot points at the particle itself, which is skipped like its own list entry
+        j[u] = live ? row_start[code >> 12][threadIdx.x] + (code & 4095u) : i;
+      }
+      float4 pj[4], vj[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        pj[u] = __ldg(pos + j[u]);
+        vj[u] = __ldg(vel + j[u]);
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        if (j[u] == i) continue;  // the list holds the particle itself
+        const float dx = pi.x - pj[u].x, dy_ = pi.y - pj[u].y, dz_ = pi.z - pj[u].z;
+        const float r2 = dx * dx + dy_ * dy_ + dz_ * dz_;
+        force_pair(A, pi, vi, pj[u], vj[u], dx, dy_, dz_, r2, c);
+      }
     }
   } else {  // the list overflowed: search again
 #pragma unroll 1
