@@ -338,9 +338,15 @@ def main():
     ms_step = r["ms_total"] / args.steps
     value = n * args.steps / (r["ms_total"] * 1e-3)
     peak, peak_src = measured_peak()
-    # dominant kernel: the forces pass (one launch per step)
-    f_ms = r["pass_ms"]["forces"] / max(1, r["pass_launches"]["forces"])
-    achieved = ALGO_BYTES["forces"] * n / (f_ms * 1e-3) / 1e9
+    # dominant kernel: whichever of the two neighbour passes takes longer (one launch per step each)
+    dom = max(("density", "forces"), key=lambda k: r["pass_ms"][k])
+    f_ms = r["pass_ms"][dom] / max(1, r["pass_launches"][dom])
+    achieved = ALGO_BYTES[dom] * n / (f_ms * 1e-3) / 1e9
+    traffic = None
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))[dom].get(str(n))
+    except Exception:
+        pass
     radix_passes = (max(1, r["grid_cell_count"].bit_length()) + 7) // 8
     step_bytes = STEP_BYTES_FUSED.get(radix_passes, 301)
     per_pass = {}
@@ -357,9 +363,12 @@ def main():
                     radix_passes=radix_passes, l2="inputs exceed L2 (positions alone are %d MB)" % (16 * n >> 20),
                     parallelism="1 GPU", secondary=secondary),
         clocks=r["clocks"], gpu_launches=r["launches"],
-        roofline=dict(bound="hbm", kernel="forces pass (k_forces_*)", achieved=achieved, peak=peak, unit="GB/s",
-                      frac=achieved / peak, traffic=None, peak_source=peak_src,
-                      algorithmic_bytes_per_particle=ALGO_BYTES["forces"], launch_ms=f_ms,
+        roofline=dict(bound="hbm", kernel={"density": "density + pressure pass (k_density_list)",
+                                           "forces": "forces pass (k_forces_nlist)"}[dom],
+                      achieved=achieved, peak=peak, unit="GB/s", frac=achieved / peak, traffic=traffic,
+                      peak_source=peak_src, algorithmic_bytes_per_particle=ALGO_BYTES[dom], launch_ms=f_ms,
+                      note="both neighbour passes are L1/issue-bound, not HBM-bound (DESIGN.md section 3); "
+                           "traffic = ncu dram bytes per launch, mostly the neighbour list handed to the forces pass",
                       whole_step=dict(algorithmic_bytes_per_particle=step_bytes,
                                       achieved=step_bytes * n / (ms_step * 1e-3) / 1e9,
                                       frac=step_bytes * n / (ms_step * 1e-3) / 1e9 / peak)),
