@@ -237,7 +237,14 @@ __global__ void __launch_bounds__(kBlock)
     for (uint32_t dy = 0; dy < 2; ++dy) {
       const uint32_t row = ((z0 + dz) * c.fny + (y0 + dy)) * c.fnx + x0;
       const uint32_t s = __ldg(ftable + row), e = __ldg(ftable + row + 2);
-      for (uint32_t j = s; j < e; ++j) before += (__ldg(rank_prev + j) < mine) ? 1u : 0u;
+      // four independent loads in flight; slots past the run re-read its last element
+      for (uint32_t j = s; j < e; j += 4) {
+        const uint32_t last = e - 1;
+        const uint32_t r0 = __ldg(rank_prev + j), r1 = __ldg(rank_prev + min(j + 1, last)),
+                       r2 = __ldg(rank_prev + min(j + 2, last)), r3 = __ldg(rank_prev + min(j + 3, last));
+        before += (r0 < mine ? 1u : 0u) + ((j + 1 < e && r1 < mine) ? 1u : 0u) +
+                  ((j + 2 < e && r2 < mine) ? 1u : 0u) + ((j + 3 < e && r3 < mine) ? 1u : 0u);
+      }
     }
   rank_new[i] = (m < c.grid_cell_count ? __ldg(ref_table + m) : 0u) + before;
 }
