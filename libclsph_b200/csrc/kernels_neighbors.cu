@@ -62,93 +62,196 @@ __device__ __forceinline__ CellFrac cell_frac(const float4& p, uint32_t fx, uint
   return f;
 }
 
-// First / one-past-last particle of the x-run of row (fy + dy, fz + dz) that can hold a
-// neighbour of a particle at `f` inside cell (fx, fy, fz): a neighbouring cell is visited only
-// if its nearest point is closer than h.  An empty range when nothing in the row can be.
+// Which cells of the x-run of row (fy + dy, fz + dz) can hold a neighbour of a particle at `f`
+// inside cell (fx, fy, fz): a neighbouring cell is visited only if its nearest point is closer
+// than h.  `on` = the row's own-x cell is reachable; left / right = the cells beside it are.
 constexpr float kReach2 = 1.0f + 1.0e-3f;  // (h * (1 + slack))^2 in units of h^2
+struct Reach {
+  bool on, left, right;
+};
+__device__ __forceinline__ Reach row_reach(const StepConsts& c, uint32_t fx, const CellFrac& f, int dy,
+                                           int dz) {
+  const float gy = dy < 0 ? f.lo[1] : (dy > 0 ? f.hi[1] : 0.f);
+  const float gz = dz < 0 ? f.lo[2] : (dz > 0 ? f.hi[2] : 0.f);
+  const float q = gy * gy + gz * gz;
+  Reach r;
+  r.on = q < kReach2;
+  r.left = r.on && fx > 0 && q + f.lo[0] * f.lo[0] < kReach2;
+  r.right = r.on && fx + 1 < c.fnx && q + f.hi[0] * f.hi[0] < kReach2;
+  return r;
+}
+
+// First / one-past-last particle of that run; an empty range when nothing in the row can be.
 __device__ __forceinline__ void row_range(const uint32_t* __restrict__ ftable, const StepConsts& c,
                                           uint32_t fx, uint32_t fy, uint32_t fz, const CellFrac& f,
                                           int dy, int dz, uint32_t& s, uint32_t& e) {
   s = e = 0;
   const uint32_t y = fy + dy, z = fz + dz;  // wraps to a huge value below 0
   if (y >= c.fny || z >= c.fnz) return;
-  const float gy = dy < 0 ? f.lo[1] : (dy > 0 ? f.hi[1] : 0.f);
-  const float gz = dz < 0 ? f.lo[2] : (dz > 0 ? f.hi[2] : 0.f);
-  const float q = gy * gy + gz * gz;
-  if (q >= kReach2) return;
-  const bool left = fx > 0 && q + f.lo[0] * f.lo[0] < kReach2;
-  const bool right = fx + 1 < c.fnx && q + f.hi[0] * f.hi[0] < kReach2;
+  const Reach r = row_reach(c, fx, f, dy, dz);
+  if (!r.on) return;
   const uint32_t row = (z * c.fny + y) * c.fnx + fx;
-  s = __ldg(ftable + row - (left ? 1u : 0u));
-  e = __ldg(ftable + row + (right ? 2u : 1u));
+  s = __ldg(ftable + row - (r.left ? 1u : 0u));
+  e = __ldg(ftable + row + (r.right ? 2u : 1u));
 }
 
-// ---- density + pressure: one thread per particle walking the 9 rows -----------------------
+// ---- density + pressure: one thread per PAIR of consecutive particles, walking the 9 rows ----
+// Two particles that are neighbours in the sorted array sit in the same or in x-adjacent cells
+// four times out of five, so their candidate runs coincide: one thread tests every candidate
+// against both, which halves the 16-byte candidate loads (the pass is bound by L1 wavefronts
+// and issue slots, not by HBM).  A pair that is NOT in the same row / adjacent cells is walked
+// in two passes, one particle at a time (the idle one is given a NaN position, which fails
+// every distance test).
+//
 // Besides the density sum, the pass RECORDS which candidates were inside h, so that the forces
 // pass does not have to search again: a neighbour is stored as a 16-bit code
-// (row 0..8) << 12 | (offset of the neighbour inside that row's run), staged per thread in
-// shared memory and flushed k-major (nlist[k * n + i]) so that the stores — and the forces
-// pass's loads — are coalesced across the warp.  count 255 = "list unusable" (more than
-// kListCap neighbours, or a row run longer than 4096): the forces pass then searches itself.
+// (row 0..8) << 12 | (offset of the neighbour inside the run that was walked for that row),
+// staged per particle in a shared-memory column and flushed k-major (nlist[k * n + i]) so that
+// the stores — and the forces pass's loads — are coalesced across the warp.  Where the walked
+// run began is recorded as 2 bits per row (nback: own cell x + 1 - first cell x).  count 255 =
+// "list unusable" (more than kListCap neighbours, or a run longer than 4096): the forces pass
+// then searches itself.
 constexpr int kListCap = 64;
 constexpr uint32_t kListOverflow = 255;
+constexpr int kPairBlock = 64;                  // threads per CTA; 2 particles each
+constexpr int kPairCols = 2 * kPairBlock;       // shared-memory columns (one per particle)
+constexpr int kDumpRows = 4;                    // rows past the capacity that absorb a group's hits
+constexpr uint32_t kColStride = 2u * kPairCols; // bytes between two entries of a column
 
-__global__ void __launch_bounds__(kBlock)
-    k_density_list(float4* pos, float4* vel, const uint32_t* __restrict__ keys,
+__device__ __forceinline__ uint32_t* nback_of(const uint16_t* nlist, uint32_t n) {
+  return reinterpret_cast<uint32_t*>(const_cast<uint16_t*>(nlist) + (size_t)kListCap * n);
+}
+
+// one candidate against one particle: clamped cubic term, predicated store of the code
+__device__ __forceinline__ void density_test(const float4& q, const float4& pj, float h2, float& sum,
+                                             uint32_t& cursor, uint32_t code) {
+  const float dx = q.x - pj.x, dy = q.y - pj.y, dz = q.z - pj.z;
+  const float t = fmaf(-dz, dz, fmaf(-dy, dy, fmaf(-dx, dx, h2)));
+  const float t2 = t * t;
+  // one predicate drives the cubic term, the store and the cursor (NaN compares false)
+  asm volatile(
+      "{ .reg .pred p; setp.gt.f32 p, %3, 0f00000000;\n"
+      "  @p fma.rn.f32 %0, %4, %3, %0;\n"
+      "  @p st.shared.u16 [%1], %2;\n"
+      "  @p add.u32 %1, %1, %5; }"
+      : "+f"(sum), "+r"(cursor)
+      : "h"((uint16_t)code), "f"(t), "f"(t2), "n"(kColStride)
+      : "memory");
+}
+
+__global__ void __launch_bounds__(kPairBlock)
+    k_density_pair(float4* pos, float4* vel, const uint32_t* __restrict__ keys,
                    const uint32_t* __restrict__ ftable, float* __restrict__ rho,
                    float* __restrict__ prs, uint16_t* __restrict__ nlist,
                    uint8_t* __restrict__ ncount, StepConsts c) {
-  // one column per thread; row kListCap is a dump row that absorbs writes past the capacity
-  __shared__ uint16_t hit[(kListCap + 1) * kBlock];
-  const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
-  if (i >= c.n) return;
-  const float4 pi = pos[i];
-  uint32_t fx, fy, fz;
-  fine_coords_of(__ldg(keys + i), c, fx, fy, fz);
-  const CellFrac f = cell_frac(pi, fx, fy, fz, c);
-  float sum = 0.f;
-  // The inner loop is branch-free: the cubic term is clamped instead of skipped, and a hit
-  // (the particle itself included — the forces pass skips it) is recorded with a predicated
-  // store at a cursor that advances only on hits.
-  // (shared-window byte addresses, so that the store is one predicated STS)
-  const uint32_t hit_base = (uint32_t)__cvta_generic_to_shared(hit) + 2u * threadIdx.x;
-  uint32_t cursor = hit_base;
-  const uint32_t cursor_end = hit_base + 2u * kListCap * kBlock;
+  __shared__ uint16_t hit[(kListCap + kDumpRows) * kPairCols];
+  const uint32_t ia = 2u * (blockIdx.x * kPairBlock + threadIdx.x);
+  if (ia >= c.n) return;
+  const bool has_b = ia + 1 < c.n;
+  const uint32_t ib = has_b ? ia + 1 : ia;
+  const float4 pa = pos[ia], pb = pos[ib];
+  uint32_t fxa, fya, fza, fxb, fyb, fzb;
+  fine_coords_of(__ldg(keys + ia), c, fxa, fya, fza);
+  fine_coords_of(__ldg(keys + ib), c, fxb, fyb, fzb);
+  const CellFrac fa = cell_frac(pa, fxa, fya, fza, c), fb = cell_frac(pb, fxb, fyb, fzb, c);
+  // sorted by row-major cell: inside a row, b's cell is never left of a's
+  const bool together = has_b && fya == fyb && fza == fzb && fxb - fxa <= 1u;
+  const int npass = (has_b && !together) ? 2 : 1;
+  const float nan = __int_as_float(0x7fc00000);
+  const float4 nowhere = make_float4(nan, nan, nan, 0.f);
+
+  // (shared-window byte addresses, so that a store is one predicated STS)
+  const uint32_t base_a = (uint32_t)__cvta_generic_to_shared(hit) + 4u * threadIdx.x, base_b = base_a + 2u;
+  const uint32_t end_a = base_a + kListCap * kColStride, end_b = base_b + kListCap * kColStride;
+  uint32_t cur_a = base_a, cur_b = base_b, back_a = 0, back_b = 0;
+  float sum_a = 0.f, sum_b = 0.f;
   bool overflow = false;
-  uint32_t tag = 0;
+  const float4* cand = reinterpret_cast<const float4*>(pos);
 #pragma unroll 1
-  for (int dz = -1; dz <= 1; ++dz)
+  for (int pass = 0; pass < npass; ++pass) {
+    const bool la = pass == 0, lb = together || pass == 1;
+    const float4 qa = la ? pa : nowhere, qb = lb ? pb : nowhere;
+    const uint32_t ry = la ? fya : fyb, rz = la ? fza : fzb;
+    uint32_t tag = 0, shift = 0;
 #pragma unroll 1
-    for (int dy = -1; dy <= 1; ++dy, tag += 4096u) {
-      uint32_t s, e;
-      row_range(ftable, c, fx, fy, fz, f, dy, dz, s, e);
-      if (e - s > 4096u) overflow = true;
-      uint32_t code = tag;
-#pragma unroll 4
-      for (uint32_t j = s; j < e; ++j, ++code) {
-        const float4 pj = __ldg(reinterpret_cast<const float4*>(pos) + j);
-        const float dx = pi.x - pj.x, dy_ = pi.y - pj.y, dz_ = pi.z - pj.z;
-        const float t = c.h2 - (dx * dx + dy_ * dy_ + dz_ * dz_);
-        const bool inside = t > 0.f;
-        const float tt = fmaxf(t, 0.f);
-        sum = fmaf(tt * tt, tt, sum);
-        asm volatile("{ .reg .pred p; setp.ne.u32 p, %2, 0; @p st.shared.u16 [%0], %1; }"
-                     :: "r"(cursor), "h"((uint16_t)code), "r"((uint32_t)inside) : "memory");
-        cursor = min(cursor + (inside ? 2u * kBlock : 0u), cursor_end);
+    for (int dz = -1; dz <= 1; ++dz, tag += 3u * 4096u, shift += 6u) {
+      const uint32_t z = rz + dz;  // wraps to a huge value below 0
+      if (z >= c.fnz) continue;
+      // the three rows of this plane are planned together, so that their six table loads
+      // are in flight at once (one load latency per plane, not one per row)
+      uint32_t rs[3], re[3];
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        const int dy = k - 1;
+        const uint32_t y = ry + dy;
+        const Reach A = row_reach(c, fxa, fa, dy, dz), B = row_reach(c, fxb, fb, dy, dz);
+        const bool ona = la && A.on, onb = lb && B.on;
+        const uint32_t lo_a = fxa - (A.left ? 1u : 0u), hi_a = fxa + (A.right ? 2u : 1u);
+        const uint32_t lo_b = fxb - (B.left ? 1u : 0u), hi_b = fxb + (B.right ? 2u : 1u);
+        const uint32_t x_lo = ona ? (onb ? min(lo_a, lo_b) : lo_a) : lo_b;
+        const uint32_t x_hi = ona ? (onb ? max(hi_a, hi_b) : hi_a) : hi_b;
+        rs[k] = re[k] = 0;
+        if (y < c.fny && (ona || onb)) {
+          const uint32_t rowbase = (z * c.fny + y) * c.fnx;
+          rs[k] = __ldg(ftable + rowbase + x_lo);
+          re[k] = __ldg(ftable + rowbase + x_hi);
+          if (la) back_a |= (fxa + 1u - x_lo) << (shift + 2u * k);
+          if (lb) back_b |= (fxb + 1u - x_lo) << (shift + 2u * k);
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        const uint32_t e = re[k];
+        uint32_t j = rs[k], code = tag + 4096u * k;
+        if (e - j > 4096u) overflow = true;
+        // The loop body is branch-free: the cubic term is clamped instead of skipped, and a hit
+        // (the particle itself included — the forces pass skips it) is recorded with a
+        // predicated store at a cursor that advances only on hits; the cursors are pulled
+        // back into the dump rows once per group of four candidates.
+        for (; j + 4u <= e; j += 4u, code += 4u) {
+          const float4 p0 = __ldg(cand + j), p1 = __ldg(cand + j + 1), p2 = __ldg(cand + j + 2),
+                       p3 = __ldg(cand + j + 3);
+          density_test(qa, p0, c.h2, sum_a, cur_a, code);
+          density_test(qb, p0, c.h2, sum_b, cur_b, code);
+          density_test(qa, p1, c.h2, sum_a, cur_a, code + 1u);
+          density_test(qb, p1, c.h2, sum_b, cur_b, code + 1u);
+          density_test(qa, p2, c.h2, sum_a, cur_a, code + 2u);
+          density_test(qb, p2, c.h2, sum_b, cur_b, code + 2u);
+          density_test(qa, p3, c.h2, sum_a, cur_a, code + 3u);
+          density_test(qb, p3, c.h2, sum_b, cur_b, code + 3u);
+          cur_a = min(cur_a, end_a);
+          cur_b = min(cur_b, end_b);
+        }
+        for (; j < e; ++j, ++code) {
+          const float4 p0 = __ldg(cand + j);
+          density_test(qa, p0, c.h2, sum_a, cur_a, code);
+          density_test(qb, p0, c.h2, sum_b, cur_b, code);
+          cur_a = min(cur_a, end_a);
+          cur_b = min(cur_b, end_b);
+        }
       }
     }
-  const float density = (c.mass * c.c_poly6) * sum;
-  const float pressure = tait_pressure(density, c);
-  rho[i] = density;
-  prs[i] = pressure;
-  // derived per-particle factors for the forces pass (only the w lanes are written)
-  reinterpret_cast<float*>(pos + i)[3] = pressure / (density * density);
-  reinterpret_cast<float*>(vel + i)[3] = c.mass / density;
-  const uint32_t cnt = (cursor - hit_base) / (2u * kBlock);
-  if (cnt >= (uint32_t)kListCap) overflow = true;  // the dump row was reached
-  ncount[i] = overflow ? (uint8_t)kListOverflow : (uint8_t)cnt;
-  if (!overflow)
-    for (uint32_t k = 0; k < cnt; ++k) nlist[(size_t)k * c.n + i] = hit[k * kBlock + threadIdx.x];
+  }
+  uint32_t* const nback = nback_of(nlist, c.n);
+  const uint16_t* col = hit + 2 * threadIdx.x;
+#pragma unroll
+  for (int w = 0; w < 2; ++w) {
+    if (w == 1 && !has_b) break;
+    const uint32_t i = w ? ib : ia;
+    const float density = (c.mass * c.c_poly6) * (w ? sum_b : sum_a);
+    const float pressure = tait_pressure(density, c);
+    rho[i] = density;
+    prs[i] = pressure;
+    // derived per-particle factors for the forces pass (only the w lanes are written)
+    reinterpret_cast<float*>(pos + i)[3] = pressure / (density * density);
+    reinterpret_cast<float*>(vel + i)[3] = c.mass / density;
+    const uint32_t cnt = ((w ? cur_b : cur_a) - (w ? base_b : base_a)) / kColStride;
+    const bool over = overflow || cnt >= (uint32_t)kListCap;  // the dump rows were reached
+    ncount[i] = over ? (uint8_t)kListOverflow : (uint8_t)cnt;
+    nback[i] = w ? back_b : back_a;
+    if (!over)
+      for (uint32_t k = 0; k < cnt; ++k) nlist[(size_t)k * c.n + i] = col[k * kPairCols + w];
+  }
 }
 
 struct ForceAcc {
@@ -276,30 +379,38 @@ __global__ void __launch_bounds__(kBlock)
   const float4 pi = __ldg(pos + i), vi = __ldg(vel + i);
   uint32_t fx, fy, fz;
   fine_coords_of(__ldg(keys + i), c, fx, fy, fz);
-  const CellFrac f = cell_frac(pi, fx, fy, fz, c);
   const uint32_t cnt = ncount[i];
   ForceAcc A = {};
   if (cnt != kListOverflow) {
-    int row = 0;
+    // where the run the density pass walked for each row began: 2 bits per row
+    uint32_t back = __ldg(nback_of(nlist, c.n) + i);
 #pragma unroll
     for (int dz = -1; dz <= 1; ++dz)
 #pragma unroll
-      for (int dy = -1; dy <= 1; ++dy, ++row) {
-        uint32_t s, e;
-        row_range(ftable, c, fx, fy, fz, f, dy, dz, s, e);
-        row_start[row][threadIdx.x] = s;
+      for (int dy = -1; dy <= 1; ++dy, back >>= 2) {
+        const uint32_t y = fy + dy, z = fz + dz;
+        uint32_t s = 0;
+        if (y < c.fny && z < c.fnz) s = __ldg(ftable + ((z * c.fny + y) * c.fnx + fx + 1u - (back & 3u)));
+        row_start[(dz + 1) * 3 + (dy + 1)][threadIdx.x] = s;
       }
     // four neighbours per trip: their codes, then their eight float4 loads, are issued together
     // (each is a dependent chain code -> row start -> position / velocity -> ~45 flops)
     const uint16_t* mine = nlist + i;
+    uint32_t code[4], next[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) next[u] = (uint32_t)u < cnt ? mine[(size_t)u * c.n] : 0u;
     for (uint32_t k = 0; k < cnt; k += 4) {
       uint32_t j[4];
+      // the next trip's codes are requested before this trip's gathers are
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
-        const bool live = k + u < cnt;
-        const uint32_t code = live ? mine[(size_t)(k + u) * c.n] : 0u;
+        code[u] = next[u];
+        next[u] = k + 4 + u < cnt ? mine[(size_t)(k + 4 + u) * c.n] : 0u;
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
         // a dead slot points at the particle itself, which is skipped like its own list entry
-        j[u] = live ? row_start[code >> 12][threadIdx.x] + (code & 4095u) : i;
+        j[u] = k + u < cnt ? row_start[code[u] >> 12][threadIdx.x] + (code[u] & 4095u) : i;
       }
       float4 pj[4], vj[4];
 #pragma unroll
@@ -316,6 +427,7 @@ __global__ void __launch_bounds__(kBlock)
       }
     }
   } else {  // the list overflowed: search again
+    const CellFrac f = cell_frac(pi, fx, fy, fz, c);
 #pragma unroll 1
     for (int dz = -1; dz <= 1; ++dz)
 #pragma unroll 1
@@ -337,13 +449,16 @@ inline unsigned blocks_for(uint32_t n) { return (n + kBlock - 1) / kBlock; }
 
 }  // namespace
 
-size_t neighbor_list_entries(uint32_t n) { return (size_t)kListCap * n; }
+// kListCap codes per particle + one 32-bit nback word (stored behind the codes)
+size_t neighbor_list_entries(uint32_t n) { return (size_t)(kListCap + 2) * n; }
 
 int launch_density(float4* pos, float4* vel, const uint32_t* keys, const uint32_t* ftable,
                    float* rho, float* prs, uint16_t* nlist, uint8_t* ncount, const StepConsts& c,
                    int variant, cudaStream_t s) {
   (void)variant;  // the list is recorded either way; variant 1 just does not use it
-  k_density_list<<<blocks_for(c.n), kBlock, 0, s>>>(pos, vel, keys, ftable, rho, prs, nlist, ncount, c);
+  const unsigned pairs = (c.n + 1u) / 2u;
+  k_density_pair<<<(pairs + kPairBlock - 1) / kPairBlock, kPairBlock, 0, s>>>(pos, vel, keys, ftable, rho, prs,
+                                                                             nlist, ncount, c);
   return 1;
 }
 
