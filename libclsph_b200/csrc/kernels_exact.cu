@@ -219,34 +219,56 @@ __global__ void __launch_bounds__(kBlock)
   if (valid && lane == __ffs(peers) - 1 && m < c.grid_cell_count) atomicAdd(hist + m, __popc(peers));
 }
 
+// One thread per PAIR of consecutive particles: they share their Morton cell nine times out of
+// ten, and then every previous rank that is loaded serves two comparisons.  A pair that straddles
+// two cells is walked twice, one particle at a time.
 __global__ void __launch_bounds__(kBlock)
     k_reference_rank(const uint32_t* __restrict__ fine_keys, const uint32_t* __restrict__ ftable,
                      const uint32_t* __restrict__ rank_prev, const uint32_t* __restrict__ ref_table,
                      uint32_t* __restrict__ rank_new, StepConsts c) {
-  const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
-  if (i >= c.n) return;
-  uint32_t fx, fy, fz;
-  fine_coords_of(__ldg(fine_keys + i), c, fx, fy, fz);
-  const uint32_t m = morton3(fx >> 1, fy >> 1, fz >> 1);
-  const uint32_t mine = __ldg(rank_prev + i);
-  const uint32_t x0 = fx & ~1u, y0 = fy & ~1u, z0 = fz & ~1u;
-  uint32_t before = 0;
+  const uint32_t ia = 2u * (blockIdx.x * kBlock + threadIdx.x);
+  if (ia >= c.n) return;
+  const bool has_b = ia + 1 < c.n;
+  const uint32_t ib = has_b ? ia + 1 : ia;
+  uint32_t fx[2], fy[2], fz[2], m[2];
+  fine_coords_of(__ldg(fine_keys + ia), c, fx[0], fy[0], fz[0]);
+  fine_coords_of(__ldg(fine_keys + ib), c, fx[1], fy[1], fz[1]);
 #pragma unroll
-  for (uint32_t dz = 0; dz < 2; ++dz)
+  for (int w = 0; w < 2; ++w) m[w] = morton3(fx[w] >> 1, fy[w] >> 1, fz[w] >> 1);
+  const uint32_t mine_a = __ldg(rank_prev + ia), mine_b = __ldg(rank_prev + ib);
+  const bool together = has_b && m[0] == m[1];
+  const int npass = (has_b && !together) ? 2 : 1;
+  uint32_t before_a = 0, before_b = 0;
+#pragma unroll 1
+  for (int pass = 0; pass < npass; ++pass) {
+    // a particle that sits out a pass compares against 0: nothing is smaller
+    const uint32_t qa = pass == 0 ? mine_a : 0u, qb = (together || pass == 1) ? mine_b : 0u;
+    const uint32_t x0 = fx[pass] & ~1u, y0 = fy[pass] & ~1u, z0 = fz[pass] & ~1u;
+    uint32_t rs[4], re[4];
 #pragma unroll
-    for (uint32_t dy = 0; dy < 2; ++dy) {
-      const uint32_t row = ((z0 + dz) * c.fny + (y0 + dy)) * c.fnx + x0;
-      const uint32_t s = __ldg(ftable + row), e = __ldg(ftable + row + 2);
-      // four independent loads in flight; slots past the run re-read its last element
-      for (uint32_t j = s; j < e; j += 4) {
+    for (uint32_t k = 0; k < 4; ++k) {
+      const uint32_t row = ((z0 + (k >> 1)) * c.fny + (y0 + (k & 1u))) * c.fnx + x0;
+      rs[k] = __ldg(ftable + row);
+      re[k] = __ldg(ftable + row + 2);
+    }
+#pragma unroll
+    for (uint32_t k = 0; k < 4; ++k) {
+      const uint32_t e = re[k];
+      // four independent loads in flight; a slot past the run reads its last element as "huge"
+      for (uint32_t j = rs[k]; j < e; j += 4) {
         const uint32_t last = e - 1;
-        const uint32_t r0 = __ldg(rank_prev + j), r1 = __ldg(rank_prev + min(j + 1, last)),
-                       r2 = __ldg(rank_prev + min(j + 2, last)), r3 = __ldg(rank_prev + min(j + 3, last));
-        before += (r0 < mine ? 1u : 0u) + ((j + 1 < e && r1 < mine) ? 1u : 0u) +
-                  ((j + 2 < e && r2 < mine) ? 1u : 0u) + ((j + 3 < e && r3 < mine) ? 1u : 0u);
+#pragma unroll
+        for (uint32_t u = 0; u < 4; ++u) {
+          uint32_t r = __ldg(rank_prev + min(j + u, last));
+          if (j + u > last) r = 0xFFFFFFFFu;
+          before_a += r < qa ? 1u : 0u;
+          before_b += r < qb ? 1u : 0u;
+        }
       }
     }
-  rank_new[i] = (m < c.grid_cell_count ? __ldg(ref_table + m) : 0u) + before;
+  }
+  rank_new[ia] = (m[0] < c.grid_cell_count ? __ldg(ref_table + m[0]) : 0u) + before_a;
+  if (has_b) rank_new[ib] = (m[1] < c.grid_cell_count ? __ldg(ref_table + m[1]) : 0u) + before_b;
 }
 
 __global__ void __launch_bounds__(kBlock)
@@ -558,7 +580,7 @@ int launch_reference_rank(const uint32_t* fine_keys, const uint32_t* ftable, con
   cudaMemsetAsync(ref_table, 0, sizeof(uint32_t) * ((size_t)c.grid_cell_count + 1), s);
   k_morton_hist<<<blocks_for(c.n), kBlock, 0, s>>>(fine_keys, ref_table, ckey, c);
   int l = 1 + launch_exclusive_sum(ref_table, c.grid_cell_count + 1, scratch, s);
-  k_reference_rank<<<blocks_for(c.n), kBlock, 0, s>>>(fine_keys, ftable, rank_prev, ref_table, rank_new, c);
+  k_reference_rank<<<blocks_for((c.n + 1u) / 2u), kBlock, 0, s>>>(fine_keys, ftable, rank_prev, ref_table, rank_new, c);
   return l + 1;
 }
 

@@ -234,6 +234,8 @@ __global__ void __launch_bounds__(kPairBlock)
   }
   uint32_t* const nback = nback_of(nlist, c.n);
   const uint16_t* col = hit + 2 * threadIdx.x;
+  uint32_t cnt2[2];
+  bool over2[2];
 #pragma unroll
   for (int w = 0; w < 2; ++w) {
     if (w == 1 && !has_b) break;
@@ -245,12 +247,25 @@ __global__ void __launch_bounds__(kPairBlock)
     // derived per-particle factors for the forces pass (only the w lanes are written)
     reinterpret_cast<float*>(pos + i)[3] = pressure / (density * density);
     reinterpret_cast<float*>(vel + i)[3] = c.mass / density;
-    const uint32_t cnt = ((w ? cur_b : cur_a) - (w ? base_b : base_a)) / kColStride;
-    const bool over = overflow || cnt >= (uint32_t)kListCap;  // the dump rows were reached
-    ncount[i] = over ? (uint8_t)kListOverflow : (uint8_t)cnt;
+    cnt2[w] = ((w ? cur_b : cur_a) - (w ? base_b : base_a)) / kColStride;
+    over2[w] = overflow || cnt2[w] >= (uint32_t)kListCap;  // the dump rows were reached
+    ncount[i] = over2[w] ? (uint8_t)kListOverflow : (uint8_t)cnt2[w];
     nback[i] = w ? back_b : back_a;
-    if (!over)
-      for (uint32_t k = 0; k < cnt; ++k) nlist[(size_t)k * c.n + i] = col[k * kPairCols + w];
+  }
+  if (has_b && !over2[0] && !over2[1] && (c.n & 1u) == 0u) {
+    // both columns of the thread leave as one aligned 32-bit store per entry (entries past the
+    // shorter list's count are never read)
+    const uint32_t m = max(cnt2[0], cnt2[1]);
+    const uint32_t* col32 = reinterpret_cast<const uint32_t*>(col);
+    uint32_t* out = reinterpret_cast<uint32_t*>(nlist + ia);
+    for (uint32_t k = 0; k < m; ++k) out[(size_t)k * (c.n / 2u)] = col32[k * (kPairCols / 2)];
+  } else {
+#pragma unroll
+    for (int w = 0; w < 2; ++w) {
+      if ((w == 1 && !has_b) || over2[w]) continue;
+      const uint32_t i = w ? ib : ia;
+      for (uint32_t k = 0; k < cnt2[w]; ++k) nlist[(size_t)k * c.n + i] = col[k * kPairCols + w];
+    }
   }
 }
 
