@@ -116,6 +116,15 @@ int sphb_get_parameters(sphb_engine* e, sphb_params* out);
  * reference would hold.  Padding lanes are written as 0. */
 int sphb_download(sphb_engine* e, sphb_particle* aos);
 
+/* The same read-back, split so that the device -> host copy overlaps later steps (SURVEY 8(f)-1;
+ * the reference blocks in enqueueReadBuffer, sph_simulation.cpp:396-404): _begin snapshots the
+ * state on the device and starts the copy on the engine's copy stream; `aos` (page-locked for
+ * a truly asynchronous copy) is complete when _wait returns.  sphb_step may be called in
+ * between; the next _begin / sphb_upload waits for a copy still in flight.  _wait may be
+ * called from another host thread. */
+int sphb_download_begin(sphb_engine* e, sphb_particle* aos);
+int sphb_download_wait(sphb_engine* e);
+
 /* Parity hooks for the last step (each pointer nullable):
  *   keys[N]   sorted grid_index of every particle,
  *   perm[N]   perm[k] = position BEFORE this step's sort of the particle now at k,

@@ -62,6 +62,9 @@ int sphb_destroy(sphb_engine* e) {
   if (e->ev_fork) cudaEventDestroy(e->ev_fork);
   if (e->ev_join) cudaEventDestroy(e->ev_join);
   if (e->side) cudaStreamDestroy(e->side);
+  if (e->ev_staged) cudaEventDestroy(e->ev_staged);
+  if (e->ev_copied) cudaEventDestroy(e->ev_copied);
+  if (e->copy) cudaStreamDestroy(e->copy);
   if (e->stream) cudaStreamDestroy(e->stream);
   delete e;
   return 0;
@@ -118,6 +121,9 @@ int sphb_create_with_capacity(const sphb_params* params, const sphb_terms* terms
   }
   TRY_OR_DESTROY(cudaEventCreateWithFlags(&e->ev_fork, cudaEventDisableTiming));
   TRY_OR_DESTROY(cudaEventCreateWithFlags(&e->ev_join, cudaEventDisableTiming));
+  TRY_OR_DESTROY(cudaStreamCreateWithFlags(&e->copy, cudaStreamNonBlocking));
+  TRY_OR_DESTROY(cudaEventCreateWithFlags(&e->ev_staged, cudaEventDisableTiming));
+  TRY_OR_DESTROY(cudaEventCreateWithFlags(&e->ev_copied, cudaEventDisableTiming));
   for (int k = 0; k < 2; ++k) {
     TRY_OR_DESTROY(dev_alloc(&e->pos[k], n));
     TRY_OR_DESTROY(dev_alloc(&e->vel[k], n));
@@ -305,6 +311,7 @@ int sphb_upload(sphb_engine* e, const sphb_particle* aos, uint32_t n) {
   if (!e || !aos) return SPHB_ERR_INVALID;
   if (n != e->n) SPHB_FAIL(e, SPHB_ERR_INVALID, "upload of %u particles into an engine of %u", n, e->n);
   CUDA_TRY(e, cudaSetDevice(e->device));
+  if (int rc = sphb_download_wait(e)) return rc;
   if (!e->aos_stage) CUDA_TRY(e, dev_alloc(&e->aos_stage, n));
   CUDA_TRY(e, cudaMemcpyAsync(e->aos_stage, aos, sizeof(sphb_particle) * n, cudaMemcpyHostToDevice,
                               e->stream));
@@ -427,17 +434,39 @@ int sphb_get_parameters(sphb_engine* e, sphb_params* out) {
   return 0;
 }
 
-int sphb_download(sphb_engine* e, sphb_particle* aos) {
+int sphb_download_begin(sphb_engine* e, sphb_particle* aos) {
   if (!e || !aos) return SPHB_ERR_INVALID;
   if (!e->have_state) SPHB_FAIL(e, SPHB_ERR_INVALID, "sphb_download before sphb_upload");
   CUDA_TRY(e, cudaSetDevice(e->device));
+  if (int rc = sphb_download_wait(e)) return rc;  // the stage is reused
   if (!e->aos_stage) CUDA_TRY(e, dev_alloc(&e->aos_stage, e->n));
   e->launches += launch_soa_to_aos(e->aos_stage, e->n, e->pos[e->cur], e->vel[e->cur], e->vhf[e->cur],
                                    e->acc, e->rho, e->prs, e->ckey, e->rank_cur, e->stream);
   CUDA_TRY(e, cudaGetLastError());
+  // the snapshot is complete once the stage is written; the copy then runs beside later steps
+  CUDA_TRY(e, cudaEventRecord(e->ev_staged, e->stream));
+  CUDA_TRY(e, cudaStreamWaitEvent(e->copy, e->ev_staged, 0));
   CUDA_TRY(e, cudaMemcpyAsync(aos, e->aos_stage, sizeof(sphb_particle) * e->n, cudaMemcpyDeviceToHost,
-                              e->stream));
-  CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+                              e->copy));
+  CUDA_TRY(e, cudaEventRecord(e->ev_copied, e->copy));
+  e->download_pending = true;
+  return 0;
+}
+
+// May be called from another host thread than the one that steps the engine (it touches only
+// the event), and any number of times.
+int sphb_download_wait(sphb_engine* e) {
+  if (!e) return SPHB_ERR_INVALID;
+  if (!e->download_pending) return 0;
+  CUDA_TRY(e, cudaSetDevice(e->device));
+  CUDA_TRY(e, cudaEventSynchronize(e->ev_copied));
+  return 0;
+}
+
+int sphb_download(sphb_engine* e, sphb_particle* aos) {
+  if (int rc = sphb_download_begin(e, aos)) return rc;
+  if (int rc = sphb_download_wait(e)) return rc;
+  e->download_pending = false;
   return 0;
 }
 

@@ -18,6 +18,10 @@ struct sphb_engine {
   cudaStream_t stream = nullptr;
   cudaStream_t side = nullptr;  // the reference-order bookkeeping runs beside the neighbour passes
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  // asynchronous read-back (sphb_download_begin / _wait): device -> host copy on its own stream
+  cudaStream_t copy = nullptr;
+  cudaEvent_t ev_staged = nullptr, ev_copied = nullptr;
+  bool download_pending = false;
   uint32_t n = 0;    // particles the kernels run over (slab mode: owned + ghosts of this step)
   uint32_t cap = 0;  // allocated particle slots (== n outside slab mode)
   // slab mode (multi-GPU, slab.cu): this engine owns the particles with x in [xlo, xhi)

@@ -73,7 +73,8 @@ PASS_NAMES = ["bbox", "locate", "sort", "reorder", "celltable", "density", "forc
 # every symbol include/sphb.h declares (tests check the library exports each one)
 SYMBOLS = [
     "sphb_create", "sphb_destroy", "sphb_set_scene", "sphb_get_distance_field", "sphb_upload",
-    "sphb_step", "sphb_get_parameters", "sphb_download", "sphb_download_debug",
+    "sphb_step", "sphb_get_parameters", "sphb_download", "sphb_download_begin", "sphb_download_wait",
+    "sphb_download_debug",
     "sphb_profile_enable", "sphb_profile_reset", "sphb_get_pass_times", "sphb_launch_count",
     "sphb_stream", "sphb_set_option", "sphb_last_error", "sphb_error_string",
     "sphb_host_alloc", "sphb_host_free", "sphb_debug_advect", "sphb_event_record", "sphb_event_elapsed_ms",
@@ -115,6 +116,8 @@ def lib():
         L.sphb_step.argtypes = [vp, f32, C.POINTER(f32)]
         L.sphb_get_parameters.argtypes = [vp, vp]
         L.sphb_download.argtypes = [vp, vp]
+        L.sphb_download_begin.argtypes = [vp, vp]
+        L.sphb_download_wait.argtypes = [vp]
         L.sphb_download_debug.argtypes = [vp, vp, vp, vp, u32, C.POINTER(i32)]
         L.sphb_profile_enable.argtypes = [vp, i32]
         L.sphb_profile_reset.argtypes = [vp]
@@ -236,6 +239,14 @@ class Engine:
 
     def download_ptr(self, ptr):
         self._check(self.L.sphb_download(self.h, C.c_void_p(ptr)))
+
+    def download_begin(self, ptr):
+        """Snapshot the state and start copying it to host address `ptr` (page-locked memory from
+        host_alloc for a copy that overlaps later steps); complete after download_wait()."""
+        self._check(self.L.sphb_download_begin(self.h, C.c_void_p(ptr)))
+
+    def download_wait(self):
+        self._check(self.L.sphb_download_wait(self.h))
 
     def debug(self):
         """dict(keys, perm, cell_table, attempts) of the last step."""

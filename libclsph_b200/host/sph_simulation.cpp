@@ -197,6 +197,30 @@ void sph_simulation::simulate() {
   };
   if (save_frame) spawn_save();
 
+  // Without pre/post hooks nobody but the save thread reads the host array, so the per-frame
+  // read-back need not block the step loop: the state is snapshot on the device,
+  // the copy to the host runs beside the next frame's steps, and the save thread waits for it.
+  const bool async_frames = save_frame && !pre_frame && !post_frame;
+  auto read_and_save = [&]() {
+    savet.join();  // the previous save still reads the host array
+    if (!async_frames) {
+      read_particles(particles);
+      spawn_save();
+      return;
+    }
+    SPHB_CHECK(sphb_download_begin(engine_, reinterpret_cast<sphb_particle*>(particles)));
+    const simulation_parameters snapshot = parameters;
+    sphb_engine* const eng = engine_;
+    savet = std::thread([this, eng, particles, snapshot] {
+      const int rc = sphb_download_wait(eng);
+      if (rc != 0) {
+        std::cerr << "sphb_download_wait: " << sphb_last_error(eng) << std::endl;
+        exit(-1);
+      }
+      save_frame(particles, snapshot);
+    });
+  };
+
   bool stop = false;
   while (time < parameters.simulation_time && !stop) {
     std::cout << "Simulating frame " << currentFrame << " (" << time << "s)" << std::endl;
@@ -214,10 +238,8 @@ void sph_simulation::simulate() {
       if (timeleft < dt) dt = timeleft;
       if (!quiet) std::cout << "temps restant pour la frame :" << timeleft << std::endl;
       if (save_frame && write_intermediate_frames) {
-        savet.join();  // the previous save still reads the host array
-        read_particles(particles);
+        read_and_save();
         readParticle = false;
-        spawn_save();
       }
       if (write_intermediate_frames && post_frame)
         readParticle = run_hook(post_frame, particles, readParticle, false);
@@ -230,10 +252,8 @@ void sph_simulation::simulate() {
     ++currentFrame;
 
     if (!write_intermediate_frames && save_frame) {
-      savet.join();
-      read_particles(particles);
+      read_and_save();
       readParticle = false;
-      spawn_save();
     }
     if (!write_intermediate_frames && post_frame)
       readParticle = run_hook(post_frame, particles, readParticle, true);

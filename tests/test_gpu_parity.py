@@ -259,3 +259,36 @@ def test_sort_variants_give_the_reference_order(sort):
             want = {k: g[f"s{s}_{k}"] for k in ("pos", "vel", "vhf", "acc", "rho", "prs")}
             check_floats(state_arrays(out), want, float(params["K"][0]), float(params["fluid_density"][0]),
                          f"sort {sort} step {s}")
+
+
+def test_split_download_is_a_snapshot():
+    """sphb_download_begin / _wait (the read-back that overlaps later steps): what arrives is the
+    state at the time of _begin, bit for bit, however many steps were queued behind it."""
+    import ctypes as C
+    from libclsph_b200 import PARTICLE, Engine
+    from libclsph_b200.engine import lib
+    g = np.load(os.path.join(GOLDEN, "steps_box_water.npz"))
+    sc = np.load(os.path.join(GOLDEN, "scene_box_water.npz"))
+    n = len(g["initial"])
+    ptr = C.c_void_p()
+    assert lib().sphb_host_alloc(C.byref(ptr), n * PARTICLE.itemsize) == 0
+    try:
+        late = np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_uint8)), (n * PARTICLE.itemsize,)).view(PARTICLE)
+        with Engine(g["params0"].copy(), g["terms"]) as e:
+            e.set_scene(sc["bbs"], sc["transforms"], sc["rvertices"], int(sc["total_gridpoints"]))
+            e.upload(g["initial"])
+            dt = e.step(float(g["dt0"]))
+            want = e.download()
+            late[:] = np.zeros(1, PARTICLE)[0]
+            e.download_begin(ptr.value)
+            for _ in range(3):
+                dt = e.step(dt)
+            e.download_wait()
+            assert late.tobytes() == want.tobytes()
+            after = e.download()  # a later blocking download sees the later state
+            assert after.tobytes() != want.tobytes()
+            e.download_begin(ptr.value)  # and a second split download can follow
+            e.download_wait()
+            assert late.tobytes() == after.tobytes()
+    finally:
+        lib().sphb_host_free(ptr)
