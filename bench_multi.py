@@ -77,6 +77,7 @@ def main_multi(args, rank, world, local, workload):
     for _ in range(warmup):
         dt = drv.step(dt)
     e.profile(True)
+    drv.profile = True
     l0 = e.launch_count()
     sampler = B.ClockSampler(B.physical_device(local)) if rank == 0 else None
     torch.cuda.synchronize()
@@ -98,7 +99,8 @@ def main_multi(args, rank, world, local, workload):
     launches = e.launch_count() - l0
     pass_ms, pass_launches, _ = e.pass_times()
     stats = torch.tensor([ms, wall * 1e3, float(launches), float(drv.n_owned), float(drv.n_ghost),
-                          float(drv.bytes_sent - bytes0)] + [pass_ms[k] for k in sorted(pass_ms)],
+                          float(drv.bytes_sent - bytes0), drv.phase_s["exchange"] * 1e3, drv.phase_s["forces_advect"] * 1e3,
+                          drv.phase_s["retries_commit"] * 1e3] + [pass_ms[k] for k in sorted(pass_ms)],
                          dtype=torch.float64, device="cuda")
     allstats = [torch.zeros_like(stats) for _ in range(world)]
     dist.all_gather(allstats, stats)
@@ -127,7 +129,10 @@ def main_multi(args, rank, world, local, workload):
         for r, s in enumerate(allstats):
             per_rank.append(dict(rank=r, ms_per_step=float(s[0]) / args.steps, owned=int(s[3]), ghosts=int(s[4]),
                                  halo_bytes_per_step=float(s[5]) / args.steps,
-                                 pass_ms_per_step={k: float(s[6 + i]) / args.steps for i, k in enumerate(names)}))
+                                 host_phase_ms_per_step=dict(pack_exchange_unpack=float(s[6]) / args.steps,
+                                                            sort_to_first_advect=float(s[7]) / args.steps,
+                                                            retries_commit=float(s[8]) / args.steps),
+                                 pass_ms_per_step={k: float(s[9 + i]) / args.steps for i, k in enumerate(names)}))
         slow = max(per_rank, key=lambda d: d["ms_per_step"])
         f_ms = slow["pass_ms_per_step"]["forces"]
         n_loc = slow["owned"]

@@ -22,6 +22,7 @@ struct sphb_engine {
   cudaStream_t copy = nullptr;
   cudaEvent_t ev_staged = nullptr, ev_copied = nullptr;
   bool download_pending = false;
+  int slab_attempt = 0;  // advection attempts of the current slab step
   uint32_t n = 0;    // particles the kernels run over (slab mode: owned + ghosts of this step)
   uint32_t cap = 0;  // allocated particle slots (== n outside slab mode)
   // slab mode (multi-GPU, slab.cu): this engine owns the particles with x in [xlo, xhi)

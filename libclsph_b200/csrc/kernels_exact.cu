@@ -320,11 +320,10 @@ __global__ void __launch_bounds__(kBlock)
       const uint32_t id = __ldg(slab.ids + i);
       if (id & 0x80000000u) continue;
       o = __ldg(slab.dst + i);
-      slab.ids_out[o] = id;
-      slab.src_of[o] = i;
-      slab.ckey_out[o] = morton3((uint32_t)((x0.x - slab.gminx) / slab.cell),
-                                 (uint32_t)((x0.y - slab.gminy) / slab.cell),
-                                 (uint32_t)((x0.z - slab.gminz) / slab.cell));
+      if (slab.write_aux) {
+        slab.ids_out[o] = id;
+        slab.src_of[o] = i;
+      }
     }
     // leapfrog
     const float nx = vh.x + a.x * dt, ny = vh.y + a.y * dt, nz = vh.z + a.z * dt;

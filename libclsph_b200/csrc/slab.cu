@@ -206,6 +206,7 @@ int sphb_slab_forces(sphb_engine* e, const float gmin[3], const float gmax[3]) {
   e->launches += launch_slab_owned_scan(e->rank_cur, n, e->free_keys, e->scan_scratch, e->n_owned_dev, s);
   CUDA_TRY(e, cudaGetLastError());
   e->slab_in = e->cur;
+  e->slab_attempt = 0;
   e->stepped = true;
   if (e->profile) {
     CUDA_TRY(e, cudaStreamSynchronize(s));
@@ -230,10 +231,8 @@ int sphb_slab_advect(sphb_engine* e, float dt, float* out8_dev) {
       sa.dst = e->free_keys;
       sa.ids_out = e->rank_prev;
       sa.src_of = e->src_of;
-      sa.ckey_out = e->ckey;
-      sa.gminx = e->params.min_point.s[0]; sa.gminy = e->params.min_point.s[1];
-      sa.gminz = e->params.min_point.s[2];
-      sa.cell = e->params.h * 2;
+      sa.write_aux = e->slab_attempt == 0;
+      ++e->slab_attempt;
       l += launch_advect(e->pos[in], e->vhf[in], e->acc, e->pos[out], e->vel[out], e->vhf[out], e->n, dt,
                          e->params.restitution, e->faces, e->face_count, e->df, e->red, s, &sa, &e->bin);
     }
@@ -280,7 +279,8 @@ int sphb_slab_download(sphb_engine* e, sphb_particle* aos, uint32_t* ids, uint32
   const int cur = e->cur;
   e->launches += launch_slab_to_aos(e->aos_stage, ids_dev, e->n_owned_dev, n, e->pos[cur], e->vel[cur],
                                     e->vhf[cur], e->rank_cur, e->committed ? e->src_of : nullptr, e->acc,
-                                    e->rho, e->prs, e->ckey, s);
+                                    e->rho, e->prs, e->pos[cur ^ 1], e->params.min_point.s[0],
+                                    e->params.min_point.s[1], e->params.min_point.s[2], e->params.h * 2, s);
   CUDA_TRY(e, cudaGetLastError());
   CUDA_TRY(e, cudaMemcpyAsync(aos, e->aos_stage, sizeof(sphb_particle) * n, cudaMemcpyDeviceToHost, s));
   CUDA_TRY(e, cudaMemcpyAsync(ids, ids_dev, sizeof(uint32_t) * n, cudaMemcpyDeviceToHost, s));

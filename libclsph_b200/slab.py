@@ -13,6 +13,8 @@ tests/ (world_size-2 gloo tests of the protocol on CPU).
 """
 import ctypes as C
 
+import time
+
 import numpy as np
 
 RECORD_BYTES = 48
@@ -135,6 +137,11 @@ class SlabDriver:
         self.n_owned = self.n_ghost = 0
         self.attempts = 0
         self.bytes_sent = 0
+        # wall-clock seconds per phase, split at the step's host synchronisation points
+        # (filled when `profile` is set: pack + exchange + unpack | sort .. forces + first
+        # advection attempt + all-reduce | further attempts + commit)
+        self.profile = False
+        self.phase_s = dict(exchange=0.0, forces_advect=0.0, retries_commit=0.0)
 
     # -- collectives ---------------------------------------------------------------------------
     def _allreduce_max(self, t):
@@ -174,24 +181,34 @@ class SlabDriver:
         """One simulate_single_frame over all slabs; returns the computed dt (identical on
         every rank)."""
         loc = self.local
+        t0 = time.perf_counter() if self.profile else 0.0
         with loc.stream_context():
             loc.pack(self.send_l, self.send_r)
             self._exchange()
-            self.n_owned, self.n_ghost = loc.unpack(self.recv_l, self.recv_r)
+            self.n_owned, self.n_ghost = loc.unpack(self.recv_l, self.recv_r)  # host sync
+            t1 = time.perf_counter() if self.profile else 0.0
             loc.forces(self.gmin, self.gmax)
             computed = dt
             self.attempts = 0
+            t2 = t1
             while True:
                 dt = computed
                 loc.advect(dt, self.red8)
                 self._allreduce_max(self.red8)
-                r = loc.red8_to_host(self.red8)
+                r = loc.red8_to_host(self.red8)  # host sync
+                if self.profile and self.attempts == 0:
+                    t2 = time.perf_counter()
                 computed = loc.compute_dt(r[6], r[7])
                 self.attempts += 1
                 if not needs_retry(dt, computed):
                     break
             loc.commit()
             self._set_bbox(r)
+        if self.profile:
+            t3 = time.perf_counter()
+            self.phase_s["exchange"] += t1 - t0
+            self.phase_s["forces_advect"] += t2 - t1
+            self.phase_s["retries_commit"] += t3 - t2
         return computed
 
 
