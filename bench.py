@@ -363,7 +363,7 @@ def main():
                     radix_passes=radix_passes, l2="inputs exceed L2 (positions alone are %d MB)" % (16 * n >> 20),
                     parallelism="1 GPU", secondary=secondary),
         clocks=r["clocks"], gpu_launches=r["launches"],
-        roofline=dict(bound="hbm", kernel={"density": "density + pressure pass (k_density_list)",
+        roofline=dict(bound="hbm", kernel={"density": "density + pressure pass (k_density_pair)",
                                            "forces": "forces pass (k_forces_nlist)"}[dom],
                       achieved=achieved, peak=peak, unit="GB/s", frac=achieved / peak, traffic=traffic,
                       peak_source=peak_src, algorithmic_bytes_per_particle=ALGO_BYTES[dom], launch_ms=f_ms,
