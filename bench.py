@@ -80,12 +80,30 @@ def write_json(path, d):
         fh.write(json.dumps(d, indent=4) + ";")
 
 
+MUCUS = dict(fluid_density=1000, dynamic_viscosity=36, restitution=0.5, k=5, surface_tension_threshold=5,
+             surface_tension=6, particles_inside_influence_radius=40)
+
+
+def fixture_scene(name, params):
+    z = np.load(os.path.join(ROOT, "tests", "golden", f"scene_{name}.npz"))
+    assert np.float32(z["threshold"]) == np.float32(params["h"][0]) * 2
+    return dict(bbs=z["bbs"], transforms=z["transforms"], rvertices=z["rvertices"],
+                total_gridpoints=int(z["total_gridpoints"]), faces=len(z["bbs"]))
+
+
 def build_case(tmp, n, kind):
     """Settings / lattice / scene through the PRODUCT's host layer (libclsph_b200.host)."""
     from libclsph_b200 import host
-    write_json(os.path.join(tmp, "fluid.json"), WATER)
+    write_json(os.path.join(tmp, "fluid.json"), MUCUS if kind == "mucus_monkeybox" else WATER)
     write_json(os.path.join(tmp, "sim.json"), dict(SIM, particles_count=int(n)))
     params, terms, vol, _, _ = host.load_settings(os.path.join(tmp, "fluid.json"), os.path.join(tmp, "sim.json"))
+    if kind == "mucus_monkeybox" or kind.startswith("scene:"):
+        # a reference scene (monkeybox.obj: 978 faces, labyrinth.obj: 606, river.obj: 332 ...) as
+        # the reference's scene::load made it (tests/golden/make_golden.py); the .obj files
+        # themselves are reference data and are not in the repo
+        name = "monkeybox_mucus" if kind == "mucus_monkeybox" else kind[6:] + "_water"
+        sc = fixture_scene(name, params)
+        return dict(params=params, terms=terms, volume=vol, scene=sc, dims=None, n=int(n))
     dims = water_box_dims(n) if kind == "water_box" else dam_break_dims(n)
     obj = os.path.join(tmp, f"{kind}_{n}.obj")
     write_box_obj(obj, *dims)
@@ -167,7 +185,7 @@ def pinned_particles(n):
     return np.frombuffer(buf, dtype=PARTICLE), ptr
 
 
-def run_gpu_case(case, steps, warmup, device, e2e_steps, sampler=None):
+def run_gpu_case(case, steps, warmup, device, e2e_steps, sampler=None, options=()):
     """Times `steps` resident steps (after `warmup`), then `e2e_steps` host-buffer steps."""
     from libclsph_b200 import Engine, PASS_NAMES, host
     n = case["n"]
@@ -175,6 +193,8 @@ def run_gpu_case(case, steps, warmup, device, e2e_steps, sampler=None):
     stage, stage_ptr = pinned_particles(n)
     host.lattice(n, case["volume"], out=stage)
     e = Engine(case["params"], case["terms"], device)
+    for k, v in options:
+        e.set_option(k, v)
     e.set_scene(sc["bbs"], sc["transforms"], sc["rvertices"], sc["total_gridpoints"])
     e.upload_ptr(stage_ptr.value, n)
     dt = 1.0 / 600.0
@@ -291,6 +311,8 @@ def main():
     ap.add_argument("--cpu-budget", type=float, default=20.0, help="seconds of CPU baseline work")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="N > 1: one --particles block per GPU (weak) or the N = 1 workload cut in N (strong)")
+    ap.add_argument("--scene", default="box", choices=["box", "labyrinth", "river", "shower", "monkey"],
+                    help="N > 1, --scaling strong: a reference scene instead of the open-top box")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-secondary", action="store_true", help="skip the 1 M dam-break leg")
     args = ap.parse_args()
@@ -334,6 +356,20 @@ def main():
                              value=c2["n"] * max(args.steps, 20) / (r2["ms_total"] * 1e-3), unit="particle-steps/s",
                              ms_per_step=r2["ms_total"] / max(args.steps, 20),
                              pass_ms_per_step={k: v / max(args.steps, 20) for k, v in r2["pass_ms"].items()})
+            # collision-heavy leg (SURVEY 8d config 5's size, config 2's fluid and mesh): the
+            # advection pass with the triangle bin, and with the reference's all-faces scan
+            c3 = build_case(tmp, 4096000, "mucus_monkeybox")
+            k3 = max(args.steps, 10)
+            legs = {}
+            for name, opt in (("triangle_bin", 1), ("all_faces_scan", 0)):
+                r3 = run_gpu_case(c3, k3, warmup, local, 0, options=(("triangle_bin", opt),))
+                legs[name] = dict(ms_per_step=r3["ms_total"] / k3, value=c3["n"] * k3 / (r3["ms_total"] * 1e-3),
+                                  advect_ms_per_launch=r3["pass_ms"]["advect"] / max(1, r3["pass_launches"]["advect"]) * 2,
+                                  pass_ms_per_step={k: v / k3 for k, v in r3["pass_ms"].items() if v})
+            secondary["collision_heavy"] = dict(
+                workload="synthetic 4096000-particle mucus.json lattice in the 978-face monkeybox scene "
+                         "(BASELINE.json configs[1] physics and mesh at configs[4]'s particle count)",
+                unit="particle-steps/s", **legs)
     n = case["n"]
     ms_step = r["ms_total"] / args.steps
     value = n * args.steps / (r["ms_total"] * 1e-3)

@@ -60,9 +60,17 @@ def main_multi(args, rank, world, local, workload):
             cuts = [-np.inf] + [float(x0 + np.float32(r) * pitch - np.float32(spacing) / 2) for r in range(1, world)] + [np.inf]
             d = B.water_box_dims(n0)
             dims = (d[0], float(d[1] + np.float32(world - 1) * pitch), d[2], d[3], d[4], d[5])
-        obj = os.path.join(tmp, f"box_rank{rank}.obj")
-        B.write_box_obj(obj, *dims)
-        sc = host.load_scene(obj, float(params["h"][0]) * 2)
+        scene_name = getattr(args, "scene", "box")
+        if scene_name != "box":
+            if not strong:
+                raise SystemExit("--scene needs --scaling strong")
+            sc = B.fixture_scene(scene_name + "_water", params)
+            workload = (f"synthetic {n0}-particle water lattice in the reference's {scene_name}.obj "
+                        f"({sc['faces']} faces, {sc['total_gridpoints']} distance-field points), SURVEY 8(d) config 5")
+        else:
+            obj = os.path.join(tmp, f"box_rank{rank}.obj")
+            B.write_box_obj(obj, *dims)
+            sc = host.load_scene(obj, float(params["h"][0]) * 2)
     n_mine = len(mine_p)
     # ghost layer: 2 layers of thickness 2h across the slab's cross-section, with head-room
     planes = 2 * float(params["h"][0]) / spacing + 1  # lattice planes inside a 2h layer

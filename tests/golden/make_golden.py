@@ -54,7 +54,8 @@ def scene_fixture(orc, name, root_dir, filename, threshold, soup, out):
         out, threshold=np.float32(threshold), soup=soup, bbs=sc["bbs"], transforms=sc["transforms"],
         rvertices=sc["rvertices"], face_normals=sc["face_normals"],
         total_gridpoints=np.uint32(sc["total_gridpoints"]),
-        df_sample=df[::97].copy(), df_sha256=np.array(hashlib.sha256(df.tobytes()).hexdigest()))
+        df_sample=df[::97].copy() if len(df) < (1 << 21) else df[::997].copy(),
+        df_sha256=np.array(hashlib.sha256(df.tobytes()).hexdigest()))
     print(name, "faces", sc["face_count"], "grid points", sc["total_gridpoints"])
     return sc, df
 
@@ -135,6 +136,16 @@ def main():
     print("advect_random: collided", int(moved.sum()), "of", n)
 
 
+def extra_scenes(orc):
+    """The reference's remaining scenes at water's h (scene::load products + distance-field
+    checksum): the collision-heavy meshes of SURVEY.md 8(d) config 5 and the small ones."""
+    hw = float(orc.settings(FLUIDS["water"], DEFAULT_SIM)[0]["h"][0])
+    for name, fn in [("labyrinth_water", "labyrinth.obj"), ("river_water", "river.obj"),
+                     ("shower_water", "shower.obj"), ("monkey_water", "monkey.obj"), ("plane_water", "plane.obj")]:
+        soup = parse_obj_triangles(os.path.join(REF, "scenes", fn))
+        scene_fixture(orc, name, REF, fn, np.float32(hw) * 2, soup, os.path.join(HERE, f"scene_{name}.npz"))
+
+
 def geo_fixture(orc):
     """One frame written by the reference's own houdini_file_saver (+ HoudiniFileDumpHelper)."""
     import ctypes as C
@@ -161,9 +172,13 @@ def geo_fixture(orc):
 
 
 if __name__ == "__main__":
-    if "--geo-only" in sys.argv:
+    if "--extra-scenes" in sys.argv:
+        pyorc.build("reference")
+        extra_scenes(pyorc.load("reference"))
+    elif "--geo-only" in sys.argv:
         pyorc.build("reference")
         geo_fixture(pyorc.load("reference"))
     else:
         main()
+        extra_scenes(pyorc.load("reference"))
         geo_fixture(pyorc.load("reference"))

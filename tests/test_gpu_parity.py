@@ -99,13 +99,17 @@ def test_distance_field_bit_exact_vs_fixtures():
     from libclsph_b200 import Engine
     for scene, steps in [("scene_box_water", "steps_box_water"), ("scene_cube_water", "steps_box_water"),
                          ("scene_cone_water", "steps_box_water"), ("scene_dambreak_water", "steps_box_water"),
-                         ("scene_monkeybox_mucus", "steps_monkeybox_mucus")]:
+                         ("scene_monkeybox_mucus", "steps_monkeybox_mucus"),
+                         ("scene_labyrinth_water", "steps_box_water"), ("scene_shower_water", "steps_box_water"),
+                         ("scene_monkey_water", "steps_box_water"), ("scene_plane_water", "steps_box_water"),
+                         ("scene_river_water", "steps_box_water")]:
         g = np.load(os.path.join(GOLDEN, steps + ".npz"))
         sc = np.load(os.path.join(GOLDEN, scene + ".npz"))
         with Engine(g["params0"], g["terms"]) as e:
             e.set_scene(sc["bbs"], sc["transforms"], sc["rvertices"], int(sc["total_gridpoints"]))
             df = e.distance_field()
-        assert np.array_equal(df[::97].view(np.uint32), sc["df_sample"].view(np.uint32)), scene
+        sample = df[::97] if len(df) < (1 << 21) else df[::997]
+        assert np.array_equal(sample.view(np.uint32), sc["df_sample"].view(np.uint32)), scene
         assert hashlib.sha256(df.tobytes()).hexdigest() == str(sc["df_sha256"]), scene
 
 

@@ -65,7 +65,9 @@ def test_struct_layouts(built):
 
 
 @pytest.mark.parametrize("name", ["scene_box_water", "scene_cube_water", "scene_cone_water",
-                                  "scene_dambreak_water", "scene_monkeybox_mucus"])
+                                  "scene_dambreak_water", "scene_monkeybox_mucus", "scene_labyrinth_water",
+                                  "scene_shower_water", "scene_monkey_water", "scene_plane_water",
+                                  "scene_river_water"])
 def test_scene_load_matches_reference(built, tmp_path, name):
     from libclsph_b200 import host
     z = np.load(os.path.join(GOLDEN, name + ".npz"))
