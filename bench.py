@@ -313,6 +313,8 @@ def main():
                     help="N > 1: one --particles block per GPU (weak) or the N = 1 workload cut in N (strong)")
     ap.add_argument("--scene", default="box", choices=["box", "labyrinth", "river", "shower", "monkey"],
                     help="N > 1, --scaling strong: a reference scene instead of the open-top box")
+    ap.add_argument("--driver", default="native", choices=["native", "python"],
+                    help="N > 1: the library's own NCCL step driver, or the Python protocol driver")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-secondary", action="store_true", help="skip the 1 M dam-break leg")
     args = ap.parse_args()

@@ -77,6 +77,8 @@ def main_multi(args, rank, world, local, workload):
     exch = int(1.5 * per_side * per_side * planes) + 65536
     cap = int(n_mine * 1.25) + 2 * exch
     loc = CudaSlab(params, terms, sc, local, cap, exch)
+    if getattr(args, "driver", "native") == "native":
+        loc.comm_init(rank, world, dist)  # the library drives exchange + all-reduce itself
     drv = SlabDriver(loc, cuts, rank, world, dist)
     drv.start(mine_p, ids)
     del block, mine_p
@@ -156,6 +158,7 @@ def main_multi(args, rank, world, local, workload):
                         box=[round(float(v), 4) for v in dims],
                         parallelism=f"{world} x-slabs, 2h ghost layer + migration by NCCL send/recv, "
                                     f"1 all-reduce(8 floats) per advection attempt",
+                        driver="sphb_slab_step (C, NCCL by dlopen)" if drv.native else "SlabDriver (Python, torch.distributed)",
                         l2="inputs exceed L2", exchange_capacity_records=exch, owned_total=owned_total),
             clocks=clocks, gpu_launches=int(sum(float(s[2]) for s in allstats)),
             roofline=dict(bound="hbm", kernel="forces pass (k_forces_nlist), slowest rank", achieved=achieved,

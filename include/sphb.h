@@ -177,6 +177,24 @@ int sphb_slab_download(sphb_engine* e, sphb_particle* aos, uint32_t* ids, uint32
 /* computeTimeStep's host arithmetic (libclsph/sph_simulation.cpp:598-602) */
 float sphb_compute_dt(const sphb_params* params, float max_v2, float max_a2);
 
+/* ---- the same step driven natively: one call per step and rank (csrc/slab_nccl.cu) -------
+ * The exchange (ncclSend / ncclRecv with the two x-neighbours) and the 8-float all-reduce are
+ * issued on the engine's stream by the library itself; libnccl.so.2 is resolved at run time
+ * (SPHB_ERR_NCCL_MISSING if it cannot be).  Set-up, collective over all ranks:
+ *   rank 0: sphb_nccl_unique_id(id); [caller broadcasts the 128 bytes]
+ *   sphb_slab_comm_init(e, id, rank, world)      rank r owns slab r; neighbours are r-1, r+1
+ *   sphb_slab_configure + sphb_slab_upload, then sphb_slab_start(e)   (global bbox)
+ * and then, per step,
+ *   sphb_slab_step(e, dt_in, &dt_out, &attempts, &n_owned, &n_ghost)
+ * which is pack / exchange / unpack / forces / { advect, all-reduce } / commit as listed above.
+ * All ranks must pass the same dt_in; they all receive the same dt_out. */
+int sphb_nccl_unique_id(unsigned char id_out[128]);
+int sphb_slab_comm_init(sphb_engine* e, const unsigned char id[128], int rank, int world);
+int sphb_slab_start(sphb_engine* e);
+int sphb_slab_step(sphb_engine* e, float dt_in, float* dt_out, int* attempts_out, uint32_t* n_owned_out,
+                   uint32_t* n_ghost_out);
+uint64_t sphb_slab_bytes_sent(sphb_engine* e); /* halo bytes sent since sphb_slab_start */
+
 /* ---- measurement ------------------------------------------------------------------ */
 enum {
   SPHB_PASS_BBOX = 0,    /* min/max of positions (only after an upload; otherwise fused in advect) */

@@ -32,6 +32,7 @@ SOURCES = {
     "kernels_neighbors.cu": [],
     "kernels_slab.cu": ["-fmad=false"],
     "slab.cu": [],
+    "slab_nccl.cu": [],
 }
 
 

@@ -36,6 +36,7 @@ const char* sphb_last_error(sphb_engine* e) { return e ? e->err.c_str() : g_crea
 
 int sphb_destroy(sphb_engine* e) {
   if (!e) return 0;
+  sphb_slab_comm_release(e);
   cudaSetDevice(e->device);
   if (e->stream) cudaStreamSynchronize(e->stream);
   for (int k = 0; k < 2; ++k) {

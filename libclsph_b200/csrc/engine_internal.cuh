@@ -23,6 +23,15 @@ struct sphb_engine {
   cudaEvent_t ev_staged = nullptr, ev_copied = nullptr;
   bool download_pending = false;
   int slab_attempt = 0;  // advection attempts of the current slab step
+  // native multi-GPU driver (slab_nccl.cu): communicator, the four halo messages
+  // (send left, recv left, send right, recv right), the 8-float reduction cell, the global bbox
+  void* comm = nullptr;
+  int comm_rank = 0, comm_world = 1;
+  void* msg[4] = {nullptr, nullptr, nullptr, nullptr};
+  float* red8_dev = nullptr;
+  float* red8_host = nullptr;
+  float gmin[3] = {0.f, 0.f, 0.f}, gmax[3] = {0.f, 0.f, 0.f};
+  uint64_t bytes_sent = 0;
   uint32_t n = 0;    // particles the kernels run over (slab mode: owned + ghosts of this step)
   uint32_t cap = 0;  // allocated particle slots (== n outside slab mode)
   // slab mode (multi-GPU, slab.cu): this engine owns the particles with x in [xlo, xhi)
@@ -106,6 +115,7 @@ struct sphb_engine {
 };
 
 std::string& sphb_create_error_slot();
+void sphb_slab_comm_release(sphb_engine* e);  // slab_nccl.cu
 extern "C" int sphb_create_with_capacity(const sphb_params* params, const sphb_terms* terms, int device,
                                          uint32_t capacity, sphb_engine** out);
 

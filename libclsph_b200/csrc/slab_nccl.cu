@@ -1,0 +1,219 @@
+// The slab step driven natively: one C call per step and rank, with the halo + migration
+// exchange (ncclSend / ncclRecv with the two x-neighbours) and the 8-float all-reduce issued
+// on the engine's own stream.  The same protocol as libclsph_b200/slab.py::SlabDriver.step —
+// that Python driver remains the reference implementation of the protocol (and is what the
+// gloo tests run) — minus the interpreter between the kernels: at small slabs the step is
+// bound by launch and host overhead, not by the GPU.
+//
+// NCCL is resolved at run time (dlopen of the libnccl already in the process, else by name),
+// so that libsphb.so itself carries no link-time dependency on it and single-GPU users need
+// no NCCL at all.  Only plain-C entry points with ABI-stable enum values are used.
+#include <dlfcn.h>
+
+#include "engine_internal.cuh"
+
+namespace {
+
+// the subset of nccl.h this file needs (values are part of NCCL's stable ABI)
+typedef struct ncclComm* ncclComm_t;
+typedef struct { char internal[128]; } ncclUniqueId;
+enum { kNcclSuccess = 0, kNcclUint8 = 1, kNcclFloat32 = 7, kNcclMax = 2 };
+
+struct NcclApi {
+  void* handle = nullptr;
+  int (*GetUniqueId)(ncclUniqueId*) = nullptr;
+  int (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+  int (*CommDestroy)(ncclComm_t) = nullptr;
+  int (*GroupStart)() = nullptr;
+  int (*GroupEnd)() = nullptr;
+  int (*Send)(const void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+  int (*Recv)(void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+  int (*AllReduce)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+  const char* (*GetErrorString)(int) = nullptr;
+  bool ok = false;
+};
+
+NcclApi& nccl() {
+  static NcclApi api;
+  static bool tried = false;
+  if (tried) return api;
+  tried = true;
+  const char* names[] = {"libnccl.so.2", "libnccl.so"};
+  for (const char* nm : names) {
+    api.handle = dlopen(nm, RTLD_NOW | RTLD_NOLOAD | RTLD_GLOBAL);  // the copy already loaded (torch's)
+    if (api.handle) break;
+  }
+  for (const char* nm : names) {
+    if (api.handle) break;
+    api.handle = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
+  }
+  if (!api.handle) return api;
+#define SPHB_NCCL_SYM(field, name) \
+  *reinterpret_cast<void**>(&api.field) = dlsym(api.handle, name); \
+  if (!api.field) return api;
+  SPHB_NCCL_SYM(GetUniqueId, "ncclGetUniqueId")
+  SPHB_NCCL_SYM(CommInitRank, "ncclCommInitRank")
+  SPHB_NCCL_SYM(CommDestroy, "ncclCommDestroy")
+  SPHB_NCCL_SYM(GroupStart, "ncclGroupStart")
+  SPHB_NCCL_SYM(GroupEnd, "ncclGroupEnd")
+  SPHB_NCCL_SYM(Send, "ncclSend")
+  SPHB_NCCL_SYM(Recv, "ncclRecv")
+  SPHB_NCCL_SYM(AllReduce, "ncclAllReduce")
+  SPHB_NCCL_SYM(GetErrorString, "ncclGetErrorString")
+#undef SPHB_NCCL_SYM
+  api.ok = true;
+  return api;
+}
+
+int nccl_fail(sphb_engine* e, int rc, const char* what, const char* file, int line) {
+  NcclApi& a = nccl();
+  return fail(e, SPHB_ERR_NCCL_BASE + rc, file, line, "%s -> NCCL error %d (%s)", what, rc,
+              a.GetErrorString ? a.GetErrorString(rc) : "?");
+}
+#define NCCL_TRY(e, call)                                                        \
+  do {                                                                           \
+    const int nccl_rc_ = (call);                                                 \
+    if (nccl_rc_ != kNcclSuccess) return nccl_fail((e), nccl_rc_, #call, __FILE__, __LINE__); \
+  } while (0)
+
+int require_comm(sphb_engine* e) {
+  if (!e) return SPHB_ERR_INVALID;
+  if (!e->slab) SPHB_FAIL(e, SPHB_ERR_INVALID, "not a slab engine (use sphb_slab_create)");
+  if (!e->comm) SPHB_FAIL(e, SPHB_ERR_INVALID, "no communicator (call sphb_slab_comm_init)");
+  return 0;
+}
+
+// all-reduce MAX of the 8 floats at e->red8_dev, then bring them to the host
+int reduce8(sphb_engine* e) {
+  NcclApi& a = nccl();
+  if (e->comm_world > 1)
+    NCCL_TRY(e, a.AllReduce(e->red8_dev, e->red8_dev, 8, kNcclFloat32, kNcclMax,
+                            static_cast<ncclComm_t>(e->comm), e->stream));
+  CUDA_TRY(e, cudaMemcpyAsync(e->red8_host, e->red8_dev, 8 * sizeof(float), cudaMemcpyDeviceToHost, e->stream));
+  CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+  return 0;
+}
+
+void bbox_from_red8(sphb_engine* e) {
+  for (int a = 0; a < 3; ++a) {
+    e->gmin[a] = -e->red8_host[a];
+    e->gmax[a] = e->red8_host[3 + a];
+  }
+}
+
+}  // namespace
+
+void sphb_slab_comm_release(sphb_engine* e) {
+  if (!e) return;
+  if (e->comm) {
+    NcclApi& a = nccl();
+    if (a.ok) a.CommDestroy(static_cast<ncclComm_t>(e->comm));
+    e->comm = nullptr;
+  }
+  for (int k = 0; k < 4; ++k) {
+    if (e->msg[k]) cudaFree(e->msg[k]);
+    e->msg[k] = nullptr;
+  }
+  if (e->red8_dev) cudaFree(e->red8_dev);
+  if (e->red8_host) cudaFreeHost(e->red8_host);
+  e->red8_dev = nullptr;
+  e->red8_host = nullptr;
+}
+
+extern "C" {
+
+int sphb_nccl_unique_id(unsigned char id_out[128]) {
+  if (!id_out) return SPHB_ERR_INVALID;
+  NcclApi& a = nccl();
+  if (!a.ok) return fail(nullptr, SPHB_ERR_NCCL_MISSING, __FILE__, __LINE__, "libnccl.so.2 could not be loaded");
+  ncclUniqueId id;
+  const int rc = a.GetUniqueId(&id);
+  if (rc != kNcclSuccess) return nccl_fail(nullptr, rc, "ncclGetUniqueId", __FILE__, __LINE__);
+  memcpy(id_out, id.internal, 128);
+  return 0;
+}
+
+int sphb_slab_comm_init(sphb_engine* e, const unsigned char id_in[128], int rank, int world) {
+  if (!e || !id_in || world < 1 || rank < 0 || rank >= world) return SPHB_ERR_INVALID;
+  if (!e->slab) SPHB_FAIL(e, SPHB_ERR_INVALID, "not a slab engine (use sphb_slab_create)");
+  NcclApi& a = nccl();
+  if (!a.ok) SPHB_FAIL(e, SPHB_ERR_NCCL_MISSING, "libnccl.so.2 could not be loaded");
+  CUDA_TRY(e, cudaSetDevice(e->device));
+  sphb_slab_comm_release(e);
+  ncclUniqueId id;
+  memcpy(id.internal, id_in, 128);
+  ncclComm_t comm = nullptr;
+  NCCL_TRY(e, a.CommInitRank(&comm, world, id, rank));
+  e->comm = comm;
+  e->comm_rank = rank;
+  e->comm_world = world;
+  const size_t bytes = slab_message_bytes(e->exch_cap);
+  for (int k = 0; k < 4; ++k) {
+    CUDA_TRY(e, cudaMalloc(&e->msg[k], bytes));
+    CUDA_TRY(e, cudaMemsetAsync(e->msg[k], 0, 16, e->stream));
+  }
+  CUDA_TRY(e, cudaMalloc(reinterpret_cast<void**>(&e->red8_dev), 8 * sizeof(float)));
+  CUDA_TRY(e, cudaMallocHost(reinterpret_cast<void**>(&e->red8_host), 8 * sizeof(float)));
+  CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+  return 0;
+}
+
+// After sphb_slab_configure + sphb_slab_upload on every rank: the global bbox of the initial
+// state (collective).
+int sphb_slab_start(sphb_engine* e) {
+  if (int rc = require_comm(e)) return rc;
+  if (int rc = sphb_slab_bbox(e, e->red8_dev)) return rc;
+  if (int rc = reduce8(e)) return rc;
+  bbox_from_red8(e);
+  e->bytes_sent = 0;
+  return 0;
+}
+
+// One simulate_single_frame over all slabs (collective; the same dt_in on every rank gives the
+// same dt_out on every rank).  sph_simulation.cpp:200-263 with the exchange in front.
+int sphb_slab_step(sphb_engine* e, float dt_in, float* dt_out, int* attempts_out, uint32_t* n_owned_out,
+                   uint32_t* n_ghost_out) {
+  if (int rc = require_comm(e)) return rc;
+  NcclApi& a = nccl();
+  ncclComm_t comm = static_cast<ncclComm_t>(e->comm);
+  void* send_l = e->msg[0]; void* recv_l = e->msg[1]; void* send_r = e->msg[2]; void* recv_r = e->msg[3];
+  if (int rc = sphb_slab_pack(e, send_l, send_r)) return rc;
+  const size_t bytes = slab_message_bytes(e->exch_cap);
+  if (e->has_left || e->has_right) {
+    // a fixed order (left pair, then right pair) on every rank keeps the pairs matched
+    NCCL_TRY(e, a.GroupStart());
+    if (e->has_left) {
+      NCCL_TRY(e, a.Send(send_l, bytes, kNcclUint8, e->comm_rank - 1, comm, e->stream));
+      NCCL_TRY(e, a.Recv(recv_l, bytes, kNcclUint8, e->comm_rank - 1, comm, e->stream));
+    }
+    if (e->has_right) {
+      NCCL_TRY(e, a.Send(send_r, bytes, kNcclUint8, e->comm_rank + 1, comm, e->stream));
+      NCCL_TRY(e, a.Recv(recv_r, bytes, kNcclUint8, e->comm_rank + 1, comm, e->stream));
+    }
+    NCCL_TRY(e, a.GroupEnd());
+    e->bytes_sent += bytes * ((e->has_left ? 1 : 0) + (e->has_right ? 1 : 0));
+  }
+  uint32_t n_owned = 0, n_ghost = 0;
+  if (int rc = sphb_slab_unpack(e, recv_l, recv_r, &n_owned, &n_ghost)) return rc;
+  if (int rc = sphb_slab_forces(e, e->gmin, e->gmax)) return rc;
+  float dt = dt_in, computed = dt_in;
+  int attempts = 0;
+  do {
+    dt = computed;
+    if (int rc = sphb_slab_advect(e, dt, e->red8_dev)) return rc;
+    if (int rc = reduce8(e)) return rc;
+    computed = dt_from_maxima(e->params, e->red8_host[6], e->red8_host[7]);
+    ++attempts;
+  } while (dt - computed > 0.00001);  // sph_simulation.cpp:260
+  if (int rc = sphb_slab_commit(e)) return rc;
+  bbox_from_red8(e);
+  if (dt_out) *dt_out = computed;
+  if (attempts_out) *attempts_out = attempts;
+  if (n_owned_out) *n_owned_out = n_owned;
+  if (n_ghost_out) *n_ghost_out = n_ghost;
+  return 0;
+}
+
+uint64_t sphb_slab_bytes_sent(sphb_engine* e) { return e ? e->bytes_sent : 0; }
+
+}  // extern "C"

@@ -113,6 +113,33 @@ class CudaSlab:
             self._chk(self.e.L.sphb_slab_download(self.e.h, _ptr(out), _ptr(ids), n.value, C.byref(n)))
         return out, ids
 
+    # -- the native driver (csrc/slab_nccl.cu): exchange and all-reduce inside the library ------
+    def comm_init(self, rank, world, dist=None, group=None):
+        """Collective.  Rank 0 creates the NCCL id; `dist` (torch.distributed) only carries its
+        128 bytes to the other ranks."""
+        ident = np.zeros(128, np.uint8)
+        if rank == 0:
+            self._chk(self.e.L.sphb_nccl_unique_id(ident.ctypes.data))
+        if world > 1:
+            box = [ident.tobytes()]
+            dist.broadcast_object_list(box, src=0, group=group)
+            ident = np.frombuffer(box[0], np.uint8).copy()
+        self._chk(self.e.L.sphb_slab_comm_init(self.e.h, ident.ctypes.data, int(rank), int(world)))
+        self.native = True
+
+    def native_start(self):
+        self._chk(self.e.L.sphb_slab_start(self.e.h))
+
+    def native_step(self, dt):
+        """(computed dt, attempts, owned, ghosts) — one C call: pack, exchange, unpack, forces,
+        advection attempts with their all-reduce, commit."""
+        out, att, no, ng = C.c_float(), C.c_int(), C.c_uint32(), C.c_uint32()
+        self._chk(self.e.L.sphb_slab_step(self.e.h, dt, C.byref(out), C.byref(att), C.byref(no), C.byref(ng)))
+        return out.value, att.value, no.value, ng.value
+
+    def native_bytes_sent(self):
+        return int(self.e.L.sphb_slab_bytes_sent(self.e.h))
+
     def close(self):
         self.e.close()
 
@@ -128,20 +155,29 @@ class SlabDriver:
         self.right = rank + 1 if rank + 1 < world else None
         self.cuts = [float(np.float32(c)) for c in cuts]
         local.configure(self.cuts[rank], self.cuts[rank + 1], self.left is not None, self.right is not None)
+        # the library drives the step itself when the local engine holds a communicator
+        # (CudaSlab.comm_init); otherwise the protocol below runs here, over `dist`
+        self.native = bool(getattr(local, "native", False))
+        self.n_owned = self.n_ghost = 0
+        self.attempts = 0
+        self._bytes_sent = 0
+        self.profile = False
+        self.phase_s = dict(exchange=0.0, forces_advect=0.0, retries_commit=0.0)
+        if self.native:
+            return
         self.send_l = local.new_message() if self.left is not None else None
         self.recv_l = local.new_message() if self.left is not None else None
         self.send_r = local.new_message() if self.right is not None else None
         self.recv_r = local.new_message() if self.right is not None else None
         self.red8 = local.new_red8()
         self.gmin = self.gmax = None
-        self.n_owned = self.n_ghost = 0
-        self.attempts = 0
-        self.bytes_sent = 0
-        # wall-clock seconds per phase, split at the step's host synchronisation points
+        # phase_s: wall-clock seconds per phase, split at the step's host synchronisation points
         # (filled when `profile` is set: pack + exchange + unpack | sort .. forces + first
         # advection attempt + all-reduce | further attempts + commit)
-        self.profile = False
-        self.phase_s = dict(exchange=0.0, forces_advect=0.0, retries_commit=0.0)
+
+    @property
+    def bytes_sent(self):
+        return self.local.native_bytes_sent() if self.native else self._bytes_sent
 
     # -- collectives ---------------------------------------------------------------------------
     def _allreduce_max(self, t):
@@ -162,7 +198,7 @@ class SlabDriver:
             ops.append(d.P2POp(d.irecv, self.recv_r, self.right, self.group))
         for req in d.batch_isend_irecv(ops):
             req.wait()
-        self.bytes_sent += sum(int(t.numel()) for t in (self.send_l, self.send_r) if t is not None)
+        self._bytes_sent += sum(int(t.numel()) for t in (self.send_l, self.send_r) if t is not None)
 
     def _set_bbox(self, r):
         self.gmin = np.array([-r[0], -r[1], -r[2]], np.float32)
@@ -171,6 +207,10 @@ class SlabDriver:
     # -- life cycle ----------------------------------------------------------------------------
     def start(self, particles, ids):
         """Uploads this rank's particles and agrees on the initial global bbox."""
+        if self.native:
+            self.local.upload(particles, ids)
+            self.local.native_start()
+            return
         with self.local.stream_context():
             self.local.upload(particles, ids)
             self.local.bbox(self.red8)
@@ -181,6 +221,9 @@ class SlabDriver:
         """One simulate_single_frame over all slabs; returns the computed dt (identical on
         every rank)."""
         loc = self.local
+        if self.native:
+            computed, self.attempts, self.n_owned, self.n_ghost = loc.native_step(dt)
+            return computed
         t0 = time.perf_counter() if self.profile else 0.0
         with loc.stream_context():
             loc.pack(self.send_l, self.send_r)

@@ -28,6 +28,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--particles", type=int, default=262144)
     ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--driver", default="native", choices=["native", "python"])
     a = ap.parse_args()
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
@@ -42,7 +43,10 @@ def main():
     mine = (x >= np.float32(cuts[rank])) & (x < np.float32(cuts[rank + 1]))
     cap = int(1.5 * n / world) + 65536
     loc = CudaSlab(case["params"], case["terms"], case["scene"], local, cap, max(65536, n // 4))
+    if a.driver == "native":
+        loc.comm_init(rank, world, dist)
     drv = SlabDriver(loc, cuts, rank, world, dist)
+    assert drv.native == (a.driver == "native")
     drv.start(p[mine], ids[mine])
     ref = reference_run(case, a.steps) if rank == 0 else None
     dt = 1.0 / 600.0

@@ -113,13 +113,17 @@ def test_slab_capacity_errors(tmp_path):
     assert ei.value.code == -6  # SPHB_ERR_CAPACITY: the ghost layer does not fit 8 records
 
 
-def test_two_processes_over_nccl(tmp_path):
+@pytest.mark.parametrize("driver", ["native", "python"])
+def test_two_processes_over_nccl(tmp_path, driver):
+    """One process per GPU: the library's own NCCL driver (sphb_slab_step) and the Python protocol
+    driver over torch.distributed, each against the whole-domain engine."""
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
-           "--master-addr", "127.0.0.1", "--master-port", "29517",
-           os.path.join(ROOT, "tests", "multi_gpu_check.py"), "--particles", "262144", "--steps", "3"]
+           "--master-addr", "127.0.0.1", "--master-port", "29517" if driver == "native" else "29518",
+           os.path.join(ROOT, "tests", "multi_gpu_check.py"), "--particles", "262144", "--steps", "3",
+           "--driver", driver]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "MULTI_GPU_CHECK OK" in r.stdout
