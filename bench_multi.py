@@ -86,8 +86,6 @@ def main_multi(args, rank, world, local, workload):
     dt = 1.0 / 600.0
     for _ in range(warmup):
         dt = drv.step(dt)
-    e.profile(True)
-    drv.profile = True
     l0 = e.launch_count()
     sampler = B.ClockSampler(B.physical_device(local)) if rank == 0 else None
     torch.cuda.synchronize()
@@ -104,12 +102,21 @@ def main_multi(args, rank, world, local, workload):
     ms = e.event_elapsed_ms(0, 1)
     torch.cuda.synchronize()
     wall = time.perf_counter() - t0
+    bytes_timed = drv.bytes_sent - bytes0
     dist.barrier()
     clocks = sampler.finish() if sampler else None
     launches = e.launch_count() - l0
+    # per-pass CUDA-event times and host phase times come from `steps` FURTHER steps: engine
+    # profiling synchronises inside the step, which the timed region above must not
+    e.profile(True)
+    drv.profile = True
+    for _ in range(args.steps):
+        dt = drv.step(dt)
     pass_ms, pass_launches, _ = e.pass_times()
+    e.profile(False)
+    drv.profile = False
     stats = torch.tensor([ms, wall * 1e3, float(launches), float(drv.n_owned), float(drv.n_ghost),
-                          float(drv.bytes_sent - bytes0), drv.phase_s["exchange"] * 1e3, drv.phase_s["forces_advect"] * 1e3,
+                          float(bytes_timed), drv.phase_s["exchange"] * 1e3, drv.phase_s["forces_advect"] * 1e3,
                           drv.phase_s["retries_commit"] * 1e3] + [pass_ms[k] for k in sorted(pass_ms)],
                          dtype=torch.float64, device="cuda")
     allstats = [torch.zeros_like(stats) for _ in range(world)]

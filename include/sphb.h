@@ -194,6 +194,14 @@ int sphb_slab_start(sphb_engine* e);
 int sphb_slab_step(sphb_engine* e, float dt_in, float* dt_out, int* attempts_out, uint32_t* n_owned_out,
                    uint32_t* n_ghost_out);
 uint64_t sphb_slab_bytes_sent(sphb_engine* e); /* halo bytes sent since sphb_slab_start */
+/* A halo message carries last step's record count + max(1/8 of it, option "halo_margin" = 4096)
+ * records (option value 0: no spare room at all, which exercises the resend path);
+ * one that outgrew that is exchanged again at full capacity by the pair concerned: how often */
+uint64_t sphb_slab_resends(sphb_engine* e);
+/* host wall-clock milliseconds accumulated by sphb_slab_step, split at its synchronisation points:
+ * pack + exchange + unpack | sort .. forces + first advection attempt + all-reduce | further
+ * attempts + commit */
+int sphb_slab_phase_ms(sphb_engine* e, double out3[3], int reset);
 
 /* ---- measurement ------------------------------------------------------------------ */
 enum {

@@ -603,6 +603,10 @@ int sphb_set_option(sphb_engine* e, const char* name, int value) {
     e->neighbor_variant = value;
     return 0;
   }
+  if (!strcmp(name, "halo_margin")) {  // sphb_slab_step: spare records per halo message
+    e->halo_margin = value < 0 ? 0u : (uint32_t)value;
+    return 0;
+  }
   SPHB_FAIL(e, SPHB_ERR_INVALID, "unknown option '%s'", name);
 }
 

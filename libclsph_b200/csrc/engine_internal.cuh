@@ -32,6 +32,12 @@ struct sphb_engine {
   float* red8_host = nullptr;
   float gmin[3] = {0.f, 0.f, 0.f}, gmax[3] = {0.f, 0.f, 0.f};
   uint64_t bytes_sent = 0;
+  // records moved per message last step ([0] to / [1] from the left, [2] to / [3] from the right):
+  // the next step's messages carry that many + a margin instead of the full capacity
+  uint32_t last_records[4] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu};
+  uint64_t resends = 0;
+  uint32_t halo_margin = 4096;  // option "halo_margin"
+  double phase_ms[3] = {0.0, 0.0, 0.0};  // pack..unpack | sort..first reduction | retries + commit
   uint32_t n = 0;    // particles the kernels run over (slab mode: owned + ghosts of this step)
   uint32_t cap = 0;  // allocated particle slots (== n outside slab mode)
   // slab mode (multi-GPU, slab.cu): this engine owns the particles with x in [xlo, xhi)
@@ -116,6 +122,9 @@ struct sphb_engine {
 
 std::string& sphb_create_error_slot();
 void sphb_slab_comm_release(sphb_engine* e);  // slab_nccl.cu
+int slab_read_counts(sphb_engine* e, const void* recv_left_dev, const void* recv_right_dev);  // slab.cu
+int slab_apply_unpack(sphb_engine* e, const void* recv_left_dev, const void* recv_right_dev,
+                      uint32_t* n_owned_out, uint32_t* n_ghost_out);
 extern "C" int sphb_create_with_capacity(const sphb_params* params, const sphb_terms* terms, int device,
                                          uint32_t capacity, sphb_engine** out);
 

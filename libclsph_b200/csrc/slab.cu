@@ -116,19 +116,31 @@ int sphb_slab_pack(sphb_engine* e, void* msg_left_dev, void* msg_right_dev) {
   return 0;
 }
 
-int sphb_slab_unpack(sphb_engine* e, const void* recv_left_dev, const void* recv_right_dev,
-                     uint32_t* n_owned_out, uint32_t* n_ghost_out) {
+}  // extern "C"
+
+// The step's first host synchronisation: the headers of the two received messages, this
+// rank's own pack counters and its particle count, into e->host_counts
+// ([0..3] recv left header, [4..7] recv right header, [8..11] pack counters, [12] owned before).
+int slab_read_counts(sphb_engine* e, const void* recv_left_dev, const void* recv_right_dev) {
   if (int rc = require_slab(e)) return rc;
   if ((e->has_left && !recv_left_dev) || (e->has_right && !recv_right_dev)) return SPHB_ERR_INVALID;
   CUDA_TRY(e, cudaSetDevice(e->device));
   cudaStream_t s = e->stream;
-  uint32_t* hc = e->host_counts;  // [0..3] recv left header, [4..7] recv right header, [8..11] pack counters, [12] owned before
+  uint32_t* hc = e->host_counts;
   memset(hc, 0, 16 * sizeof(uint32_t));
   if (e->has_left) CUDA_TRY(e, cudaMemcpyAsync(hc + 0, recv_left_dev, 16, cudaMemcpyDeviceToHost, s));
   if (e->has_right) CUDA_TRY(e, cudaMemcpyAsync(hc + 4, recv_right_dev, 16, cudaMemcpyDeviceToHost, s));
   CUDA_TRY(e, cudaMemcpyAsync(hc + 8, e->counters, 16, cudaMemcpyDeviceToHost, s));
   CUDA_TRY(e, cudaMemcpyAsync(hc + 12, e->n_owned_dev, 4, cudaMemcpyDeviceToHost, s));
   CUDA_TRY(e, cudaStreamSynchronize(s));
+  return 0;
+}
+
+// Appends the received records (counts already in e->host_counts).
+int slab_apply_unpack(sphb_engine* e, const void* recv_left_dev, const void* recv_right_dev,
+                      uint32_t* n_owned_out, uint32_t* n_ghost_out) {
+  cudaStream_t s = e->stream;
+  const uint32_t* hc = e->host_counts;
   const uint32_t in_l = hc[0], mig_in_l = hc[1], in_r = hc[4], mig_in_r = hc[5];
   const uint32_t out_l = hc[8], mig_out_l = hc[9], out_r = hc[10], mig_out_r = hc[11];
   const uint32_t before = hc[12];
@@ -152,6 +164,14 @@ int sphb_slab_unpack(sphb_engine* e, const void* recv_left_dev, const void* recv
   if (n_owned_out) *n_owned_out = e->n_owned;
   if (n_ghost_out) *n_ghost_out = e->n - e->n_owned;
   return 0;
+}
+
+extern "C" {
+
+int sphb_slab_unpack(sphb_engine* e, const void* recv_left_dev, const void* recv_right_dev,
+                     uint32_t* n_owned_out, uint32_t* n_ghost_out) {
+  if (int rc = slab_read_counts(e, recv_left_dev, recv_right_dev)) return rc;
+  return slab_apply_unpack(e, recv_left_dev, recv_right_dev, n_owned_out, n_ghost_out);
 }
 
 int sphb_slab_forces(sphb_engine* e, const float gmin[3], const float gmax[3]) {

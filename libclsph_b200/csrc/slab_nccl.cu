@@ -10,6 +10,8 @@
 // no NCCL at all.  Only plain-C entry points with ABI-stable enum values are used.
 #include <dlfcn.h>
 
+#include <chrono>
+
 #include "engine_internal.cuh"
 
 namespace {
@@ -166,6 +168,9 @@ int sphb_slab_start(sphb_engine* e) {
   if (int rc = reduce8(e)) return rc;
   bbox_from_red8(e);
   e->bytes_sent = 0;
+  e->resends = 0;
+  for (int k = 0; k < 4; ++k) e->last_records[k] = 0xFFFFFFFFu;
+  e->phase_ms[0] = e->phase_ms[1] = e->phase_ms[2] = 0.0;
   return 0;
 }
 
@@ -176,37 +181,75 @@ int sphb_slab_step(sphb_engine* e, float dt_in, float* dt_out, int* attempts_out
   if (int rc = require_comm(e)) return rc;
   NcclApi& a = nccl();
   ncclComm_t comm = static_cast<ncclComm_t>(e->comm);
+  typedef std::chrono::steady_clock clk;
+  const clk::time_point t0 = clk::now();
+  clk::time_point t1 = t0, t2 = t0;
   void* send_l = e->msg[0]; void* recv_l = e->msg[1]; void* send_r = e->msg[2]; void* recv_r = e->msg[3];
   if (int rc = sphb_slab_pack(e, send_l, send_r)) return rc;
-  const size_t bytes = slab_message_bytes(e->exch_cap);
-  if (e->has_left || e->has_right) {
+  // A message carries the records its predecessor carried one step ago plus a margin, not the
+  // full capacity: both ends of a pair know that count (the sender counted it, the receiver
+  // read it from the header), so both post the same size.  A message that outgrew its size is
+  // detected on both ends too (count in the header > records carried) and the pair repeats
+  // that one exchange at full capacity.
+  uint32_t rec[4];  // to the left, from the left, to the right, from the right
+  for (int k = 0; k < 4; ++k) {
+    const uint32_t last = e->last_records[k];
+    uint64_t want = last == 0xFFFFFFFFu ? e->exch_cap : (uint64_t)last + (e->halo_margin == 0 ? 0u : (last / 8u > e->halo_margin ? last / 8u : e->halo_margin));
+    rec[k] = want > e->exch_cap ? e->exch_cap : (uint32_t)want;
+  }
+  auto exchange = [&](bool left, bool right, const uint32_t r[4]) -> int {
+    if (!left && !right) return 0;
     // a fixed order (left pair, then right pair) on every rank keeps the pairs matched
     NCCL_TRY(e, a.GroupStart());
-    if (e->has_left) {
-      NCCL_TRY(e, a.Send(send_l, bytes, kNcclUint8, e->comm_rank - 1, comm, e->stream));
-      NCCL_TRY(e, a.Recv(recv_l, bytes, kNcclUint8, e->comm_rank - 1, comm, e->stream));
+    if (left) {
+      NCCL_TRY(e, a.Send(send_l, slab_message_bytes(r[0]), kNcclUint8, e->comm_rank - 1, comm, e->stream));
+      NCCL_TRY(e, a.Recv(recv_l, slab_message_bytes(r[1]), kNcclUint8, e->comm_rank - 1, comm, e->stream));
+      e->bytes_sent += slab_message_bytes(r[0]);
     }
-    if (e->has_right) {
-      NCCL_TRY(e, a.Send(send_r, bytes, kNcclUint8, e->comm_rank + 1, comm, e->stream));
-      NCCL_TRY(e, a.Recv(recv_r, bytes, kNcclUint8, e->comm_rank + 1, comm, e->stream));
+    if (right) {
+      NCCL_TRY(e, a.Send(send_r, slab_message_bytes(r[2]), kNcclUint8, e->comm_rank + 1, comm, e->stream));
+      NCCL_TRY(e, a.Recv(recv_r, slab_message_bytes(r[3]), kNcclUint8, e->comm_rank + 1, comm, e->stream));
+      e->bytes_sent += slab_message_bytes(r[2]);
     }
     NCCL_TRY(e, a.GroupEnd());
-    e->bytes_sent += bytes * ((e->has_left ? 1 : 0) + (e->has_right ? 1 : 0));
+    return 0;
+  };
+  if (int rc = exchange(e->has_left, e->has_right, rec)) return rc;
+  if (int rc = slab_read_counts(e, recv_l, recv_r)) return rc;  // host sync
+  {
+    const uint32_t* hc = e->host_counts;
+    const bool redo_l = e->has_left && (hc[8] > rec[0] || hc[0] > rec[1]);
+    const bool redo_r = e->has_right && (hc[10] > rec[2] || hc[4] > rec[3]);
+    if (redo_l || redo_r) {
+      const uint32_t full[4] = {e->exch_cap, e->exch_cap, e->exch_cap, e->exch_cap};
+      if (int rc = exchange(redo_l, redo_r, full)) return rc;
+      if (int rc = slab_read_counts(e, recv_l, recv_r)) return rc;
+      ++e->resends;
+    }
+    const uint32_t now[4] = {hc[8], hc[0], hc[10], hc[4]};
+    for (int k = 0; k < 4; ++k) e->last_records[k] = now[k] > e->exch_cap ? e->exch_cap : now[k];
   }
   uint32_t n_owned = 0, n_ghost = 0;
-  if (int rc = sphb_slab_unpack(e, recv_l, recv_r, &n_owned, &n_ghost)) return rc;
+  if (int rc = slab_apply_unpack(e, recv_l, recv_r, &n_owned, &n_ghost)) return rc;
+  t1 = clk::now();
   if (int rc = sphb_slab_forces(e, e->gmin, e->gmax)) return rc;
   float dt = dt_in, computed = dt_in;
   int attempts = 0;
   do {
     dt = computed;
     if (int rc = sphb_slab_advect(e, dt, e->red8_dev)) return rc;
-    if (int rc = reduce8(e)) return rc;
+    if (int rc = reduce8(e)) return rc;  // host sync
+    if (attempts == 0) t2 = clk::now();
     computed = dt_from_maxima(e->params, e->red8_host[6], e->red8_host[7]);
     ++attempts;
   } while (dt - computed > 0.00001);  // sph_simulation.cpp:260
   if (int rc = sphb_slab_commit(e)) return rc;
   bbox_from_red8(e);
+  // wall-clock per phase, split at the step's host synchronisation points
+  const clk::time_point t3 = clk::now();
+  e->phase_ms[0] += std::chrono::duration<double, std::milli>(t1 - t0).count();
+  e->phase_ms[1] += std::chrono::duration<double, std::milli>(t2 - t1).count();
+  e->phase_ms[2] += std::chrono::duration<double, std::milli>(t3 - t2).count();
   if (dt_out) *dt_out = computed;
   if (attempts_out) *attempts_out = attempts;
   if (n_owned_out) *n_owned_out = n_owned;
@@ -215,5 +258,15 @@ int sphb_slab_step(sphb_engine* e, float dt_in, float* dt_out, int* attempts_out
 }
 
 uint64_t sphb_slab_bytes_sent(sphb_engine* e) { return e ? e->bytes_sent : 0; }
+uint64_t sphb_slab_resends(sphb_engine* e) { return e ? e->resends : 0; }
+
+int sphb_slab_phase_ms(sphb_engine* e, double out3[3], int reset) {
+  if (!e || !out3) return SPHB_ERR_INVALID;
+  for (int k = 0; k < 3; ++k) {
+    out3[k] = e->phase_ms[k];
+    if (reset) e->phase_ms[k] = 0.0;
+  }
+  return 0;
+}
 
 }  // extern "C"

@@ -137,6 +137,14 @@ class CudaSlab:
         self._chk(self.e.L.sphb_slab_step(self.e.h, dt, C.byref(out), C.byref(att), C.byref(no), C.byref(ng)))
         return out.value, att.value, no.value, ng.value
 
+    def native_phase_ms(self, reset=False):
+        out = np.zeros(3, np.float64)
+        self._chk(self.e.L.sphb_slab_phase_ms(self.e.h, out.ctypes.data, int(reset)))
+        return out
+
+    def native_resends(self):
+        return int(self.e.L.sphb_slab_resends(self.e.h))
+
     def native_bytes_sent(self):
         return int(self.e.L.sphb_slab_bytes_sent(self.e.h))
 
@@ -222,7 +230,13 @@ class SlabDriver:
         every rank)."""
         loc = self.local
         if self.native:
+            if self.profile:
+                loc.native_phase_ms(reset=True)
             computed, self.attempts, self.n_owned, self.n_ghost = loc.native_step(dt)
+            if self.profile:
+                ph = loc.native_phase_ms()
+                for k, v in zip(("exchange", "forces_advect", "retries_commit"), ph):
+                    self.phase_s[k] += v * 1e-3
             return computed
         t0 = time.perf_counter() if self.profile else 0.0
         with loc.stream_context():

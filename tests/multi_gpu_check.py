@@ -29,6 +29,8 @@ def main():
     ap.add_argument("--particles", type=int, default=262144)
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--driver", default="native", choices=["native", "python"])
+    ap.add_argument("--halo-margin", type=int, default=-1,
+                    help="native driver: spare records per halo message (0 forces the resend path)")
     a = ap.parse_args()
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
@@ -45,6 +47,8 @@ def main():
     loc = CudaSlab(case["params"], case["terms"], case["scene"], local, cap, max(65536, n // 4))
     if a.driver == "native":
         loc.comm_init(rank, world, dist)
+        if a.halo_margin >= 0:
+            loc.e.set_option("halo_margin", a.halo_margin)
     drv = SlabDriver(loc, cuts, rank, world, dist)
     assert drv.native == (a.driver == "native")
     drv.start(p[mine], ids[mine])
@@ -74,6 +78,8 @@ def main():
                 ok &= bool(np.array_equal(got["grid_index"], want["grid_index"]))
                 ok &= gathered[0][3] == want_attempts
     dist.barrier()
+    if a.driver == "native":
+        print(f"rank {rank}: halo resends {loc.native_resends()} bytes sent {loc.native_bytes_sent()}", flush=True)
     if rank == 0:
         print("MULTI_GPU_CHECK OK" if ok else "MULTI_GPU_CHECK FAILED", flush=True)
     loc.close()

@@ -127,3 +127,22 @@ def test_two_processes_over_nccl(tmp_path, driver):
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "MULTI_GPU_CHECK OK" in r.stdout
+
+
+def test_halo_message_resend_over_nccl(tmp_path):
+    """Native driver with no spare room in the trimmed halo messages: a message that grew since the
+    previous step is exchanged again at full capacity, and the result is unchanged."""
+    import re
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+           "--master-addr", "127.0.0.1", "--master-port", "29519",
+           os.path.join(ROOT, "tests", "multi_gpu_check.py"), "--particles", "262144", "--steps", "6",
+           "--driver", "native", "--halo-margin", "0"]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert "MULTI_GPU_CHECK OK" in r.stdout
+    resends = [int(m) for m in re.findall(r"halo resends (\d+)", r.stdout)]
+    assert len(resends) == 2 and resends[0] == resends[1], r.stdout[-2000:]
+    print("resends per rank:", resends)
