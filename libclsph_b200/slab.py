@@ -102,16 +102,19 @@ class CudaSlab:
     def compute_dt(self, max_v2, max_a2):
         return float(self.e.L.sphb_compute_dt(self.params.ctypes.data, float(max_v2), float(max_a2)))
 
-    def download(self):
-        """(owned particles in local order, their ids)"""
+    def download(self, out=None, ids=None):
+        """(owned particles in local order, their ids).  `out` / `ids`: caller-owned arrays to fill
+        (page-locked ones make the copy run at PCIe speed); views of their first n entries return."""
         from .engine import PARTICLE, _ptr
         n = C.c_uint32()
         self._chk(self.e.L.sphb_slab_download(self.e.h, None, None, 0, C.byref(n)))
-        out = np.zeros(n.value, PARTICLE)
-        ids = np.zeros(n.value, np.uint32)
+        if out is None:
+            out = np.zeros(n.value, PARTICLE)
+            ids = np.zeros(n.value, np.uint32)
+        assert len(out) >= n.value and len(ids) >= n.value
         if n.value:
-            self._chk(self.e.L.sphb_slab_download(self.e.h, _ptr(out), _ptr(ids), n.value, C.byref(n)))
-        return out, ids
+            self._chk(self.e.L.sphb_slab_download(self.e.h, _ptr(out), _ptr(ids), len(out), C.byref(n)))
+        return out[: n.value], ids[: n.value]
 
     # -- the native driver (csrc/slab_nccl.cu): exchange and all-reduce inside the library ------
     def comm_init(self, rank, world, dist=None, group=None):
