@@ -144,7 +144,7 @@ class ClockSampler(threading.Thread):
                         self.reasons.add(name)
             except Exception:
                 pass
-            self._stop_evt.wait(0.1)
+            self._stop_evt.wait(0.005)
 
     def finish(self):
         self._stop_evt.set()
@@ -211,14 +211,21 @@ def run_gpu_case(case, steps, warmup, device, e2e_steps, sampler=None, options=(
     clocks = sampler.finish() if sampler else None
     launches = e.launch_count() - l0
     # per-pass CUDA-event times come from `steps` FURTHER steps, so that the timed region above
-    # carries no profiling events
+    # carries no profiling events; the reference-rank kernels, which otherwise run on a side
+    # stream beside the density pass, are kept on the main stream there, so that every pass
+    # time is that pass's own kernels' time
+    e.set_option("side_stream", 0)
     e.profile(True)
+    e.event_record(0)
     for _ in range(steps):
         dt = e.step(dt)
+    e.event_record(1)
+    ms_serial = e.event_elapsed_ms(0, 1)
     pass_ms, pass_launches, psteps = e.pass_times()
     e.profile(False)
+    e.set_option("side_stream", 1)
     params_now = e.parameters()
-    res = dict(ms_total=ms, launches=launches, pass_ms=pass_ms, pass_launches=pass_launches,
+    res = dict(ms_total=ms, ms_profiled_serial=ms_serial, launches=launches, pass_ms=pass_ms, pass_launches=pass_launches,
                clocks=clocks, dt=dt, grid=[int(params_now[k][0]) for k in ("grid_size_x", "grid_size_y", "grid_size_z")],
                grid_cell_count=int(params_now["grid_cell_count"][0]))
     # end to end: host buffers in, host buffers out, every step
@@ -403,7 +410,11 @@ def main():
         dtype="f32", data="synthetic",
         config=dict(workload=workload, particles=n, box=[round(x, 4) for x in case["dims"]], grid=r["grid"],
                     radix_passes=radix_passes, l2="inputs exceed L2 (positions alone are %d MB)" % (16 * n >> 20),
-                    parallelism="1 GPU", secondary=secondary),
+                    parallelism="1 GPU",
+                    pass_times="CUDA events over %d further steps with the reference-rank kernels kept on the "
+                               "main stream (%.3f ms per step that way; the timed steps overlap them with the "
+                               "density pass)" % (args.steps, r["ms_profiled_serial"] / args.steps),
+                    secondary=secondary),
         clocks=r["clocks"], gpu_launches=r["launches"],
         roofline=dict(bound="hbm", kernel={"density": "density + pressure pass (k_density_pair)",
                                            "forces": "forces pass (k_forces_nlist)"}[dom],

@@ -373,14 +373,19 @@ int sphb_step(sphb_engine* e, float dt_in, float* dt_out) {
   // the reference's cell table (kernels/sort.cl:61-78) and every particle's place in the
   // reference's sorted array: nothing in the step depends on it, so it runs on the side
   // stream while the (compute-bound) neighbour passes run, and is joined before the step ends
-  CUDA_TRY(e, cudaEventRecord(e->ev_fork, s));
-  CUDA_TRY(e, cudaStreamWaitEvent(e->side, e->ev_fork, 0));
-  {
-    PassTimer t(e, SPHB_PASS_REFRANK, e->side);
-    t.done(launch_reference_rank(skeys, e->ftable, e->rank_prev, e->ref_table, e->ckey,
-                                 e->rank_cur, c, e->scan_scratch, e->side));
+  // (option "side_stream" = 0 keeps it on the main stream: per-pass times are then each
+  // kernel's own)
+  cudaStream_t rs = e->use_side_stream ? e->side : s;
+  if (e->use_side_stream) {
+    CUDA_TRY(e, cudaEventRecord(e->ev_fork, s));
+    CUDA_TRY(e, cudaStreamWaitEvent(e->side, e->ev_fork, 0));
   }
-  CUDA_TRY(e, cudaEventRecord(e->ev_join, e->side));
+  {
+    PassTimer t(e, SPHB_PASS_REFRANK, rs);
+    t.done(launch_reference_rank(skeys, e->ftable, e->rank_prev, e->ref_table, e->ckey,
+                                 e->rank_cur, c, e->scan_scratch, rs));
+  }
+  if (e->use_side_stream) CUDA_TRY(e, cudaEventRecord(e->ev_join, e->side));
   // 4. density_pressure (kernels/sphb.cl:3-35), 5. forces (:37-126)
   {
     PassTimer t(e, SPHB_PASS_DENSITY);
@@ -392,7 +397,7 @@ int sphb_step(sphb_engine* e, float dt_in, float* dt_out) {
     t.done(launch_forces(e->pos[e->cur], e->vel[e->cur], skeys, e->ftable, e->rho,
                          e->nlist, e->ncount, e->acc, c, e->neighbor_variant, s));
   }
-  CUDA_TRY(e, cudaStreamWaitEvent(s, e->ev_join, 0));
+  if (e->use_side_stream) CUDA_TRY(e, cudaStreamWaitEvent(s, e->ev_join, 0));
   CUDA_TRY(e, cudaGetLastError());
 
   // 6. do { advection_collision(dt); computed = computeTimeStep } while (dt - computed > 1e-5)
@@ -601,6 +606,10 @@ int sphb_set_option(sphb_engine* e, const char* name, int value) {
   }
   if (!strcmp(name, "neighbor_kernel")) {
     e->neighbor_variant = value;
+    return 0;
+  }
+  if (!strcmp(name, "side_stream")) {
+    e->use_side_stream = value != 0;
     return 0;
   }
   if (!strcmp(name, "halo_margin")) {  // sphb_slab_step: spare records per halo message

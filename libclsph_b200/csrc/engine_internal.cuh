@@ -18,6 +18,7 @@ struct sphb_engine {
   cudaStream_t stream = nullptr;
   cudaStream_t side = nullptr;  // the reference-order bookkeeping runs beside the neighbour passes
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  bool use_side_stream = true;  // option "side_stream"
   // asynchronous read-back (sphb_download_begin / _wait): device -> host copy on its own stream
   cudaStream_t copy = nullptr;
   cudaEvent_t ev_staged = nullptr, ev_copied = nullptr;
