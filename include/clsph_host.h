@@ -44,6 +44,18 @@ void clsph_lattice(sphb_particle* out, uint32_t count, float initial_volume);
 size_t clsph_geo_text(const sphb_particle* particles, uint32_t count, float particle_mass,
                       uint32_t threads, char* out, size_t cap);
 
+/* The Bgeo-V5 bytes of the reference's USE_PARTIO build for the same frame
+ * (util/partio/PartioFunctions.h:5-65 + Partio::write, libclsph/file_save_delegates/
+ * houdini_file_saver.cpp:78-89; partio itself is not vendored in the reference).  Same return
+ * convention as clsph_geo_text. */
+size_t clsph_bgeo_bytes(const sphb_particle* particles, const sphb_params* params, uint32_t threads,
+                        char* out, size_t cap);
+
+/* One houdini_file_saver::writeFrameToFile call on a fresh saver: writes
+ * <frames_prefix>frames/frame0000001.geo, or .bgeo when use_partio is non-zero. */
+int clsph_save_frame(const char* frames_prefix, int use_partio, sphb_particle* particles,
+                     const sphb_params* params);
+
 /* Headless sph_simulation::simulate() (:265-432) with a save_frame hook installed (frames are
  * written as .geo under <frames_prefix>frames/ when frames_prefix is non-NULL).  Stops after
  * max_steps sub-steps when max_steps > 0.  final_state / final_params receive what the last

@@ -9,7 +9,8 @@ from .engine import BB, PARAMS, PARTICLE, TERMS, HERE, _ptr, lib as _engine_lib
 
 SYMBOLS = [
     "clsph_scene_load", "clsph_scene_face_count", "clsph_scene_total_grid_points", "clsph_scene_copy",
-    "clsph_scene_free", "clsph_load_settings", "clsph_lattice", "clsph_geo_text", "clsph_simulate",
+    "clsph_scene_free", "clsph_load_settings", "clsph_lattice", "clsph_geo_text", "clsph_bgeo_bytes",
+    "clsph_save_frame", "clsph_simulate",
 ]
 
 _lib = None
@@ -44,6 +45,9 @@ def lib():
         L.clsph_lattice.restype = None
         L.clsph_geo_text.argtypes = [vp, u32, f32, u32, vp, C.c_size_t]
         L.clsph_geo_text.restype = C.c_size_t
+        L.clsph_bgeo_bytes.argtypes = [vp, vp, u32, vp, C.c_size_t]
+        L.clsph_bgeo_bytes.restype = C.c_size_t
+        L.clsph_save_frame.argtypes = [C.c_char_p, i32, vp, vp]
         L.clsph_simulate.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, i32, C.c_uint64, C.c_char_p, vp, vp,
                                      C.POINTER(C.c_uint64), C.POINTER(u32), C.c_char_p, C.c_size_t]
         _lib = L
@@ -99,6 +103,27 @@ def geo_text(particles, particle_mass, threads=0):
     buf = C.create_string_buffer(n)
     L.clsph_geo_text(_ptr(particles), len(particles), particle_mass, threads, buf, n)
     return buf.raw[:n]
+
+
+def bgeo_bytes(particles, params, threads=0):
+    """The .bgeo the reference's USE_PARTIO build writes for this frame (params: PARAMS[1])."""
+    particles = np.ascontiguousarray(particles, PARTICLE)
+    params = np.ascontiguousarray(params, PARAMS)
+    assert int(params["particles_count"][0]) == len(particles)
+    L = lib()
+    n = L.clsph_bgeo_bytes(_ptr(particles), _ptr(params), threads, None, 0)
+    buf = C.create_string_buffer(n)
+    L.clsph_bgeo_bytes(_ptr(particles), _ptr(params), threads, buf, n)
+    return buf.raw[:n]
+
+
+def save_frame(frames_prefix, particles, params, use_partio=False):
+    """houdini_file_saver(prefix).writeFrameToFile(particles, params): frame0000001.geo / .bgeo"""
+    particles = np.ascontiguousarray(particles, PARTICLE)
+    params = np.ascontiguousarray(params, PARAMS)
+    rc = lib().clsph_save_frame(os.fsencode(frames_prefix), int(use_partio), _ptr(particles), _ptr(params))
+    if rc != 0:
+        raise RuntimeError("clsph_save_frame failed")
 
 
 def simulate(fluid_json, sim_json, obj_path, device=-1, max_steps=0, frames_prefix=None, n=None):

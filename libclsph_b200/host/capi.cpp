@@ -105,6 +105,27 @@ size_t clsph_geo_text(const sphb_particle* particles, uint32_t count, float part
   return text.size();
 }
 
+size_t clsph_bgeo_bytes(const sphb_particle* particles, const sphb_params* params, uint32_t threads,
+                        char* out, size_t cap) {
+  if (!particles || !params) return 0;
+  simulation_parameters p;
+  std::memcpy(&p, params, sizeof p);
+  const std::string bytes =
+      sphb_host::houdini_bgeo_bytes(reinterpret_cast<const particle*>(particles), p, threads);
+  if (out && cap >= bytes.size()) std::memcpy(out, bytes.data(), bytes.size());
+  return bytes.size();
+}
+
+int clsph_save_frame(const char* frames_prefix, int use_partio, sphb_particle* particles,
+                     const sphb_params* params) {
+  if (!frames_prefix || !particles || !params) return -1;
+  simulation_parameters p;
+  std::memcpy(&p, params, sizeof p);
+  houdini_file_saver saver(frames_prefix);
+  saver.use_partio = use_partio != 0;
+  return saver.writeFrameToFile(reinterpret_cast<particle*>(particles), p);
+}
+
 int clsph_simulate(const char* fluid_json, const char* sim_json, const char* obj_path, int device,
                    uint64_t max_steps, const char* frames_prefix, sphb_particle* final_state,
                    sphb_params* final_params, uint64_t* steps_done, uint32_t* frames_saved,

@@ -1,5 +1,6 @@
 #include "file_save_delegates/houdini_file_saver.h"
 
+#include <cstdint>
 #include <cstdio>
 #include <cstring>
 #include <fstream>
@@ -94,7 +95,134 @@ void geo_chunks(const particle* ps, unsigned int count, float mass, unsigned int
   chunks.push_back(" [0\t0]\nbox_object1 unordered\n1 1\nbeginExtra\nendExtra\n");
 }
 
+// ---- Bgeo V5 (binary Houdini geometry), every multi-byte value big-endian ----
+inline char* put_be32(char* p, uint32_t v) {
+  p[0] = (char)(v >> 24); p[1] = (char)(v >> 16); p[2] = (char)(v >> 8); p[3] = (char)v;
+  return p + 4;
+}
+inline char* put_be16(char* p, unsigned int v) {
+  p[0] = (char)(v >> 8); p[1] = (char)v;
+  return p + 2;
+}
+inline char* put_bef(char* p, float f) {
+  uint32_t u;
+  std::memcpy(&u, &f, 4);
+  return put_be32(p, u);
+}
+inline void append_be32(std::string& s, uint32_t v) { char b[4]; put_be32(b, v); s.append(b, 4); }
+inline void append_be16(std::string& s, unsigned int v) { char b[2]; put_be16(b, v); s.append(b, 2); }
+inline void append_hstr(std::string& s, const char* text) {  // 16-bit length, then the characters
+  const size_t n = std::strlen(text);
+  append_be16(s, (unsigned int)n);
+  s.append(text, n);
+}
+// a point attribute's dictionary entry: name, size, Houdini type (0 float, 1 int, 5 vector),
+// `size` zero defaults
+inline void append_attr(std::string& s, const char* name, unsigned int size, uint32_t type) {
+  append_hstr(s, name);
+  append_be16(s, size);
+  append_be32(s, type);
+  for (unsigned int k = 0; k < size; ++k) append_be32(s, 0);
+}
+
+constexpr size_t kBgeoWordsPerPoint = 4 + 3 + 3 + 1 + 1 + 1;
+
+// points [lo, hi): position + homogeneous 1, then the attributes in the order makeData adds
+// them (velocity, color, id, mass, pscale)
+void bgeo_points(const particle* ps, unsigned int lo, unsigned int hi, float mass, float h, char* out) {
+  for (unsigned int i = lo; i < hi; ++i) {
+    const particle& q = ps[i];
+    float r, g, b;
+    density_colour(q.density, r, g, b);
+    out = put_bef(out, q.position.s[0]);
+    out = put_bef(out, q.position.s[1]);
+    out = put_bef(out, q.position.s[2]);
+    out = put_bef(out, 1.f);
+    // PartioFunctions.h:36-38 assigns vel[0] three times: y and z are never written and keep
+    // what partio's freshly grown attribute array held — zero here
+    out = put_bef(out, q.velocity.s[0]);
+    out = put_bef(out, 0.f);
+    out = put_bef(out, 0.f);
+    out = put_bef(out, r);
+    out = put_bef(out, g);
+    out = put_bef(out, b);
+    out = put_be32(out, (uint32_t)i);
+    out = put_bef(out, mass);
+    out = put_bef(out, h);
+  }
+}
+
+void bgeo_indices(unsigned int lo, unsigned int hi, bool wide, char* out) {
+  if (wide)
+    for (unsigned int i = lo; i < hi; ++i) out = put_be32(out, i);
+  else
+    for (unsigned int i = lo; i < hi; ++i) out = put_be16(out, i);
+}
+
 }  // namespace
+
+std::string houdini_bgeo_bytes(const particle* particles, const simulation_parameters& parameters,
+                               unsigned int threads) {
+  const unsigned int count = parameters.particles_count;
+  if (threads == 0) {
+    threads = std::thread::hardware_concurrency();
+    if (threads == 0) threads = 1;
+  }
+  if (threads > 64) threads = 64;
+  if (count < 4096) threads = 1;
+  std::string head;
+  append_be32(head, 0x4267656fu);  // "Bgeo"
+  head.push_back('V');
+  append_be32(head, 5);
+  append_be32(head, count);  // NPoints
+  append_be32(head, 1);      // NPrims: one particle-system primitive
+  append_be32(head, 0);      // NPointGroups
+  append_be32(head, 0);      // NPrimGroups
+  append_be32(head, 5);      // NPointAttrib: everything but the position
+  append_be32(head, 0);      // NVertexAttrib
+  append_be32(head, 1);      // NPrimAttrib
+  append_be32(head, 0);      // NAttrib
+  append_attr(head, "velocity", 3, 5);
+  append_attr(head, "color", 3, 5);
+  append_attr(head, "id", 1, 1);
+  append_attr(head, "mass", 1, 0);
+  append_attr(head, "pscale", 1, 0);
+  std::string mid;  // primitive attribute dictionary, then the primitive's header
+  append_hstr(mid, "generator");
+  append_be16(mid, 1);
+  append_be32(mid, 4);  // index-string attribute ...
+  append_be32(mid, 1);  // ... with one string
+  append_hstr(mid, "papi");
+  append_be32(mid, 0x8000);  // particle system
+  append_be32(mid, count);
+  const bool wide = (int)count > (1 << 16);  // vertex numbers: 16-bit up to 65536 points
+  std::string tail;
+  append_be32(tail, 0);  // the primitive's "generator" index
+  tail.push_back((char)0x00);
+  tail.push_back((char)0xff);
+
+  const size_t points_bytes = (size_t)count * kBgeoWordsPerPoint * 4, index_bytes = (size_t)count * (wide ? 4 : 2);
+  std::string all;
+  all.resize(head.size() + points_bytes + mid.size() + index_bytes + tail.size());
+  char* base = &all[0];
+  std::memcpy(base, head.data(), head.size());
+  char* points = base + head.size();
+  std::memcpy(points + points_bytes, mid.data(), mid.size());
+  char* indices = points + points_bytes + mid.size();
+  std::memcpy(indices + index_bytes, tail.data(), tail.size());
+  std::vector<std::thread> pool;
+  for (unsigned int t = 0; t < threads; ++t) {
+    const unsigned int lo = (unsigned int)((unsigned long long)count * t / threads);
+    const unsigned int hi = (unsigned int)((unsigned long long)count * (t + 1) / threads);
+    const float mass = parameters.particle_mass, h = parameters.h;
+    pool.push_back(std::thread([=] {
+      bgeo_points(particles, lo, hi, mass, h, points + (size_t)lo * kBgeoWordsPerPoint * 4);
+      bgeo_indices(lo, hi, wide, indices + (size_t)lo * (wide ? 4 : 2));
+    }));
+  }
+  for (size_t t = 0; t < pool.size(); ++t) pool[t].join();
+  return all;
+}
 
 std::string houdini_geo_text(const particle* particles, unsigned int count, float particle_mass,
                              unsigned int threads) {
@@ -112,6 +240,18 @@ int houdini_file_saver::writeFrameToFile(particle* particles, const simulation_p
   ++frame_count;
   // setw(9)/setfill('0') then keep the last 7 characters (houdini_file_saver.cpp:15-23)
   std::snprintf(name, sizeof name, "%07d", frame_count % 10000000);
+  if (use_partio) {  // houdini_file_saver.cpp:78-89
+    const std::string fileName = frames_folder_prefix + "frames/frame" + name + ".bgeo";
+    const std::string bytes = sphb_host::houdini_bgeo_bytes(particles, parameters, 0);
+    std::ofstream out(fileName.c_str(), std::ios::out | std::ios::binary);
+    // Partio::write reports failure on stderr and returns; the delegate still returns 0
+    if (!out.is_open()) {
+      std::cerr << "Partio: Unable to open file " << fileName << std::endl;
+      return 0;
+    }
+    out.write(bytes.data(), (std::streamsize)bytes.size());
+    return 0;
+  }
   const std::string fileName = frames_folder_prefix + "frames/frame" + name + ".geo";
 
   std::vector<std::string> chunks;

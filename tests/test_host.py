@@ -139,3 +139,77 @@ def test_geo_writer_matches_reference(built):
     # the parallel path (>= 4096 particles) must give the same bytes as the serial one
     big = np.tile(z["particles"], 20)
     assert host.geo_text(big, 0.05, 1) == host.geo_text(big, 0.05, 7)
+
+
+def _bgeo_expected(particles, mass, h):
+    """Independent restatement (numpy + struct) of what partio's Bgeo-V5 writer emits for the
+    attributes makeData adds (util/partio/PartioFunctions.h:5-65): header, five point
+    attributes, points, the one particle-system primitive, trailer.  partio is not vendored in
+    the reference and not installed here: parity of the .bgeo branch is UNPINNED (this pins the
+    C++ writer to the format restated here, not to bytes a partio build produced)."""
+    import struct
+    n = len(particles)
+    hs = lambda s: struct.pack(">H", len(s)) + s
+    out = struct.pack(">IcIIIIIIIII", 0x4267656F, b"V", 5, n, 1, 0, 0, 5, 0, 1, 0)
+    for name, size, typ in ((b"velocity", 3, 5), (b"color", 3, 5), (b"id", 1, 1), (b"mass", 1, 0),
+                            (b"pscale", 1, 0)):
+        out += hs(name) + struct.pack(">Hi", size, typ) + b"\0" * (4 * size)
+    d = particles["density"].astype(np.float32)
+    one, k, half = np.float32(1), np.float32(1000), np.float32(500)
+    with np.errstate(invalid="ignore"):
+        r = np.where((d > k) & (d <= 2 * k), (d - k) / k, np.float32(0))
+        g = np.where((d >= 0) & (d < k), one - d / k, np.float32(0))
+        b = np.where((d >= half) & (d <= k), (d - half) / half,
+                     np.where((d >= k) & (d <= np.float32(1500)), one - (d - k) / half, np.float32(0)))
+    rec = np.zeros(n, dtype=[("p", ">f4", 4), ("v", ">f4", 3), ("c", ">f4", 3), ("id", ">i4"), ("m", ">f4"),
+                             ("s", ">f4")])
+    rec["p"][:, :3] = particles["position"][:, :3]
+    rec["p"][:, 3] = 1.0
+    rec["v"][:, 0] = particles["velocity"][:, 0]  # y, z never written by makeData (:36-38)
+    rec["c"] = np.stack([r, g, b], axis=1).astype(np.float32)
+    rec["id"] = np.arange(n)
+    rec["m"] = mass
+    rec["s"] = h
+    out += rec.tobytes()
+    out += hs(b"generator") + struct.pack(">Hii", 1, 4, 1) + hs(b"papi")
+    out += struct.pack(">ii", 0x8000, n)
+    out += np.arange(n).astype(">u4" if n > 65536 else ">u2").tobytes()
+    out += struct.pack(">i", 0) + b"\x00\xff"
+    return out
+
+
+@pytest.mark.parametrize("count", [0, 1, 100, 5000, 70000])
+def test_bgeo_writer_matches_format(built, count):
+    from libclsph_b200 import host
+    from libclsph_b200.engine import PARAMS
+    z = np.load(os.path.join(GOLDEN, "geo_frame.npz"))
+    rng = np.random.default_rng(7)
+    ps = np.tile(z["particles"], count // len(z["particles"]) + 1)[:count].copy()
+    if count:
+        ps["density"] = rng.uniform(-100, 2300, count).astype(np.float32)
+        ps["density"][::17] = np.float32(1000)
+        ps["density"][::19] = np.nan
+    p = np.zeros(1, PARAMS)
+    p["particles_count"] = count
+    p["particle_mass"] = 0.05
+    p["h"] = 0.06207
+    want = _bgeo_expected(ps, np.float32(0.05), np.float32(0.06207))
+    for threads in (1, 5):
+        assert host.bgeo_bytes(ps, p, threads) == want
+
+
+def test_saver_writes_geo_or_bgeo(built, tmp_path):
+    from libclsph_b200 import host
+    from libclsph_b200.engine import PARAMS
+    z = np.load(os.path.join(GOLDEN, "geo_frame.npz"))
+    ps = z["particles"]
+    p = np.zeros(1, PARAMS)
+    p["particles_count"] = len(ps)
+    p["particle_mass"] = float(z["particle_mass"])
+    p["h"] = 0.1
+    (tmp_path / "frames").mkdir()
+    prefix = str(tmp_path) + "/"
+    host.save_frame(prefix, ps, p, use_partio=False)
+    host.save_frame(prefix, ps, p, use_partio=True)
+    assert (tmp_path / "frames" / "frame0000001.geo").read_bytes() == z["text"].tobytes()
+    assert (tmp_path / "frames" / "frame0000001.bgeo").read_bytes() == host.bgeo_bytes(ps, p)
