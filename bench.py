@@ -198,15 +198,17 @@ def run_gpu_case(case, steps, warmup, device, e2e_steps, sampler=None, options=(
     e.set_scene(sc["bbs"], sc["transforms"], sc["rvertices"], sc["total_gridpoints"])
     e.upload_ptr(stage_ptr.value, n)
     dt = 1.0 / 600.0
-    for _ in range(warmup):
-        dt = e.step(dt)
+    # the timed steps go through sphb_run_frame, the call sph_simulation::simulate() makes for a
+    # frame's sub-steps, in its default mode (device-driven CUDA-graph steps up to 6 M particles,
+    # one host round trip per step above)
+    dt, _, _ = e.run_frame(dt, 1.0, warmup)
     l0 = e.launch_count()
     if sampler:
         sampler.start()
     e.event_record(0)
-    for _ in range(steps):
-        dt = e.step(dt)
+    dt, _, done = e.run_frame(dt, 1.0, steps)
     e.event_record(1)
+    assert done == steps
     ms = e.event_elapsed_ms(0, 1)
     clocks = sampler.finish() if sampler else None
     launches = e.launch_count() - l0
@@ -228,6 +230,24 @@ def run_gpu_case(case, steps, warmup, device, e2e_steps, sampler=None, options=(
     res = dict(ms_total=ms, ms_profiled_serial=ms_serial, launches=launches, pass_ms=pass_ms, pass_launches=pass_launches,
                clocks=clocks, dt=dt, grid=[int(params_now[k][0]) for k in ("grid_size_x", "grid_size_y", "grid_size_z")],
                grid_cell_count=int(params_now["grid_cell_count"][0]))
+    # the frame loop as one engine call (sphb_run_frame): the same steps enqueued without a host
+    # round trip per step, against the per-step path, `steps` steps each
+    res["frame_loop_ms_per_step"] = {}
+    for name, opts in (("host_round_trip_per_step", (("device_loop", 0),)),
+                       ("device_loop", (("device_loop", 1), ("graph", 0))),
+                       ("device_loop_graph", (("device_loop", 1), ("graph", 1)))):
+        for k, v in opts:
+            e.set_option(k, v)
+        # every mode runs the same trajectory: the lattice again, `warmup` steps, `steps` timed steps
+        e.upload_ptr(stage_ptr.value, n)
+        dt, _, _ = e.run_frame(1.0 / 600.0, 1.0, warmup)
+        e.event_record(0)
+        dt, _, done = e.run_frame(dt, 1.0, steps)
+        e.event_record(1)
+        res["frame_loop_ms_per_step"][name] = e.event_elapsed_ms(0, 1) / max(1, done)
+    res["queued_steps"] = e.queued_steps()
+    e.set_option("graph", 1)
+    e.set_option("device_loop", 2)
     # end to end: host buffers in, host buffers out, every step
     if e2e_steps > 0:
         e.download_ptr(stage_ptr.value)
@@ -242,6 +262,20 @@ def run_gpu_case(case, steps, warmup, device, e2e_steps, sampler=None, options=(
             e.download_ptr(stage_ptr.value)
         res["e2e_s"] = time.perf_counter() - t0
         res["e2e_steps"] = e2e_steps
+        # the pattern sph_simulation::simulate() itself has (sph_simulation.cpp:374-427): the state
+        # stays on the device, every frame of 10 sub-steps ends with ONE read-back of all particles
+        # into the host array (here overlapped with the next frame's steps, as simulate() does when
+        # only save_frame is hooked)
+        frames, substeps = max(2, e2e_steps), 10
+        e.download_begin(stage_ptr.value)
+        t0 = time.perf_counter()
+        for _ in range(frames):
+            dt, _, _ = e.run_frame(dt, 1.0, substeps)
+            e.download_wait()
+            e.download_begin(stage_ptr.value)
+        e.download_wait()
+        res["frames_s"] = time.perf_counter() - t0
+        res["frames"] = (frames, substeps)
         res["finite"] = bool(np.isfinite(stage["position"][:: max(1, n // 4096), :3]).all())
     e.close()
     del stage
@@ -368,7 +402,8 @@ def main():
             secondary = dict(workload="synthetic 1000000-particle water dam break, BASELINE.json configs[2]",
                              value=c2["n"] * max(args.steps, 20) / (r2["ms_total"] * 1e-3), unit="particle-steps/s",
                              ms_per_step=r2["ms_total"] / max(args.steps, 20),
-                             pass_ms_per_step={k: v / max(args.steps, 20) for k, v in r2["pass_ms"].items()})
+                             pass_ms_per_step={k: v / max(args.steps, 20) for k, v in r2["pass_ms"].items()},
+                             frame_loop_ms_per_step=r2["frame_loop_ms_per_step"])
             # collision-heavy leg (SURVEY 8d config 5's size, config 2's fluid and mesh): the
             # advection pass with the triangle bin, and with the reference's all-faces scan
             c3 = build_case(tmp, 4096000, "mucus_monkeybox")
@@ -416,6 +451,9 @@ def main():
                                "density pass)" % (args.steps, r["ms_profiled_serial"] / args.steps),
                     secondary=secondary),
         clocks=r["clocks"], gpu_launches=r["launches"],
+        frame_loop=dict(ms_per_step=r["frame_loop_ms_per_step"], steps_without_host_round_trip=r["queued_steps"],
+                        note="sphb_run_frame over %d steps per mode, each from the same state; `value` is "
+                             "its default mode (device_loop_graph up to 6 M particles)" % args.steps),
         roofline=dict(bound="hbm", kernel={"density": "density + pressure pass (k_density_pair)",
                                            "forces": "forces pass (k_forces_nlist)"}[dom],
                       achieved=achieved, peak=peak, unit="GB/s", frac=achieved / peak, traffic=traffic,
@@ -429,7 +467,13 @@ def main():
     if "e2e_s" in r:
         line["e2e"] = dict(value=n * r["e2e_steps"] / r["e2e_s"], unit="particle-steps/s",
                            h2d_bytes_per_step=80 * n, d2h_bytes_per_step=80 * n + 32, steps=r["e2e_steps"],
-                           finite=r["finite"])
+                           finite=r["finite"],
+                           simulate_frames=dict(
+                               value=n * r["frames"][0] * r["frames"][1] / r["frames_s"], unit="particle-steps/s",
+                               note="the copy pattern of sph_simulation::simulate(): state resident, %d frames of %d "
+                                    "sub-steps (sphb_run_frame), one %d-byte read-back per frame overlapped with the "
+                                    "next frame's steps" % (r["frames"][0], r["frames"][1], 80 * n),
+                               d2h_bytes_per_step=80 * n // r["frames"][1], h2d_bytes_per_step=0))
     if not args.no_cpu:
         cb = cpu_arm(args.cpu_budget, 2, 1)
         line["cpu_baseline"] = dict(value=cb["value"], unit=cb["unit"], cores=cb["cores"], kind=cb["kind"],

@@ -107,6 +107,25 @@ int sphb_upload(sphb_engine* e, const sphb_particle* aos, uint32_t n);
  * *dt_out = the value the reference returns (time advanced and next step's dt). */
 int sphb_step(sphb_engine* e, float dt_in, float* dt_out);
 
+/* Replaces the sub-step loop of one frame in sph_simulation::simulate()
+ * (libclsph/sph_simulation.cpp:384-409, without write_all_frames):
+ *     timeleft = frame_time;
+ *     while (timeleft > 0) { dt = simulate_single_frame(dt); timeleft -= dt;
+ *                            if (timeleft < dt) dt = timeleft; }
+ * with the same results as calling sphb_step in that loop, but without a host round trip per
+ * step: the next step's grid (findMinMaxPosition's host half, :668-727), the new dt
+ * (computeTimeStep's host half, :598-602) and the advection retry (:260) are evaluated by
+ * one-thread kernels, and a frame's steps are enqueued back to back (option "graph" = 1: one
+ * CUDA graph launch per step).  The host steps in only when a cell table must grow, when dt
+ * needs more than two advection attempts, and for the first step after an upload.
+ * max_steps > 0 stops after that many steps.  *dt_out = the loop's dt afterwards; *steps_out =
+ * steps run; timeleft_log[k] (k < log_cap) = timeleft after step k — what the reference prints
+ * per step.  One engine per device at a time may be inside this call. */
+int sphb_run_frame(sphb_engine* e, float dt_in, float frame_time, uint64_t max_steps, float* dt_out,
+                   uint32_t* steps_out, float* timeleft_log, uint32_t log_cap);
+/* Steps that sphb_run_frame ran without a host round trip since the engine was created. */
+uint64_t sphb_queued_steps(sphb_engine* e);
+
 /* The engine's copy of `parameters` as the reference mutates it every step
  * (min_point, max_point, grid_size_*, grid_cell_count; sph_simulation.cpp:670-727). */
 int sphb_get_parameters(sphb_engine* e, sphb_params* out);
@@ -239,7 +258,18 @@ void* sphb_stream(sphb_engine* e);
  *                      sort of (key, index) pairs.  Both give the same order.
  *   "triangle_bin"     1 (default) = scenes of 17+ faces get a uniform-grid triangle bin for the
  *                      collision pass; 0 = every particle tests every face (set before
- *                      sphb_set_scene) */
+ *                      sphb_set_scene)
+ *   "side_stream"      1 (default) = the reference-order bookkeeping runs on a side stream
+ *   "device_loop"      sphb_run_frame: 1 = steps are enqueued without host round trips; 0 = one
+ *                      sphb_step per step; 2 (default) = 1 up to 6 M particles, where a step is
+ *                      short enough for the round trip to show, else 0
+ *   "graph"            1 (default) = a device-driven step is one CUDA graph launch; 0 = its
+ *                      kernels are launched one by one
+ *   "queued_attempts"  advection attempts enqueued per device-driven step (default 2, 1..4);
+ *                      a step that needs more is finished from the host
+ *   "table_headroom"   1 (default) = cell tables are allocated with 1.5x spare entries; 0 = exact
+ *                      (tests: every grid growth then goes through the host)
+ *   "halo_margin"      sphb_slab_step: spare records per halo message */
 int sphb_set_option(sphb_engine* e, const char* name, int value);
 
 /* Page-locked host memory for the particle array (the reference asks OpenCL for

@@ -112,10 +112,108 @@ __host__ __device__ inline uint32_t compact10(uint32_t v) {
   return v;
 }
 
+// ---- host arithmetic of a step, shared by the host path and the device-driven path ---------
+// libclsph/sph_simulation.cpp:668-727 — fp32, same expressions.  Returns false when a grid
+// dimension reached 1024 (the reference asserts, :722-724).
+__host__ __device__ inline bool grid_from_bbox_hd(sphb_params& P, const float mn[3], const float mx[3]) {
+  const float side = (P.h * 2);
+  int32_t gs[3];
+  for (int a = 0; a < 3; ++a) {
+    P.min_point.s[a] = mn[a] - 2 * side;
+    P.max_point.s[a] = mx[a] + 2 * side;
+    gs[a] = (int32_t)static_cast<uint32_t>((P.max_point.s[a] - P.min_point.s[a]) / (side));
+  }
+  P.grid_size_x = gs[0]; P.grid_size_y = gs[1]; P.grid_size_z = gs[2];
+  if (!(gs[0] < 1024) || !(gs[1] < 1024) || !(gs[2] < 1024) || gs[0] < 0 || gs[1] < 0 || gs[2] < 0)
+    return false;
+  P.grid_cell_count = morton3((uint32_t)gs[0], (uint32_t)gs[1], (uint32_t)gs[2]);
+  return true;
+}
+
+// libclsph/sph_simulation.cpp:598-602 — fp32 arithmetic; comparisons against the double
+// literal 0.00001 as written.
+__host__ __device__ inline float dt_from_maxima(const sphb_params& P, float max_v2, float max_a2) {
+  float maxVel2 = max_v2;
+  float maxVel = sqrtf(max_v2);
+  float maxAccel = sqrtf(max_a2);
+  float dt = (sqrtf(2 * maxAccel * P.h + maxVel2) - maxVel) / (2 * maxAccel);
+  if (dt < 0.00001) dt = 0.00001;
+  if (dt > 1.0f / (P.target_fps) * P.simulation_scale) dt = 1.0f / (P.target_fps) * P.simulation_scale;
+  return dt;
+}
+
+__host__ __device__ inline StepConsts make_consts_hd(const sphb_params& P, const sphb_terms& T,
+                                                     float spiky_eps, uint32_t n) {
+  StepConsts c;
+  c.n = n;
+  c.grid_cell_count = P.grid_cell_count;
+  c.h = P.h;
+  c.h2 = P.h * P.h;
+  c.cell = (P.h * 2);
+  c.minx = P.min_point.s[0]; c.miny = P.min_point.s[1]; c.minz = P.min_point.s[2];
+  c.mass = P.particle_mass; c.K = P.K; c.rho0 = P.fluid_density; c.mu = P.dynamic_viscosity;
+  c.st_threshold = P.surface_tension_threshold; c.st = P.surface_tension;
+  c.gx = P.constant_acceleration.s[0]; c.gy = P.constant_acceleration.s[1];
+  c.gz = P.constant_acceleration.s[2];
+  c.c_poly6 = T.poly_6; c.c_poly6_grad = T.poly_6_gradient;
+  c.c_poly6_lap = T.poly_6_laplacian; c.c_spiky = T.spiky;
+  c.c_visc = T.viscosity;
+  c.spiky_eps = spiky_eps;
+  c.fnx = 2u * (uint32_t)P.grid_size_x;
+  c.fny = 2u * (uint32_t)P.grid_size_y;
+  c.fnz = 2u * (uint32_t)P.grid_size_z;
+  c.nfine = c.fnx * c.fny * c.fnz;
+  return c;
+}
+
+// ---- device-driven stepping (sphb_run_frame) ------------------------------------------------
+// What the host decides between two steps of the reference's sub-step loop
+// (libclsph/sph_simulation.cpp:384-409 and :246-260) — the next grid, whether the advection must
+// be repeated with a smaller dt, how much of the frame is left — is decided by one-thread
+// kernels instead, so a whole frame's steps are enqueued without a read-back.  Every kernel of
+// a queued step has fixed launch arguments: the step's constants reach it through a
+// __constant__ copy of QueueHot (refreshed by a device-to-device copy per step), dt and the
+// retry decision through the QueueCtl block in global memory.
+enum {
+  SPHB_Q_RUNNING = 0,   // the batch ended with the frame unfinished: enqueue more
+  SPHB_Q_DONE = 1,      // timeleft <= 0
+  SPHB_Q_GROW = 2,      // the next step's tables exceed their capacity: the host grows them
+  SPHB_Q_GRID = 3,      // a grid dimension reached 1024
+  SPHB_Q_ATTEMPTS = 4,  // the queued advection attempts did not settle dt: the host continues
+  SPHB_Q_BUDGET = 5     // the step budget (max_steps) is used up
+};
+struct QueueHot {
+  StepConsts c;
+  uint32_t active;  // the step's kernels run
+  uint32_t pad[3];
+};
+struct QueueCtl {
+  QueueHot hot;
+  sphb_params params;     // the reference's `parameters` as of the last step that started
+  sphb_terms terms;
+  float spiky_eps;
+  float dt;               // dt of the next advection attempt; between steps: the loop's `dt`
+  float timeleft;
+  uint32_t attempt;       // the next advection attempt runs
+  uint32_t status;        // SPHB_Q_*
+  uint32_t steps;         // steps completed since the block was seeded
+  uint32_t attempts;      // advection attempts of the current / last step
+  uint32_t budget;        // steps that may still start
+  uint32_t fcap, rcap;    // capacities of the two cell tables (entries)
+  uint32_t log_cap;       // entries of the timeleft log
+};
+// kernels_exact.cu / kernels_neighbors.cu each keep a __constant__ QueueHot; these enqueue the
+// device-to-device refresh from ctl->hot
+int queue_refresh_exact(const QueueCtl* ctl, cudaStream_t s);
+int queue_refresh_neighbors(const QueueCtl* ctl, cudaStream_t s);
+// one-thread kernels: before a step / after an advection attempt (`last`: no attempt follows)
+int launch_queue_plan(QueueCtl* ctl, const Reduce* red, cudaStream_t s);
+int launch_queue_attempt(QueueCtl* ctl, const Reduce* red, float* timeleft_log, int last, cudaStream_t s);
+
 // ---- launchers (each enqueues on `s` and returns the number of kernels launched) -------
 // kernels_exact.cu  (compiled with -fmad=false: results are those of the literal
 // expression trees, bit-identical to the CPU checker)
-int launch_reduce_init(Reduce* red, cudaStream_t s);
+int launch_reduce_init(Reduce* red, cudaStream_t s, const QueueCtl* q = nullptr);
 int launch_bbox(const float4* pos, uint32_t n, Reduce* red, cudaStream_t s);
 int launch_locate(const float4* pos, uint32_t* keys, const StepConsts& c, cudaStream_t s);
 // Counting sort by search cell (locate fused in): on return keys_sorted[d] = cell key of the
@@ -124,10 +222,10 @@ int launch_locate(const float4* pos, uint32_t* keys, const StepConsts& c, cudaSt
 // src_tmp: n-entry scratch.
 int launch_cell_sort(const float4* pos, const StepConsts& c, uint32_t* keys_tmp, uint32_t* slot_tmp,
                      uint32_t* ftable, uint32_t* scan_scratch, uint32_t* keys_sorted, uint32_t* src_tmp,
-                     uint32_t* perm, cudaStream_t s);
+                     uint32_t* perm, cudaStream_t s, bool queued = false, size_t table_entries = 0);
 int launch_reorder(const uint32_t* perm, uint32_t n, const float4* pos_in, const float4* vel_in,
                    const float4* vhf_in, const uint32_t* rank_in, float4* pos_out, float4* vel_out,
-                   float4* vhf_out, uint32_t* rank_out, cudaStream_t s);
+                   float4* vhf_out, uint32_t* rank_out, cudaStream_t s, bool queued = false);
 // fine cell table: ftable[f] = index of the first sorted particle whose fine key is >= f,
 // for f in [0, nfine]; ftable must hold nfine + 1 entries.  scratch: scan_scratch_entries().
 int launch_fine_table(const uint32_t* sorted_keys, uint32_t n, uint32_t* ftable, uint32_t nfine,
@@ -139,14 +237,15 @@ int launch_fine_table(const uint32_t* sorted_keys, uint32_t n, uint32_t* ftable,
 // (= position in the array the reference would hold after its stable sort by Morton key).
 int launch_reference_rank(const uint32_t* fine_keys, const uint32_t* ftable, const uint32_t* rank_prev,
                           uint32_t* ref_table, uint32_t* ckey, uint32_t* rank_new, const StepConsts& c,
-                          uint32_t* scratch, cudaStream_t s);
+                          uint32_t* scratch, cudaStream_t s, bool queued = false, size_t table_entries = 0);
 // keys_ref[rank[i]] = ckey[i], perm_ref[rank[i]] = rank_prev[i]
 int launch_reference_debug(const uint32_t* rank, const uint32_t* rank_prev, const uint32_t* ckey,
                            uint32_t n, uint32_t* keys_ref, uint32_t* perm_ref, cudaStream_t s);
 int launch_advect(const float4* pos, const float4* vhf, const float4* acc, float4* pos_out,
                   float4* vel_out, float4* vhf_out, uint32_t n, float dt, float restitution,
                   const Face* faces, uint32_t face_count, const float* df, Reduce* red,
-                  cudaStream_t s, const SlabAdvect* slab = nullptr, const FaceBin* bin = nullptr);
+                  cudaStream_t s, const SlabAdvect* slab = nullptr, const FaceBin* bin = nullptr,
+                  const QueueCtl* q = nullptr);
 int launch_distance_field(float* df, const Face* faces, const uint32_t* face_offsets,
                           const float* transforms, const float* rvertices, uint32_t face_count,
                           uint32_t gridcount, cudaStream_t s);
@@ -185,11 +284,11 @@ int launch_exclusive_max(uint32_t* data, uint32_t len, uint32_t* scratch, cudaSt
 size_t neighbor_list_entries(uint32_t n);
 int launch_density(float4* pos, float4* vel, const uint32_t* keys, const uint32_t* ftable,
                    float* rho, float* prs, uint16_t* nlist, uint8_t* ncount, const StepConsts& c,
-                   int variant, cudaStream_t s);
+                   int variant, cudaStream_t s, bool queued = false);
 int launch_forces(const float4* pos, const float4* vel, const uint32_t* keys,
                   const uint32_t* ftable, const float* rho, const uint16_t* nlist,
                   const uint8_t* ncount, float4* acc, const StepConsts& c, int variant,
-                  cudaStream_t s, const uint32_t* ghost_ids = nullptr);
+                  cudaStream_t s, const uint32_t* ghost_ids = nullptr, bool queued = false);
 
 // kernels_slab.cu — the slab-decomposed (multi-GPU) step
 size_t slab_message_bytes(uint32_t record_capacity);

@@ -12,6 +12,14 @@
 
 #include "engine_internal.cuh"
 
+namespace {
+constexpr uint32_t kQueueLog = 4096;  // timeleft log entries = most steps one batch may hold
+// Device-driven stepping pays where a step is short enough for the host round trip to show:
+// measured on a B200 (tools/ab_frame.py, ms per step, host round trip per step -> graph per step)
+// 0.355 -> 0.324 at 1 M particles, 1.169 -> 1.147 at 4.1 M, 4.716 -> 4.74 at 16.7 M.
+constexpr uint32_t kQueueAutoMax = 6000000;
+}  // namespace
+
 std::string& sphb_create_error_slot() {
   static thread_local std::string slot;
   return slot;
@@ -54,6 +62,10 @@ int sphb_destroy(sphb_engine* e) {
   cudaFree(e->bin_start); cudaFree(e->bin_faces);
   cudaFree(e->red);
   if (e->red_host) cudaFreeHost(e->red_host);
+  if (e->qgraph) cudaGraphExecDestroy(e->qgraph);
+  cudaFree(e->qctl); cudaFree(e->qlog);
+  if (e->qctl_host) cudaFreeHost(e->qctl_host);
+  if (e->qlog_host) cudaFreeHost(e->qlog_host);
   if (e->ev_created)
     for (int p = 0; p <= SPHB_PASS_COUNT; ++p) {
       cudaEventDestroy(e->ev[p][0]);
@@ -144,6 +156,10 @@ int sphb_create_with_capacity(const sphb_params* params, const sphb_terms* terms
   TRY_OR_DESTROY(dev_alloc(&e->sortb.block_sums, sort_block_sum_entries(n)));
   TRY_OR_DESTROY(dev_alloc(&e->red, 1));
   TRY_OR_DESTROY(cudaMallocHost(reinterpret_cast<void**>(&e->red_host), sizeof(Reduce)));
+  TRY_OR_DESTROY(dev_alloc(&e->qctl, 1));
+  TRY_OR_DESTROY(dev_alloc(&e->qlog, kQueueLog));
+  TRY_OR_DESTROY(cudaMallocHost(reinterpret_cast<void**>(&e->qctl_host), sizeof(QueueCtl)));
+  TRY_OR_DESTROY(cudaMallocHost(reinterpret_cast<void**>(&e->qlog_host), sizeof(float) * kQueueLog));
   for (int p = 0; p <= SPHB_PASS_COUNT; ++p) {
     TRY_OR_DESTROY(cudaEventCreate(&e->ev[p][0]));
     TRY_OR_DESTROY(cudaEventCreate(&e->ev[p][1]));
@@ -326,6 +342,221 @@ int sphb_upload(sphb_engine* e, const sphb_particle* aos, uint32_t n) {
 }
 
 
+}  // extern "C"
+
+namespace {
+// do { advection_collision(dt); computed = computeTimeStep } while (dt - computed > 1e-5)
+// (sph_simulation.cpp:246-260), from the post-forces state in the live half: one 32-byte
+// read-back per attempt.  `attempts_before`: attempts the device-driven path already made.
+int advect_until_settled(sphb_engine* e, float dt_first, int attempts_before, float* computed_out) {
+  cudaStream_t s = e->stream;
+  int attempts = attempts_before;
+  float dt = dt_first, computed = dt_first;
+  const int in = e->cur, out = in ^ 1;
+  do {
+    dt = computed;
+    {
+      PassTimer t(e, SPHB_PASS_ADVECT);
+      int l = launch_reduce_init(e->red, s);
+      l += launch_advect(e->pos[in], e->vhf[in], e->acc, e->pos[out], e->vel[out], e->vhf[out], e->n,
+                         dt, e->params.restitution, e->faces, e->face_count, e->df, e->red, s, nullptr, &e->bin);
+      t.done(l);
+    }
+    CUDA_TRY(e, cudaGetLastError());
+    if (int rc = fetch_reduce(e)) return rc;
+    if (e->profile) accumulate_pass(e, SPHB_PASS_ADVECT);
+    ++attempts;
+    computed = dt_from_maxima(e->params, dec_float(e->red_host->max_v2), dec_float(e->red_host->max_a2));
+  } while (dt - computed > 0.00001);
+  e->cur = out;
+  e->bbox_valid = true;
+  e->last_attempts = attempts;
+  e->stepped = true;
+  *computed_out = computed;
+  return 0;
+}
+
+// One device-driven step (common.cuh: QueueCtl): the launches of sphb_step with every argument
+// fixed — the grid, dt and the retry decision come from e->qctl.  Leaves e->cur as it was (the
+// reorder and the advection flip it once each).
+int enqueue_queued_step(sphb_engine* e) {
+  cudaStream_t s = e->stream;
+  const StepConsts c = make_consts(e);  // only c.n shapes the launches; the kernels read g_hot
+  SortBuffers& b = e->sortb;
+  const int in = e->cur, mid = in ^ 1;
+  int l = launch_queue_plan(e->qctl, e->red, s);
+  CUDA_TRY(e, (cudaError_t)queue_refresh_exact(e->qctl, s));
+  CUDA_TRY(e, (cudaError_t)queue_refresh_neighbors(e->qctl, s));
+  l += launch_cell_sort(e->pos[in], c, b.keys[0], b.vals[0], e->ftable, e->scan_scratch, b.keys[1], b.vals[1],
+                        b.vals[0], s, true, e->ftable_cap);
+  const uint32_t* skeys = b.keys[1];
+  const uint32_t* perm = b.vals[0];
+  l += launch_reorder(perm, e->n, e->pos[in], e->vel[in], e->vhf[in], e->rank_cur, e->pos[mid], e->vel[mid],
+                      e->vhf[mid], e->rank_prev, s, true);
+  cudaStream_t rs = e->use_side_stream ? e->side : s;
+  if (e->use_side_stream) {
+    CUDA_TRY(e, cudaEventRecord(e->ev_fork, s));
+    CUDA_TRY(e, cudaStreamWaitEvent(e->side, e->ev_fork, 0));
+  }
+  l += launch_reference_rank(skeys, e->ftable, e->rank_prev, e->ref_table, e->ckey, e->rank_cur, c,
+                             e->scan_scratch, rs, true, e->ref_table_cap);
+  if (e->use_side_stream) CUDA_TRY(e, cudaEventRecord(e->ev_join, e->side));
+  l += launch_density(e->pos[mid], e->vel[mid], skeys, e->ftable, e->rho, e->prs, e->nlist, e->ncount, c, 0, s,
+                      true);
+  l += launch_forces(e->pos[mid], e->vel[mid], skeys, e->ftable, e->rho, e->nlist, e->ncount, e->acc, c, 0, s,
+                     nullptr, true);
+  if (e->use_side_stream) CUDA_TRY(e, cudaStreamWaitEvent(s, e->ev_join, 0));
+  for (int a = 0; a < e->queued_attempts; ++a) {
+    l += launch_reduce_init(e->red, s, e->qctl);
+    l += launch_advect(e->pos[mid], e->vhf[mid], e->acc, e->pos[in], e->vel[in], e->vhf[in], e->n, 0.f,
+                       e->params.restitution, e->faces, e->face_count, e->df, e->red, s, nullptr, &e->bin,
+                       e->qctl);
+    l += launch_queue_attempt(e->qctl, e->red, e->qlog, a + 1 == e->queued_attempts, s);
+  }
+  CUDA_TRY(e, cudaGetLastError());
+  e->launches += l;
+  return 0;
+}
+
+// The same step as one CUDA graph launch; re-captured when an argument it froze has changed.
+int launch_queued_graph(sphb_engine* e) {
+  const uint64_t key[8] = {(uint64_t)(uintptr_t)e->ftable, (uint64_t)(uintptr_t)e->ref_table,
+                           (uint64_t)e->ftable_cap, (uint64_t)e->ref_table_cap,
+                           (uint64_t)(uintptr_t)e->scan_scratch, (uint64_t)(uintptr_t)e->df,
+                           (uint64_t)(uintptr_t)e->bin.start,
+                           ((uint64_t)e->face_count << 8) | ((uint64_t)e->queued_attempts << 4) |
+                               ((uint64_t)e->cur << 1) | (e->use_side_stream ? 1u : 0u)};
+  if (!e->qgraph || memcmp(key, e->qgraph_key, sizeof key) != 0) {
+    if (e->qgraph) cudaGraphExecDestroy(e->qgraph);
+    e->qgraph = nullptr;
+    cudaGraph_t g = nullptr;
+    const uint64_t before = e->launches;
+    CUDA_TRY(e, cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeThreadLocal));
+    const int rc = enqueue_queued_step(e);
+    const cudaError_t end = cudaStreamEndCapture(e->stream, &g);
+    e->qgraph_launches = (uint32_t)(e->launches - before);
+    e->launches = before;
+    if (rc) {
+      if (g) cudaGraphDestroy(g);
+      return rc;
+    }
+    CUDA_TRY(e, end);
+    const cudaError_t inst = cudaGraphInstantiate(&e->qgraph, g, 0);
+    cudaGraphDestroy(g);
+    CUDA_TRY(e, inst);
+    memcpy(e->qgraph_key, key, sizeof key);
+  }
+  CUDA_TRY(e, cudaGraphLaunch(e->qgraph, e->stream));
+  e->launches += e->qgraph_launches;
+  return 0;
+}
+}  // namespace
+
+extern "C" {
+
+// The sub-step loop of one frame (libclsph/sph_simulation.cpp:384-409):
+//   while (timeleft > 0) { dt = simulate_single_frame(dt); timeleft -= dt; if (timeleft < dt) dt = timeleft; }
+// The steps are enqueued in batches without a host round trip between them: the grid of the
+// next step, dt and the advection retry are decided on the device (common.cuh: QueueCtl).
+int sphb_run_frame(sphb_engine* e, float dt_in, float frame_time, uint64_t max_steps, float* dt_out,
+                   uint32_t* steps_out, float* timeleft_log, uint32_t log_cap) {
+  if (!e) return SPHB_ERR_INVALID;
+  if (!e->have_state) SPHB_FAIL(e, SPHB_ERR_INVALID, "sphb_run_frame before sphb_upload");
+  if (!e->have_scene) SPHB_FAIL(e, SPHB_ERR_NO_SCENE, "sphb_run_frame before sphb_set_scene");
+  if (e->slab) SPHB_FAIL(e, SPHB_ERR_INVALID, "sphb_run_frame on a slab engine (use sphb_slab_step)");
+  CUDA_TRY(e, cudaSetDevice(e->device));
+  float dt = dt_in, timeleft = frame_time;
+  uint64_t steps = 0;
+  auto finish_step = [&](float computed) {  // the caller's half of the loop
+    dt = computed;
+    timeleft -= dt;
+    if (timeleft < dt) dt = timeleft;
+    if (timeleft_log && steps < log_cap) timeleft_log[steps] = timeleft;
+    ++steps;
+  };
+  while (timeleft > 0.0) {
+    if (max_steps && steps >= max_steps) break;
+    const bool want_queue = e->use_queue == 1 || (e->use_queue == 2 && e->n <= kQueueAutoMax);
+    const bool can_queue = want_queue && e->bbox_valid && e->sort_variant == 0 && e->neighbor_variant == 0 &&
+                           !e->profile && e->ftable_cap && e->ref_table_cap && e->scan_scratch;
+    if (!can_queue) {  // the first step after an upload (its bbox needs a pass of its own), or an option
+      float computed = dt;
+      if (int rc = sphb_step(e, dt, &computed)) return rc;
+      finish_step(computed);
+      continue;
+    }
+    // dt never exceeds simulation_scale / target_fps, so the frame needs at least this many steps
+    const float dt_cap = 1.0f / e->params.target_fps * e->params.simulation_scale;
+    double want = dt_cap > 0.f ? ceil((double)timeleft / (double)dt_cap) : 1.0;
+    if (!(want >= 1.0)) want = 1.0;
+    if (want > 64.0) want = 64.0;
+    uint32_t batch = (uint32_t)want;
+    if (max_steps && (uint64_t)batch > max_steps - steps) batch = (uint32_t)(max_steps - steps);
+    QueueCtl& h = *e->qctl_host;
+    memset(&h, 0, sizeof h);
+    h.hot.c = make_consts(e);
+    h.params = e->params;
+    h.terms = e->terms;
+    h.spiky_eps = e->spiky_eps;
+    h.dt = dt;
+    h.timeleft = timeleft;
+    h.status = SPHB_Q_RUNNING;
+    h.budget = batch;
+    h.fcap = (uint32_t)(e->ftable_cap > 0xFFFFFFFFull ? 0xFFFFFFFFull : e->ftable_cap);
+    h.rcap = (uint32_t)(e->ref_table_cap > 0xFFFFFFFFull ? 0xFFFFFFFFull : e->ref_table_cap);
+    h.log_cap = kQueueLog;
+    cudaStream_t s = e->stream;
+    CUDA_TRY(e, cudaMemcpyAsync(e->qctl, &h, sizeof h, cudaMemcpyHostToDevice, s));
+    for (uint32_t k = 0; k < batch; ++k)
+      if (int rc = e->use_graph ? launch_queued_graph(e) : enqueue_queued_step(e)) return rc;
+    CUDA_TRY(e, cudaMemcpyAsync(&h, e->qctl, sizeof h, cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(e, cudaMemcpyAsync(e->qlog_host, e->qlog, sizeof(float) * batch, cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(e, cudaMemcpyAsync(e->red_host, e->red, sizeof(Reduce), cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(e, cudaStreamSynchronize(s));
+    // bookkeeping sphb_step would have done
+    e->sorted = 1;
+    e->free_keys = e->sortb.keys[0];
+    e->free_vals = e->sortb.vals[1];
+    e->params = h.params;
+    for (uint32_t k = 0; k < h.steps; ++k) {
+      if (timeleft_log && steps < log_cap) timeleft_log[steps] = e->qlog_host[k];
+      ++steps;
+    }
+    if (h.steps) {
+      e->stepped = true;
+      e->last_attempts = (int)h.attempts;
+      e->queued_steps += h.steps;
+    }
+    dt = h.dt;
+    timeleft = h.timeleft;
+    switch (h.status) {
+      case SPHB_Q_GRID:
+        SPHB_FAIL(e, SPHB_ERR_GRID, "grid %d x %d x %d: a dimension reached 1024 (the reference asserts, "
+                  "sph_simulation.cpp:722-724)", e->params.grid_size_x, e->params.grid_size_y, e->params.grid_size_z);
+      case SPHB_Q_GROW: {  // one host-driven step: it grows the tables
+        float computed = dt;
+        if (int rc = sphb_step(e, dt, &computed)) return rc;
+        finish_step(computed);
+        break;
+      }
+      case SPHB_Q_ATTEMPTS: {  // forces are done; the advection goes on from the host
+        float computed = dt;
+        e->cur ^= 1;  // the reordered half is live, as in sphb_step after the reorder
+        if (int rc = advect_until_settled(e, dt, (int)h.attempts, &computed)) return rc;
+        finish_step(computed);
+        break;
+      }
+      default:
+        break;
+    }
+  }
+  if (dt_out) *dt_out = dt;
+  if (steps_out) *steps_out = (uint32_t)steps;
+  return 0;
+}
+
+uint64_t sphb_queued_steps(sphb_engine* e) { return e ? e->queued_steps : 0; }
+
 int sphb_step(sphb_engine* e, float dt_in, float* dt_out) {
   if (!e) return SPHB_ERR_INVALID;
   if (!e->have_state) SPHB_FAIL(e, SPHB_ERR_INVALID, "sphb_step before sphb_upload");
@@ -401,29 +632,8 @@ int sphb_step(sphb_engine* e, float dt_in, float* dt_out) {
   CUDA_TRY(e, cudaGetLastError());
 
   // 6. do { advection_collision(dt); computed = computeTimeStep } while (dt - computed > 1e-5)
-  //    (sph_simulation.cpp:246-260)
-  int attempts = 0;
-  float dt = dt_in, computed = dt_in;
-  const int in = e->cur, out = in ^ 1;
-  do {
-    dt = computed;
-    {
-      PassTimer t(e, SPHB_PASS_ADVECT);
-      int l = launch_reduce_init(e->red, s);
-      l += launch_advect(e->pos[in], e->vhf[in], e->acc, e->pos[out], e->vel[out], e->vhf[out], n,
-                         dt, e->params.restitution, e->faces, e->face_count, e->df, e->red, s, nullptr, &e->bin);
-      t.done(l);
-    }
-    CUDA_TRY(e, cudaGetLastError());
-    if (int rc = fetch_reduce(e)) return rc;
-    if (e->profile) accumulate_pass(e, SPHB_PASS_ADVECT);
-    ++attempts;
-    computed = dt_from_maxima(e->params, dec_float(e->red_host->max_v2), dec_float(e->red_host->max_a2));
-  } while (dt - computed > 0.00001);
-  e->cur = out;
-  e->bbox_valid = true;
-  e->last_attempts = attempts;
-  e->stepped = true;
+  float computed = dt_in;
+  if (int rc = advect_until_settled(e, dt_in, 0, &computed)) return rc;
   if (e->profile) {
     if (ran_bbox) accumulate_pass(e, SPHB_PASS_BBOX);
     for (int p = SPHB_PASS_LOCATE; p < SPHB_PASS_COUNT; ++p)
@@ -606,6 +816,22 @@ int sphb_set_option(sphb_engine* e, const char* name, int value) {
   }
   if (!strcmp(name, "neighbor_kernel")) {
     e->neighbor_variant = value;
+    return 0;
+  }
+  if (!strcmp(name, "device_loop")) {  // sphb_run_frame: 0 = one host round trip per step
+    e->use_queue = value < 0 || value > 2 ? 2 : value;
+    return 0;
+  }
+  if (!strcmp(name, "queued_attempts")) {  // advection attempts enqueued per device-driven step
+    e->queued_attempts = value < 1 ? 1 : (value > 4 ? 4 : value);
+    return 0;
+  }
+  if (!strcmp(name, "table_headroom")) {  // 0: cell tables are allocated without spare entries
+    e->table_headroom = value != 0;
+    return 0;
+  }
+  if (!strcmp(name, "graph")) {  // sphb_run_frame: a device-driven step is one CUDA graph launch
+    e->use_graph = value != 0;
     return 0;
   }
   if (!strcmp(name, "side_stream")) {

@@ -106,6 +106,20 @@ struct sphb_engine {
   int last_attempts = 0;
   bool stepped = false;
 
+  // device-driven stepping (sphb_run_frame; common.cuh: QueueCtl)
+  QueueCtl* qctl = nullptr;       // device
+  QueueCtl* qctl_host = nullptr;  // pinned
+  float* qlog = nullptr;          // device: timeleft after every step of a batch
+  float* qlog_host = nullptr;     // pinned
+  int use_queue = 2;              // option "device_loop": 0 off, 1 on, 2 = on below kQueueAutoMax particles
+  bool use_graph = true;          // option "graph": a queued step is one CUDA graph launch
+  int queued_attempts = 2;        // option "queued_attempts": advection attempts enqueued per step
+  bool table_headroom = true;     // option "table_headroom": cell tables keep 1.5x spare entries
+  cudaGraphExec_t qgraph = nullptr;
+  uint32_t qgraph_launches = 0;   // kernels inside the captured step
+  uint64_t qgraph_key[8] = {};    // what the captured step's launch arguments depend on
+  uint64_t queued_steps = 0;      // steps that ran without a host round trip
+
   // options / measurement
   int neighbor_variant = 0;
   bool profile = false;
@@ -161,59 +175,16 @@ cudaError_t dev_alloc(T** p, size_t count) {
   return cudaMalloc(reinterpret_cast<void**>(p), sizeof(T) * (count ? count : 1));
 }
 
-// libclsph/sph_simulation.cpp:668-727 — host fp32 arithmetic, same expressions.
+// libclsph/sph_simulation.cpp:668-727 (arithmetic in common.cuh: grid_from_bbox_hd)
 int grid_from_bbox(sphb_engine* e, const float mn[3], const float mx[3]) {
   sphb_params& P = e->params;
-  const float side = (P.h * 2);
-  int32_t* gs[3] = {&P.grid_size_x, &P.grid_size_y, &P.grid_size_z};
-  for (int a = 0; a < 3; ++a) {
-    P.min_point.s[a] = mn[a] - 2 * side;
-    P.max_point.s[a] = mx[a] + 2 * side;
-    *gs[a] = (int32_t)static_cast<uint32_t>((P.max_point.s[a] - P.min_point.s[a]) / (side));
-  }
-  if (!(P.grid_size_x < 1024) || !(P.grid_size_y < 1024) || !(P.grid_size_z < 1024) ||
-      P.grid_size_x < 0 || P.grid_size_y < 0 || P.grid_size_z < 0)
+  if (!grid_from_bbox_hd(P, mn, mx))
     SPHB_FAIL(e, SPHB_ERR_GRID, "grid %d x %d x %d: a dimension reached 1024 (the reference asserts, "
               "sph_simulation.cpp:722-724)", P.grid_size_x, P.grid_size_y, P.grid_size_z);
-  P.grid_cell_count = morton3((uint32_t)P.grid_size_x, (uint32_t)P.grid_size_y, (uint32_t)P.grid_size_z);
   return 0;
 }
 
-// libclsph/sph_simulation.cpp:598-602 — host fp32 arithmetic; comparisons against the
-// double literal 0.00001 as written.
-float dt_from_maxima(const sphb_params& P, float max_v2, float max_a2) {
-  float maxVel2 = max_v2;
-  float maxVel = std::sqrt(max_v2);
-  float maxAccel = std::sqrt(max_a2);
-  float dt = (std::sqrt(2 * maxAccel * P.h + maxVel2) - maxVel) / (2 * maxAccel);
-  if (dt < 0.00001) dt = 0.00001;
-  if (dt > 1.0f / (P.target_fps) * P.simulation_scale) dt = 1.0f / (P.target_fps) * P.simulation_scale;
-  return dt;
-}
-
-StepConsts make_consts(const sphb_engine* e) {
-  const sphb_params& P = e->params;
-  StepConsts c;
-  c.n = e->n;
-  c.grid_cell_count = P.grid_cell_count;
-  c.h = P.h;
-  c.h2 = P.h * P.h;
-  c.cell = (P.h * 2);
-  c.minx = P.min_point.s[0]; c.miny = P.min_point.s[1]; c.minz = P.min_point.s[2];
-  c.mass = P.particle_mass; c.K = P.K; c.rho0 = P.fluid_density; c.mu = P.dynamic_viscosity;
-  c.st_threshold = P.surface_tension_threshold; c.st = P.surface_tension;
-  c.gx = P.constant_acceleration.s[0]; c.gy = P.constant_acceleration.s[1];
-  c.gz = P.constant_acceleration.s[2];
-  c.c_poly6 = e->terms.poly_6; c.c_poly6_grad = e->terms.poly_6_gradient;
-  c.c_poly6_lap = e->terms.poly_6_laplacian; c.c_spiky = e->terms.spiky;
-  c.c_visc = e->terms.viscosity;
-  c.spiky_eps = e->spiky_eps;
-  c.fnx = 2u * (uint32_t)P.grid_size_x;
-  c.fny = 2u * (uint32_t)P.grid_size_y;
-  c.fnz = 2u * (uint32_t)P.grid_size_z;
-  c.nfine = c.fnx * c.fny * c.fnz;
-  return c;
-}
+StepConsts make_consts(const sphb_engine* e) { return make_consts_hd(e->params, e->terms, e->spiky_eps, e->n); }
 
 struct PassTimer {
   sphb_engine* e;
@@ -260,13 +231,13 @@ int ensure_tables(sphb_engine* e, size_t fine_entries, size_t ref_entries) {
   if (grow_f) {
     cudaFree(e->ftable);
     e->ftable = nullptr;
-    e->ftable_cap = fine_entries + fine_entries / 2 + 1024;
+    e->ftable_cap = e->table_headroom ? fine_entries + fine_entries / 2 + 1024 : fine_entries;
     CUDA_TRY(e, dev_alloc(&e->ftable, e->ftable_cap));
   }
   if (grow_r) {
     cudaFree(e->ref_table);
     e->ref_table = nullptr;
-    e->ref_table_cap = ref_entries + ref_entries / 2 + 1024;
+    e->ref_table_cap = e->table_headroom ? ref_entries + ref_entries / 2 + 1024 : ref_entries;
     CUDA_TRY(e, dev_alloc(&e->ref_table, e->ref_table_cap));
   }
   size_t longest = e->ftable_cap > e->ref_table_cap ? e->ftable_cap : e->ref_table_cap;

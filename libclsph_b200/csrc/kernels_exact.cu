@@ -14,6 +14,15 @@ namespace {
 
 constexpr int kBlock = 256;
 
+// Device-driven stepping (common.cuh: QueueCtl): a queued step's kernels (template argument
+// Q = true) take their constants from this copy, refreshed per step by queue_refresh_exact, and
+// return at once when the step is not to run.  Q = false is the host-driven path: constants by
+// value, no checks.
+__constant__ QueueHot g_hot;
+#define SPHB_Q_PROLOGUE(c)               \
+  if (Q && !g_hot.active) return;        \
+  const StepConsts& cc = Q ? g_hot.c : (c)
+
 __device__ __forceinline__ float warp_min(float v) {
   for (int o = 16; o > 0; o >>= 1) v = fminf(v, __shfl_xor_sync(0xffffffffu, v, o));
   return v;
@@ -52,7 +61,9 @@ __device__ __forceinline__ void block_reduce_to(Reduce* red, float (&vals)[8], u
   }
 }
 
-__global__ void k_reduce_init(Reduce* red) {
+template <bool Q>
+__global__ void k_reduce_init(Reduce* red, const QueueCtl* q) {
+  if (Q && !q->attempt) return;
   if (threadIdx.x == 0) {
     for (int a = 0; a < 3; ++a) {
       red->min_enc[a] = enc_float(INFINITY);
@@ -113,12 +124,14 @@ __global__ void __launch_bounds__(kBlock) k_locate(const float4* __restrict__ po
 // canonicalisation that orders each cell's members by their previous index, so that the
 // result is exactly the stable sort a radix sort would give (atomics decide the slots, so
 // without it the order inside a cell would vary from run to run).
+template <bool Q>
 __global__ void __launch_bounds__(kBlock)
     k_locate_count(const float4* __restrict__ pos, uint32_t* __restrict__ keys, uint32_t* __restrict__ slot,
                    uint32_t* __restrict__ count, StepConsts c) {
+  SPHB_Q_PROLOGUE(c);
   const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
-  const bool valid = i < c.n;
-  const uint32_t key = valid ? fine_key_of(__ldg(pos + i), c) : 0xFFFFFFFFu;
+  const bool valid = i < cc.n;
+  const uint32_t key = valid ? fine_key_of(__ldg(pos + i), cc) : 0xFFFFFFFFu;
   const unsigned peers = __match_any_sync(0xffffffffu, key);
   const int lane = threadIdx.x & 31;
   const int leader = __ffs(peers) - 1;
@@ -131,10 +144,12 @@ __global__ void __launch_bounds__(kBlock)
   }
 }
 
+template <bool Q>
 __global__ void __launch_bounds__(kBlock)
     k_place(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ slot,
             const uint32_t* __restrict__ start, uint32_t n, uint32_t* __restrict__ keys_sorted,
             uint32_t* __restrict__ src_tmp) {
+  if (Q && !g_hot.active) return;
   const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
   if (i >= n) return;
   const uint32_t key = __ldg(keys + i);
@@ -143,9 +158,11 @@ __global__ void __launch_bounds__(kBlock)
   src_tmp[d] = i;
 }
 
+template <bool Q>
 __global__ void __launch_bounds__(kBlock)
     k_canonical_order(const uint32_t* __restrict__ keys_sorted, const uint32_t* __restrict__ src_tmp,
                       const uint32_t* __restrict__ start, uint32_t n, uint32_t* __restrict__ perm) {
+  if (Q && !g_hot.active) return;
   const uint32_t d = blockIdx.x * kBlock + threadIdx.x;
   if (d >= n) return;
   const uint32_t key = __ldg(keys_sorted + d);
@@ -160,12 +177,14 @@ __global__ void __launch_bounds__(kBlock)
 // (kernels/sort.cl:41-59); here only (key, index) pairs are sorted and the carried state
 // (position, velocity, intermediate_velocity: 36 of the 80 bytes, + the 4-byte reference
 // rank) is gathered ONCE.
+template <bool Q>
 __global__ void __launch_bounds__(kBlock)
     k_reorder(const uint32_t* __restrict__ perm, uint32_t n, const float4* __restrict__ pos_in,
               const float4* __restrict__ vel_in, const float4* __restrict__ vhf_in,
               const uint32_t* __restrict__ rank_in, float4* __restrict__ pos_out,
               float4* __restrict__ vel_out, float4* __restrict__ vhf_out,
               uint32_t* __restrict__ rank_out) {
+  if (Q && !g_hot.active) return;
   const uint32_t k = blockIdx.x * kBlock + threadIdx.x;
   if (k >= n) return;
   const uint32_t src = __ldg(perm + k);
@@ -202,37 +221,41 @@ __device__ __forceinline__ void fine_coords_of(uint32_t key, const StepConsts& c
 }
 
 // histogram over Morton cells; lanes of a warp that share a cell add once
+template <bool Q>
 __global__ void __launch_bounds__(kBlock)
     k_morton_hist(const uint32_t* __restrict__ fine_keys, uint32_t* __restrict__ hist,
                   uint32_t* __restrict__ ckey, StepConsts c) {
+  SPHB_Q_PROLOGUE(c);
   const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
-  const bool valid = i < c.n;
+  const bool valid = i < cc.n;
   uint32_t m = 0xFFFFFFFFu;
   if (valid) {
     uint32_t fx, fy, fz;
-    fine_coords_of(__ldg(fine_keys + i), c, fx, fy, fz);
+    fine_coords_of(__ldg(fine_keys + i), cc, fx, fy, fz);
     m = morton3(fx >> 1, fy >> 1, fz >> 1);
     ckey[i] = m;
   }
   const unsigned peers = __match_any_sync(0xffffffffu, m);
   const int lane = threadIdx.x & 31;
-  if (valid && lane == __ffs(peers) - 1 && m < c.grid_cell_count) atomicAdd(hist + m, __popc(peers));
+  if (valid && lane == __ffs(peers) - 1 && m < cc.grid_cell_count) atomicAdd(hist + m, __popc(peers));
 }
 
 // One thread per PAIR of consecutive particles: they share their Morton cell nine times out of
 // ten, and then every previous rank that is loaded serves two comparisons.  A pair that straddles
 // two cells is walked twice, one particle at a time.
+template <bool Q>
 __global__ void __launch_bounds__(kBlock)
     k_reference_rank(const uint32_t* __restrict__ fine_keys, const uint32_t* __restrict__ ftable,
                      const uint32_t* __restrict__ rank_prev, const uint32_t* __restrict__ ref_table,
                      uint32_t* __restrict__ rank_new, StepConsts c) {
+  SPHB_Q_PROLOGUE(c);
   const uint32_t ia = 2u * (blockIdx.x * kBlock + threadIdx.x);
-  if (ia >= c.n) return;
-  const bool has_b = ia + 1 < c.n;
+  if (ia >= cc.n) return;
+  const bool has_b = ia + 1 < cc.n;
   const uint32_t ib = has_b ? ia + 1 : ia;
   uint32_t fx[2], fy[2], fz[2], m[2];
-  fine_coords_of(__ldg(fine_keys + ia), c, fx[0], fy[0], fz[0]);
-  fine_coords_of(__ldg(fine_keys + ib), c, fx[1], fy[1], fz[1]);
+  fine_coords_of(__ldg(fine_keys + ia), cc, fx[0], fy[0], fz[0]);
+  fine_coords_of(__ldg(fine_keys + ib), cc, fx[1], fy[1], fz[1]);
 #pragma unroll
   for (int w = 0; w < 2; ++w) m[w] = morton3(fx[w] >> 1, fy[w] >> 1, fz[w] >> 1);
   const uint32_t mine_a = __ldg(rank_prev + ia), mine_b = __ldg(rank_prev + ib);
@@ -247,7 +270,7 @@ __global__ void __launch_bounds__(kBlock)
     uint32_t rs[4], re[4];
 #pragma unroll
     for (uint32_t k = 0; k < 4; ++k) {
-      const uint32_t row = ((z0 + (k >> 1)) * c.fny + (y0 + (k & 1u))) * c.fnx + x0;
+      const uint32_t row = ((z0 + (k >> 1)) * cc.fny + (y0 + (k & 1u))) * cc.fnx + x0;
       rs[k] = __ldg(ftable + row);
       re[k] = __ldg(ftable + row + 2);
     }
@@ -267,8 +290,8 @@ __global__ void __launch_bounds__(kBlock)
       }
     }
   }
-  rank_new[ia] = (m[0] < c.grid_cell_count ? __ldg(ref_table + m[0]) : 0u) + before_a;
-  if (has_b) rank_new[ib] = (m[1] < c.grid_cell_count ? __ldg(ref_table + m[1]) : 0u) + before_b;
+  rank_new[ia] = (m[0] < cc.grid_cell_count ? __ldg(ref_table + m[0]) : 0u) + before_a;
+  if (has_b) rank_new[ib] = (m[1] < cc.grid_cell_count ? __ldg(ref_table + m[1]) : 0u) + before_b;
 }
 
 __global__ void __launch_bounds__(kBlock)
@@ -302,12 +325,18 @@ __device__ __forceinline__ float len3(float x, float y, float z) {
 // collisionsv2.cl:249-336 (handle_collisions) + :9-22 (respond), with the reductions of
 // computeTimeStep (reduction.cl:66-124) and of the NEXT step's findMinMaxPosition
 // (reduction.cl:2-64) fused in, so that a step ends with one 32-byte read-back.
+template <bool Q>
 __global__ void __launch_bounds__(kBlock)
     k_advect(const float4* __restrict__ pos, const float4* __restrict__ vhf,
              const float4* __restrict__ acc, float4* __restrict__ pos_out,
              float4* __restrict__ vel_out, float4* __restrict__ vhf_out, uint32_t n, float dt,
              float restitution, const Face* __restrict__ faces, uint32_t face_count,
-             const float* __restrict__ df, Reduce* red, SlabAdvect slab, FaceBin bin) {
+             const float* __restrict__ df, Reduce* red, SlabAdvect slab, FaceBin bin,
+             const QueueCtl* __restrict__ q) {
+  if (Q) {  // device-driven: this attempt runs only if the last one did not settle dt
+    if (!q->attempt) return;
+    dt = q->dt;
+  }
   // grid-stride over a grid sized to the machine: one set of 8 atomics per CTA, not per 256
   // particles (65 536 CTAs hammering the same 8 words serialise in L2)
   float rv[8] = {INFINITY, INFINITY, INFINITY, -INFINITY, -INFINITY, -INFINITY, -INFINITY, -INFINITY};
@@ -530,9 +559,102 @@ inline unsigned blocks_for(uint32_t n) { return (n + kBlock - 1) / kBlock; }
 
 }  // namespace
 
-int launch_reduce_init(Reduce* red, cudaStream_t s) {
-  k_reduce_init<<<1, 32, 0, s>>>(red);
+int launch_reduce_init(Reduce* red, cudaStream_t s, const QueueCtl* q) {
+  if (q) k_reduce_init<true><<<1, 32, 0, s>>>(red, q);
+  else k_reduce_init<false><<<1, 32, 0, s>>>(red, nullptr);
   return 1;
+}
+
+// ---- device-driven stepping: the two one-thread kernels that stand in for the host ----------
+__global__ void k_queue_plan(QueueCtl* q, const Reduce* __restrict__ red) {
+  if (threadIdx.x) return;
+  q->hot.active = 0;
+  q->attempt = 0;
+  if (q->status != SPHB_Q_RUNNING) return;
+  if (!(q->timeleft > 0.0)) {  // while (timeleft > 0.0), sph_simulation.cpp:384
+    q->status = SPHB_Q_DONE;
+    return;
+  }
+  if (q->budget == 0) {
+    q->status = SPHB_Q_BUDGET;
+    return;
+  }
+  // findMinMaxPosition's host half (:668-727) on the bbox the last advection reduced
+  float mn[3], mx[3];
+  for (int a = 0; a < 3; ++a) {
+    mn[a] = dec_float(red->min_enc[a]);
+    mx[a] = dec_float(red->max_enc[a]);
+  }
+  sphb_params P = q->params;
+  if (!grid_from_bbox_hd(P, mn, mx)) {
+    q->params = P;
+    q->status = SPHB_Q_GRID;
+    return;
+  }
+  const StepConsts c = make_consts_hd(P, q->terms, q->spiky_eps, q->hot.c.n);
+  const unsigned long long fine = (unsigned long long)c.fnx * c.fny * c.fnz + 1ull;
+  if (fine > q->fcap || (unsigned long long)P.grid_cell_count + 1ull > q->rcap) {
+    q->status = SPHB_Q_GROW;  // nothing of this step has been committed
+    return;
+  }
+  q->params = P;
+  q->hot.c = c;
+  q->hot.active = 1;
+  q->attempt = 1;
+  q->attempts = 0;
+  q->budget -= 1;
+}
+
+__global__ void k_queue_attempt(QueueCtl* q, const Reduce* __restrict__ red, float* __restrict__ log, int last) {
+  if (threadIdx.x) return;
+  if (!q->attempt) return;
+  // computeTimeStep's host half (:598-602) and the retry test (:260)
+  const float dt = q->dt;
+  const float computed = dt_from_maxima(q->params, dec_float(red->max_v2), dec_float(red->max_a2));
+  q->attempts += 1;
+  if (dt - computed > 0.00001) {
+    q->dt = computed;  // the next attempt's dt
+    if (last) {
+      q->status = SPHB_Q_ATTEMPTS;
+      q->attempt = 0;
+    }
+    return;
+  }
+  // the step is done; the caller's loop (:390-394)
+  q->attempt = 0;
+  float timeleft = q->timeleft;
+  float next = computed;
+  timeleft -= next;
+  if (timeleft < next) next = timeleft;
+  q->timeleft = timeleft;
+  q->dt = next;
+  if (q->steps < q->log_cap) log[q->steps] = timeleft;
+  q->steps += 1;
+}
+
+int launch_queue_plan(QueueCtl* ctl, const Reduce* red, cudaStream_t s) {
+  k_queue_plan<<<1, 32, 0, s>>>(ctl, red);
+  return 1;
+}
+
+int launch_queue_attempt(QueueCtl* ctl, const Reduce* red, float* timeleft_log, int last, cudaStream_t s) {
+  k_queue_attempt<<<1, 32, 0, s>>>(ctl, red, timeleft_log, last);
+  return 1;
+}
+
+int queue_refresh_exact(const QueueCtl* ctl, cudaStream_t s) {
+  // the symbol's address is looked up once per device: a plain device-to-device copy after that
+  static thread_local void* addr[64] = {};
+  int dev = 0;
+  cudaError_t err = cudaGetDevice(&dev);
+  if (err != cudaSuccess) return (int)err;
+  void* local = nullptr;
+  void*& slot = (dev >= 0 && dev < 64) ? addr[dev] : local;
+  if (!slot) {
+    err = cudaGetSymbolAddress(&slot, g_hot);
+    if (err != cudaSuccess) return (int)err;
+  }
+  return (int)cudaMemcpyAsync(slot, &ctl->hot, sizeof(QueueHot), cudaMemcpyDeviceToDevice, s);
 }
 
 int launch_bbox(const float4* pos, uint32_t n, Reduce* red, cudaStream_t s) {
@@ -547,22 +669,36 @@ int launch_locate(const float4* pos, uint32_t* keys, const StepConsts& c, cudaSt
   return 1;
 }
 
+// `table_entries`: how much of ftable is cleared and scanned — nfine + 1 on the host-driven path;
+// on the device-driven path (queued) the whole capacity, because the live length is only known
+// on the device (entries past it scan to n and are never read).
 int launch_cell_sort(const float4* pos, const StepConsts& c, uint32_t* keys_tmp, uint32_t* slot_tmp,
                      uint32_t* ftable, uint32_t* scan_scratch, uint32_t* keys_sorted, uint32_t* src_tmp,
-                     uint32_t* perm, cudaStream_t s) {
-  cudaMemsetAsync(ftable, 0, sizeof(uint32_t) * ((size_t)c.nfine + 1), s);
-  k_locate_count<<<blocks_for(c.n), kBlock, 0, s>>>(pos, keys_tmp, slot_tmp, ftable, c);
-  int l = 1 + launch_exclusive_sum(ftable, c.nfine + 1, scan_scratch, s);
-  k_place<<<blocks_for(c.n), kBlock, 0, s>>>(keys_tmp, slot_tmp, ftable, c.n, keys_sorted, src_tmp);
-  k_canonical_order<<<blocks_for(c.n), kBlock, 0, s>>>(keys_sorted, src_tmp, ftable, c.n, perm);
+                     uint32_t* perm, cudaStream_t s, bool queued, size_t table_entries) {
+  if (!queued) table_entries = (size_t)c.nfine + 1;
+  cudaMemsetAsync(ftable, 0, sizeof(uint32_t) * table_entries, s);
+  if (queued) k_locate_count<true><<<blocks_for(c.n), kBlock, 0, s>>>(pos, keys_tmp, slot_tmp, ftable, c);
+  else k_locate_count<false><<<blocks_for(c.n), kBlock, 0, s>>>(pos, keys_tmp, slot_tmp, ftable, c);
+  int l = 1 + launch_exclusive_sum(ftable, (uint32_t)table_entries, scan_scratch, s);
+  if (queued) {
+    k_place<true><<<blocks_for(c.n), kBlock, 0, s>>>(keys_tmp, slot_tmp, ftable, c.n, keys_sorted, src_tmp);
+    k_canonical_order<true><<<blocks_for(c.n), kBlock, 0, s>>>(keys_sorted, src_tmp, ftable, c.n, perm);
+  } else {
+    k_place<false><<<blocks_for(c.n), kBlock, 0, s>>>(keys_tmp, slot_tmp, ftable, c.n, keys_sorted, src_tmp);
+    k_canonical_order<false><<<blocks_for(c.n), kBlock, 0, s>>>(keys_sorted, src_tmp, ftable, c.n, perm);
+  }
   return l + 2;
 }
 
 int launch_reorder(const uint32_t* perm, uint32_t n, const float4* pos_in, const float4* vel_in,
                    const float4* vhf_in, const uint32_t* rank_in, float4* pos_out, float4* vel_out,
-                   float4* vhf_out, uint32_t* rank_out, cudaStream_t s) {
-  k_reorder<<<blocks_for(n), kBlock, 0, s>>>(perm, n, pos_in, vel_in, vhf_in, rank_in, pos_out,
-                                             vel_out, vhf_out, rank_out);
+                   float4* vhf_out, uint32_t* rank_out, cudaStream_t s, bool queued) {
+  if (queued)
+    k_reorder<true><<<blocks_for(n), kBlock, 0, s>>>(perm, n, pos_in, vel_in, vhf_in, rank_in, pos_out,
+                                                     vel_out, vhf_out, rank_out);
+  else
+    k_reorder<false><<<blocks_for(n), kBlock, 0, s>>>(perm, n, pos_in, vel_in, vhf_in, rank_in, pos_out,
+                                                      vel_out, vhf_out, rank_out);
   return 1;
 }
 
@@ -575,11 +711,18 @@ int launch_fine_table(const uint32_t* sorted_keys, uint32_t n, uint32_t* ftable,
 
 int launch_reference_rank(const uint32_t* fine_keys, const uint32_t* ftable, const uint32_t* rank_prev,
                           uint32_t* ref_table, uint32_t* ckey, uint32_t* rank_new, const StepConsts& c,
-                          uint32_t* scratch, cudaStream_t s) {
-  cudaMemsetAsync(ref_table, 0, sizeof(uint32_t) * ((size_t)c.grid_cell_count + 1), s);
-  k_morton_hist<<<blocks_for(c.n), kBlock, 0, s>>>(fine_keys, ref_table, ckey, c);
-  int l = 1 + launch_exclusive_sum(ref_table, c.grid_cell_count + 1, scratch, s);
-  k_reference_rank<<<blocks_for((c.n + 1u) / 2u), kBlock, 0, s>>>(fine_keys, ftable, rank_prev, ref_table, rank_new, c);
+                          uint32_t* scratch, cudaStream_t s, bool queued, size_t table_entries) {
+  if (!queued) table_entries = (size_t)c.grid_cell_count + 1;
+  cudaMemsetAsync(ref_table, 0, sizeof(uint32_t) * table_entries, s);
+  if (queued) k_morton_hist<true><<<blocks_for(c.n), kBlock, 0, s>>>(fine_keys, ref_table, ckey, c);
+  else k_morton_hist<false><<<blocks_for(c.n), kBlock, 0, s>>>(fine_keys, ref_table, ckey, c);
+  int l = 1 + launch_exclusive_sum(ref_table, (uint32_t)table_entries, scratch, s);
+  if (queued)
+    k_reference_rank<true><<<blocks_for((c.n + 1u) / 2u), kBlock, 0, s>>>(fine_keys, ftable, rank_prev, ref_table,
+                                                                          rank_new, c);
+  else
+    k_reference_rank<false><<<blocks_for((c.n + 1u) / 2u), kBlock, 0, s>>>(fine_keys, ftable, rank_prev, ref_table,
+                                                                           rank_new, c);
   return l + 1;
 }
 
@@ -592,15 +735,19 @@ int launch_reference_debug(const uint32_t* rank, const uint32_t* rank_prev, cons
 int launch_advect(const float4* pos, const float4* vhf, const float4* acc, float4* pos_out,
                   float4* vel_out, float4* vhf_out, uint32_t n, float dt, float restitution,
                   const Face* faces, uint32_t face_count, const float* df, Reduce* red,
-                  cudaStream_t s, const SlabAdvect* slab, const FaceBin* bin) {
+                  cudaStream_t s, const SlabAdvect* slab, const FaceBin* bin, const QueueCtl* q) {
   FaceBin b = {};
   if (bin) b = *bin;
   SlabAdvect sa = {};
   if (slab) sa = *slab;
   unsigned grid = blocks_for(n);
   if (grid > 148 * 8) grid = 148 * 8;  // 8 resident CTAs of 256 threads on each of 148 SMs
-  k_advect<<<grid, kBlock, 0, s>>>(pos, vhf, acc, pos_out, vel_out, vhf_out, n, dt,
-                                            restitution, faces, face_count, df, red, sa, b);
+  if (q)
+    k_advect<true><<<grid, kBlock, 0, s>>>(pos, vhf, acc, pos_out, vel_out, vhf_out, n, dt, restitution, faces,
+                                           face_count, df, red, sa, b, q);
+  else
+    k_advect<false><<<grid, kBlock, 0, s>>>(pos, vhf, acc, pos_out, vel_out, vhf_out, n, dt, restitution, faces,
+                                            face_count, df, red, sa, b, nullptr);
   return 1;
 }
 

@@ -26,6 +26,9 @@ namespace {
 
 constexpr int kBlock = 128;
 
+// device-driven stepping (common.cuh: QueueCtl): see kernels_exact.cu
+__constant__ QueueHot g_hot;
+
 // Tait equation, sphb.cl:32-34: K * ((rho/rho0)^7 - 1), pown as repeated multiplication
 __device__ __forceinline__ float tait_pressure(float rho, const StepConsts& c) {
   const float q = rho / c.rho0;
@@ -139,11 +142,14 @@ __device__ __forceinline__ void density_test(const float4& q, const float4& pj, 
       : "memory");
 }
 
+template <bool Q>
 __global__ void __launch_bounds__(kPairBlock)
     k_density_pair(float4* pos, float4* vel, const uint32_t* __restrict__ keys,
                    const uint32_t* __restrict__ ftable, float* __restrict__ rho,
                    float* __restrict__ prs, uint16_t* __restrict__ nlist,
-                   uint8_t* __restrict__ ncount, StepConsts c) {
+                   uint8_t* __restrict__ ncount, StepConsts c_arg) {
+  if (Q && !g_hot.active) return;
+  const StepConsts& c = Q ? g_hot.c : c_arg;
   __shared__ uint16_t hit[(kListCap + kDumpRows) * kPairCols];
   const uint32_t ia = 2u * (blockIdx.x * kPairBlock + threadIdx.x);
   if (ia >= c.n) return;
@@ -378,12 +384,15 @@ __global__ void __launch_bounds__(kBlock)
 }
 
 // Forces from the neighbour list the density pass recorded.
+template <bool Q>
 __global__ void __launch_bounds__(kBlock)
     k_forces_nlist(const float4* __restrict__ pos, const float4* __restrict__ vel,
                    const uint32_t* __restrict__ keys, const uint32_t* __restrict__ ftable,
                    const float* __restrict__ rho, const uint16_t* __restrict__ nlist,
-                   const uint8_t* __restrict__ ncount, float4* __restrict__ acc, StepConsts c,
+                   const uint8_t* __restrict__ ncount, float4* __restrict__ acc, StepConsts c_arg,
                    const uint32_t* __restrict__ ghost_ids) {
+  if (Q && !g_hot.active) return;
+  const StepConsts& c = Q ? g_hot.c : c_arg;
   __shared__ uint32_t row_start[9][kBlock];
   const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
   if (i >= c.n) return;
@@ -469,22 +478,41 @@ size_t neighbor_list_entries(uint32_t n) { return (size_t)(kListCap + 2) * n; }
 
 int launch_density(float4* pos, float4* vel, const uint32_t* keys, const uint32_t* ftable,
                    float* rho, float* prs, uint16_t* nlist, uint8_t* ncount, const StepConsts& c,
-                   int variant, cudaStream_t s) {
+                   int variant, cudaStream_t s, bool queued) {
   (void)variant;  // the list is recorded either way; variant 1 just does not use it
-  const unsigned pairs = (c.n + 1u) / 2u;
-  k_density_pair<<<(pairs + kPairBlock - 1) / kPairBlock, kPairBlock, 0, s>>>(pos, vel, keys, ftable, rho, prs,
-                                                                             nlist, ncount, c);
+  const unsigned pairs = (c.n + 1u) / 2u, grid = (pairs + kPairBlock - 1) / kPairBlock;
+  if (queued) k_density_pair<true><<<grid, kPairBlock, 0, s>>>(pos, vel, keys, ftable, rho, prs, nlist, ncount, c);
+  else k_density_pair<false><<<grid, kPairBlock, 0, s>>>(pos, vel, keys, ftable, rho, prs, nlist, ncount, c);
   return 1;
+}
+
+int queue_refresh_neighbors(const QueueCtl* ctl, cudaStream_t s) {
+  // the symbol's address is looked up once per device: a plain device-to-device copy after that
+  static thread_local void* addr[64] = {};
+  int dev = 0;
+  cudaError_t err = cudaGetDevice(&dev);
+  if (err != cudaSuccess) return (int)err;
+  void* local = nullptr;
+  void*& slot = (dev >= 0 && dev < 64) ? addr[dev] : local;
+  if (!slot) {
+    err = cudaGetSymbolAddress(&slot, g_hot);
+    if (err != cudaSuccess) return (int)err;
+  }
+  return (int)cudaMemcpyAsync(slot, &ctl->hot, sizeof(QueueHot), cudaMemcpyDeviceToDevice, s);
 }
 
 int launch_forces(const float4* pos, const float4* vel, const uint32_t* keys,
                   const uint32_t* ftable, const float* rho, const uint16_t* nlist,
                   const uint8_t* ncount, float4* acc, const StepConsts& c, int variant,
-                  cudaStream_t s, const uint32_t* ghost_ids) {
-  if (variant == 1 && !ghost_ids)
+                  cudaStream_t s, const uint32_t* ghost_ids, bool queued) {
+  if (queued)  // always from the recorded list (sphb_run_frame steps one at a time under variant 1)
+    k_forces_nlist<true><<<blocks_for(c.n), kBlock, 0, s>>>(pos, vel, keys, ftable, rho, nlist, ncount, acc, c,
+                                                            ghost_ids);
+  else if (variant == 1 && !ghost_ids)
     k_forces_list<<<blocks_for(c.n), kBlock, 0, s>>>(pos, vel, keys, ftable, rho, acc, c);
   else
-    k_forces_nlist<<<blocks_for(c.n), kBlock, 0, s>>>(pos, vel, keys, ftable, rho, nlist, ncount, acc, c, ghost_ids);
+    k_forces_nlist<false><<<blocks_for(c.n), kBlock, 0, s>>>(pos, vel, keys, ftable, rho, nlist, ncount, acc, c,
+                                                             ghost_ids);
   return 1;
 }
 

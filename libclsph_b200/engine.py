@@ -73,7 +73,7 @@ PASS_NAMES = ["bbox", "locate", "sort", "reorder", "celltable", "density", "forc
 # every symbol include/sphb.h declares (tests check the library exports each one)
 SYMBOLS = [
     "sphb_create", "sphb_destroy", "sphb_set_scene", "sphb_get_distance_field", "sphb_upload",
-    "sphb_step", "sphb_get_parameters", "sphb_download", "sphb_download_begin", "sphb_download_wait",
+    "sphb_step", "sphb_run_frame", "sphb_queued_steps", "sphb_get_parameters", "sphb_download", "sphb_download_begin", "sphb_download_wait",
     "sphb_download_debug",
     "sphb_profile_enable", "sphb_profile_reset", "sphb_get_pass_times", "sphb_launch_count",
     "sphb_stream", "sphb_set_option", "sphb_last_error", "sphb_error_string",
@@ -116,6 +116,9 @@ def lib():
         L.sphb_get_distance_field.argtypes = [vp, vp]
         L.sphb_upload.argtypes = [vp, vp, u32]
         L.sphb_step.argtypes = [vp, f32, C.POINTER(f32)]
+        L.sphb_run_frame.argtypes = [vp, f32, f32, C.c_uint64, C.POINTER(f32), C.POINTER(u32), vp, u32]
+        L.sphb_queued_steps.argtypes = [vp]
+        L.sphb_queued_steps.restype = C.c_uint64
         L.sphb_get_parameters.argtypes = [vp, vp]
         L.sphb_download.argtypes = [vp, vp]
         L.sphb_download_begin.argtypes = [vp, vp]
@@ -236,6 +239,18 @@ class Engine:
         out = C.c_float()
         self._check(self.L.sphb_step(self.h, dt, C.byref(out)))
         return out.value
+
+    def run_frame(self, dt, frame_time, max_steps=0, log_cap=4096):
+        """The sub-step loop of one frame on the device -> (dt afterwards, timeleft after each step)."""
+        out = C.c_float()
+        steps = C.c_uint32()
+        log = np.zeros(log_cap, np.float32)
+        self._check(self.L.sphb_run_frame(self.h, dt, frame_time, max_steps, C.byref(out), C.byref(steps),
+                                          _ptr(log), log_cap))
+        return out.value, log[:min(steps.value, log_cap)].copy(), steps.value
+
+    def queued_steps(self):
+        return int(self.L.sphb_queued_steps(self.h))
 
     def parameters(self):
         p = np.zeros(1, PARAMS)

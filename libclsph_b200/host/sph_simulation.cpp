@@ -11,6 +11,7 @@
 #include <iostream>
 #include <stdexcept>
 #include <thread>
+#include <vector>
 
 #include "sphb.h"
 #include "util/json_min.h"
@@ -145,6 +146,30 @@ float sph_simulation::simulate_single_frame(float dt) {
   return computed;
 }
 
+// The sub-step loop of one frame (libclsph/sph_simulation.cpp:384-409) as one engine call.
+void sph_simulation::run_frame_on_device(float& dt, float& timeleft) {
+  const unsigned int log_cap = 4096;
+  std::vector<float> log(log_cap);
+  unsigned int steps = 0;
+  const unsigned long left = max_steps ? (max_steps > steps_done ? max_steps - steps_done : 1) : 0;
+  SPHB_CHECK(sphb_run_frame(engine_, dt, timeleft, left, &dt, &steps, log.data(), log_cap));
+  sphb_params now;
+  SPHB_CHECK(sphb_get_parameters(engine_, &now));
+  parameters.grid_size_x = now.grid_size_x;
+  parameters.grid_size_y = now.grid_size_y;
+  parameters.grid_size_z = now.grid_size_z;
+  parameters.grid_cell_count = now.grid_cell_count;
+  for (int a = 0; a < 4; ++a) {
+    parameters.min_point.s[a] = now.min_point.s[a];
+    parameters.max_point.s[a] = now.max_point.s[a];
+  }
+  steps_done += steps;
+  if (!quiet)
+    for (unsigned int k = 0; k < steps && k < log_cap; ++k)
+      std::cout << "temps restant pour la frame :" << log[k] << std::endl;
+  if (steps) timeleft = log[(steps < log_cap ? steps : log_cap) - 1];
+}
+
 void sph_simulation::read_particles(particle* particles) {
   SPHB_CHECK(sphb_download(engine_, reinterpret_cast<sphb_particle*>(particles)));
 }
@@ -229,7 +254,15 @@ void sph_simulation::simulate() {
       readParticle = run_hook(pre_frame, particles, readParticle, true);
 
     float timeleft = timeperframe;
-    while (timeleft > 0.0) {
+    if (!write_intermediate_frames && device_loop) {
+      // Nothing looks at the state between the sub-steps of this frame: the whole loop below runs
+      // inside the engine, without a host round trip per step, and the lines the
+      // reference prints per step are printed afterwards from the engine's log.
+      run_frame_on_device(dt, timeleft);
+      readParticle = true;
+      if (max_steps && steps_done >= max_steps) stop = true;
+    }
+    while (timeleft > 0.0 && !stop) {
       if (write_intermediate_frames && pre_frame)
         readParticle = run_hook(pre_frame, particles, readParticle, false);
       readParticle = true;

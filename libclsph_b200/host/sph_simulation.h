@@ -17,7 +17,7 @@ class sph_simulation {
  public:
   sph_simulation()
       : parameters(), precomputed_terms(), write_intermediate_frames(false), serialize(false),
-        initial_volume(0.f), device(-1), quiet(false), max_steps(0), steps_done(0),
+        initial_volume(0.f), device(-1), quiet(false), max_steps(0), steps_done(0), device_loop(true),
         engine_(0) {}
 
   // Runs the whole simulation: frames of 1/target_fps seconds, each made of adaptive
@@ -48,10 +48,12 @@ class sph_simulation {
   bool quiet;               // suppress the per-sub-step progress lines
   unsigned long max_steps;  // stop after this many sub-steps (0 = run simulation_time)
   unsigned long steps_done; // sub-steps executed by the last simulate()
+  bool device_loop;         // a frame's sub-steps run as one engine call (sphb_run_frame)
 
  private:
   void init_particles(particle* buffer, const simulation_parameters&);
   float simulate_single_frame(float dt);
+  void run_frame_on_device(float& dt, float& timeleft);
   bool run_hook(std::function<bool(particle*, const simulation_parameters&, bool)>& hook,
                 particle* particles, bool readParticle, bool isFullFrame);
   void read_particles(particle* particles);
