@@ -23,6 +23,12 @@ OBJDIR = os.path.join(HERE, "build")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC",
           "-DSPHB_BUILD"]
+# experiments: SPHB_XSUB=<1|2|4> builds the engine with that many x sub-cells per cell of side h
+# (csrc/common.cuh: kXSub) into SPHB_OUT (default: the product library)
+if os.environ.get("SPHB_XSUB"):
+    COMMON.append("-DSPHB_XSUB=" + os.environ["SPHB_XSUB"])
+    OBJDIR = os.path.join(OBJDIR, "xsub" + os.environ["SPHB_XSUB"])
+    OUT = os.environ.get("SPHB_OUT", os.path.join(OBJDIR, "libsphb.so"))
 
 # source -> extra flags
 SOURCES = {

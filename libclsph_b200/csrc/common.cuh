@@ -21,11 +21,19 @@ struct StepConsts {
   float gx, gy, gz;          // constant_acceleration
   float c_poly6, c_poly6_grad, c_poly6_lap, c_spiky, c_visc;
   float spiky_eps;           // -45 / (float)(M_PI * h^6): spiky_gradient's r < 1e-7 branch
-  // The engine's own search grid: cells of side h (half a reference cell), row-major
-  // (x fastest).  fine coordinate = 2 * reference coordinate + (upper half ? 1 : 0).
-  uint32_t fnx, fny, fnz;    // fine grid dimensions = 2 * grid_size_{x,y,z}
+  // The engine's own search grid, row-major (x fastest): cells of side h (half a reference
+  // cell) in y and z, fine coordinate = 2 * reference coordinate + (upper half ? 1 : 0); along x —
+  // the direction a row of cells is walked in — the cell is cut kXSub times finer still, so
+  // that the run of candidates walked for a row can be trimmed to the chord of the support sphere
+  // at that row instead of to whole cells of side h.
+  uint32_t fnx, fny, fnz;    // fine grid dimensions = 2 * {kXSub, 1, 1} * grid_size_{x,y,z}
   uint32_t nfine;            // fnx * fny * fnz
 };
+#ifndef SPHB_XSUB
+#define SPHB_XSUB 4
+#endif
+constexpr uint32_t kXSub = SPHB_XSUB;         // x sub-cells per cell of side h
+constexpr uint32_t kXPerRef = 2u * kXSub;     // x sub-cells per reference cell (side 2h)
 
 // One face of the scene for the collision pass: inflated AABB + its distance-field grid
 // (libclsph/common/structures.h:54-65, integers pre-converted to fp32 because the
@@ -159,7 +167,7 @@ __host__ __device__ inline StepConsts make_consts_hd(const sphb_params& P, const
   c.c_poly6_lap = T.poly_6_laplacian; c.c_spiky = T.spiky;
   c.c_visc = T.viscosity;
   c.spiky_eps = spiky_eps;
-  c.fnx = 2u * (uint32_t)P.grid_size_x;
+  c.fnx = kXPerRef * (uint32_t)P.grid_size_x;
   c.fny = 2u * (uint32_t)P.grid_size_y;
   c.fnz = 2u * (uint32_t)P.grid_size_z;
   c.nfine = c.fnx * c.fny * c.fnz;

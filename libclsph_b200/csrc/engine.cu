@@ -401,10 +401,10 @@ int enqueue_queued_step(sphb_engine* e) {
   l += launch_reference_rank(skeys, e->ftable, e->rank_prev, e->ref_table, e->ckey, e->rank_cur, c,
                              e->scan_scratch, rs, true, e->ref_table_cap);
   if (e->use_side_stream) CUDA_TRY(e, cudaEventRecord(e->ev_join, e->side));
-  l += launch_density(e->pos[mid], e->vel[mid], skeys, e->ftable, e->rho, e->prs, e->nlist, e->ncount, c, 0, s,
-                      true);
-  l += launch_forces(e->pos[mid], e->vel[mid], skeys, e->ftable, e->rho, e->nlist, e->ncount, e->acc, c, 0, s,
-                     nullptr, true);
+  l += launch_density(e->pos[mid], e->vel[mid], skeys, e->ftable, e->rho, e->prs, e->nlist, e->ncount, c,
+                      e->neighbor_variant, s, true);
+  l += launch_forces(e->pos[mid], e->vel[mid], skeys, e->ftable, e->rho, e->nlist, e->ncount, e->acc, c,
+                     e->neighbor_variant, s, nullptr, true);
   if (e->use_side_stream) CUDA_TRY(e, cudaStreamWaitEvent(s, e->ev_join, 0));
   for (int a = 0; a < e->queued_attempts; ++a) {
     l += launch_reduce_init(e->red, s, e->qctl);
@@ -424,7 +424,8 @@ int launch_queued_graph(sphb_engine* e) {
                            (uint64_t)e->ftable_cap, (uint64_t)e->ref_table_cap,
                            (uint64_t)(uintptr_t)e->scan_scratch, (uint64_t)(uintptr_t)e->df,
                            (uint64_t)(uintptr_t)e->bin.start,
-                           ((uint64_t)e->face_count << 8) | ((uint64_t)e->queued_attempts << 4) |
+                           ((uint64_t)e->face_count << 12) | ((uint64_t)e->neighbor_variant << 8) |
+                               ((uint64_t)e->queued_attempts << 4) |
                                ((uint64_t)e->cur << 1) | (e->use_side_stream ? 1u : 0u)};
   if (!e->qgraph || memcmp(key, e->qgraph_key, sizeof key) != 0) {
     if (e->qgraph) cudaGraphExecDestroy(e->qgraph);
@@ -477,7 +478,7 @@ int sphb_run_frame(sphb_engine* e, float dt_in, float frame_time, uint64_t max_s
   while (timeleft > 0.0) {
     if (max_steps && steps >= max_steps) break;
     const bool want_queue = e->use_queue == 1 || (e->use_queue == 2 && e->n <= kQueueAutoMax);
-    const bool can_queue = want_queue && e->bbox_valid && e->sort_variant == 0 && e->neighbor_variant == 0 &&
+    const bool can_queue = want_queue && e->bbox_valid && e->sort_variant == 0 && e->neighbor_variant != 1 &&
                            !e->profile && e->ftable_cap && e->ref_table_cap && e->scan_scratch;
     if (!can_queue) {  // the first step after an upload (its bbox needs a pass of its own), or an option
       float computed = dt;

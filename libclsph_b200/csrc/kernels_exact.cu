@@ -101,8 +101,18 @@ __device__ __forceinline__ uint32_t fine_coord(float p, float mn, float cell, fl
   return 2u * c + (within >= h ? 1u : 0u);
 }
 
+// Along x the cell of side 2h is cut into kXPerRef sub-cells (common.cuh: kXSub); the reference
+// cell is still exactly (fine x) / kXPerRef.
+__device__ __forceinline__ uint32_t fine_coord_x(float p, float mn, float cell, float h) {
+  const float rel = p - mn;
+  const uint32_t c = (uint32_t)(rel / cell);
+  const float within = rel - (float)c * cell;
+  const uint32_t sub = (uint32_t)(within / (h / (float)kXSub));  // negative / NaN convert to 0
+  return kXPerRef * c + min(sub, kXPerRef - 1u);
+}
+
 __device__ __forceinline__ uint32_t fine_key_of(const float4& p, const StepConsts& c) {
-  uint32_t fx = fine_coord(p.x, c.minx, c.cell, c.h);
+  uint32_t fx = fine_coord_x(p.x, c.minx, c.cell, c.h);
   uint32_t fy = fine_coord(p.y, c.miny, c.cell, c.h);
   uint32_t fz = fine_coord(p.z, c.minz, c.cell, c.h);
   // NaN / runaway positions: park them in the last cell instead of indexing out of bounds
@@ -232,7 +242,7 @@ __global__ void __launch_bounds__(kBlock)
   if (valid) {
     uint32_t fx, fy, fz;
     fine_coords_of(__ldg(fine_keys + i), cc, fx, fy, fz);
-    m = morton3(fx >> 1, fy >> 1, fz >> 1);
+    m = morton3(fx / kXPerRef, fy >> 1, fz >> 1);
     ckey[i] = m;
   }
   const unsigned peers = __match_any_sync(0xffffffffu, m);
@@ -257,7 +267,7 @@ __global__ void __launch_bounds__(kBlock)
   fine_coords_of(__ldg(fine_keys + ia), cc, fx[0], fy[0], fz[0]);
   fine_coords_of(__ldg(fine_keys + ib), cc, fx[1], fy[1], fz[1]);
 #pragma unroll
-  for (int w = 0; w < 2; ++w) m[w] = morton3(fx[w] >> 1, fy[w] >> 1, fz[w] >> 1);
+  for (int w = 0; w < 2; ++w) m[w] = morton3(fx[w] / kXPerRef, fy[w] >> 1, fz[w] >> 1);
   const uint32_t mine_a = __ldg(rank_prev + ia), mine_b = __ldg(rank_prev + ib);
   const bool together = has_b && m[0] == m[1];
   const int npass = (has_b && !together) ? 2 : 1;
@@ -266,13 +276,13 @@ __global__ void __launch_bounds__(kBlock)
   for (int pass = 0; pass < npass; ++pass) {
     // a particle that sits out a pass compares against 0: nothing is smaller
     const uint32_t qa = pass == 0 ? mine_a : 0u, qb = (together || pass == 1) ? mine_b : 0u;
-    const uint32_t x0 = fx[pass] & ~1u, y0 = fy[pass] & ~1u, z0 = fz[pass] & ~1u;
+    const uint32_t x0 = fx[pass] / kXPerRef * kXPerRef, y0 = fy[pass] & ~1u, z0 = fz[pass] & ~1u;
     uint32_t rs[4], re[4];
 #pragma unroll
     for (uint32_t k = 0; k < 4; ++k) {
       const uint32_t row = ((z0 + (k >> 1)) * cc.fny + (y0 + (k & 1u))) * cc.fnx + x0;
       rs[k] = __ldg(ftable + row);
-      re[k] = __ldg(ftable + row + 2);
+      re[k] = __ldg(ftable + row + kXPerRef);
     }
 #pragma unroll
     for (uint32_t k = 0; k < 4; ++k) {

@@ -8,8 +8,11 @@
 // grid of side h instead — 27 cells of side h hold ~130 candidates — and (b) skip pairs with
 // r >= h before doing any work on them; results are unchanged up to summation order.
 //
-// Particles are sorted by the row-major index of their fine cell, so the three x-adjacent
-// cells of each of the 9 (dy, dz) rows are ONE contiguous run [ftable[row], ftable[row + 3]).
+// Particles are sorted by the row-major index of their fine cell — side h in y and z, h / kXSub
+// along x (common.cuh) — so the x-adjacent cells of each of the 9 (dy, dz) rows are ONE contiguous
+// run [ftable[row + first], ftable[row + last + 1]), and that run is trimmed to the chord of the
+// support sphere at the row (row_reach below): ~70 candidates per particle at kXSub = 4 instead
+// of the ~100 of whole cells of side h.
 //
 // This translation unit is compiled with FMA contraction ON and uses rsqrt for 1/r; it is
 // checked against the CPU oracle to a stated tolerance (tests/test_gpu_parity.py), unlike
@@ -46,31 +49,38 @@ __device__ __forceinline__ void fine_coords_of(uint32_t key, const StepConsts& c
   fz = t / c.fny;
 }
 
-// Where a particle sits inside its fine cell, in units of h: lo = distance to the cell's lower
-// face, hi = distance to its upper face (both clamped to [0, 1]).
+// Where a particle sits inside its fine cell in y and z, in units of h: lo = distance to the
+// cell's lower face, hi = distance to its upper face (both clamped to [0, 1]); ux = its x
+// coordinate in units of the x sub-cell (h / kXSub), from the grid origin.
 struct CellFrac {
   float lo[3], hi[3];
+  float ux;
 };
 __device__ __forceinline__ CellFrac cell_frac(const float4& p, uint32_t fx, uint32_t fy, uint32_t fz,
                                               const StepConsts& c) {
   CellFrac f;
   const float inv_h = 1.f / c.h;
-  const float u[3] = {(p.x - c.minx) * inv_h - (float)fx, (p.y - c.miny) * inv_h - (float)fy,
-                      (p.z - c.minz) * inv_h - (float)fz};
+  (void)fx;
+  const float u[3] = {0.f, (p.y - c.miny) * inv_h - (float)fy, (p.z - c.minz) * inv_h - (float)fz};
 #pragma unroll
   for (int a = 0; a < 3; ++a) {
     f.lo[a] = fminf(fmaxf(u[a], 0.f), 1.f);
     f.hi[a] = 1.f - f.lo[a];
   }
+  f.ux = (p.x - c.minx) * (inv_h * (float)kXSub);
   return f;
 }
 
-// Which cells of the x-run of row (fy + dy, fz + dz) can hold a neighbour of a particle at `f`
-// inside cell (fx, fy, fz): a neighbouring cell is visited only if its nearest point is closer
-// than h.  `on` = the row's own-x cell is reachable; left / right = the cells beside it are.
+// Which x sub-cells of row (fy + dy, fz + dz) can hold a neighbour of a particle at `f` inside
+// cell (fx, fy, fz): the row is visited only if its nearest line is closer than h, and then only
+// over the chord of the support sphere at that distance, [x - w, x + w] with
+// w = sqrt(h^2 - gy^2 - gz^2), rounded out to whole sub-cells.  The radius carries a slack, so
+// that rounding in this arithmetic (or in the sub-cell a candidate was sorted into) can only add
+// candidates, never lose a pair with r < h.
 constexpr float kReach2 = 1.0f + 1.0e-3f;  // (h * (1 + slack))^2 in units of h^2
 struct Reach {
-  bool on, left, right;
+  bool on;
+  uint32_t lo, hi;  // first / last sub-cell (inclusive); always lo <= fx <= hi
 };
 __device__ __forceinline__ Reach row_reach(const StepConsts& c, uint32_t fx, const CellFrac& f, int dy,
                                            int dz) {
@@ -79,8 +89,10 @@ __device__ __forceinline__ Reach row_reach(const StepConsts& c, uint32_t fx, con
   const float q = gy * gy + gz * gz;
   Reach r;
   r.on = q < kReach2;
-  r.left = r.on && fx > 0 && q + f.lo[0] * f.lo[0] < kReach2;
-  r.right = r.on && fx + 1 < c.fnx && q + f.hi[0] * f.hi[0] < kReach2;
+  const float w = sqrtf(fmaxf(kReach2 - q, 0.f)) * (float)kXSub;
+  // float -> unsigned conversion saturates at 0 for negatives and NaN
+  r.lo = min((uint32_t)fmaxf(f.ux - w, 0.f), fx);
+  r.hi = min(max((uint32_t)fmaxf(f.ux + w, 0.f), fx), c.fnx - 1u);
   return r;
 }
 
@@ -93,9 +105,9 @@ __device__ __forceinline__ void row_range(const uint32_t* __restrict__ ftable, c
   if (y >= c.fny || z >= c.fnz) return;
   const Reach r = row_reach(c, fx, f, dy, dz);
   if (!r.on) return;
-  const uint32_t row = (z * c.fny + y) * c.fnx + fx;
-  s = __ldg(ftable + row - (r.left ? 1u : 0u));
-  e = __ldg(ftable + row + (r.right ? 2u : 1u));
+  const uint32_t row = (z * c.fny + y) * c.fnx;
+  s = __ldg(ftable + row + r.lo);
+  e = __ldg(ftable + row + r.hi + 1u);
 }
 
 // ---- density + pressure: one thread per PAIR of consecutive particles, walking the 9 rows ----
@@ -111,9 +123,14 @@ __device__ __forceinline__ void row_range(const uint32_t* __restrict__ ftable, c
 // (row 0..8) << 12 | (offset of the neighbour inside the run that was walked for that row),
 // staged per particle in a shared-memory column and flushed k-major (nlist[k * n + i]) so that
 // the stores — and the forces pass's loads — are coalesced across the warp.  Where the walked
-// run began is recorded as 2 bits per row (nback: own cell x + 1 - first cell x).  count 255 =
+// run began is recorded as kBackBits bits per row (nback: own sub-cell x - first sub-cell x).  count 255 =
 // "list unusable" (more than kListCap neighbours, or a run longer than 4096): the forces pass
 // then searches itself.
+// Where a walked run began is recorded per row as (own sub-cell - first sub-cell) in kBackBits
+// bits: at most kTogether (the partner's lead) + kXSub + 1 (the chord, rounded out).
+constexpr uint32_t kTogether = kXSub >= 2 ? 2u : 1u;  // sub-cells two particles of a thread may be apart
+constexpr uint32_t kBackBits = 3;
+static_assert(kTogether + kXSub + 1u < (1u << kBackBits), "run starts do not fit their bit field");
 constexpr int kListCap = 64;
 constexpr uint32_t kListOverflow = 255;
 constexpr int kPairBlock = 64;                  // threads per CTA; 2 particles each
@@ -161,7 +178,7 @@ __global__ void __launch_bounds__(kPairBlock)
   fine_coords_of(__ldg(keys + ib), c, fxb, fyb, fzb);
   const CellFrac fa = cell_frac(pa, fxa, fya, fza, c), fb = cell_frac(pb, fxb, fyb, fzb, c);
   // sorted by row-major cell: inside a row, b's cell is never left of a's
-  const bool together = has_b && fya == fyb && fza == fzb && fxb - fxa <= 1u;
+  const bool together = has_b && fya == fyb && fza == fzb && fxb - fxa <= kTogether;
   const int npass = (has_b && !together) ? 2 : 1;
   const float nan = __int_as_float(0x7fc00000);
   const float4 nowhere = make_float4(nan, nan, nan, 0.f);
@@ -180,7 +197,7 @@ __global__ void __launch_bounds__(kPairBlock)
     const uint32_t ry = la ? fya : fyb, rz = la ? fza : fzb;
     uint32_t tag = 0, shift = 0;
 #pragma unroll 1
-    for (int dz = -1; dz <= 1; ++dz, tag += 3u * 4096u, shift += 6u) {
+    for (int dz = -1; dz <= 1; ++dz, tag += 3u * 4096u, shift += 3u * kBackBits) {
       const uint32_t z = rz + dz;  // wraps to a huge value below 0
       if (z >= c.fnz) continue;
       // the three rows of this plane are planned together, so that their six table loads
@@ -192,17 +209,17 @@ __global__ void __launch_bounds__(kPairBlock)
         const uint32_t y = ry + dy;
         const Reach A = row_reach(c, fxa, fa, dy, dz), B = row_reach(c, fxb, fb, dy, dz);
         const bool ona = la && A.on, onb = lb && B.on;
-        const uint32_t lo_a = fxa - (A.left ? 1u : 0u), hi_a = fxa + (A.right ? 2u : 1u);
-        const uint32_t lo_b = fxb - (B.left ? 1u : 0u), hi_b = fxb + (B.right ? 2u : 1u);
-        const uint32_t x_lo = ona ? (onb ? min(lo_a, lo_b) : lo_a) : lo_b;
-        const uint32_t x_hi = ona ? (onb ? max(hi_a, hi_b) : hi_a) : hi_b;
+        const uint32_t x_lo = ona ? (onb ? min(A.lo, B.lo) : A.lo) : B.lo;
+        const uint32_t x_hi = (ona ? (onb ? max(A.hi, B.hi) : A.hi) : B.hi) + 1u;
         rs[k] = re[k] = 0;
         if (y < c.fny && (ona || onb)) {
           const uint32_t rowbase = (z * c.fny + y) * c.fnx;
           rs[k] = __ldg(ftable + rowbase + x_lo);
           re[k] = __ldg(ftable + rowbase + x_hi);
-          if (la) back_a |= (fxa + 1u - x_lo) << (shift + 2u * k);
-          if (lb) back_b |= (fxb + 1u - x_lo) << (shift + 2u * k);
+          // (a particle that cannot reach the row records nothing there: the union's start may
+          // lie beyond its own sub-cell)
+          if (ona) back_a |= (fxa - x_lo) << (shift + kBackBits * k);
+          if (onb) back_b |= (fxb - x_lo) << (shift + kBackBits * k);
         }
       }
 #pragma unroll
@@ -406,15 +423,16 @@ __global__ void __launch_bounds__(kBlock)
   const uint32_t cnt = ncount[i];
   ForceAcc A = {};
   if (cnt != kListOverflow) {
-    // where the run the density pass walked for each row began: 2 bits per row
+    // where the run the density pass walked for each row began: kBackBits bits per row
     uint32_t back = __ldg(nback_of(nlist, c.n) + i);
 #pragma unroll
     for (int dz = -1; dz <= 1; ++dz)
 #pragma unroll
-      for (int dy = -1; dy <= 1; ++dy, back >>= 2) {
+      for (int dy = -1; dy <= 1; ++dy, back >>= kBackBits) {
         const uint32_t y = fy + dy, z = fz + dz;
         uint32_t s = 0;
-        if (y < c.fny && z < c.fnz) s = __ldg(ftable + ((z * c.fny + y) * c.fnx + fx + 1u - (back & 3u)));
+        if (y < c.fny && z < c.fnz)
+          s = __ldg(ftable + ((z * c.fny + y) * c.fnx + fx - (back & ((1u << kBackBits) - 1u))));
         row_start[(dz + 1) * 3 + (dy + 1)][threadIdx.x] = s;
       }
     // four neighbours per trip: their codes, then their eight float4 loads, are issued together
@@ -469,6 +487,7 @@ __global__ void __launch_bounds__(kBlock)
   acc[i] = force_finish(A, __ldg(rho + i), vi.w, c);
 }
 
+
 inline unsigned blocks_for(uint32_t n) { return (n + kBlock - 1) / kBlock; }
 
 }  // namespace
@@ -479,8 +498,8 @@ size_t neighbor_list_entries(uint32_t n) { return (size_t)(kListCap + 2) * n; }
 int launch_density(float4* pos, float4* vel, const uint32_t* keys, const uint32_t* ftable,
                    float* rho, float* prs, uint16_t* nlist, uint8_t* ncount, const StepConsts& c,
                    int variant, cudaStream_t s, bool queued) {
-  (void)variant;  // the list is recorded either way; variant 1 just does not use it
   const unsigned pairs = (c.n + 1u) / 2u, grid = (pairs + kPairBlock - 1) / kPairBlock;
+  (void)variant;  // the list is recorded either way; variant 1 just does not use it
   if (queued) k_density_pair<true><<<grid, kPairBlock, 0, s>>>(pos, vel, keys, ftable, rho, prs, nlist, ncount, c);
   else k_density_pair<false><<<grid, kPairBlock, 0, s>>>(pos, vel, keys, ftable, rho, prs, nlist, ncount, c);
   return 1;

@@ -193,7 +193,7 @@ int sphb_slab_forces(sphb_engine* e, const float gmin[3], const float gmax[3]) {
   if (e->has_right) hi = fminf(hi, e->xhi + halo + 2.f * c.cell);
   if (!(hi > lo)) hi = lo + c.cell;
   c.minx = lo;
-  c.fnx = 2u * ((uint32_t)((hi - lo) / c.cell) + 1u);
+  c.fnx = kXPerRef * ((uint32_t)((hi - lo) / c.cell) + 1u);
   c.nfine = c.fnx * c.fny * c.fnz;
   if (int rc = ensure_tables(e, (size_t)c.nfine + 1, 1)) return rc;
   if (n == 0) {

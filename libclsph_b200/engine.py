@@ -93,7 +93,8 @@ class SphbError(RuntimeError):
 
 
 def lib_path():
-    return os.path.join(HERE, "libsphb.so")
+    # SPHB_LIB: an engine built with other compile-time parameters (experiments, tools/ab_frame.py)
+    return os.environ.get("SPHB_LIB") or os.path.join(HERE, "libsphb.so")
 
 
 _lib = None

@@ -17,9 +17,10 @@ def main():
     steps, warmup, repeats = 10, 3, 3
     legs = [("host", dict(device_loop=0, side_stream=1)), ("host_noside", dict(device_loop=0, side_stream=0)),
             ("queue", dict(device_loop=1, graph=0, side_stream=1)),
-            ("queue_noside", dict(device_loop=1, graph=0, side_stream=0)),
             ("graph", dict(device_loop=1, graph=1, side_stream=1)),
             ("graph_noside", dict(device_loop=1, graph=1, side_stream=0))]
+    if os.environ.get("AB_LEGS"):
+        legs = [(k, v) for k, v in legs if k in os.environ["AB_LEGS"].split(",")]
     out = {}
     with tempfile.TemporaryDirectory() as tmp:
         for n in sizes:
@@ -40,6 +41,15 @@ def main():
                     dt, _, done = e.run_frame(dt, 1.0, steps)
                     e.event_record(1)
                     res.setdefault(name, []).append(round(e.event_elapsed_ms(0, 1) / done, 4))
+                    if rep == 0 and os.environ.get("AB_PASSES"):
+                        e.set_option("side_stream", 0)
+                        e.profile(True)
+                        for _ in range(steps):
+                            dt = e.step(dt)
+                        ms, _, k = e.pass_times()
+                        e.profile(False)
+                        e.set_option("side_stream", 1)
+                        res[name + "_passes"] = {p: round(v / k, 4) for p, v in ms.items() if v}
             e.close()
             lib().sphb_host_free(stage_ptr)
             out[n] = res
