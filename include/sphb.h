@@ -95,6 +95,8 @@ int sphb_set_scene(sphb_engine* e, const sphb_bb* bbs, uint32_t face_count,
                    uint32_t total_grid_points);
 /* Copies the device distance field (total_grid_points floats) to `out` — for parity tests. */
 int sphb_get_distance_field(sphb_engine* e, float* out);
+/* Device milliseconds the last sphb_set_scene spent in the distance-field kernel (0: no faces). */
+float sphb_scene_build_ms(sphb_engine* e);
 
 /* Replaces the initial enqueueWriteBuffer (libclsph/sph_simulation.cpp:334-336) and the
  * write-back after a pre/post-frame hook returned true (:743-745, :763-765).
@@ -253,6 +255,10 @@ void* sphb_stream(sphb_engine* e);
 /* named integer options; unknown names return SPHB_ERR_INVALID.
  *   "neighbor_kernel"  0 (default) = the density pass records a neighbour list that the forces
  *                      pass consumes; 1 = both passes search the grid on their own
+ *   "df_face_lists"    1 (default) = the distance-field build tests, per grid point, only the
+ *                      faces whose box meets the box of the face that owns the point; 0 = all
+ *                      faces, as kernels/collisionsv2.cl:70-76 does (set before sphb_set_scene).
+ *                      Same field either way.
  *   "sort"             0 (default) = counting sort by search cell (the scan of the counts is the
  *                      cell table), made stable by a per-cell canonical order; 1 = LSD radix
  *                      sort of (key, index) pairs.  Both give the same order.

@@ -254,9 +254,12 @@ int launch_advect(const float4* pos, const float4* vhf, const float4* acc, float
                   const Face* faces, uint32_t face_count, const float* df, Reduce* red,
                   cudaStream_t s, const SlabAdvect* slab = nullptr, const FaceBin* bin = nullptr,
                   const QueueCtl* q = nullptr);
+// cand_start / cand_faces: per owning face, the ascending list of faces whose box can hold one
+// of its grid points (nullptr: every face is walked, as the reference does)
 int launch_distance_field(float* df, const Face* faces, const uint32_t* face_offsets,
-                          const float* transforms, const float* rvertices, uint32_t face_count,
-                          uint32_t gridcount, cudaStream_t s);
+                          const float* transforms, const float* rvertices,
+                          const uint32_t* cand_start, const uint32_t* cand_faces,
+                          uint32_t face_count, uint32_t gridcount, cudaStream_t s);
 // upload: particle i of the AoS array gets reference rank i
 int launch_aos_to_soa(const sphb_particle* aos, uint32_t n, float4* pos, float4* vel, float4* vhf,
                       float4* acc, float* rho, float* prs, uint32_t* ckey, uint32_t* rank,

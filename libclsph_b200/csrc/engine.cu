@@ -291,6 +291,9 @@ int sphb_set_scene(sphb_engine* e, const sphb_bb* bbs, uint32_t face_count, cons
   CUDA_TRY(e, cudaMemsetAsync(e->df, 0, sizeof(float) * df_len, e->stream));
   float* d_tr = nullptr;
   float* d_rv = nullptr;
+  uint32_t* d_cs = nullptr;
+  uint32_t* d_cf = nullptr;
+  e->df_build_ms = 0.f;
   if (face_count) {
     CUDA_TRY(e, cudaMemcpyAsync(e->faces, faces.data(), sizeof(Face) * face_count,
                                 cudaMemcpyHostToDevice, e->stream));
@@ -302,13 +305,52 @@ int sphb_set_scene(sphb_engine* e, const sphb_bb* bbs, uint32_t face_count, cons
                                 cudaMemcpyHostToDevice, e->stream));
     CUDA_TRY(e, cudaMemcpyAsync(d_rv, rvertices, sizeof(float) * 4 * face_count,
                                 cudaMemcpyHostToDevice, e->stream));
-    e->launches += launch_distance_field(e->df, e->faces, e->face_offsets, d_tr, d_rv, face_count,
-                                         total_grid_points, e->stream);
+    // Which faces can hold a grid point of face o's grid: those whose box meets o's box.  The
+    // grid points are min + k * (max - min) / (size - 1) in fp32 (collisionsv2.cl:84-86), which
+    // can land a few ulps outside [min, max]; the margin covers that, and a face let in by it
+    // merely fails the per-point test the kernel still makes.  Ascending order = the
+    // reference's loop order (:70), so ties resolve as they do there.
+    if (e->df_face_lists && face_count > 1) {
+      std::vector<uint32_t> cstart(face_count + 1, 0), cfaces;
+      for (uint32_t o = 0; o < face_count; ++o) {
+        const sphb_bb& a = bbs[o];
+        const float mx = 1e-4f * (fabsf(a.maxx) + fabsf(a.minx)) + 1e-6f;
+        const float my = 1e-4f * (fabsf(a.maxy) + fabsf(a.miny)) + 1e-6f;
+        const float mz = 1e-4f * (fabsf(a.maxz) + fabsf(a.minz)) + 1e-6f;
+        for (uint32_t i = 0; i < face_count; ++i) {
+          const sphb_bb& b = bbs[i];
+          const bool apart = b.minx > a.maxx + mx || b.maxx < a.minx - mx || b.miny > a.maxy + my ||
+                             b.maxy < a.miny - my || b.minz > a.maxz + mz || b.maxz < a.minz - mz;
+          if (!apart) cfaces.push_back(i);  // (NaN boxes compare false everywhere: kept)
+        }
+        cstart[o + 1] = (uint32_t)cfaces.size();
+      }
+      CUDA_TRY(e, dev_alloc(&d_cs, cstart.size()));
+      CUDA_TRY(e, dev_alloc(&d_cf, cfaces.size()));
+      CUDA_TRY(e, cudaMemcpyAsync(d_cs, cstart.data(), sizeof(uint32_t) * cstart.size(),
+                                  cudaMemcpyHostToDevice, e->stream));
+      CUDA_TRY(e, cudaMemcpyAsync(d_cf, cfaces.data(), sizeof(uint32_t) * cfaces.size(),
+                                  cudaMemcpyHostToDevice, e->stream));
+      // (pageable sources: both copies have been staged when the calls return)
+    }
+    cudaEvent_t t0 = nullptr, t1 = nullptr;
+    CUDA_TRY(e, cudaEventCreate(&t0));
+    CUDA_TRY(e, cudaEventCreate(&t1));
+    CUDA_TRY(e, cudaEventRecord(t0, e->stream));
+    e->launches += launch_distance_field(e->df, e->faces, e->face_offsets, d_tr, d_rv, d_cs, d_cf,
+                                         face_count, total_grid_points, e->stream);
     CUDA_TRY(e, cudaGetLastError());
+    CUDA_TRY(e, cudaEventRecord(t1, e->stream));
+    CUDA_TRY(e, cudaEventSynchronize(t1));
+    CUDA_TRY(e, cudaEventElapsedTime(&e->df_build_ms, t0, t1));
+    cudaEventDestroy(t0);
+    cudaEventDestroy(t1);
   }
   CUDA_TRY(e, cudaStreamSynchronize(e->stream));
   cudaFree(d_tr);
   cudaFree(d_rv);
+  cudaFree(d_cs);
+  cudaFree(d_cf);
   if (int rc = build_face_bin(e, bbs, face_count)) return rc;
   e->have_scene = true;
   return 0;
@@ -323,6 +365,8 @@ int sphb_get_distance_field(sphb_engine* e, float* out) {
   CUDA_TRY(e, cudaStreamSynchronize(e->stream));
   return 0;
 }
+
+float sphb_scene_build_ms(sphb_engine* e) { return e ? e->df_build_ms : 0.f; }
 
 int sphb_upload(sphb_engine* e, const sphb_particle* aos, uint32_t n) {
   if (!e || !aos) return SPHB_ERR_INVALID;
@@ -809,6 +853,10 @@ int sphb_set_option(sphb_engine* e, const char* name, int value) {
   if (!e || !name) return SPHB_ERR_INVALID;
   if (!strcmp(name, "triangle_bin")) {  // takes effect at the next sphb_set_scene
     e->bin_min_faces = value ? 17 : 0x7fffffff;
+    return 0;
+  }
+  if (!strcmp(name, "df_face_lists")) {  // takes effect at the next sphb_set_scene
+    e->df_face_lists = value != 0;
     return 0;
   }
   if (!strcmp(name, "sort")) {

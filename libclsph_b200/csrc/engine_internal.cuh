@@ -97,6 +97,8 @@ struct sphb_engine {
   uint32_t* bin_start = nullptr;  // device storage behind `bin`
   uint32_t* bin_faces = nullptr;
   int bin_min_faces = 17;         // scenes with fewer faces scan them all (option "triangle_bin")
+  bool df_face_lists = true;      // distance-field build walks per-face candidate lists (option "df_face_lists")
+  float df_build_ms = 0.f;        // device time of the last distance-field build
 
   // reductions
   Reduce* red = nullptr;       // device

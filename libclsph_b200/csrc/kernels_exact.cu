@@ -475,10 +475,16 @@ __device__ float dist_point_segment(float x, float y, float z, float x1, float y
 // libclsph/kernels/collisionsv2.cl:57-138 — one thread per distance-field grid point.
 // The reference finds the owning face by a linear walk down the offsets (:58-68); offsets
 // are strictly increasing, so an upper_bound gives the same face.
+// The reference then tests EVERY face's box against the point (:70-76); here only the faces
+// whose box meets the owning face's box are walked (cand_start / cand_faces: ascending face
+// index per owner, built by sphb_set_scene with a margin), with the same per-point test — the
+// faces left out fail it for every point of the owner's grid, so the field is unchanged.
 __global__ void __launch_bounds__(kBlock)
     k_distance_field(float* __restrict__ df, const Face* __restrict__ faces,
                      const uint32_t* __restrict__ offsets, const float* __restrict__ tr,
-                     const float* __restrict__ rv, uint32_t face_count, uint32_t gridcount) {
+                     const float* __restrict__ rv, const uint32_t* __restrict__ cand_start,
+                     const uint32_t* __restrict__ cand_faces, uint32_t face_count,
+                     uint32_t gridcount) {
   const uint32_t g = blockIdx.x * kBlock + threadIdx.x;
   if (g >= gridcount) return;
   uint32_t lo = 0, hi = face_count;  // largest index with offsets[index] <= g (index 0 if none)
@@ -498,7 +504,10 @@ __global__ void __launch_bounds__(kBlock)
 
   float temd = 20;
   const float4* f4 = reinterpret_cast<const float4*>(faces);
-  for (int i = 0; i < (int)face_count; ++i) {
+  const uint32_t k0 = cand_start ? __ldg(cand_start + lo) : 0u;
+  const uint32_t k1 = cand_start ? __ldg(cand_start + lo + 1) : face_count;
+  for (uint32_t k = k0; k < k1; ++k) {
+    const int i = cand_start ? (int)__ldg(cand_faces + k) : (int)k;
     const float4 b0 = __ldg(f4 + 3 * i);
     const float4 b1 = __ldg(f4 + 3 * i + 1);
     if (px <= b0.x && px >= b0.w && py <= b0.y && py >= b1.x && pz <= b0.z && pz >= b1.y) {
@@ -762,11 +771,13 @@ int launch_advect(const float4* pos, const float4* vhf, const float4* acc, float
 }
 
 int launch_distance_field(float* df, const Face* faces, const uint32_t* face_offsets,
-                          const float* transforms, const float* rvertices, uint32_t face_count,
-                          uint32_t gridcount, cudaStream_t s) {
+                          const float* transforms, const float* rvertices,
+                          const uint32_t* cand_start, const uint32_t* cand_faces,
+                          uint32_t face_count, uint32_t gridcount, cudaStream_t s) {
   if (gridcount == 0 || face_count == 0) return 0;
   k_distance_field<<<blocks_for(gridcount), kBlock, 0, s>>>(df, faces, face_offsets, transforms,
-                                                            rvertices, face_count, gridcount);
+                                                            rvertices, cand_start, cand_faces,
+                                                            face_count, gridcount);
   return 1;
 }
 

@@ -80,7 +80,7 @@ SYMBOLS = [
     "sphb_host_alloc", "sphb_host_free", "sphb_debug_advect", "sphb_event_record", "sphb_event_elapsed_ms",
     "sphb_slab_create", "sphb_slab_message_bytes", "sphb_slab_configure", "sphb_slab_upload", "sphb_slab_bbox",
     "sphb_slab_pack", "sphb_slab_unpack", "sphb_slab_forces", "sphb_slab_advect", "sphb_slab_commit",
-    "sphb_slab_download", "sphb_compute_dt",
+    "sphb_slab_download", "sphb_compute_dt", "sphb_scene_build_ms",
     "sphb_nccl_unique_id", "sphb_slab_comm_init", "sphb_slab_start", "sphb_slab_step", "sphb_slab_bytes_sent",
     "sphb_slab_phase_ms", "sphb_slab_resends",
 ]
@@ -160,6 +160,8 @@ def lib():
         L.sphb_slab_resends.restype = C.c_uint64
         L.sphb_compute_dt.argtypes = [vp, f32, f32]
         L.sphb_compute_dt.restype = f32
+        L.sphb_scene_build_ms.argtypes = [vp]
+        L.sphb_scene_build_ms.restype = f32
         L.sphb_debug_advect.argtypes = [vp, f32]
         L.sphb_event_record.argtypes = [vp, i32]
         L.sphb_event_elapsed_ms.argtypes = [vp, i32, i32, C.POINTER(f32)]
@@ -222,6 +224,10 @@ class Engine:
         self.total_grid_points = int(total_grid_points)
         self._check(self.L.sphb_set_scene(self.h, _ptr(bbs), len(bbs), _ptr(transforms), _ptr(rvertices),
                                           self.total_grid_points))
+
+    def scene_build_ms(self):
+        """device milliseconds of the last distance-field build"""
+        return float(self.L.sphb_scene_build_ms(self.h))
 
     def distance_field(self):
         out = np.zeros(self.total_grid_points, np.float32)

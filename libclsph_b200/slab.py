@@ -284,7 +284,10 @@ class LoopbackWorld:
         self.attempts = 0
 
     def _allreduce(self):
-        hosts = [d.local.red8_to_host(d.red8) for d in self.ranks]
+        hosts = []
+        for d in self.ranks:  # the read-back must be ordered behind the rank's own (non-blocking) stream
+            with d.local.stream_context():
+                hosts.append(d.local.red8_to_host(d.red8))
         return np.maximum.reduce(hosts).astype(np.float32)
 
     def start(self, parts):

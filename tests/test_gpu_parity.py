@@ -105,12 +105,18 @@ def test_distance_field_bit_exact_vs_fixtures():
                          ("scene_river_water", "steps_box_water")]:
         g = np.load(os.path.join(GOLDEN, steps + ".npz"))
         sc = np.load(os.path.join(GOLDEN, scene + ".npz"))
-        with Engine(g["params0"], g["terms"]) as e:
-            e.set_scene(sc["bbs"], sc["transforms"], sc["rvertices"], int(sc["total_gridpoints"]))
-            df = e.distance_field()
-        sample = df[::97] if len(df) < (1 << 21) else df[::997]
-        assert np.array_equal(sample.view(np.uint32), sc["df_sample"].view(np.uint32)), scene
-        assert hashlib.sha256(df.tobytes()).hexdigest() == str(sc["df_sha256"]), scene
+        # with the per-face candidate lists (default), and with the reference's loop over all faces
+        for face_lists in (1, 0):
+            with Engine(g["params0"], g["terms"]) as e:
+                e.set_option("df_face_lists", face_lists)
+                e.set_scene(sc["bbs"], sc["transforms"], sc["rvertices"], int(sc["total_gridpoints"]))
+                df = e.distance_field()
+                ms = e.scene_build_ms()
+            where = f"{scene} face_lists={face_lists}"
+            print(f"{where}: {len(sc['bbs'])} faces, {len(df)} grid points, {ms:.3f} ms")
+            sample = df[::97] if len(df) < (1 << 21) else df[::997]
+            assert np.array_equal(sample.view(np.uint32), sc["df_sample"].view(np.uint32)), where
+            assert hashlib.sha256(df.tobytes()).hexdigest() == str(sc["df_sha256"]), where
 
 
 @pytest.mark.parametrize("triangle_bin", [1, 0])
