@@ -65,6 +65,18 @@ int clsph_simulate(const char* fluid_json, const char* sim_json, const char* obj
                    sphb_params* final_params, uint64_t* steps_done, uint32_t* frames_saved,
                    char* err, size_t err_cap);
 
+/* The same over `devices` GPUs of one box (device, device + 1, ...): sph_simulation::devices —
+ * the particles are partitioned into slabs along x, one slab engine and one host thread per GPU,
+ * halo exchange over NCCL inside every step (libclsph_b200/host/sph_simulation_slabs.cpp).
+ * rebalance: re-cut the slabs when one holds more than this multiple of its fair share (0 =
+ * never); *recuts: how often that happened.  final_state is ordered by grid_index.
+ * devices < 0: |devices| GPUs with sph_simulation::force_slabs (-1 = one slab engine on one GPU
+ * through the same path). */
+int clsph_simulate_devices(const char* fluid_json, const char* sim_json, const char* obj_path, int device,
+                           int devices, float rebalance, uint64_t max_steps, const char* frames_prefix,
+                           sphb_particle* final_state, sphb_params* final_params, uint64_t* steps_done,
+                           uint32_t* frames_saved, uint64_t* recuts, char* err, size_t err_cap);
+
 #ifdef __cplusplus
 }
 #endif

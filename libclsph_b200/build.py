@@ -89,7 +89,7 @@ def build(force=False, verbose=False):
 HOST = os.path.join(HERE, "host")
 HOST_OUT = os.path.join(HERE, "libclsph_host.so")
 CLI_OUT = os.path.join(HERE, "clsphparticles")
-HOST_SOURCES = ["scene.cpp", "sph_simulation.cpp", "capi.cpp", "util/obj_reader.cpp",
+HOST_SOURCES = ["scene.cpp", "sph_simulation.cpp", "sph_simulation_slabs.cpp", "capi.cpp", "util/obj_reader.cpp",
                 "file_save_delegates/houdini_file_saver.cpp"]
 # -ffp-contract=off: scene preparation is compared bit for bit with the reference's
 HOST_FLAGS = ["-std=c++11", "-O2", "-ffp-contract=off", "-fPIC", "-Wall", "-pthread",

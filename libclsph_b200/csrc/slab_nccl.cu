@@ -35,11 +35,8 @@ struct NcclApi {
   bool ok = false;
 };
 
-NcclApi& nccl() {
-  static NcclApi api;
-  static bool tried = false;
-  if (tried) return api;
-  tried = true;
+NcclApi load_nccl() {
+  NcclApi api;
   const char* names[] = {"libnccl.so.2", "libnccl.so"};
   for (const char* nm : names) {
     api.handle = dlopen(nm, RTLD_NOW | RTLD_NOLOAD | RTLD_GLOBAL);  // the copy already loaded (torch's)
@@ -64,6 +61,13 @@ NcclApi& nccl() {
   SPHB_NCCL_SYM(GetErrorString, "ncclGetErrorString")
 #undef SPHB_NCCL_SYM
   api.ok = true;
+  return api;
+}
+
+// resolved once, whichever thread asks first (several slab engines of one process are driven by
+// one host thread each: libclsph_b200/host/sph_simulation_slabs.cpp)
+NcclApi& nccl() {
+  static NcclApi api = load_nccl();
   return api;
 }
 

@@ -10,7 +10,7 @@ from .engine import BB, PARAMS, PARTICLE, TERMS, HERE, _ptr, lib as _engine_lib
 SYMBOLS = [
     "clsph_scene_load", "clsph_scene_face_count", "clsph_scene_total_grid_points", "clsph_scene_copy",
     "clsph_scene_free", "clsph_load_settings", "clsph_lattice", "clsph_geo_text", "clsph_bgeo_bytes",
-    "clsph_save_frame", "clsph_simulate",
+    "clsph_save_frame", "clsph_simulate", "clsph_simulate_devices",
 ]
 
 _lib = None
@@ -50,6 +50,9 @@ def lib():
         L.clsph_save_frame.argtypes = [C.c_char_p, i32, vp, vp]
         L.clsph_simulate.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, i32, C.c_uint64, C.c_char_p, vp, vp,
                                      C.POINTER(C.c_uint64), C.POINTER(u32), C.c_char_p, C.c_size_t]
+        L.clsph_simulate_devices.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, i32, i32, f32, C.c_uint64,
+                                             C.c_char_p, vp, vp, C.POINTER(C.c_uint64), C.POINTER(u32),
+                                             C.POINTER(C.c_uint64), C.c_char_p, C.c_size_t]
         _lib = L
     return _lib
 
@@ -126,8 +129,10 @@ def save_frame(frames_prefix, particles, params, use_partio=False):
         raise RuntimeError("clsph_save_frame failed")
 
 
-def simulate(fluid_json, sim_json, obj_path, device=-1, max_steps=0, frames_prefix=None, n=None):
-    """Headless sph_simulation::simulate(); returns dict(state, params, steps, frames)."""
+def simulate(fluid_json, sim_json, obj_path, device=-1, max_steps=0, frames_prefix=None, n=None, devices=1,
+             rebalance=1.25):
+    """Headless sph_simulation::simulate(); returns dict(state, params, steps, frames[, recuts]).
+    devices > 1: sph_simulation::devices — slabs over GPUs device .. device + devices - 1."""
     L = lib()
     if n is None:
         n = int(load_settings(fluid_json, sim_json)[0]["particles_count"][0])
@@ -136,6 +141,16 @@ def simulate(fluid_json, sim_json, obj_path, device=-1, max_steps=0, frames_pref
     steps = C.c_uint64()
     frames = C.c_uint32()
     err = C.create_string_buffer(512)
+    if devices != 1:
+        recuts = C.c_uint64()
+        rc = L.clsph_simulate_devices(os.fsencode(fluid_json), os.fsencode(sim_json), os.fsencode(obj_path),
+                                      max(device, 0), devices, float(rebalance), max_steps,
+                                      os.fsencode(frames_prefix) if frames_prefix is not None else None,
+                                      _ptr(state), _ptr(params), C.byref(steps), C.byref(frames),
+                                      C.byref(recuts), err, len(err))
+        if rc != 0:
+            raise RuntimeError(err.value.decode())
+        return dict(state=state, params=params, steps=steps.value, frames=frames.value, recuts=recuts.value)
     rc = L.clsph_simulate(os.fsencode(fluid_json), os.fsencode(sim_json), os.fsencode(obj_path), device,
                           max_steps, os.fsencode(frames_prefix) if frames_prefix is not None else None,
                           _ptr(state), _ptr(params), C.byref(steps), C.byref(frames), err, len(err))

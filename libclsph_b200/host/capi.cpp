@@ -130,7 +130,15 @@ int clsph_simulate(const char* fluid_json, const char* sim_json, const char* obj
                    uint64_t max_steps, const char* frames_prefix, sphb_particle* final_state,
                    sphb_params* final_params, uint64_t* steps_done, uint32_t* frames_saved,
                    char* err, size_t err_cap) {
-  if (!fluid_json || !sim_json || !obj_path) return -1;
+  return clsph_simulate_devices(fluid_json, sim_json, obj_path, device, 1, 0.f, max_steps, frames_prefix,
+                                final_state, final_params, steps_done, frames_saved, 0, err, err_cap);
+}
+
+int clsph_simulate_devices(const char* fluid_json, const char* sim_json, const char* obj_path, int device,
+                           int devices, float rebalance, uint64_t max_steps, const char* frames_prefix,
+                           sphb_particle* final_state, sphb_params* final_params, uint64_t* steps_done,
+                           uint32_t* frames_saved, uint64_t* recuts, char* err, size_t err_cap) {
+  if (!fluid_json || !sim_json || !obj_path || devices == 0) return -1;
   try {
     mute_cout quiet(true);
     sph_simulation sim;
@@ -140,6 +148,9 @@ int clsph_simulate(const char* fluid_json, const char* sim_json, const char* obj
       return -1;
     }
     sim.device = device;
+    sim.devices = devices < 0 ? -devices : devices;
+    sim.force_slabs = devices < 0;
+    if (devices != 1) sim.rebalance = rebalance;
     sim.quiet = true;
     sim.max_steps = (unsigned long)max_steps;
     houdini_file_saver saver(frames_prefix ? frames_prefix : "");
@@ -154,6 +165,7 @@ int clsph_simulate(const char* fluid_json, const char* sim_json, const char* obj
     sim.simulate();
     if (steps_done) *steps_done = sim.steps_done;
     if (frames_saved) *frames_saved = saved;
+    if (recuts) *recuts = sim.slab_recuts;
   } catch (const std::exception& ex) {
     set_err(err, err_cap, ex.what());
     return -1;

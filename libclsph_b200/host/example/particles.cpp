@@ -1,9 +1,10 @@
 // Command-line driver with the interface of the reference's example/particles.cpp:
-//   ./sph <fluid_name> <simulation_properties_name> <scene_name> <frames_folder_prefix> [-y]
+//   ./sph <fluid_name> <simulation_properties_name> <scene_name> <frames_folder_prefix> [-y] [-g N]
 // reads fluid_properties/<fluid>.json, simulation_properties/<sim>.json, scenes/<scene>,
 // writes <prefix>frames/frameNNNNNNN.geo and (with "serialize") last_frame.bin, asks for a key
 // before starting (skipped with -y) and prints the CPU-clock duration of simulate().
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <ctime>
 #include <fstream>
@@ -28,9 +29,16 @@ int main(int argc, char** argv) {
                  "<frames_folder_prefix>" << std::endl;
     return -1;
   }
-  const bool assume_yes = argc > 5 && std::strcmp(argv[5], "-y") == 0;
+  // additions after the reference's four arguments: -y (do not wait for a key), -g N (N GPUs)
+  bool assume_yes = false;
+  int gpus = 1;
+  for (int a = 5; a < argc; ++a) {
+    if (std::strcmp(argv[a], "-y") == 0) assume_yes = true;
+    else if (std::strcmp(argv[a], "-g") == 0 && a + 1 < argc) gpus = std::atoi(argv[++a]);
+  }
 
   sph_simulation simulation;
+  simulation.devices = gpus < 1 ? 1 : gpus;
   houdini_file_saver saver = houdini_file_saver(std::string(argv[4]));
   try {
     simulation.load_settings(std::string("fluid_properties/") + argv[1] + ".json",

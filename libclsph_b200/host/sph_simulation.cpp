@@ -129,6 +129,7 @@ void sph_simulation::init_particles(particle* buffer, const simulation_parameter
 }
 
 float sph_simulation::simulate_single_frame(float dt) {
+  if (team_) return slabs_step(dt);
   float computed = dt;
   SPHB_CHECK(sphb_step(engine_, dt, &computed));
   // the reference mutates `parameters` in findMinMaxPosition (:670-727); hooks see that
@@ -171,7 +172,14 @@ void sph_simulation::run_frame_on_device(float& dt, float& timeleft) {
 }
 
 void sph_simulation::read_particles(particle* particles) {
+  if (team_) return slabs_read(particles);
   SPHB_CHECK(sphb_download(engine_, reinterpret_cast<sphb_particle*>(particles)));
+}
+
+void sph_simulation::upload_particles(const particle* particles) {
+  if (team_) return slabs_upload(particles, false);
+  SPHB_CHECK(sphb_upload(engine_, reinterpret_cast<const sphb_particle*>(particles),
+                         parameters.particles_count));
 }
 
 // executePreFrameOpperation / executePostFrameOpperation (:730-768)
@@ -181,9 +189,7 @@ bool sph_simulation::run_hook(std::function<bool(particle*, const simulation_par
     read_particles(particles);
     readParticle = false;
   }
-  if (hook(particles, parameters, isFullFrame))
-    SPHB_CHECK(sphb_upload(engine_, reinterpret_cast<const sphb_particle*>(particles),
-                           parameters.particles_count));
+  if (hook(particles, parameters, isFullFrame)) upload_particles(particles);
   return readParticle;
 }
 
@@ -192,8 +198,12 @@ void sph_simulation::simulate() {
   bool readParticle = true;
   steps_done = 0;
 
-  SPHB_CHECK(sphb_create(reinterpret_cast<const sphb_params*>(&parameters),
-                         reinterpret_cast<const sphb_terms*>(&precomputed_terms), device, &engine_));
+  const bool slabs = devices > 1 || force_slabs;
+  if (devices < 1) devices = 1;
+  slab_recuts = 0;
+  if (!slabs)
+    SPHB_CHECK(sphb_create(reinterpret_cast<const sphb_params*>(&parameters),
+                           reinterpret_cast<const sphb_terms*>(&precomputed_terms), device, &engine_));
 
   particle* particles = 0;
   // pinned, so the per-frame read-back runs at full PCIe speed
@@ -201,8 +211,7 @@ void sph_simulation::simulate() {
                              sizeof(particle) * (size_t)parameters.particles_count));
   for (size_t i = 0; i < parameters.particles_count; ++i) particles[i] = particle();
   init_particles(particles, parameters);
-  SPHB_CHECK(sphb_upload(engine_, reinterpret_cast<const sphb_particle*>(particles),
-                         parameters.particles_count));
+  if (!slabs) upload_particles(particles);
 
   float time = 0.0;
   const float timeperframe = 1.0f / parameters.target_fps;
@@ -211,9 +220,16 @@ void sph_simulation::simulate() {
 
   // computeDistanceField (:607-632): built on the device from the scene::load products
   std::cout << "totalgpoints " << current_scene.totalGridpoints << std::endl;
-  SPHB_CHECK(sphb_set_scene(engine_, reinterpret_cast<const sphb_bb*>(current_scene.bbs.data()),
-                            current_scene.face_count, current_scene.transforms.data(),
-                            current_scene.rvertices.data(), current_scene.totalGridpoints));
+  if (slabs) {
+    // one slab engine per GPU, each with its own copy of the scene; the particles are dealt out
+    // by equal-count faces along x (sph_simulation_slabs.cpp)
+    slabs_begin();
+    slabs_upload(particles, true);
+  } else {
+    SPHB_CHECK(sphb_set_scene(engine_, reinterpret_cast<const sphb_bb*>(current_scene.bbs.data()),
+                              current_scene.face_count, current_scene.transforms.data(),
+                              current_scene.rvertices.data(), current_scene.totalGridpoints));
+  }
 
   // one save in flight at most; the host array is borrowed until the next join
   auto spawn_save = [&]() {
@@ -225,7 +241,7 @@ void sph_simulation::simulate() {
   // Without pre/post hooks nobody but the save thread reads the host array, so the per-frame
   // read-back need not block the step loop: the state is snapshot on the device,
   // the copy to the host runs beside the next frame's steps, and the save thread waits for it.
-  const bool async_frames = save_frame && !pre_frame && !post_frame;
+  const bool async_frames = save_frame && !pre_frame && !post_frame && !slabs;
   auto read_and_save = [&]() {
     savet.join();  // the previous save still reads the host array
     if (!async_frames) {
@@ -254,7 +270,7 @@ void sph_simulation::simulate() {
       readParticle = run_hook(pre_frame, particles, readParticle, true);
 
     float timeleft = timeperframe;
-    if (!write_intermediate_frames && device_loop) {
+    if (!write_intermediate_frames && device_loop && !slabs) {
       // Nothing looks at the state between the sub-steps of this frame: the whole loop below runs
       // inside the engine, without a host round trip per step, and the lines the
       // reference prints per step are printed afterwards from the engine's log.
@@ -293,6 +309,7 @@ void sph_simulation::simulate() {
   }
   if (save_frame) savet.join();
   sphb_host_free(particles);
-  sphb_destroy(engine_);
+  if (slabs) slabs_end();
+  else sphb_destroy(engine_);
   engine_ = 0;
 }

@@ -12,13 +12,14 @@
 #include "scene.h"
 
 struct sphb_engine;
+namespace sphb_host { struct slab_team; }
 
 class sph_simulation {
  public:
   sph_simulation()
       : parameters(), precomputed_terms(), write_intermediate_frames(false), serialize(false),
         initial_volume(0.f), device(-1), quiet(false), max_steps(0), steps_done(0), device_loop(true),
-        engine_(0) {}
+        devices(1), rebalance(1.25f), slab_recuts(0), force_slabs(false), engine_(0), team_(0) {}
 
   // Runs the whole simulation: frames of 1/target_fps seconds, each made of adaptive
   // sub-steps, calling the hooks below exactly where the reference does
@@ -49,6 +50,13 @@ class sph_simulation {
   unsigned long max_steps;  // stop after this many sub-steps (0 = run simulation_time)
   unsigned long steps_done; // sub-steps executed by the last simulate()
   bool device_loop;         // a frame's sub-steps run as one engine call (sphb_run_frame)
+  // Several GPUs of one box (sph_simulation_slabs.cpp): the particles are partitioned into
+  // `devices` slabs along x, GPU device + r stepping slab r, with a halo exchange over NCCL in
+  // every step.  Hooks and save_frame see all particles, ordered by grid_index.
+  int devices;              // 1 = the reference's single device
+  float rebalance;          // re-cut the slabs when one holds more than this multiple of its fair share (0 = never)
+  unsigned long slab_recuts;  // re-cuts done by the last simulate()
+  bool force_slabs;         // route even devices == 1 through the slab path (one slab: tests)
 
  private:
   void init_particles(particle* buffer, const simulation_parameters&);
@@ -57,9 +65,17 @@ class sph_simulation {
   bool run_hook(std::function<bool(particle*, const simulation_parameters&, bool)>& hook,
                 particle* particles, bool readParticle, bool isFullFrame);
   void read_particles(particle* particles);
+  void upload_particles(const particle* particles);
   void check(int rc, const char* file, int line);
+  void slabs_begin();
+  void slabs_end();
+  void slabs_upload(const particle* particles, bool recut);
+  void slabs_read(particle* particles);
+  float slabs_step(float dt);
+  void slabs_fail(int rc, int rank, const char* what);
 
   sphb_engine* engine_;
+  sphb_host::slab_team* team_;
 };
 
 #endif

@@ -1,0 +1,314 @@
+// sph_simulation over several GPUs of one box (addition: the reference is single-device,
+// libclsph/sph_simulation.cpp:273-275).  `devices` > 1 partitions the particles into slabs along
+// x, one slab engine per GPU (include/sphb.h, "slab engines"), each driven by its own host thread:
+// a step is one sphb_slab_step per rank, issued by all the threads at once — the halo exchange and
+// the 8-float all-reduce inside it go over NCCL between the engines' streams.  The frame loop, the
+// hooks and save_frame stay those of the single-device path (sph_simulation.cpp); only its three
+// primitives — step, read the particles back, upload them — are routed here.
+//
+// What a hook / save_frame sees: all N particles, stably ordered by grid_index (the reference's
+// Morton key under the global grid) with the slabs taken left to right — the reference's
+// cell-sorted order up to the order inside a cell, which there depends on the history of the
+// sort and is not reproduced across slabs.
+#include <algorithm>
+#include <cmath>
+#include <condition_variable>
+#include <cstdlib>
+#include <cstring>
+#include <iostream>
+#include <limits>
+#include <mutex>
+#include <thread>
+#include <vector>
+
+#include "sph_simulation.h"
+#include "sphb.h"
+
+namespace sphb_host {
+
+// n persistent host threads; run(f) executes f(rank) on all of them at once and waits
+class worker_team {
+ public:
+  explicit worker_team(int n) : job_(0), generation_(0), pending_(0), quit_(false), rc_(n, 0) {
+    for (int r = 0; r < n; ++r) threads_.push_back(std::thread(&worker_team::loop, this, r));
+  }
+  ~worker_team() {
+    {
+      std::lock_guard<std::mutex> lock(m_);
+      quit_ = true;
+      ++generation_;
+    }
+    go_.notify_all();
+    for (size_t r = 0; r < threads_.size(); ++r) threads_[r].join();
+  }
+  // the first non-zero result in rank order (and which rank it came from), else 0
+  int run(const std::function<int(int)>& f, int* failed_rank = 0) {
+    std::unique_lock<std::mutex> lock(m_);
+    job_ = &f;
+    pending_ = (int)threads_.size();
+    ++generation_;
+    go_.notify_all();
+    while (pending_ > 0) done_.wait(lock);
+    job_ = 0;
+    for (size_t r = 0; r < rc_.size(); ++r)
+      if (rc_[r] != 0) {
+        if (failed_rank) *failed_rank = (int)r;
+        return rc_[r];
+      }
+    return 0;
+  }
+
+ private:
+  void loop(int rank) {
+    unsigned long seen = 0;
+    for (;;) {
+      const std::function<int(int)>* job = 0;
+      {
+        std::unique_lock<std::mutex> lock(m_);
+        while (generation_ == seen) go_.wait(lock);
+        seen = generation_;
+        if (quit_) return;
+        job = job_;
+      }
+      const int rc = (*job)(rank);
+      {
+        std::lock_guard<std::mutex> lock(m_);
+        rc_[rank] = rc;
+        if (--pending_ == 0) done_.notify_all();
+      }
+    }
+  }
+  std::vector<std::thread> threads_;
+  std::mutex m_;
+  std::condition_variable go_, done_;
+  const std::function<int(int)>* job_;
+  unsigned long generation_;
+  int pending_;
+  bool quit_;
+  std::vector<int> rc_;
+};
+
+struct slab_team {
+  explicit slab_team(int n) : world(n), workers(n), engines(n, (sphb_engine*)0), owned(n, 0), capacity(0), exchange_capacity(0) {}
+  int world;
+  worker_team workers;
+  std::vector<sphb_engine*> engines;
+  std::vector<float> cuts;           // world + 1 slab faces, -inf ... +inf
+  std::vector<uint32_t> ids;         // id of the particle at each index of the caller's host array
+  std::vector<particle> stage;       // particles in rank order (uploads and downloads)
+  std::vector<uint32_t> stage_ids;
+  std::vector<uint32_t> owned;       // particles each rank owns
+  std::vector<particle> recut;       // a re-cut's own gather buffer (the caller's array may be on loan to save_frame)
+  uint32_t capacity, exchange_capacity;
+};
+
+// Slab faces for `world` ranks holding (nearly) equal counts: a face lies midway between two
+// neighbouring DISTINCT x values, so that a lattice plane is never split; the outer faces are
+// -inf / +inf.  (libclsph_b200/slab.py::equal_count_cuts is the same rule.)
+std::vector<float> equal_count_cuts(const particle* p, size_t n, int world) {
+  std::vector<float> xs(n);
+  for (size_t i = 0; i < n; ++i) xs[i] = p[i].position.s[0];
+  std::sort(xs.begin(), xs.end());  // (NaN positions are not expected here)
+  std::vector<float> cuts;
+  cuts.push_back(-std::numeric_limits<float>::infinity());
+  for (int r = 1; r < world; ++r) {
+    const size_t k = n * (size_t)r / (size_t)world;
+    const float lo = n ? (k > 0 ? xs[k - 1] : xs[0]) : 0.f;
+    const size_t j = (size_t)(std::upper_bound(xs.begin(), xs.end(), lo) - xs.begin());
+    const float hi = j < n ? xs[j] : lo;
+    cuts.push_back((float)(((double)lo + (double)hi) / 2));
+  }
+  cuts.push_back(std::numeric_limits<float>::infinity());
+  return cuts;
+}
+
+// which slab [cuts[r], cuts[r+1]) holds x
+inline int slab_of(const std::vector<float>& cuts, float x) {
+  const int world = (int)cuts.size() - 1;
+  int r = (int)(std::upper_bound(cuts.begin() + 1, cuts.end() - 1, x) - (cuts.begin() + 1));
+  return r < 0 ? 0 : (r >= world ? world - 1 : r);
+}
+
+}  // namespace sphb_host
+
+using sphb_host::slab_team;
+
+void sph_simulation::slabs_fail(int rc, int rank, const char* what) {
+  std::cerr << "A CUDA engine error occured (" << what << ", GPU rank " << rank << ")-> "
+            << ((team_ && team_->engines[rank]) ? sphb_last_error(team_->engines[rank]) : sphb_error_string(rc))
+            << std::endl;
+  std::exit(-1);
+}
+
+// Engines, scene, communicator.  Every rank gets room for 1.6 x its fair share plus two ghost
+// layers; a halo message holds up to N / 4 records (at least 65 536).
+void sph_simulation::slabs_begin() {
+  const int world = devices;
+  const uint32_t n = parameters.particles_count;
+  team_ = new slab_team(world);
+  slab_team& T = *team_;
+  uint64_t exch = n / 4u;
+  if (exch < 65536u) exch = 65536u;
+  if (exch > n) exch = n ? n : 1u;
+  uint64_t cap = (uint64_t)(1.6 * (double)n / world) + 2u * exch + 1024u;
+  if (cap > n) cap = n ? n : 1u;
+  T.capacity = (uint32_t)cap;
+  T.exchange_capacity = (uint32_t)exch;
+  T.ids.resize(n);
+  for (uint32_t i = 0; i < n; ++i) T.ids[i] = i;
+  T.stage.resize(n);
+  T.stage_ids.resize(n);
+
+  unsigned char id[128];
+  int rc = sphb_nccl_unique_id(id);
+  if (rc != 0) {
+    std::cerr << "A CUDA engine error occured (NCCL)-> " << sphb_last_error(0) << std::endl;
+    std::exit(-1);
+  }
+  const int base = device < 0 ? 0 : device;
+  const sphb_params* P = reinterpret_cast<const sphb_params*>(&parameters);
+  const sphb_terms* K = reinterpret_cast<const sphb_terms*>(&precomputed_terms);
+  int bad = 0;
+  rc = T.workers.run([&](int r) -> int {
+    sphb_engine* e = 0;
+    if (int c = sphb_slab_create(P, K, base + r, T.capacity, T.exchange_capacity, &e)) return c;
+    T.engines[r] = e;
+    return sphb_set_scene(e, reinterpret_cast<const sphb_bb*>(current_scene.bbs.data()),
+                          current_scene.face_count, current_scene.transforms.data(),
+                          current_scene.rvertices.data(), current_scene.totalGridpoints);
+  }, &bad);
+  if (rc != 0) slabs_fail(rc, bad, "slab set-up");
+  // (collective: entered only once every rank has an engine, so a missing GPU is an error
+  // message above and not a rendezvous that never completes)
+  rc = T.workers.run([&](int r) -> int { return sphb_slab_comm_init(T.engines[r], id, r, world); }, &bad);
+  if (rc != 0) slabs_fail(rc, bad, "NCCL communicator");
+}
+
+void sph_simulation::slabs_end() {
+  if (!team_) return;
+  slab_team& T = *team_;
+  T.workers.run([&](int r) -> int {
+    if (T.engines[r]) sphb_destroy(T.engines[r]);
+    T.engines[r] = 0;
+    return 0;
+  });
+  delete team_;
+  team_ = 0;
+}
+
+// The caller's host array -> the slab engines.  `recut`: new equal-count faces from the current
+// positions (else the particles are dealt out by the faces in force).
+void sph_simulation::slabs_upload(const particle* particles, bool recut) {
+  slab_team& T = *team_;
+  const uint32_t n = parameters.particles_count;
+  if (recut || T.cuts.empty()) T.cuts = sphb_host::equal_count_cuts(particles, n, T.world);
+  std::vector<uint32_t> start(T.world + 1, 0);
+  std::vector<int> where(n);
+  for (uint32_t i = 0; i < n; ++i) {
+    where[i] = sphb_host::slab_of(T.cuts, particles[i].position.s[0]);
+    ++start[where[i] + 1];
+  }
+  for (int r = 0; r < T.world; ++r) start[r + 1] += start[r];
+  std::vector<uint32_t> cursor(start.begin(), start.end() - 1);
+  for (uint32_t i = 0; i < n; ++i) {
+    const uint32_t d = cursor[where[i]]++;
+    T.stage[d] = particles[i];
+    T.stage_ids[d] = T.ids[i];
+  }
+  for (int r = 0; r < T.world; ++r) T.owned[r] = start[r + 1] - start[r];
+  int bad = 0;
+  const int rc = T.workers.run([&](int r) -> int {
+    sphb_engine* e = T.engines[r];
+    if (int c = sphb_slab_configure(e, T.cuts[r], T.cuts[r + 1], r > 0, r + 1 < T.world)) return c;
+    if (int c = sphb_slab_upload(e, reinterpret_cast<const sphb_particle*>(T.stage.data() + start[r]),
+                                 T.stage_ids.data() + start[r], T.owned[r]))
+      return c;
+    return sphb_slab_start(e);  // collective: the global bbox
+  }, &bad);
+  if (rc != 0) slabs_fail(rc, bad, "slab upload");
+}
+
+// The slab engines -> the caller's host array, ordered by grid_index (see the file header).
+void sph_simulation::slabs_read(particle* particles) {
+  slab_team& T = *team_;
+  const uint32_t n = parameters.particles_count;
+  int bad = 0;
+  int rc = T.workers.run([&](int r) -> int {
+    uint32_t cnt = 0;
+    const int c = sphb_slab_download(T.engines[r], 0, 0, 0, &cnt);
+    T.owned[r] = cnt;
+    return c;
+  }, &bad);
+  if (rc != 0) slabs_fail(rc, bad, "slab download");
+  std::vector<uint32_t> start(T.world + 1, 0);
+  for (int r = 0; r < T.world; ++r) start[r + 1] = start[r] + T.owned[r];
+  if (start[T.world] != n) {
+    std::cerr << "slab engines hold " << start[T.world] << " particles, expected " << n << std::endl;
+    std::exit(-1);
+  }
+  rc = T.workers.run([&](int r) -> int {
+    uint32_t cnt = 0;
+    if (!T.owned[r]) return 0;
+    return sphb_slab_download(T.engines[r], reinterpret_cast<sphb_particle*>(T.stage.data() + start[r]),
+                              T.stage_ids.data() + start[r], T.owned[r], &cnt);
+  }, &bad);
+  if (rc != 0) slabs_fail(rc, bad, "slab download");
+  // stable counting sort by grid_index; keys past the grid's Morton bound (runaway particles)
+  // share one last bucket
+  const uint32_t cells = parameters.grid_cell_count;
+  std::vector<uint32_t> first((size_t)cells + 2, 0);
+  for (uint32_t i = 0; i < n; ++i) {
+    const uint32_t k = T.stage[i].grid_index < cells ? T.stage[i].grid_index : cells;
+    ++first[(size_t)k + 1];
+  }
+  for (size_t c = 0; c <= cells; ++c) first[c + 1] += first[c];
+  for (uint32_t i = 0; i < n; ++i) {
+    const uint32_t k = T.stage[i].grid_index < cells ? T.stage[i].grid_index : cells;
+    const uint32_t d = first[k]++;
+    particles[d] = T.stage[i];
+    T.ids[d] = T.stage_ids[i];
+  }
+}
+
+// One simulate_single_frame over all slabs; afterwards, when the fullest slab has outgrown
+// `rebalance` x the mean, the particles are gathered and dealt out again by fresh equal-count faces.
+float sph_simulation::slabs_step(float dt) {
+  slab_team& T = *team_;
+  std::vector<float> out(T.world, dt);
+  int bad = 0;
+  const int rc = T.workers.run([&](int r) -> int {
+    int attempts = 0;
+    uint32_t ghosts = 0;
+    return sphb_slab_step(T.engines[r], dt, &out[r], &attempts, &T.owned[r], &ghosts);
+  }, &bad);
+  if (rc != 0) slabs_fail(rc, bad, "slab step");
+  for (int r = 1; r < T.world; ++r)
+    if (std::memcmp(&out[r], &out[0], sizeof(float)) != 0) {
+      std::cerr << "slab ranks disagree on the time step (" << out[0] << " vs " << out[r] << ")" << std::endl;
+      std::exit(-1);
+    }
+  sphb_params now;
+  check(sphb_get_parameters(T.engines[0], &now), __FILE__, __LINE__);
+  parameters.grid_size_x = now.grid_size_x;
+  parameters.grid_size_y = now.grid_size_y;
+  parameters.grid_size_z = now.grid_size_z;
+  parameters.grid_cell_count = now.grid_cell_count;
+  for (int a = 0; a < 4; ++a) {
+    parameters.min_point.s[a] = now.min_point.s[a];
+    parameters.max_point.s[a] = now.max_point.s[a];
+  }
+  ++steps_done;
+  if (rebalance > 0.f && (T.world > 1 || force_slabs)) {
+    uint32_t most = 0;
+    for (int r = 0; r < T.world; ++r) most = std::max(most, T.owned[r]);
+    if ((double)most > (double)rebalance * parameters.particles_count / T.world) {
+      // (sphb_slab_step's counts are those before the step's own migration: one step late, which
+      // the capacity head-room covers)
+      T.recut.resize(parameters.particles_count);
+      slabs_read(T.recut.data());
+      slabs_upload(T.recut.data(), true);
+      ++slab_recuts;
+    }
+  }
+  return out[0];
+}
