@@ -315,8 +315,8 @@ int launch_slab_owned_scan(const uint32_t* ids, uint32_t n, uint32_t* dst, uint3
 int launch_slab_to_aos(sphb_particle* aos, uint32_t* ids_out, const uint32_t* n_owned_dev, uint32_t n_upper,
                        const float4* pos, const float4* vel, const float4* vhf, const uint32_t* ids,
                        const uint32_t* src_of, const float4* acc, const float* rho, const float* prs,
-                       const float4* pos_before, float gminx, float gminy, float gminz, float cell,
-                       cudaStream_t s);
+                       const float4* pos_before, const uint32_t* ckey_uploaded, float gminx, float gminy,
+                       float gminz, float cell, cudaStream_t s);
 int launch_slab_reduce_floats(const Reduce* red, float* out, cudaStream_t s);
 int launch_slab_bbox(const float4* pos, const uint32_t* n_owned_dev, uint32_t n_upper, Reduce* red,
                      cudaStream_t s);

@@ -142,20 +142,46 @@ __device__ __forceinline__ uint32_t* nback_of(const uint16_t* nlist, uint32_t n)
   return reinterpret_cast<uint32_t*>(const_cast<uint16_t*>(nlist) + (size_t)kListCap * n);
 }
 
-// one candidate against one particle: clamped cubic term, predicated store of the code
-__device__ __forceinline__ void density_test(const float4& q, const float4& pj, float h2, float& sum,
-                                             uint32_t& cursor, uint32_t code) {
-  const float dx = q.x - pj.x, dy = q.y - pj.y, dz = q.z - pj.z;
-  const float t = fmaf(-dz, dz, fmaf(-dy, dy, fmaf(-dx, dx, h2)));
-  const float t2 = t * t;
-  // one predicate drives the cubic term, the store and the cursor (NaN compares false)
+// One candidate against the thread's TWO particles at once, in packed fp32x2 arithmetic (FADD2 /
+// FFMA2 / FMUL2: Blackwell's fp32 pipe retires two lanes per instruction only in this form; the
+// candidate's coordinates enter as broadcast scalar operands).  u = r^2 - h^2 per particle, then,
+// where u < 0: sum += u^3 (the caller negates the total), a predicated store of the code and the
+// cursor's advance — one predicate per particle drives all three (NaN compares false).
+__device__ __forceinline__ uint64_t pack2(float lo, float hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void density_test2(uint64_t qx, uint64_t qy, uint64_t qz, uint64_t neg_h2,
+                                              const float4& pj, float& sum_a, float& sum_b,
+                                              uint32_t& cur_a, uint32_t& cur_b, uint32_t code) {
   asm volatile(
-      "{ .reg .pred p; setp.gt.f32 p, %3, 0f00000000;\n"
-      "  @p fma.rn.f32 %0, %4, %3, %0;\n"
-      "  @p st.shared.u16 [%1], %2;\n"
-      "  @p add.u32 %1, %1, %5; }"
-      : "+f"(sum), "+r"(cursor)
-      : "h"((uint16_t)code), "f"(t), "f"(t2), "n"(kColStride)
+      "{ .reg .b64 bx, by, bz, dx, dy, dz, u, u2;\n"
+      "  .reg .f32 ua, ub, va, vb;\n"
+      "  .reg .pred pa, pb;\n"
+      "  mov.b64 bx, {%9, %9};\n"
+      "  mov.b64 by, {%10, %10};\n"
+      "  mov.b64 bz, {%11, %11};\n"
+      "  sub.rn.f32x2 dx, %5, bx;\n"
+      "  sub.rn.f32x2 dy, %6, by;\n"
+      "  sub.rn.f32x2 dz, %7, bz;\n"
+      "  fma.rn.f32x2 u, dx, dx, %8;\n"
+      "  fma.rn.f32x2 u, dy, dy, u;\n"
+      "  fma.rn.f32x2 u, dz, dz, u;\n"
+      "  mul.rn.f32x2 u2, u, u;\n"
+      "  mov.b64 {ua, ub}, u;\n"
+      "  mov.b64 {va, vb}, u2;\n"
+      "  setp.lt.f32 pa, ua, 0f00000000;\n"
+      "  setp.lt.f32 pb, ub, 0f00000000;\n"
+      "  @pa fma.rn.f32 %0, va, ua, %0;\n"
+      "  @pb fma.rn.f32 %1, vb, ub, %1;\n"
+      "  @pa st.shared.u16 [%2], %4;\n"
+      "  @pb st.shared.u16 [%3], %4;\n"
+      "  @pa add.u32 %2, %2, %12;\n"
+      "  @pb add.u32 %3, %3, %12; }"
+      : "+f"(sum_a), "+f"(sum_b), "+r"(cur_a), "+r"(cur_b)
+      : "h"((uint16_t)code), "l"(qx), "l"(qy), "l"(qz), "l"(neg_h2), "f"(pj.x), "f"(pj.y), "f"(pj.z),
+        "n"(kColStride)
       : "memory");
 }
 
@@ -194,6 +220,8 @@ __global__ void __launch_bounds__(kPairBlock)
   for (int pass = 0; pass < npass; ++pass) {
     const bool la = pass == 0, lb = together || pass == 1;
     const float4 qa = la ? pa : nowhere, qb = lb ? pb : nowhere;
+    const uint64_t qx = pack2(qa.x, qb.x), qy = pack2(qa.y, qb.y), qz = pack2(qa.z, qb.z);
+    const uint64_t neg_h2 = pack2(-c.h2, -c.h2);
     const uint32_t ry = la ? fya : fyb, rz = la ? fza : fzb;
     uint32_t tag = 0, shift = 0;
 #pragma unroll 1
@@ -234,21 +262,16 @@ __global__ void __launch_bounds__(kPairBlock)
         for (; j + 4u <= e; j += 4u, code += 4u) {
           const float4 p0 = __ldg(cand + j), p1 = __ldg(cand + j + 1), p2 = __ldg(cand + j + 2),
                        p3 = __ldg(cand + j + 3);
-          density_test(qa, p0, c.h2, sum_a, cur_a, code);
-          density_test(qb, p0, c.h2, sum_b, cur_b, code);
-          density_test(qa, p1, c.h2, sum_a, cur_a, code + 1u);
-          density_test(qb, p1, c.h2, sum_b, cur_b, code + 1u);
-          density_test(qa, p2, c.h2, sum_a, cur_a, code + 2u);
-          density_test(qb, p2, c.h2, sum_b, cur_b, code + 2u);
-          density_test(qa, p3, c.h2, sum_a, cur_a, code + 3u);
-          density_test(qb, p3, c.h2, sum_b, cur_b, code + 3u);
+          density_test2(qx, qy, qz, neg_h2, p0, sum_a, sum_b, cur_a, cur_b, code);
+          density_test2(qx, qy, qz, neg_h2, p1, sum_a, sum_b, cur_a, cur_b, code + 1u);
+          density_test2(qx, qy, qz, neg_h2, p2, sum_a, sum_b, cur_a, cur_b, code + 2u);
+          density_test2(qx, qy, qz, neg_h2, p3, sum_a, sum_b, cur_a, cur_b, code + 3u);
           cur_a = min(cur_a, end_a);
           cur_b = min(cur_b, end_b);
         }
         for (; j < e; ++j, ++code) {
           const float4 p0 = __ldg(cand + j);
-          density_test(qa, p0, c.h2, sum_a, cur_a, code);
-          density_test(qb, p0, c.h2, sum_b, cur_b, code);
+          density_test2(qx, qy, qz, neg_h2, p0, sum_a, sum_b, cur_a, cur_b, code);
           cur_a = min(cur_a, end_a);
           cur_b = min(cur_b, end_b);
         }
@@ -263,7 +286,7 @@ __global__ void __launch_bounds__(kPairBlock)
   for (int w = 0; w < 2; ++w) {
     if (w == 1 && !has_b) break;
     const uint32_t i = w ? ib : ia;
-    const float density = (c.mass * c.c_poly6) * (w ? sum_b : sum_a);
+    const float density = (c.mass * c.c_poly6) * -(w ? sum_b : sum_a);  // the sums hold -(h^2 - r^2)^3
     const float pressure = tait_pressure(density, c);
     rho[i] = density;
     prs[i] = pressure;

@@ -125,8 +125,9 @@ __global__ void __launch_bounds__(kBlock)
                   const float4* __restrict__ vel, const float4* __restrict__ vhf,
                   const uint32_t* __restrict__ ids, const uint32_t* __restrict__ src_of,
                   const float4* __restrict__ acc, const float* __restrict__ rho,
-                  const float* __restrict__ prs, const float4* __restrict__ pos_before, float gminx,
-                  float gminy, float gminz, float cell) {
+                  const float* __restrict__ prs, const float4* __restrict__ pos_before,
+                  const uint32_t* __restrict__ ckey_uploaded, float gminx, float gminy, float gminz,
+                  float cell) {
   const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
   if (i >= *n_owned) return;
   float4 p = pos[i], v = vel[i], w = vhf[i];
@@ -141,6 +142,10 @@ __global__ void __launch_bounds__(kBlock)
     const float4 x0 = pos_before[s];
     key = morton3((uint32_t)((x0.x - gminx) / cell), (uint32_t)((x0.y - gminy) / cell),
                   (uint32_t)((x0.z - gminz) / cell));
+  } else {  // no step since the upload: what was uploaded comes back
+    a = acc[i]; a.w = 0.f;
+    d = rho[i]; pr = prs[i];
+    key = ckey_uploaded[i];
   }
   float4* dst = reinterpret_cast<float4*>(aos + i);
   dst[0] = p; dst[1] = v; dst[2] = w; dst[3] = a;
@@ -223,11 +228,12 @@ int launch_slab_owned_scan(const uint32_t* ids, uint32_t n, uint32_t* dst, uint3
 int launch_slab_to_aos(sphb_particle* aos, uint32_t* ids_out, const uint32_t* n_owned_dev, uint32_t n_upper,
                        const float4* pos, const float4* vel, const float4* vhf, const uint32_t* ids,
                        const uint32_t* src_of, const float4* acc, const float* rho, const float* prs,
-                       const float4* pos_before, float gminx, float gminy, float gminz, float cell,
-                       cudaStream_t s) {
+                       const float4* pos_before, const uint32_t* ckey_uploaded, float gminx, float gminy,
+                       float gminz, float cell, cudaStream_t s) {
   if (n_upper == 0) return 0;
   k_slab_to_aos<<<blocks_for(n_upper), kBlock, 0, s>>>(aos, ids_out, n_owned_dev, pos, vel, vhf, ids, src_of,
-                                                      acc, rho, prs, pos_before, gminx, gminy, gminz, cell);
+                                                      acc, rho, prs, pos_before, ckey_uploaded, gminx, gminy,
+                                                      gminz, cell);
   return 1;
 }
 

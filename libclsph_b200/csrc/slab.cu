@@ -299,7 +299,7 @@ int sphb_slab_download(sphb_engine* e, sphb_particle* aos, uint32_t* ids, uint32
   const int cur = e->cur;
   e->launches += launch_slab_to_aos(e->aos_stage, ids_dev, e->n_owned_dev, n, e->pos[cur], e->vel[cur],
                                     e->vhf[cur], e->rank_cur, e->committed ? e->src_of : nullptr, e->acc,
-                                    e->rho, e->prs, e->pos[cur ^ 1], e->params.min_point.s[0],
+                                    e->rho, e->prs, e->pos[cur ^ 1], e->ckey, e->params.min_point.s[0],
                                     e->params.min_point.s[1], e->params.min_point.s[2], e->params.h * 2, s);
   CUDA_TRY(e, cudaGetLastError());
   CUDA_TRY(e, cudaMemcpyAsync(aos, e->aos_stage, sizeof(sphb_particle) * n, cudaMemcpyDeviceToHost, s));

@@ -96,6 +96,26 @@ def test_slabs_on_one_gpu_match_whole_domain(tmp_path, world):
         d.local.close()
 
 
+def test_slab_reupload_between_steps(tmp_path):
+    """A slab engine whose state is downloaded and uploaded again after every step (what a hook
+    that returns true, or a re-cut of the slabs, does) against one that runs on: the same bits;
+    and a download right after an upload returns what was uploaded, derived fields included."""
+    case = make_case(tmp_path, "water", 32768)
+    a, b = slab_world(case, 1), slab_world(case, 1)
+    dta = dtb = 1.0 / 600.0
+    for s in range(3):
+        dta, dtb = a.step(dta), b.step(dtb)
+        assert dta == dtb
+        ga, gb = a.ranks[0].local.download(), b.ranks[0].local.download()
+        sa, sb = by_id([ga]), by_id([gb])
+        assert sa.tobytes() == sb.tobytes(), f"step {s}"
+        b.start([(gb[0].copy(), gb[1].copy())])
+        back = b.ranks[0].local.download()
+        assert np.array_equal(back[1], gb[1]) and back[0].tobytes() == gb[0].tobytes(), f"echo {s}"
+    for w in (a, b):
+        w.ranks[0].local.close()
+
+
 def test_slab_capacity_errors(tmp_path):
     from libclsph_b200 import SphbError
     from libclsph_b200.slab import CudaSlab, LoopbackWorld, equal_count_cuts
