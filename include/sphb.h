@@ -102,6 +102,15 @@ float sphb_scene_build_ms(sphb_engine* e);
  * write-back after a pre/post-frame hook returned true (:743-745, :763-765).
  * n must equal particles_count. */
 int sphb_upload(sphb_engine* e, const sphb_particle* aos, uint32_t n);
+/* The same in two halves, like a non-blocking enqueueWriteBuffer: _begin starts the host ->
+ * device copy (from page-locked memory, on a stream of its own, into a stage of its own) and
+ * returns; the engine goes on stepping and reading back its current state; _commit orders the
+ * engine's stream behind the copy and makes the uploaded particles the live state.  `aos` must
+ * stay untouched until _commit's work has run (any later synchronising call).  With
+ * sphb_download_begin this lets uploads, steps and read-backs of successive batches overlap
+ * (PCIe is full duplex). */
+int sphb_upload_begin(sphb_engine* e, const sphb_particle* aos, uint32_t n);
+int sphb_upload_commit(sphb_engine* e);
 
 /* Replaces sph_simulation::simulate_single_frame (libclsph/sph_simulation.cpp:200-263):
  * bbox -> locate_in_grid -> sort_particles (+cell table) -> density_pressure -> forces ->

@@ -25,6 +25,11 @@ COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC",
           "-DSPHB_BUILD"]
 # experiments: SPHB_XSUB=<1|2|4> builds the engine with that many x sub-cells per cell of side h
 # (csrc/common.cuh: kXSub) into SPHB_OUT (default: the product library)
+# SPHB_DEFS="-DNAME=value ..." does the same for any other compile-time parameter
+if os.environ.get("SPHB_DEFS"):
+    COMMON += os.environ["SPHB_DEFS"].split()
+    OBJDIR = os.path.join(OBJDIR, "defs_" + "".join(ch if ch.isalnum() else "_" for ch in os.environ["SPHB_DEFS"]))
+    OUT = os.environ.get("SPHB_OUT", os.path.join(OBJDIR, "libsphb.so"))
 if os.environ.get("SPHB_XSUB"):
     COMMON.append("-DSPHB_XSUB=" + os.environ["SPHB_XSUB"])
     OBJDIR = os.path.join(OBJDIR, "xsub" + os.environ["SPHB_XSUB"])

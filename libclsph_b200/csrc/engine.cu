@@ -78,6 +78,10 @@ int sphb_destroy(sphb_engine* e) {
   if (e->ev_staged) cudaEventDestroy(e->ev_staged);
   if (e->ev_copied) cudaEventDestroy(e->ev_copied);
   if (e->copy) cudaStreamDestroy(e->copy);
+  if (e->ev_up_done) cudaEventDestroy(e->ev_up_done);
+  if (e->ev_up_consumed) cudaEventDestroy(e->ev_up_consumed);
+  if (e->copy_up) cudaStreamDestroy(e->copy_up);
+  cudaFree(e->aos_up);
   if (e->stream) cudaStreamDestroy(e->stream);
   delete e;
   return 0;
@@ -363,6 +367,45 @@ int sphb_get_distance_field(sphb_engine* e, float* out) {
   CUDA_TRY(e, cudaMemcpyAsync(out, e->df, sizeof(float) * e->total_grid_points,
                               cudaMemcpyDeviceToHost, e->stream));
   CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+  return 0;
+}
+
+// sphb_upload in two halves.  _begin starts the host -> device copy on a stream of its own and
+// returns; _commit makes the engine's stream wait for it and converts the stage into the live
+// state.  Between the two the engine keeps stepping (and reading back) its current state.
+int sphb_upload_begin(sphb_engine* e, const sphb_particle* aos, uint32_t n) {
+  if (!e || !aos) return SPHB_ERR_INVALID;
+  if (e->slab) SPHB_FAIL(e, SPHB_ERR_INVALID, "sphb_upload_begin on a slab engine");
+  if (n != e->n) SPHB_FAIL(e, SPHB_ERR_INVALID, "upload of %u particles into an engine of %u", n, e->n);
+  if (e->upload_pending) SPHB_FAIL(e, SPHB_ERR_INVALID, "sphb_upload_begin twice without sphb_upload_commit");
+  CUDA_TRY(e, cudaSetDevice(e->device));
+  if (!e->copy_up) {
+    CUDA_TRY(e, cudaStreamCreateWithFlags(&e->copy_up, cudaStreamNonBlocking));
+    CUDA_TRY(e, cudaEventCreateWithFlags(&e->ev_up_done, cudaEventDisableTiming));
+    CUDA_TRY(e, cudaEventCreateWithFlags(&e->ev_up_consumed, cudaEventDisableTiming));
+  }
+  if (!e->aos_up) CUDA_TRY(e, dev_alloc(&e->aos_up, n));
+  // the stage may still be being converted by the previous commit
+  if (e->up_consumed_valid) CUDA_TRY(e, cudaStreamWaitEvent(e->copy_up, e->ev_up_consumed, 0));
+  CUDA_TRY(e, cudaMemcpyAsync(e->aos_up, aos, sizeof(sphb_particle) * n, cudaMemcpyHostToDevice, e->copy_up));
+  CUDA_TRY(e, cudaEventRecord(e->ev_up_done, e->copy_up));
+  e->upload_pending = true;
+  return 0;
+}
+
+int sphb_upload_commit(sphb_engine* e) {
+  if (!e) return SPHB_ERR_INVALID;
+  if (!e->upload_pending) SPHB_FAIL(e, SPHB_ERR_INVALID, "sphb_upload_commit without sphb_upload_begin");
+  CUDA_TRY(e, cudaSetDevice(e->device));
+  CUDA_TRY(e, cudaStreamWaitEvent(e->stream, e->ev_up_done, 0));
+  e->launches += launch_aos_to_soa(e->aos_up, e->n, e->pos[e->cur], e->vel[e->cur], e->vhf[e->cur], e->acc,
+                                   e->rho, e->prs, e->ckey, e->rank_cur, e->stream);
+  CUDA_TRY(e, cudaGetLastError());
+  CUDA_TRY(e, cudaEventRecord(e->ev_up_consumed, e->stream));
+  e->up_consumed_valid = true;
+  e->upload_pending = false;
+  e->bbox_valid = false;
+  e->have_state = true;
   return 0;
 }
 

@@ -23,6 +23,12 @@ struct sphb_engine {
   cudaStream_t copy = nullptr;
   cudaEvent_t ev_staged = nullptr, ev_copied = nullptr;
   bool download_pending = false;
+  // asynchronous upload (sphb_upload_begin / _commit): host -> device copy on its own stream into
+  // its own stage, so that it runs beside a step and beside a read-back (PCIe is full duplex)
+  cudaStream_t copy_up = nullptr;
+  cudaEvent_t ev_up_done = nullptr, ev_up_consumed = nullptr;
+  sphb_particle* aos_up = nullptr;
+  bool upload_pending = false, up_consumed_valid = false;
   int slab_attempt = 0;  // advection attempts of the current slab step
   // native multi-GPU driver (slab_nccl.cu): communicator, the four halo messages
   // (send left, recv left, send right, recv right), the 8-float reduction cell, the global bbox

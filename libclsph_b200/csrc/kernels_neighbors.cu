@@ -424,8 +424,14 @@ __global__ void __launch_bounds__(kBlock)
 }
 
 // Forces from the neighbour list the density pass recorded.
+// (experiments: -DSPHB_FORCES_MINBLOCKS=<n> asks for n resident CTAs per SM)
+#ifdef SPHB_FORCES_MINBLOCKS
+#define SPHB_FORCES_BOUNDS __launch_bounds__(kBlock, SPHB_FORCES_MINBLOCKS)
+#else
+#define SPHB_FORCES_BOUNDS __launch_bounds__(kBlock)
+#endif
 template <bool Q>
-__global__ void __launch_bounds__(kBlock)
+__global__ void SPHB_FORCES_BOUNDS
     k_forces_nlist(const float4* __restrict__ pos, const float4* __restrict__ vel,
                    const uint32_t* __restrict__ keys, const uint32_t* __restrict__ ftable,
                    const float* __restrict__ rho, const uint16_t* __restrict__ nlist,

@@ -80,7 +80,7 @@ SYMBOLS = [
     "sphb_host_alloc", "sphb_host_free", "sphb_debug_advect", "sphb_event_record", "sphb_event_elapsed_ms",
     "sphb_slab_create", "sphb_slab_message_bytes", "sphb_slab_configure", "sphb_slab_upload", "sphb_slab_bbox",
     "sphb_slab_pack", "sphb_slab_unpack", "sphb_slab_forces", "sphb_slab_advect", "sphb_slab_commit",
-    "sphb_slab_download", "sphb_compute_dt", "sphb_scene_build_ms",
+    "sphb_slab_download", "sphb_compute_dt", "sphb_scene_build_ms", "sphb_upload_begin", "sphb_upload_commit",
     "sphb_nccl_unique_id", "sphb_slab_comm_init", "sphb_slab_start", "sphb_slab_step", "sphb_slab_bytes_sent",
     "sphb_slab_phase_ms", "sphb_slab_resends",
 ]
@@ -116,6 +116,8 @@ def lib():
         L.sphb_set_scene.argtypes = [vp, vp, u32, vp, vp, u32]
         L.sphb_get_distance_field.argtypes = [vp, vp]
         L.sphb_upload.argtypes = [vp, vp, u32]
+        L.sphb_upload_begin.argtypes = [vp, vp, u32]
+        L.sphb_upload_commit.argtypes = [vp]
         L.sphb_step.argtypes = [vp, f32, C.POINTER(f32)]
         L.sphb_run_frame.argtypes = [vp, f32, f32, C.c_uint64, C.POINTER(f32), C.POINTER(u32), vp, u32]
         L.sphb_queued_steps.argtypes = [vp]
@@ -237,6 +239,13 @@ class Engine:
     def upload(self, particles):
         particles = np.ascontiguousarray(particles, PARTICLE)
         self._check(self.L.sphb_upload(self.h, _ptr(particles), len(particles)))
+
+    def upload_begin(self, ptr, n):
+        """starts the host -> device copy of n particles at `ptr` (pinned memory); see upload_commit"""
+        self._check(self.L.sphb_upload_begin(self.h, C.c_void_p(ptr), n))
+
+    def upload_commit(self):
+        self._check(self.L.sphb_upload_commit(self.h))
 
     def upload_ptr(self, ptr, n):
         """ptr: address of n 80-byte particles in (ideally pinned) host memory."""

@@ -302,3 +302,48 @@ def test_split_download_is_a_snapshot():
             assert late.tobytes() == after.tobytes()
     finally:
         lib().sphb_host_free(ptr)
+
+
+def test_split_upload_overlaps_and_replaces_the_state():
+    """sphb_upload_begin / _commit (the upload that overlaps a step and a read-back): while the copy
+    is in flight the engine steps and reads back its current state undisturbed; after _commit the
+    next step starts from the uploaded particles — the same bits as after a blocking sphb_upload."""
+    import ctypes as C
+    from libclsph_b200 import PARTICLE, Engine
+    from libclsph_b200.engine import lib
+    g = np.load(os.path.join(GOLDEN, "steps_box_water.npz"))
+    sc = np.load(os.path.join(GOLDEN, "scene_box_water.npz"))
+    n = len(g["initial"])
+    ptrs = [C.c_void_p(), C.c_void_p()]
+    for p in ptrs:
+        assert lib().sphb_host_alloc(C.byref(p), n * PARTICLE.itemsize) == 0
+    try:
+        src, out = (np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), (n * PARTICLE.itemsize,)).view(PARTICLE)
+                    for p in ptrs)
+        src[:] = g["initial"]
+        dt0 = float(g["dt0"])
+        with Engine(g["params0"].copy(), g["terms"]) as e:
+            e.set_scene(sc["bbs"], sc["transforms"], sc["rvertices"], int(sc["total_gridpoints"]))
+            e.upload(g["initial"])
+            dt1 = e.step(dt0)
+            first = e.download()            # one step from the initial state
+            e.upload(first)                 # (a fresh upload fixes the order sums are taken in)
+            dt2 = e.step(dt1)
+            second = e.download()           # one step from `first`
+            assert first.tobytes() != second.tobytes()
+            # now the same through the split calls, with work in flight on every stream
+            e.upload(first)                 # state := `first`
+            e.upload_begin(ptrs[0].value, n)    # the initial state, on its way
+            got_dt2 = e.step(dt1)           # steps `first` -> `second` while the copy runs
+            e.download_begin(ptrs[1].value)
+            e.upload_commit()               # state := initial
+            got_dt1 = e.step(dt0)           # -> `first` again
+            e.download_wait()
+            assert out.tobytes() == second.tobytes() and got_dt2 == dt2
+            again = e.download()
+            assert again.tobytes() == first.tobytes() and got_dt1 == dt1
+            with pytest.raises(Exception):
+                e.upload_commit()           # nothing pending
+    finally:
+        for p in ptrs:
+            lib().sphb_host_free(p)
