@@ -78,6 +78,7 @@ def main_multi(args, rank, world, local, workload):
     cap = int(n_mine * 1.25) + 2 * exch
     loc = CudaSlab(params, terms, sc, local, cap, exch)
     if getattr(args, "driver", "native") == "native":
+        loc.e.set_option("p2p_halo", int(getattr(args, "p2p", 1)))
         loc.comm_init(rank, world, dist)  # the library drives exchange + all-reduce itself
     drv = SlabDriver(loc, cuts, rank, world, dist)
     drv.start(mine_p, ids)
@@ -172,8 +173,12 @@ def main_multi(args, rank, world, local, workload):
                         f"water box (water.json + default.json physics): BASELINE.json configs[3]'s block per GPU",
                         particles=n_total, particles_per_gpu=n0 if not strong else n_total // world,
                         box=[round(float(v), 4) for v in dims],
-                        parallelism=f"{world} x-slabs, 2h ghost layer + migration by NCCL send/recv, "
-                                    f"1 all-reduce(8 floats) per advection attempt",
+                        parallelism=f"{world} x-slabs, 2h ghost layer + migration " +
+                                    ("written by the pack kernel straight into the neighbour's inbox over NVLink "
+                                     "peer memory (CUDA IPC), " if (drv.native and loc.p2p_active()) else
+                                     "by NCCL send/recv, ") +
+                                    "1 NCCL all-reduce(8 floats) per advection attempt",
+                        p2p_halo=bool(drv.native and loc.p2p_active()),
                         driver="sphb_slab_step (C, NCCL by dlopen)" if drv.native else "SlabDriver (Python, torch.distributed)",
                         l2="inputs exceed L2", exchange_capacity_records=exch, owned_total=owned_total),
             clocks=clocks, gpu_launches=int(sum(float(s[2]) for s in allstats)),

@@ -224,6 +224,13 @@ int sphb_slab_start(sphb_engine* e);
 int sphb_slab_step(sphb_engine* e, float dt_in, float* dt_out, int* attempts_out, uint32_t* n_owned_out,
                    uint32_t* n_ghost_out);
 uint64_t sphb_slab_bytes_sent(sphb_engine* e); /* halo bytes sent since sphb_slab_start */
+/* 1 when sphb_slab_comm_init could map both neighbours' inboxes into this GPU's address space
+ * (engines of one process: peer access; one process per GPU: CUDA IPC) on EVERY rank.  The
+ * exchange then needs no ncclSend / ncclRecv: the pack kernel writes its records straight into
+ * the neighbours' inboxes over NVLink, publishes the step's sequence number behind them, and the
+ * receiving stream waits for that number (option "p2p_halo" = 0 before sphb_slab_comm_init keeps
+ * the exchange on NCCL). */
+int sphb_slab_p2p_active(sphb_engine* e);
 /* A halo message carries last step's record count + max(1/8 of it, option "halo_margin" = 4096)
  * records (option value 0: no spare room at all, which exercises the resend path);
  * one that outgrew that is exchanged again at full capacity by the pair concerned: how often */
@@ -284,7 +291,9 @@ void* sphb_stream(sphb_engine* e);
  *                      a step that needs more is finished from the host
  *   "table_headroom"   1 (default) = cell tables are allocated with 1.5x spare entries; 0 = exact
  *                      (tests: every grid growth then goes through the host)
- *   "halo_margin"      sphb_slab_step: spare records per halo message */
+ *   "halo_margin"      sphb_slab_step: spare records per halo message (NCCL exchange only)
+ *   "p2p_halo"         1 (default) = sphb_slab_comm_init tries to set up the exchange over peer
+ *                      memory (sphb_slab_p2p_active); 0 = NCCL send / receive */
 int sphb_set_option(sphb_engine* e, const char* name, int value);
 
 /* Page-locked host memory for the particle array (the reference asks OpenCL for

@@ -306,7 +306,11 @@ size_t slab_message_bytes(uint32_t record_capacity);
 int launch_slab_pack(const float4* pos, const float4* vel, const float4* vhf, uint32_t* ids,
                      const uint32_t* n_owned_dev, uint32_t n_upper, float xlo, float xhi, float halo,
                      int has_left, int has_right, void* msg_left, void* msg_right, uint32_t cap,
-                     uint32_t* counters, cudaStream_t s);
+                     uint32_t* counters, cudaStream_t s, uint32_t p2p_seq = 0);
+// peer-memory exchange: p2p_seq != 0 makes the pack publish its headers with that sequence number
+// last; the receiver's stream waits for it on its own inboxes (nullptr = no such neighbour)
+int launch_slab_wait(const void* inbox_left, const void* inbox_right, uint32_t seq, uint32_t* err,
+                     unsigned long long timeout_ns, cudaStream_t s);
 int launch_slab_unpack(const void* msg, uint32_t count, uint32_t offset, float4* pos, float4* vel,
                        float4* vhf, uint32_t* ids, cudaStream_t s);
 // dst[i] = number of owned particles before i (compute order); *n_owned_out = their total

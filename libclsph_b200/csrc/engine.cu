@@ -930,6 +930,10 @@ int sphb_set_option(sphb_engine* e, const char* name, int value) {
     e->use_side_stream = value != 0;
     return 0;
   }
+  if (!strcmp(name, "p2p_halo")) {  // before sphb_slab_comm_init: 0 = always exchange through NCCL
+    e->p2p_want = value != 0;
+    return 0;
+  }
   if (!strcmp(name, "halo_margin")) {  // sphb_slab_step: spare records per halo message
     e->halo_margin = value < 0 ? 0u : (uint32_t)value;
     return 0;

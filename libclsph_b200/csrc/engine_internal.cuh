@@ -44,6 +44,13 @@ struct sphb_engine {
   uint32_t last_records[4] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu};
   uint64_t resends = 0;
   uint32_t halo_margin = 4096;  // option "halo_margin"
+  // exchange over peer memory (option "p2p_halo"): the neighbours' inboxes as seen from this GPU
+  // ([0] the left neighbour's inbox from its right, [1] the right neighbour's inbox from its left)
+  int p2p_want = 1;
+  bool p2p_active = false;
+  void* p2p_remote[2] = {nullptr, nullptr};
+  bool p2p_ipc[2] = {false, false};  // opened with cudaIpcOpenMemHandle (to be closed)
+  uint32_t p2p_seq = 0;
   double phase_ms[3] = {0.0, 0.0, 0.0};  // pack..unpack | sort..first reduction | retries + commit
   uint32_t n = 0;    // particles the kernels run over (slab mode: owned + ghosts of this step)
   uint32_t cap = 0;  // allocated particle slots (== n outside slab mode)
@@ -146,6 +153,7 @@ struct sphb_engine {
 std::string& sphb_create_error_slot();
 void sphb_slab_comm_release(sphb_engine* e);  // slab_nccl.cu
 int slab_read_counts(sphb_engine* e, const void* recv_left_dev, const void* recv_right_dev);  // slab.cu
+int slab_pack_to(sphb_engine* e, void* msg_left_dev, void* msg_right_dev, uint32_t p2p_seq);  // slab.cu
 int slab_apply_unpack(sphb_engine* e, const void* recv_left_dev, const void* recv_right_dev,
                       uint32_t* n_owned_out, uint32_t* n_ghost_out);
 extern "C" int sphb_create_with_capacity(const sphb_params* params, const sphb_terms* terms, int device,

@@ -89,6 +89,59 @@ __global__ void k_slab_headers(const uint32_t* __restrict__ counters, float4* ms
   }
 }
 
+// ---- the exchange over peer memory -------------------------------------------------------
+// With the neighbours' inboxes mapped into this GPU's address space (slab_nccl.cu: same-process
+// peer access or CUDA IPC), k_slab_pack writes its records straight into them over NVLink and
+// there is no send / receive at all: the header goes last, its third word — the step's
+// sequence number — after a system-scope fence, and the receiver's stream waits for that number
+// (k_slab_wait) before it reads the counts.
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+__global__ void k_slab_headers_p2p(const uint32_t* __restrict__ counters, uint32_t* msg_left,
+                                   uint32_t* msg_right, uint32_t seq) {
+  if (threadIdx.x == 0) {
+    if (msg_left) {
+      volatile uint32_t* m = msg_left;
+      m[0] = counters[0]; m[1] = counters[1]; m[3] = 0;
+    }
+    if (msg_right) {
+      volatile uint32_t* m = msg_right;
+      m[0] = counters[2]; m[1] = counters[3]; m[3] = 0;
+    }
+    __threadfence_system();  // the records (previous kernel) and the counts before the number
+    if (msg_left) st_release_sys(msg_left + 2, seq);
+    if (msg_right) st_release_sys(msg_right + 2, seq);
+  }
+}
+
+// One thread polls the two local inboxes until both carry this step's number; gives up after
+// timeout_ns (a neighbour that failed must not hang the device) and says so in *err.
+__global__ void k_slab_wait(const uint32_t* inbox_left, const uint32_t* inbox_right, uint32_t seq,
+                            uint32_t* err, unsigned long long timeout_ns) {
+  if (threadIdx.x) return;
+  unsigned long long t0, t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+  const uint32_t* boxes[2] = {inbox_left, inbox_right};
+  for (int k = 0; k < 2; ++k) {
+    if (!boxes[k]) continue;
+    while (ld_acquire_sys(boxes[k] + 2) != seq) {
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+      if (t - t0 > timeout_ns) {
+        *err = 1u + (uint32_t)k;
+        return;
+      }
+      __nanosleep(100);
+    }
+  }
+}
+
 // Appends the records of one received message at [offset, offset + count).
 __global__ void __launch_bounds__(kBlock)
     k_slab_unpack(const float4* __restrict__ msg, uint32_t count, uint32_t offset, float4* __restrict__ pos,
@@ -196,14 +249,21 @@ size_t slab_message_bytes(uint32_t record_capacity) { return 16 + (size_t)48 * r
 int launch_slab_pack(const float4* pos, const float4* vel, const float4* vhf, uint32_t* ids,
                      const uint32_t* n_owned_dev, uint32_t n_upper, float xlo, float xhi, float halo,
                      int has_left, int has_right, void* msg_left, void* msg_right, uint32_t cap,
-                     uint32_t* counters, cudaStream_t s) {
+                     uint32_t* counters, cudaStream_t s, uint32_t p2p_seq) {
   cudaMemsetAsync(counters, 0, 4 * sizeof(uint32_t), s);
   if (n_upper)
     k_slab_pack<<<blocks_for(n_upper), kBlock, 0, s>>>(pos, vel, vhf, ids, n_owned_dev, xlo, xhi, halo,
                                                       has_left, has_right, (float4*)msg_left,
                                                       (float4*)msg_right, cap, counters);
-  k_slab_headers<<<1, 32, 0, s>>>(counters, (float4*)msg_left, (float4*)msg_right);
+  if (p2p_seq) k_slab_headers_p2p<<<1, 32, 0, s>>>(counters, (uint32_t*)msg_left, (uint32_t*)msg_right, p2p_seq);
+  else k_slab_headers<<<1, 32, 0, s>>>(counters, (float4*)msg_left, (float4*)msg_right);
   return 2;
+}
+
+int launch_slab_wait(const void* inbox_left, const void* inbox_right, uint32_t seq, uint32_t* err,
+                     unsigned long long timeout_ns, cudaStream_t s) {
+  k_slab_wait<<<1, 32, 0, s>>>((const uint32_t*)inbox_left, (const uint32_t*)inbox_right, seq, err, timeout_ns);
+  return 1;
 }
 
 int launch_slab_unpack(const void* msg, uint32_t count, uint32_t offset, float4* pos, float4* vel,

@@ -42,7 +42,8 @@ int sphb_slab_create(const sphb_params* params, const sphb_terms* terms, int dev
   e->exch_cap = exchange_capacity;
   cudaError_t err = cudaSuccess;
   if (err == cudaSuccess) err = dev_alloc(&e->n_owned_dev, 1);
-  if (err == cudaSuccess) err = dev_alloc(&e->counters, 4);
+  if (err == cudaSuccess) err = dev_alloc(&e->counters, 8);  // 4 pack counters + [4] exchange error
+  if (err == cudaSuccess) err = cudaMemsetAsync(e->counters, 0, 8 * sizeof(uint32_t), e->stream);
   if (err == cudaSuccess) err = dev_alloc(&e->src_of, capacity);
   if (err == cudaSuccess) err = dev_alloc(&e->aos_stage, capacity);
   if (err == cudaSuccess) err = cudaMallocHost(reinterpret_cast<void**>(&e->host_counts), 16 * sizeof(uint32_t));
@@ -103,6 +104,12 @@ int sphb_slab_bbox(sphb_engine* e, float* out8_dev) {
 }
 
 int sphb_slab_pack(sphb_engine* e, void* msg_left_dev, void* msg_right_dev) {
+  return slab_pack_to(e, msg_left_dev, msg_right_dev, 0);
+}
+
+}  // extern "C"
+
+int slab_pack_to(sphb_engine* e, void* msg_left_dev, void* msg_right_dev, uint32_t p2p_seq) {
   if (int rc = require_slab(e)) return rc;
   if (!e->have_state) SPHB_FAIL(e, SPHB_ERR_INVALID, "sphb_slab_pack before sphb_slab_upload");
   if ((e->has_left && !msg_left_dev) || (e->has_right && !msg_right_dev)) return SPHB_ERR_INVALID;
@@ -111,12 +118,11 @@ int sphb_slab_pack(sphb_engine* e, void* msg_left_dev, void* msg_right_dev) {
   e->launches += launch_slab_pack(e->pos[cur], e->vel[cur], e->vhf[cur], e->rank_cur, e->n_owned_dev,
                                   e->n_upper, e->xlo, e->xhi, kHaloCells * e->params.h, e->has_left,
                                   e->has_right, e->has_left ? msg_left_dev : nullptr,
-                                  e->has_right ? msg_right_dev : nullptr, e->exch_cap, e->counters, e->stream);
+                                  e->has_right ? msg_right_dev : nullptr, e->exch_cap, e->counters, e->stream,
+                                  p2p_seq);
   CUDA_TRY(e, cudaGetLastError());
   return 0;
 }
-
-}  // extern "C"
 
 // The step's first host synchronisation: the headers of the two received messages, this
 // rank's own pack counters and its particle count, into e->host_counts
@@ -132,6 +138,7 @@ int slab_read_counts(sphb_engine* e, const void* recv_left_dev, const void* recv
   if (e->has_right) CUDA_TRY(e, cudaMemcpyAsync(hc + 4, recv_right_dev, 16, cudaMemcpyDeviceToHost, s));
   CUDA_TRY(e, cudaMemcpyAsync(hc + 8, e->counters, 16, cudaMemcpyDeviceToHost, s));
   CUDA_TRY(e, cudaMemcpyAsync(hc + 12, e->n_owned_dev, 4, cudaMemcpyDeviceToHost, s));
+  CUDA_TRY(e, cudaMemcpyAsync(hc + 13, e->counters + 4, 4, cudaMemcpyDeviceToHost, s));
   CUDA_TRY(e, cudaStreamSynchronize(s));
   return 0;
 }

@@ -9,6 +9,7 @@
 // so that libsphb.so itself carries no link-time dependency on it and single-GPU users need
 // no NCCL at all.  Only plain-C entry points with ABI-stable enum values are used.
 #include <dlfcn.h>
+#include <unistd.h>
 
 #include <chrono>
 
@@ -109,8 +110,114 @@ void bbox_from_red8(sphb_engine* e) {
 
 }  // namespace
 
+namespace {
+void p2p_release(sphb_engine* e) {
+  for (int k = 0; k < 2; ++k) {
+    if (e->p2p_remote[k] && e->p2p_ipc[k]) cudaIpcCloseMemHandle(e->p2p_remote[k]);
+    e->p2p_remote[k] = nullptr;
+    e->p2p_ipc[k] = false;
+  }
+  e->p2p_active = false;
+}
+
+// What a rank tells a neighbour about the inbox that neighbour is to write into.
+struct InboxCard {
+  uint64_t pid;
+  int32_t device;
+  uint32_t valid;
+  uint64_t ptr;
+  cudaIpcMemHandle_t handle;
+};
+static_assert(sizeof(InboxCard) <= 128, "an inbox card travels in 128 bytes");
+
+// Maps the neighbours' inboxes into this GPU's address space and agrees with every other rank on
+// whether the exchange runs over peer memory: all of them, or none.  Collective.
+int p2p_setup(sphb_engine* e) {
+  NcclApi& a = nccl();
+  ncclComm_t comm = static_cast<ncclComm_t>(e->comm);
+  p2p_release(e);
+  const int rank = e->comm_rank, world = e->comm_world;
+  const bool left = rank > 0, right = rank + 1 < world;
+  bool ok = e->p2p_want != 0 && world > 1;
+  // cards of my two inboxes: msg[1] (from the left) goes to the left neighbour, msg[3] to the right
+  InboxCard mine[2];
+  memset(mine, 0, sizeof mine);
+  for (int k = 0; k < 2; ++k) {
+    void* box = e->msg[k == 0 ? 1 : 3];
+    mine[k].pid = (uint64_t)getpid();
+    mine[k].device = e->device;
+    mine[k].ptr = (uint64_t)(uintptr_t)box;
+    mine[k].valid = 0;
+    if (ok && cudaIpcGetMemHandle(&mine[k].handle, box) == cudaSuccess) mine[k].valid = 1;
+    else cudaGetLastError();
+  }
+  // staged through the (still unused) send / receive messages: 128 bytes each way
+  unsigned char stage[2][128];
+  memset(stage, 0, sizeof stage);
+  memcpy(stage[0], &mine[0], sizeof(InboxCard));
+  memcpy(stage[1], &mine[1], sizeof(InboxCard));
+  CUDA_TRY(e, cudaMemcpyAsync(e->msg[0], stage[0], 128, cudaMemcpyHostToDevice, e->stream));
+  CUDA_TRY(e, cudaMemcpyAsync(e->msg[2], stage[1], 128, cudaMemcpyHostToDevice, e->stream));
+  NCCL_TRY(e, a.GroupStart());
+  if (left) {
+    NCCL_TRY(e, a.Send(e->msg[0], 128, kNcclUint8, rank - 1, comm, e->stream));
+    NCCL_TRY(e, a.Recv(e->msg[1], 128, kNcclUint8, rank - 1, comm, e->stream));
+  }
+  if (right) {
+    NCCL_TRY(e, a.Send(e->msg[2], 128, kNcclUint8, rank + 1, comm, e->stream));
+    NCCL_TRY(e, a.Recv(e->msg[3], 128, kNcclUint8, rank + 1, comm, e->stream));
+  }
+  NCCL_TRY(e, a.GroupEnd());
+  InboxCard theirs[2];  // [0] the left neighbour's inbox from its right, [1] the right one's from its left
+  memset(theirs, 0, sizeof theirs);
+  if (left) CUDA_TRY(e, cudaMemcpyAsync(&theirs[0], e->msg[1], sizeof(InboxCard), cudaMemcpyDeviceToHost, e->stream));
+  if (right) CUDA_TRY(e, cudaMemcpyAsync(&theirs[1], e->msg[3], sizeof(InboxCard), cudaMemcpyDeviceToHost, e->stream));
+  CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+  for (int k = 0; k < 2 && ok; ++k) {
+    if (!(k == 0 ? left : right)) continue;
+    const InboxCard& c = theirs[k];
+    if (c.pid == (uint64_t)getpid()) {  // another engine of this process: plain peer access
+      int can = 0;
+      if (c.device == e->device) can = 1;
+      else if (cudaDeviceCanAccessPeer(&can, e->device, c.device) != cudaSuccess) can = 0;
+      if (can && c.device != e->device) {
+        const cudaError_t err = cudaDeviceEnablePeerAccess(c.device, 0);
+        if (err != cudaSuccess && err != cudaErrorPeerAccessAlreadyEnabled) can = 0;
+      }
+      cudaGetLastError();
+      if (can) e->p2p_remote[k] = (void*)(uintptr_t)c.ptr;
+      else ok = false;
+    } else if (c.valid) {
+      void* p = nullptr;
+      if (cudaIpcOpenMemHandle(&p, c.handle, cudaIpcMemLazyEnablePeerAccess) == cudaSuccess && p) {
+        e->p2p_remote[k] = p;
+        e->p2p_ipc[k] = true;
+      } else {
+        cudaGetLastError();
+        ok = false;
+      }
+    } else {
+      ok = false;
+    }
+  }
+  // the inboxes start without a sequence number; then: all ranks, or none
+  for (int k = 1; k < 4; k += 2) CUDA_TRY(e, cudaMemsetAsync(e->msg[k], 0, 128, e->stream));
+  float flag[8] = {ok ? 0.f : 1.f, 0, 0, 0, 0, 0, 0, 0};
+  CUDA_TRY(e, cudaMemcpyAsync(e->red8_dev, flag, sizeof flag, cudaMemcpyHostToDevice, e->stream));
+  if (int rc = reduce8(e)) return rc;
+  if (e->red8_host[0] != 0.f || !ok) {
+    p2p_release(e);
+    return 0;
+  }
+  e->p2p_active = true;
+  e->p2p_seq = 0;
+  return 0;
+}
+}  // namespace
+
 void sphb_slab_comm_release(sphb_engine* e) {
   if (!e) return;
+  p2p_release(e);
   if (e->comm) {
     NcclApi& a = nccl();
     if (a.ok) a.CommDestroy(static_cast<ncclComm_t>(e->comm));
@@ -161,7 +268,7 @@ int sphb_slab_comm_init(sphb_engine* e, const unsigned char id_in[128], int rank
   CUDA_TRY(e, cudaMalloc(reinterpret_cast<void**>(&e->red8_dev), 8 * sizeof(float)));
   CUDA_TRY(e, cudaMallocHost(reinterpret_cast<void**>(&e->red8_host), 8 * sizeof(float)));
   CUDA_TRY(e, cudaStreamSynchronize(e->stream));
-  return 0;
+  return p2p_setup(e);
 }
 
 // After sphb_slab_configure + sphb_slab_upload on every rank: the global bbox of the initial
@@ -189,6 +296,24 @@ int sphb_slab_step(sphb_engine* e, float dt_in, float* dt_out, int* attempts_out
   const clk::time_point t0 = clk::now();
   clk::time_point t1 = t0, t2 = t0;
   void* send_l = e->msg[0]; void* recv_l = e->msg[1]; void* send_r = e->msg[2]; void* recv_r = e->msg[3];
+  uint32_t n_owned = 0, n_ghost = 0;
+  if (e->p2p_active) {
+    // The exchange over peer memory: the pack kernel writes its records into the neighbours'
+    // inboxes over NVLink and publishes this step's number behind them; this stream waits for
+    // the same number in its own inboxes.  No send, no receive, no message sizing.
+    const uint32_t seq = ++e->p2p_seq;
+    if (int rc = slab_pack_to(e, e->p2p_remote[0], e->p2p_remote[1], seq)) return rc;
+    e->launches += launch_slab_wait(e->has_left ? recv_l : nullptr, e->has_right ? recv_r : nullptr, seq,
+                                    e->counters + 4, 20ull * 1000ull * 1000ull * 1000ull, e->stream);
+    CUDA_TRY(e, cudaGetLastError());
+    if (int rc = slab_read_counts(e, recv_l, recv_r)) return rc;  // host sync
+    const uint32_t* hc = e->host_counts;
+    if (hc[13]) SPHB_FAIL(e, SPHB_ERR_INVALID, "the %s neighbour's halo did not arrive within 20 s",
+                          hc[13] == 1 ? "left" : "right");
+    e->bytes_sent += (e->has_left ? slab_message_bytes(hc[8] > e->exch_cap ? e->exch_cap : hc[8]) : 0) +
+                     (e->has_right ? slab_message_bytes(hc[10] > e->exch_cap ? e->exch_cap : hc[10]) : 0);
+    if (int rc = slab_apply_unpack(e, recv_l, recv_r, &n_owned, &n_ghost)) return rc;
+  } else {
   if (int rc = sphb_slab_pack(e, send_l, send_r)) return rc;
   // A message carries the records its predecessor carried one step ago plus a margin, not the
   // full capacity: both ends of a pair know that count (the sender counted it, the receiver
@@ -233,8 +358,8 @@ int sphb_slab_step(sphb_engine* e, float dt_in, float* dt_out, int* attempts_out
     const uint32_t now[4] = {hc[8], hc[0], hc[10], hc[4]};
     for (int k = 0; k < 4; ++k) e->last_records[k] = now[k] > e->exch_cap ? e->exch_cap : now[k];
   }
-  uint32_t n_owned = 0, n_ghost = 0;
   if (int rc = slab_apply_unpack(e, recv_l, recv_r, &n_owned, &n_ghost)) return rc;
+  }
   t1 = clk::now();
   if (int rc = sphb_slab_forces(e, e->gmin, e->gmax)) return rc;
   float dt = dt_in, computed = dt_in;
@@ -262,6 +387,7 @@ int sphb_slab_step(sphb_engine* e, float dt_in, float* dt_out, int* attempts_out
 }
 
 uint64_t sphb_slab_bytes_sent(sphb_engine* e) { return e ? e->bytes_sent : 0; }
+int sphb_slab_p2p_active(sphb_engine* e) { return e && e->p2p_active ? 1 : 0; }
 uint64_t sphb_slab_resends(sphb_engine* e) { return e ? e->resends : 0; }
 
 int sphb_slab_phase_ms(sphb_engine* e, double out3[3], int reset) {

@@ -145,6 +145,10 @@ class CudaSlab:
         self._chk(self.e.L.sphb_slab_phase_ms(self.e.h, out.ctypes.data, int(reset)))
         return out
 
+    def p2p_active(self):
+        """the halo exchange runs over peer memory (no ncclSend / ncclRecv)"""
+        return bool(self.e.L.sphb_slab_p2p_active(self.e.h))
+
     def native_resends(self):
         return int(self.e.L.sphb_slab_resends(self.e.h))
 

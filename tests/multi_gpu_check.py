@@ -29,6 +29,9 @@ def main():
     ap.add_argument("--particles", type=int, default=262144)
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--driver", default="native", choices=["native", "python"])
+    ap.add_argument("--p2p", type=int, default=1, help="native driver: 1 = halo over peer memory when it can be "
+                    "mapped, 0 = ncclSend / ncclRecv")
+    ap.add_argument("--expect-p2p", type=int, default=-1, help="fail unless the peer-memory exchange is (1) / is not (0) active")
     ap.add_argument("--halo-margin", type=int, default=-1,
                     help="native driver: spare records per halo message (0 forces the resend path)")
     a = ap.parse_args()
@@ -46,7 +49,10 @@ def main():
     cap = int(1.5 * n / world) + 65536
     loc = CudaSlab(case["params"], case["terms"], case["scene"], local, cap, max(65536, n // 4))
     if a.driver == "native":
+        loc.e.set_option("p2p_halo", a.p2p)
         loc.comm_init(rank, world, dist)
+        if a.expect_p2p >= 0:
+            assert loc.p2p_active() == bool(a.expect_p2p), f"p2p_active = {loc.p2p_active()}"
         if a.halo_margin >= 0:
             loc.e.set_option("halo_margin", a.halo_margin)
     drv = SlabDriver(loc, cuts, rank, world, dist)
@@ -79,7 +85,8 @@ def main():
                 ok &= gathered[0][3] == want_attempts
     dist.barrier()
     if a.driver == "native":
-        print(f"rank {rank}: halo resends {loc.native_resends()} bytes sent {loc.native_bytes_sent()}", flush=True)
+        print(f"rank {rank}: halo resends {loc.native_resends()} bytes sent {loc.native_bytes_sent()} "
+              f"p2p {int(loc.p2p_active())}", flush=True)
     if rank == 0:
         print("MULTI_GPU_CHECK OK" if ok else "MULTI_GPU_CHECK FAILED", flush=True)
     loc.close()

@@ -133,17 +133,21 @@ def test_slab_capacity_errors(tmp_path):
     assert ei.value.code == -6  # SPHB_ERR_CAPACITY: the ghost layer does not fit 8 records
 
 
-@pytest.mark.parametrize("driver", ["native", "python"])
+@pytest.mark.parametrize("driver", ["native-p2p", "native-nccl", "python"])
 def test_two_processes_over_nccl(tmp_path, driver):
-    """One process per GPU: the library's own NCCL driver (sphb_slab_step) and the Python protocol
-    driver over torch.distributed, each against the whole-domain engine."""
+    """One process per GPU: the library's own driver (sphb_slab_step) with the halo written straight
+    into the neighbour's inbox over peer memory (CUDA IPC) and with ncclSend / ncclRecv, and the
+    Python protocol driver over torch.distributed, each against the whole-domain engine."""
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
+    port = {"native-p2p": "29516", "native-nccl": "29517", "python": "29518"}[driver]
+    extra = {"native-p2p": ["--p2p", "1", "--expect-p2p", "1"], "native-nccl": ["--p2p", "0", "--expect-p2p", "0"],
+             "python": []}[driver]
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
-           "--master-addr", "127.0.0.1", "--master-port", "29517" if driver == "native" else "29518",
+           "--master-addr", "127.0.0.1", "--master-port", port,
            os.path.join(ROOT, "tests", "multi_gpu_check.py"), "--particles", "262144", "--steps", "3",
-           "--driver", driver]
+           "--driver", driver.split("-")[0]] + extra
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "MULTI_GPU_CHECK OK" in r.stdout
@@ -159,7 +163,7 @@ def test_halo_message_resend_over_nccl(tmp_path):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
            "--master-addr", "127.0.0.1", "--master-port", "29519",
            os.path.join(ROOT, "tests", "multi_gpu_check.py"), "--particles", "262144", "--steps", "6",
-           "--driver", "native", "--halo-margin", "0"]
+           "--driver", "native", "--halo-margin", "0", "--p2p", "0"]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "MULTI_GPU_CHECK OK" in r.stdout
