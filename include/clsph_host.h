@@ -65,6 +65,11 @@ int clsph_simulate(const char* fluid_json, const char* sim_json, const char* obj
                    sphb_params* final_params, uint64_t* steps_done, uint32_t* frames_saved,
                    char* err, size_t err_cap);
 
+/* The slab faces sph_simulation::devices deals the particles out by: world + 1 values, -inf first,
+ * +inf last, equal counts between them, a face midway between two distinct x values.  Returns
+ * world + 1, or -1.  (No GPU involved.) */
+int clsph_equal_count_cuts(const sphb_particle* particles, uint32_t n, int world, float* cuts_out);
+
 /* The same over `devices` GPUs of one box (device, device + 1, ...): sph_simulation::devices —
  * the particles are partitioned into slabs along x, one slab engine and one host thread per GPU,
  * halo exchange over NCCL inside every step (libclsph_b200/host/sph_simulation_slabs.cpp).

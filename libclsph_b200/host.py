@@ -10,7 +10,7 @@ from .engine import BB, PARAMS, PARTICLE, TERMS, HERE, _ptr, lib as _engine_lib
 SYMBOLS = [
     "clsph_scene_load", "clsph_scene_face_count", "clsph_scene_total_grid_points", "clsph_scene_copy",
     "clsph_scene_free", "clsph_load_settings", "clsph_lattice", "clsph_geo_text", "clsph_bgeo_bytes",
-    "clsph_save_frame", "clsph_simulate", "clsph_simulate_devices",
+    "clsph_save_frame", "clsph_simulate", "clsph_simulate_devices", "clsph_equal_count_cuts",
 ]
 
 _lib = None
@@ -127,6 +127,18 @@ def save_frame(frames_prefix, particles, params, use_partio=False):
     rc = lib().clsph_save_frame(os.fsencode(frames_prefix), int(use_partio), _ptr(particles), _ptr(params))
     if rc != 0:
         raise RuntimeError("clsph_save_frame failed")
+
+
+def equal_count_cuts(particles, world):
+    """the slab faces of sph_simulation::devices (host/sph_simulation_slabs.cpp)"""
+    particles = np.ascontiguousarray(particles, PARTICLE)
+    out = np.zeros(world + 1, np.float32)
+    L = lib()
+    L.clsph_equal_count_cuts.argtypes = [C.c_void_p, C.c_uint32, C.c_int, C.c_void_p]
+    k = L.clsph_equal_count_cuts(_ptr(particles), len(particles), int(world), _ptr(out))
+    if k != world + 1:
+        raise RuntimeError("clsph_equal_count_cuts failed")
+    return out
 
 
 def simulate(fluid_json, sim_json, obj_path, device=-1, max_steps=0, frames_prefix=None, n=None, devices=1,

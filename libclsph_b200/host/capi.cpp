@@ -8,6 +8,7 @@
 #include <new>
 #include <sstream>
 #include <string>
+#include <vector>
 
 #include "file_save_delegates/houdini_file_saver.h"
 #include "scene.h"
@@ -36,6 +37,10 @@ struct mute_cout {
   }
 };
 }  // namespace
+
+namespace sphb_host {
+std::vector<float> equal_count_cuts(const particle* p, size_t n, int world);  // sph_simulation_slabs.cpp
+}
 
 extern "C" {
 
@@ -124,6 +129,13 @@ int clsph_save_frame(const char* frames_prefix, int use_partio, sphb_particle* p
   houdini_file_saver saver(frames_prefix);
   saver.use_partio = use_partio != 0;
   return saver.writeFrameToFile(reinterpret_cast<particle*>(particles), p);
+}
+
+int clsph_equal_count_cuts(const sphb_particle* particles, uint32_t n, int world, float* cuts_out) {
+  if (!particles || world < 1 || !cuts_out) return -1;
+  const std::vector<float> cuts = sphb_host::equal_count_cuts(reinterpret_cast<const particle*>(particles), n, world);
+  for (size_t k = 0; k < cuts.size(); ++k) cuts_out[k] = cuts[k];
+  return (int)cuts.size();
 }
 
 int clsph_simulate(const char* fluid_json, const char* sim_json, const char* obj_path, int device,

@@ -213,3 +213,28 @@ def test_saver_writes_geo_or_bgeo(built, tmp_path):
     host.save_frame(prefix, ps, p, use_partio=True)
     assert (tmp_path / "frames" / "frame0000001.geo").read_bytes() == z["text"].tobytes()
     assert (tmp_path / "frames" / "frame0000001.bgeo").read_bytes() == host.bgeo_bytes(ps, p)
+
+
+@pytest.mark.parametrize("world", [1, 2, 3, 8])
+def test_slab_faces_equal_counts(built, world):
+    """The faces sph_simulation::devices deals the particles out by (host/sph_simulation_slabs.cpp)
+    are those of the Python driver (libclsph_b200/slab.py): equal counts, a lattice plane never
+    split, -inf / +inf outside; also on a cloud of distinct random x values."""
+    from libclsph_b200 import PARTICLE, host
+    from libclsph_b200.slab import equal_count_cuts
+    rng = np.random.default_rng(7)
+    lattice = host.lattice(4096, 0.2)
+    cloud = np.zeros(5000, PARTICLE)
+    cloud["position"][:, 0] = rng.normal(size=5000).astype(np.float32)
+    for p in (lattice, cloud):
+        got = host.equal_count_cuts(p, world)
+        want = np.array(equal_count_cuts(p["position"][:, 0], world), np.float32)
+        assert np.array_equal(got, want)
+        assert got[0] == -np.inf and got[-1] == np.inf and np.all(np.diff(got) > 0)
+        x = p["position"][:, 0]
+        counts = [int(((x >= got[r]) & (x < got[r + 1])).sum()) for r in range(world)]
+        assert sum(counts) == len(p)
+        if p is cloud:
+            assert max(counts) - min(counts) <= 1
+        else:  # whole lattice planes of 256 particles each
+            assert all(c % 256 == 0 for c in counts) and max(counts) - min(counts) <= 256
