@@ -14,7 +14,10 @@
  *     SPHB_ERR_NCCL_BASE), < 0 is one of the SPHB_ERR_* codes below; sphb_last_error()
  *     gives the text with the file:line of the failing call (the C++ wrapper prints it and
  *     exit(-1)s, the reference's EXIT_ON_CL_ERROR convention, util/cl_boilerplate.h:32-34);
- *   - one engine = one GPU = one CUDA stream; an engine is not thread-safe;
+ *   - one engine = one GPU = one CUDA stream; an engine is not thread-safe, but different
+ *     engines may be driven from different threads of one process (sph_simulation::devices
+ *     steps one slab engine per GPU that way), and sphb_download_wait may be called from a
+ *     thread other than the one that steps the engine;
  *   - there is NO CPU fallback: without a CUDA device sphb_create() fails.
  *
  * Struct layouts are the reference's, byte for byte (OpenCL float3 = 16 bytes):
