@@ -89,14 +89,17 @@ class worker_team {
 };
 
 struct slab_team {
-  explicit slab_team(int n) : world(n), workers(n), engines(n, (sphb_engine*)0), owned(n, 0), capacity(0), exchange_capacity(0) {}
+  explicit slab_team(int n)
+      : world(n), workers(n), engines(n, (sphb_engine*)0), stage(0), stage_ids(0), hist(n), owned(n, 0),
+        capacity(0), exchange_capacity(0) {}
   int world;
   worker_team workers;
   std::vector<sphb_engine*> engines;
   std::vector<float> cuts;           // world + 1 slab faces, -inf ... +inf
   std::vector<uint32_t> ids;         // id of the particle at each index of the caller's host array
-  std::vector<particle> stage;       // particles in rank order (uploads and downloads)
-  std::vector<uint32_t> stage_ids;
+  particle* stage;                   // particles in rank order (uploads and downloads), page-locked
+  uint32_t* stage_ids;               // (so that every rank's copy runs at full PCIe rate, all at once)
+  std::vector<std::vector<uint32_t> > hist;  // per rank: particles per grid_index, then their offsets
   std::vector<uint32_t> owned;       // particles each rank owns
   std::vector<particle> recut;       // a re-cut's own gather buffer (the caller's array may be on loan to save_frame)
   uint32_t capacity, exchange_capacity;
@@ -156,8 +159,9 @@ void sph_simulation::slabs_begin() {
   T.exchange_capacity = (uint32_t)exch;
   T.ids.resize(n);
   for (uint32_t i = 0; i < n; ++i) T.ids[i] = i;
-  T.stage.resize(n);
-  T.stage_ids.resize(n);
+  check(sphb_host_alloc(reinterpret_cast<void**>(&T.stage), sizeof(particle) * (size_t)(n ? n : 1)), __FILE__, __LINE__);
+  check(sphb_host_alloc(reinterpret_cast<void**>(&T.stage_ids), sizeof(uint32_t) * (size_t)(n ? n : 1)), __FILE__,
+        __LINE__);
 
   unsigned char id[128];
   int rc = sphb_nccl_unique_id(id);
@@ -192,6 +196,8 @@ void sph_simulation::slabs_end() {
     T.engines[r] = 0;
     return 0;
   });
+  sphb_host_free(T.stage);
+  sphb_host_free(T.stage_ids);
   delete team_;
   team_ = 0;
 }
@@ -220,8 +226,8 @@ void sph_simulation::slabs_upload(const particle* particles, bool recut) {
   const int rc = T.workers.run([&](int r) -> int {
     sphb_engine* e = T.engines[r];
     if (int c = sphb_slab_configure(e, T.cuts[r], T.cuts[r + 1], r > 0, r + 1 < T.world)) return c;
-    if (int c = sphb_slab_upload(e, reinterpret_cast<const sphb_particle*>(T.stage.data() + start[r]),
-                                 T.stage_ids.data() + start[r], T.owned[r]))
+    if (int c = sphb_slab_upload(e, reinterpret_cast<const sphb_particle*>(T.stage + start[r]),
+                                 T.stage_ids + start[r], T.owned[r]))
       return c;
     return sphb_slab_start(e);  // collective: the global bbox
   }, &bad);
@@ -249,25 +255,74 @@ void sph_simulation::slabs_read(particle* particles) {
   rc = T.workers.run([&](int r) -> int {
     uint32_t cnt = 0;
     if (!T.owned[r]) return 0;
-    return sphb_slab_download(T.engines[r], reinterpret_cast<sphb_particle*>(T.stage.data() + start[r]),
-                              T.stage_ids.data() + start[r], T.owned[r], &cnt);
+    return sphb_slab_download(T.engines[r], reinterpret_cast<sphb_particle*>(T.stage + start[r]),
+                              T.stage_ids + start[r], T.owned[r], &cnt);
   }, &bad);
   if (rc != 0) slabs_fail(rc, bad, "slab download");
-  // stable counting sort by grid_index; keys past the grid's Morton bound (runaway particles)
-  // share one last bucket
+  // Stable counting sort by grid_index — slabs left to right, each in its own order — into the
+  // caller's array; keys past the grid's Morton bound (runaway particles) share one last bucket.
   const uint32_t cells = parameters.grid_cell_count;
-  std::vector<uint32_t> first((size_t)cells + 2, 0);
-  for (uint32_t i = 0; i < n; ++i) {
-    const uint32_t k = T.stage[i].grid_index < cells ? T.stage[i].grid_index : cells;
-    ++first[(size_t)k + 1];
+  if ((size_t)cells + 1 > ((size_t)1 << 26)) {  // a table per rank would be too much: one thread, one table
+    std::vector<uint32_t> first((size_t)cells + 2, 0);
+    for (uint32_t i = 0; i < n; ++i) {
+      const uint32_t k = T.stage[i].grid_index < cells ? T.stage[i].grid_index : cells;
+      ++first[(size_t)k + 1];
+    }
+    for (size_t c = 0; c <= cells; ++c) first[c + 1] += first[c];
+    for (uint32_t i = 0; i < n; ++i) {
+      const uint32_t k = T.stage[i].grid_index < cells ? T.stage[i].grid_index : cells;
+      const uint32_t d = first[k]++;
+      particles[d] = T.stage[i];
+      T.ids[d] = T.stage_ids[i];
+    }
+    return;
   }
-  for (size_t c = 0; c <= cells; ++c) first[c + 1] += first[c];
-  for (uint32_t i = 0; i < n; ++i) {
-    const uint32_t k = T.stage[i].grid_index < cells ? T.stage[i].grid_index : cells;
-    const uint32_t d = first[k]++;
-    particles[d] = T.stage[i];
-    T.ids[d] = T.stage_ids[i];
-  }
+  // The same by all the host threads at once: every rank counts its slab's keys, the keys are
+  // split into one range per thread for the prefix over (key, rank), every rank scatters its slab.
+  const size_t buckets = (size_t)cells + 1;
+  const int W = T.world;
+  std::vector<uint64_t> range_total(W, 0), range_base(W + 1, 0);
+  T.workers.run([&](int r) -> int {
+    std::vector<uint32_t>& h = T.hist[r];
+    h.assign(buckets, 0u);
+    for (uint32_t i = start[r]; i < start[r + 1]; ++i) {
+      const uint32_t k = T.stage[i].grid_index < cells ? T.stage[i].grid_index : cells;
+      ++h[k];
+    }
+    return 0;
+  });
+  T.workers.run([&](int w) -> int {
+    const size_t lo = buckets * (size_t)w / W, hi = buckets * (size_t)(w + 1) / W;
+    uint64_t sum = 0;
+    for (int r = 0; r < W; ++r) {
+      const std::vector<uint32_t>& h = T.hist[r];
+      for (size_t k = lo; k < hi; ++k) sum += h[k];
+    }
+    range_total[w] = sum;
+    return 0;
+  });
+  for (int w = 0; w < W; ++w) range_base[w + 1] = range_base[w] + range_total[w];
+  T.workers.run([&](int w) -> int {
+    const size_t lo = buckets * (size_t)w / W, hi = buckets * (size_t)(w + 1) / W;
+    uint32_t run = (uint32_t)range_base[w];
+    for (size_t k = lo; k < hi; ++k)
+      for (int r = 0; r < W; ++r) {  // within a key: slabs left to right
+        const uint32_t cnt = T.hist[r][k];
+        T.hist[r][k] = run;
+        run += cnt;
+      }
+    return 0;
+  });
+  T.workers.run([&](int r) -> int {
+    std::vector<uint32_t>& h = T.hist[r];
+    for (uint32_t i = start[r]; i < start[r + 1]; ++i) {
+      const uint32_t k = T.stage[i].grid_index < cells ? T.stage[i].grid_index : cells;
+      const uint32_t d = h[k]++;
+      particles[d] = T.stage[i];
+      T.ids[d] = T.stage_ids[i];
+    }
+    return 0;
+  });
 }
 
 // One simulate_single_frame over all slabs; afterwards, when the fullest slab has outgrown
