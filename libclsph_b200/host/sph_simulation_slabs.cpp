@@ -110,15 +110,31 @@ struct slab_team {
 // -inf / +inf.  (libclsph_b200/slab.py::equal_count_cuts is the same rule.)
 std::vector<float> equal_count_cuts(const particle* p, size_t n, int world) {
   std::vector<float> xs(n);
-  for (size_t i = 0; i < n; ++i) xs[i] = p[i].position.s[0];
-  std::sort(xs.begin(), xs.end());  // (NaN positions are not expected here)
+  for (size_t i = 0; i < n; ++i) xs[i] = p[i].position.s[0];  // (NaN positions are not expected here)
   std::vector<float> cuts;
   cuts.push_back(-std::numeric_limits<float>::infinity());
+  // only world - 1 order statistics are needed, not the sorted array: each selection works on
+  // the part of the array right of the previous one
+  size_t done = 0;  // xs[0 .. done) already hold the `done` smallest values
   for (int r = 1; r < world; ++r) {
     const size_t k = n * (size_t)r / (size_t)world;
-    const float lo = n ? (k > 0 ? xs[k - 1] : xs[0]) : 0.f;
-    const size_t j = (size_t)(std::upper_bound(xs.begin(), xs.end(), lo) - xs.begin());
-    const float hi = j < n ? xs[j] : lo;
+    float lo = 0.f, hi = 0.f;
+    if (n) {
+      const size_t at = k > 0 ? k - 1 : 0;  // lo = the (at + 1)-th smallest value
+      if (at >= done) {
+        std::nth_element(xs.begin() + done, xs.begin() + at, xs.end());
+        done = at + 1;
+      }
+      lo = xs[at];
+      // hi = the smallest value strictly greater than lo (everything left of `at` is <= lo)
+      bool found = false;
+      for (size_t i = at + 1; i < n; ++i)
+        if (xs[i] > lo && (!found || xs[i] < hi)) {
+          hi = xs[i];
+          found = true;
+        }
+      if (!found) hi = lo;
+    }
     cuts.push_back((float)(((double)lo + (double)hi) / 2));
   }
   cuts.push_back(std::numeric_limits<float>::infinity());
