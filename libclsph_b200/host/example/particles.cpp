@@ -58,30 +58,50 @@ int main(int argc, char** argv) {
   };
 
   const simulation_parameters& p = simulation.parameters;
-  std::cout << std::endl
-            << "Loaded parameters          " << std::endl
-            << "-----------------          " << std::endl
-            << "Simulation time:           " << p.simulation_time << std::endl
-            << "Target FPS:                " << p.target_fps << std::endl
-            << "Simulation scale:          " << p.simulation_scale << std::endl
-            << "Write intermediate frames: " << (simulation.write_intermediate_frames ? "true" : "false") << std::endl
-            << "Serialize frames:          " << (simulation.serialize ? "true" : "false") << std::endl
-            << std::endl
-            << "Particle count:            " << p.particles_count << std::endl
-            << "Particle mass:             " << p.particle_mass << std::endl
-            << "Total mass:                " << p.total_mass << std::endl
-            << "Initial volume:            " << simulation.initial_volume << std::endl
-            << std::endl
-            << "Fluid density:             " << p.fluid_density << std::endl
-            << "Dynamic viscosity:         " << p.dynamic_viscosity << std::endl
-            << "Surface tension threshold: " << p.surface_tension_threshold << std::endl
-            << "Surface tension:           " << p.surface_tension << std::endl
-            << "Stiffness (k):             " << p.K << std::endl
-            << "Restitution:               " << p.restitution << std::endl
-            << std::endl
-            << "Kernel support radius (h): " << p.h << std::endl
-            << std::endl
-            << "Saving to folder:          " << saver.frames_folder_prefix + "frames/" << std::endl;
+  // the parameter summary, line for line what the reference's CLI prints: labels padded to 27
+  // columns, a blank line between the groups
+  struct summary {
+    static void text(const char* label, const std::string& value) {
+      std::string cell(label);
+      cell.resize(27, ' ');
+      std::cout << cell << value << std::endl;
+    }
+    static void number(const char* label, double value) {
+      std::string cell(label);
+      cell.resize(27, ' ');
+      std::cout << cell << (float)value << std::endl;
+    }
+    static void count(const char* label, unsigned long value) {
+      std::string cell(label);
+      cell.resize(27, ' ');
+      std::cout << cell << value << std::endl;
+    }
+    static void gap() { std::cout << std::endl; }
+  };
+  summary::gap();
+  summary::text("Loaded parameters", "");
+  summary::text("-----------------", "");
+  summary::number("Simulation time:", p.simulation_time);
+  summary::number("Target FPS:", p.target_fps);
+  summary::number("Simulation scale:", p.simulation_scale);
+  summary::text("Write intermediate frames:", simulation.write_intermediate_frames ? "true" : "false");
+  summary::text("Serialize frames:", simulation.serialize ? "true" : "false");
+  summary::gap();
+  summary::count("Particle count:", p.particles_count);
+  summary::number("Particle mass:", p.particle_mass);
+  summary::number("Total mass:", p.total_mass);
+  summary::number("Initial volume:", simulation.initial_volume);
+  summary::gap();
+  summary::number("Fluid density:", p.fluid_density);
+  summary::number("Dynamic viscosity:", p.dynamic_viscosity);
+  summary::number("Surface tension threshold:", p.surface_tension_threshold);
+  summary::number("Surface tension:", p.surface_tension);
+  summary::number("Stiffness (k):", p.K);
+  summary::number("Restitution:", p.restitution);
+  summary::gap();
+  summary::number("Kernel support radius (h):", p.h);
+  summary::gap();
+  summary::text("Saving to folder:", saver.frames_folder_prefix + "frames/");
 
   if (!simulation.current_scene.load(argv[3], p.h * 2)) {
     std::cerr << "Unable to load scene: " << argv[3] << std::endl;
