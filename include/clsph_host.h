@@ -70,6 +70,12 @@ int clsph_simulate(const char* fluid_json, const char* sim_json, const char* obj
  * world + 1, or -1.  (No GPU involved.) */
 int clsph_equal_count_cuts(const sphb_particle* particles, uint32_t n, int world, float* cuts_out);
 
+/* The frame gather of sph_simulation::devices without its engines: stage[start[r] .. start[r+1])
+ * holds slab r's particles (ids beside them); out = all of them stably ordered by grid_index, slabs
+ * left to right, keys >= cells in one last bucket; done by `world` host threads.  (No GPU involved.) */
+int clsph_gather_sort(const sphb_particle* stage, const uint32_t* stage_ids, const uint32_t* start, int world,
+                      uint32_t cells, sphb_particle* particles_out, uint32_t* ids_out);
+
 /* The same over `devices` GPUs of one box (device, device + 1, ...): sph_simulation::devices —
  * the particles are partitioned into slabs along x, one slab engine and one host thread per GPU,
  * halo exchange over NCCL inside every step (libclsph_b200/host/sph_simulation_slabs.cpp).

@@ -10,7 +10,7 @@ from .engine import BB, PARAMS, PARTICLE, TERMS, HERE, _ptr, lib as _engine_lib
 SYMBOLS = [
     "clsph_scene_load", "clsph_scene_face_count", "clsph_scene_total_grid_points", "clsph_scene_copy",
     "clsph_scene_free", "clsph_load_settings", "clsph_lattice", "clsph_geo_text", "clsph_bgeo_bytes",
-    "clsph_save_frame", "clsph_simulate", "clsph_simulate_devices", "clsph_equal_count_cuts",
+    "clsph_save_frame", "clsph_simulate", "clsph_simulate_devices", "clsph_equal_count_cuts", "clsph_gather_sort",
 ]
 
 _lib = None
@@ -139,6 +139,20 @@ def equal_count_cuts(particles, world):
     if k != world + 1:
         raise RuntimeError("clsph_equal_count_cuts failed")
     return out
+
+
+def gather_sort(stage, stage_ids, start, cells):
+    """the frame gather of sph_simulation::devices (host/sph_simulation_slabs.cpp) on host arrays"""
+    stage = np.ascontiguousarray(stage, PARTICLE)
+    stage_ids = np.ascontiguousarray(stage_ids, np.uint32)
+    start = np.ascontiguousarray(start, np.uint32)
+    out, ids = np.zeros(len(stage), PARTICLE), np.zeros(len(stage), np.uint32)
+    L = lib()
+    L.clsph_gather_sort.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_uint32, C.c_void_p, C.c_void_p]
+    rc = L.clsph_gather_sort(_ptr(stage), _ptr(stage_ids), _ptr(start), len(start) - 1, int(cells), _ptr(out), _ptr(ids))
+    if rc != 0:
+        raise RuntimeError("clsph_gather_sort failed")
+    return out, ids
 
 
 def simulate(fluid_json, sim_json, obj_path, device=-1, max_steps=0, frames_prefix=None, n=None, devices=1,

@@ -40,6 +40,8 @@ struct mute_cout {
 
 namespace sphb_host {
 std::vector<float> equal_count_cuts(const particle* p, size_t n, int world);  // sph_simulation_slabs.cpp
+int gather_sort_selftest(const particle* stage, const uint32_t* stage_ids, const uint32_t* start, int world,
+                         uint32_t cells, particle* particles, uint32_t* ids_out);
 }
 
 extern "C" {
@@ -136,6 +138,13 @@ int clsph_equal_count_cuts(const sphb_particle* particles, uint32_t n, int world
   const std::vector<float> cuts = sphb_host::equal_count_cuts(reinterpret_cast<const particle*>(particles), n, world);
   for (size_t k = 0; k < cuts.size(); ++k) cuts_out[k] = cuts[k];
   return (int)cuts.size();
+}
+
+int clsph_gather_sort(const sphb_particle* stage, const uint32_t* stage_ids, const uint32_t* start, int world,
+                      uint32_t cells, sphb_particle* particles_out, uint32_t* ids_out) {
+  if (!stage || !stage_ids || !start || world < 1 || !particles_out || !ids_out) return -1;
+  return sphb_host::gather_sort_selftest(reinterpret_cast<const particle*>(stage), stage_ids, start, world, cells,
+                                         reinterpret_cast<particle*>(particles_out), ids_out);
 }
 
 int clsph_simulate(const char* fluid_json, const char* sim_json, const char* obj_path, int device,

@@ -148,6 +148,88 @@ inline int slab_of(const std::vector<float>& cuts, float x) {
   return r < 0 ? 0 : (r >= world ? world - 1 : r);
 }
 
+// Stable counting sort by grid_index — slabs left to right (stage[start[r] .. start[r+1]) is slab
+// r), each in its own order — into `particles` / `ids_out`, by all the host threads at once.
+void gather_sort(worker_team& workers, std::vector<std::vector<uint32_t> >& hist, const particle* stage,
+                 const uint32_t* stage_ids, const std::vector<uint32_t>& start, uint32_t cells,
+                 particle* particles, uint32_t* ids_out) {
+  const int world = (int)start.size() - 1;
+  const uint32_t n = start[world];
+  if ((int)hist.size() < world) hist.resize(world);
+  // keys past the grid's Morton bound (runaway particles) share one last bucket
+  if ((size_t)cells + 1 > ((size_t)1 << 26)) {  // a table per rank would be too much: one thread, one table
+    std::vector<uint32_t> first((size_t)cells + 2, 0);
+    for (uint32_t i = 0; i < n; ++i) {
+      const uint32_t k = stage[i].grid_index < cells ? stage[i].grid_index : cells;
+      ++first[(size_t)k + 1];
+    }
+    for (size_t c = 0; c <= cells; ++c) first[c + 1] += first[c];
+    for (uint32_t i = 0; i < n; ++i) {
+      const uint32_t k = stage[i].grid_index < cells ? stage[i].grid_index : cells;
+      const uint32_t d = first[k]++;
+      particles[d] = stage[i];
+      ids_out[d] = stage_ids[i];
+    }
+    return;
+  }
+  // The same by all the host threads at once: every rank counts its slab's keys, the keys are
+  // split into one range per thread for the prefix over (key, rank), every rank scatters its slab.
+  const size_t buckets = (size_t)cells + 1;
+  const int W = world;
+  std::vector<uint64_t> range_total(W, 0), range_base(W + 1, 0);
+  workers.run([&](int r) -> int {
+    std::vector<uint32_t>& h = hist[r];
+    h.assign(buckets, 0u);
+    for (uint32_t i = start[r]; i < start[r + 1]; ++i) {
+      const uint32_t k = stage[i].grid_index < cells ? stage[i].grid_index : cells;
+      ++h[k];
+    }
+    return 0;
+  });
+  workers.run([&](int w) -> int {
+    const size_t lo = buckets * (size_t)w / W, hi = buckets * (size_t)(w + 1) / W;
+    uint64_t sum = 0;
+    for (int r = 0; r < W; ++r) {
+      const std::vector<uint32_t>& h = hist[r];
+      for (size_t k = lo; k < hi; ++k) sum += h[k];
+    }
+    range_total[w] = sum;
+    return 0;
+  });
+  for (int w = 0; w < W; ++w) range_base[w + 1] = range_base[w] + range_total[w];
+  workers.run([&](int w) -> int {
+    const size_t lo = buckets * (size_t)w / W, hi = buckets * (size_t)(w + 1) / W;
+    uint32_t run = (uint32_t)range_base[w];
+    for (size_t k = lo; k < hi; ++k)
+      for (int r = 0; r < W; ++r) {  // within a key: slabs left to right
+        const uint32_t cnt = hist[r][k];
+        hist[r][k] = run;
+        run += cnt;
+      }
+    return 0;
+  });
+  workers.run([&](int r) -> int {
+    std::vector<uint32_t>& h = hist[r];
+    for (uint32_t i = start[r]; i < start[r + 1]; ++i) {
+      const uint32_t k = stage[i].grid_index < cells ? stage[i].grid_index : cells;
+      const uint32_t d = h[k]++;
+      particles[d] = stage[i];
+      ids_out[d] = stage_ids[i];
+    }
+    return 0;
+  });
+}
+
+// (tests: the gather of a frame without any engine)
+int gather_sort_selftest(const particle* stage, const uint32_t* stage_ids, const uint32_t* start, int world,
+                         uint32_t cells, particle* particles, uint32_t* ids_out) {
+  worker_team workers(world);
+  std::vector<std::vector<uint32_t> > hist(world);
+  const std::vector<uint32_t> st(start, start + world + 1);
+  gather_sort(workers, hist, stage, stage_ids, st, cells, particles, ids_out);
+  return 0;
+}
+
 }  // namespace sphb_host
 
 using sphb_host::slab_team;
@@ -275,70 +357,8 @@ void sph_simulation::slabs_read(particle* particles) {
                               T.stage_ids + start[r], T.owned[r], &cnt);
   }, &bad);
   if (rc != 0) slabs_fail(rc, bad, "slab download");
-  // Stable counting sort by grid_index — slabs left to right, each in its own order — into the
-  // caller's array; keys past the grid's Morton bound (runaway particles) share one last bucket.
-  const uint32_t cells = parameters.grid_cell_count;
-  if ((size_t)cells + 1 > ((size_t)1 << 26)) {  // a table per rank would be too much: one thread, one table
-    std::vector<uint32_t> first((size_t)cells + 2, 0);
-    for (uint32_t i = 0; i < n; ++i) {
-      const uint32_t k = T.stage[i].grid_index < cells ? T.stage[i].grid_index : cells;
-      ++first[(size_t)k + 1];
-    }
-    for (size_t c = 0; c <= cells; ++c) first[c + 1] += first[c];
-    for (uint32_t i = 0; i < n; ++i) {
-      const uint32_t k = T.stage[i].grid_index < cells ? T.stage[i].grid_index : cells;
-      const uint32_t d = first[k]++;
-      particles[d] = T.stage[i];
-      T.ids[d] = T.stage_ids[i];
-    }
-    return;
-  }
-  // The same by all the host threads at once: every rank counts its slab's keys, the keys are
-  // split into one range per thread for the prefix over (key, rank), every rank scatters its slab.
-  const size_t buckets = (size_t)cells + 1;
-  const int W = T.world;
-  std::vector<uint64_t> range_total(W, 0), range_base(W + 1, 0);
-  T.workers.run([&](int r) -> int {
-    std::vector<uint32_t>& h = T.hist[r];
-    h.assign(buckets, 0u);
-    for (uint32_t i = start[r]; i < start[r + 1]; ++i) {
-      const uint32_t k = T.stage[i].grid_index < cells ? T.stage[i].grid_index : cells;
-      ++h[k];
-    }
-    return 0;
-  });
-  T.workers.run([&](int w) -> int {
-    const size_t lo = buckets * (size_t)w / W, hi = buckets * (size_t)(w + 1) / W;
-    uint64_t sum = 0;
-    for (int r = 0; r < W; ++r) {
-      const std::vector<uint32_t>& h = T.hist[r];
-      for (size_t k = lo; k < hi; ++k) sum += h[k];
-    }
-    range_total[w] = sum;
-    return 0;
-  });
-  for (int w = 0; w < W; ++w) range_base[w + 1] = range_base[w] + range_total[w];
-  T.workers.run([&](int w) -> int {
-    const size_t lo = buckets * (size_t)w / W, hi = buckets * (size_t)(w + 1) / W;
-    uint32_t run = (uint32_t)range_base[w];
-    for (size_t k = lo; k < hi; ++k)
-      for (int r = 0; r < W; ++r) {  // within a key: slabs left to right
-        const uint32_t cnt = T.hist[r][k];
-        T.hist[r][k] = run;
-        run += cnt;
-      }
-    return 0;
-  });
-  T.workers.run([&](int r) -> int {
-    std::vector<uint32_t>& h = T.hist[r];
-    for (uint32_t i = start[r]; i < start[r + 1]; ++i) {
-      const uint32_t k = T.stage[i].grid_index < cells ? T.stage[i].grid_index : cells;
-      const uint32_t d = h[k]++;
-      particles[d] = T.stage[i];
-      T.ids[d] = T.stage_ids[i];
-    }
-    return 0;
-  });
+  sphb_host::gather_sort(T.workers, T.hist, T.stage, T.stage_ids, start, parameters.grid_cell_count, particles,
+                         T.ids.data());
 }
 
 // One simulate_single_frame over all slabs; afterwards, when the fullest slab has outgrown

@@ -242,3 +242,25 @@ def test_slab_faces_equal_counts(built, world):
             assert max(counts) - min(counts) <= 1
         else:  # whole lattice planes of 256 particles each
             assert all(c % 256 == 0 for c in counts) and max(counts) - min(counts) <= 256
+
+
+@pytest.mark.parametrize("world,cells", [(1, 500), (3, 500), (8, 4096), (2, (1 << 26))])
+def test_frame_gather_is_a_stable_sort_by_grid_index(built, world, cells):
+    """What a hook sees under sph_simulation::devices: the slabs' particles, stably sorted by
+    grid_index with the slabs taken left to right (keys past the grid's bound in one last bucket) —
+    the host threads' shared counting sort against numpy's stable argsort; the last case takes the
+    one-thread path kept for very large grids."""
+    from libclsph_b200 import PARTICLE, host
+    rng = np.random.default_rng(world)
+    n = 20000
+    stage = np.zeros(n, PARTICLE)
+    stage["position"][:, :3] = rng.normal(size=(n, 3)).astype(np.float32)
+    keys = rng.integers(0, 600 if cells < (1 << 20) else 5000, n).astype(np.uint32)  # some beyond `cells`
+    stage["grid_index"] = keys
+    ids = rng.permutation(n).astype(np.uint32)
+    cuts = np.sort(rng.integers(0, n + 1, world - 1)) if world > 1 else np.zeros(0, np.int64)
+    start = np.concatenate([[0], cuts, [n]]).astype(np.uint32)  # slabs of uneven (possibly zero) size
+    got, got_ids = host.gather_sort(stage, ids, start, cells)
+    order = np.argsort(np.minimum(keys, cells), kind="stable")
+    assert got.tobytes() == stage[order].tobytes()
+    assert np.array_equal(got_ids, ids[order])
