@@ -76,6 +76,13 @@ int clsph_equal_count_cuts(const sphb_particle* particles, uint32_t n, int world
 int clsph_gather_sort(const sphb_particle* stage, const uint32_t* stage_ids, const uint32_t* start, int world,
                       uint32_t cells, sphb_particle* particles_out, uint32_t* ids_out);
 
+/* The upload side of the same: particles (ids beside them) dealt out to the slabs
+ * [cuts[r], cuts[r+1]) — stage_out[start_out[r] .. start_out[r+1]) = slab r's particles in the order
+ * they have in `particles` — by `threads` host threads, each owning one piece of the input.
+ * world <= 255.  (No GPU involved.) */
+int clsph_deal_out(const sphb_particle* particles, const uint32_t* ids, uint32_t n, const float* cuts, int world,
+                   int threads, sphb_particle* stage_out, uint32_t* stage_ids_out, uint32_t* start_out);
+
 /* The same over `devices` GPUs of one box (device, device + 1, ...): sph_simulation::devices —
  * the particles are partitioned into slabs along x, one slab engine and one host thread per GPU,
  * halo exchange over NCCL inside every step (libclsph_b200/host/sph_simulation_slabs.cpp).

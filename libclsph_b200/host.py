@@ -11,6 +11,7 @@ SYMBOLS = [
     "clsph_scene_load", "clsph_scene_face_count", "clsph_scene_total_grid_points", "clsph_scene_copy",
     "clsph_scene_free", "clsph_load_settings", "clsph_lattice", "clsph_geo_text", "clsph_bgeo_bytes",
     "clsph_save_frame", "clsph_simulate", "clsph_simulate_devices", "clsph_equal_count_cuts", "clsph_gather_sort",
+    "clsph_deal_out",
 ]
 
 _lib = None
@@ -153,6 +154,25 @@ def gather_sort(stage, stage_ids, start, cells):
     if rc != 0:
         raise RuntimeError("clsph_gather_sort failed")
     return out, ids
+
+
+def deal_out(particles, ids, cuts, threads):
+    """the upload-side partition of sph_simulation::devices (host/sph_simulation_slabs.cpp) on host
+    arrays; returns (stage, stage_ids, start)"""
+    particles = np.ascontiguousarray(particles, PARTICLE)
+    ids = np.ascontiguousarray(ids, np.uint32)
+    cuts = np.ascontiguousarray(cuts, np.float32)
+    world = len(cuts) - 1
+    stage, stage_ids = np.zeros(len(particles), PARTICLE), np.zeros(len(particles), np.uint32)
+    start = np.zeros(world + 1, np.uint32)
+    L = lib()
+    L.clsph_deal_out.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_int, C.c_int, C.c_void_p,
+                                 C.c_void_p, C.c_void_p]
+    rc = L.clsph_deal_out(_ptr(particles), _ptr(ids), len(particles), _ptr(cuts), world, int(threads), _ptr(stage),
+                          _ptr(stage_ids), _ptr(start))
+    if rc != 0:
+        raise RuntimeError("clsph_deal_out failed")
+    return stage, stage_ids, start
 
 
 def simulate(fluid_json, sim_json, obj_path, device=-1, max_steps=0, frames_prefix=None, n=None, devices=1,

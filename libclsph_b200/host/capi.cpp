@@ -42,6 +42,8 @@ namespace sphb_host {
 std::vector<float> equal_count_cuts(const particle* p, size_t n, int world);  // sph_simulation_slabs.cpp
 int gather_sort_selftest(const particle* stage, const uint32_t* stage_ids, const uint32_t* start, int world,
                          uint32_t cells, particle* particles, uint32_t* ids_out);
+int deal_out_selftest(const particle* particles, const uint32_t* ids, uint32_t n, const float* cuts, int world,
+                      int threads, particle* stage, uint32_t* stage_ids, uint32_t* start_out);
 }
 
 extern "C" {
@@ -145,6 +147,13 @@ int clsph_gather_sort(const sphb_particle* stage, const uint32_t* stage_ids, con
   if (!stage || !stage_ids || !start || world < 1 || !particles_out || !ids_out) return -1;
   return sphb_host::gather_sort_selftest(reinterpret_cast<const particle*>(stage), stage_ids, start, world, cells,
                                          reinterpret_cast<particle*>(particles_out), ids_out);
+}
+
+int clsph_deal_out(const sphb_particle* particles, const uint32_t* ids, uint32_t n, const float* cuts, int world,
+                   int threads, sphb_particle* stage_out, uint32_t* stage_ids_out, uint32_t* start_out) {
+  if (!particles || !ids || !cuts || !stage_out || !stage_ids_out || !start_out) return -1;
+  return sphb_host::deal_out_selftest(reinterpret_cast<const particle*>(particles), ids, n, cuts, world, threads,
+                                      reinterpret_cast<particle*>(stage_out), stage_ids_out, start_out);
 }
 
 int clsph_simulate(const char* fluid_json, const char* sim_json, const char* obj_path, int device,

@@ -220,7 +220,62 @@ void gather_sort(worker_team& workers, std::vector<std::vector<uint32_t> >& hist
   });
 }
 
-// (tests: the gather of a frame without any engine)
+// The opposite direction: the caller's array dealt out to the slabs [cuts[r], cuts[r+1]) —
+// stage[start[r] .. start[r+1]) receives slab r's particles in the order they have in the
+// caller's array — by all the host threads at once, each owning one contiguous piece of the input.
+void deal_out(worker_team& workers, int threads, const std::vector<float>& cuts, const particle* particles,
+              const uint32_t* ids, uint32_t n, particle* stage, uint32_t* stage_ids, std::vector<uint32_t>& start) {
+  const int world = (int)cuts.size() - 1;
+  const int W = threads < 1 ? 1 : threads;
+  std::vector<unsigned char> where(n);  // (a communicator has at most 255 ranks here: 8 in practice)
+  std::vector<std::vector<uint32_t> > count(W, std::vector<uint32_t>(world, 0u));
+  workers.run([&](int w) -> int {
+    if (w >= W) return 0;
+    const size_t lo = (size_t)n * w / W, hi = (size_t)n * (w + 1) / W;
+    std::vector<uint32_t>& c = count[w];
+    for (size_t i = lo; i < hi; ++i) {
+      const int r = slab_of(cuts, particles[i].position.s[0]);
+      where[i] = (unsigned char)r;
+      ++c[r];
+    }
+    return 0;
+  });
+  start.assign(world + 1, 0u);
+  uint32_t run = 0;
+  for (int r = 0; r < world; ++r) {  // slab by slab, pieces of the input in order
+    start[r] = run;
+    for (int w = 0; w < W; ++w) {
+      const uint32_t c = count[w][r];
+      count[w][r] = run;
+      run += c;
+    }
+  }
+  start[world] = run;
+  workers.run([&](int w) -> int {
+    if (w >= W) return 0;
+    const size_t lo = (size_t)n * w / W, hi = (size_t)n * (w + 1) / W;
+    std::vector<uint32_t>& cursor = count[w];
+    for (size_t i = lo; i < hi; ++i) {
+      const uint32_t d = cursor[where[i]]++;
+      stage[d] = particles[i];
+      stage_ids[d] = ids[i];
+    }
+    return 0;
+  });
+}
+
+// (tests: the two directions of a frame without any engine)
+int deal_out_selftest(const particle* particles, const uint32_t* ids, uint32_t n, const float* cuts, int world,
+                      int threads, particle* stage, uint32_t* stage_ids, uint32_t* start_out) {
+  if (world < 1 || world > 255 || threads < 1) return -1;
+  worker_team workers(threads);
+  const std::vector<float> c(cuts, cuts + world + 1);
+  std::vector<uint32_t> start;
+  deal_out(workers, threads, c, particles, ids, n, stage, stage_ids, start);
+  for (int r = 0; r <= world; ++r) start_out[r] = start[r];
+  return 0;
+}
+
 int gather_sort_selftest(const particle* stage, const uint32_t* stage_ids, const uint32_t* start, int world,
                          uint32_t cells, particle* particles, uint32_t* ids_out) {
   worker_team workers(world);
@@ -246,6 +301,10 @@ void sph_simulation::slabs_fail(int rc, int rank, const char* what) {
 void sph_simulation::slabs_begin() {
   const int world = devices;
   const uint32_t n = parameters.particles_count;
+  if (world > 255) {  // (deal_out keeps a particle's slab in one byte)
+    std::cerr << "sph_simulation::devices: at most 255 GPUs" << std::endl;
+    std::exit(-1);
+  }
   team_ = new slab_team(world);
   slab_team& T = *team_;
   uint64_t exch = n / 4u;
@@ -306,19 +365,8 @@ void sph_simulation::slabs_upload(const particle* particles, bool recut) {
   slab_team& T = *team_;
   const uint32_t n = parameters.particles_count;
   if (recut || T.cuts.empty()) T.cuts = sphb_host::equal_count_cuts(particles, n, T.world);
-  std::vector<uint32_t> start(T.world + 1, 0);
-  std::vector<int> where(n);
-  for (uint32_t i = 0; i < n; ++i) {
-    where[i] = sphb_host::slab_of(T.cuts, particles[i].position.s[0]);
-    ++start[where[i] + 1];
-  }
-  for (int r = 0; r < T.world; ++r) start[r + 1] += start[r];
-  std::vector<uint32_t> cursor(start.begin(), start.end() - 1);
-  for (uint32_t i = 0; i < n; ++i) {
-    const uint32_t d = cursor[where[i]]++;
-    T.stage[d] = particles[i];
-    T.stage_ids[d] = T.ids[i];
-  }
+  std::vector<uint32_t> start;
+  sphb_host::deal_out(T.workers, T.world, T.cuts, particles, T.ids.data(), n, T.stage, T.stage_ids, start);
   for (int r = 0; r < T.world; ++r) T.owned[r] = start[r + 1] - start[r];
   int bad = 0;
   const int rc = T.workers.run([&](int r) -> int {

@@ -264,3 +264,32 @@ def test_frame_gather_is_a_stable_sort_by_grid_index(built, world, cells):
     order = np.argsort(np.minimum(keys, cells), kind="stable")
     assert got.tobytes() == stage[order].tobytes()
     assert np.array_equal(got_ids, ids[order])
+
+
+@pytest.mark.parametrize("world,threads", [(1, 1), (2, 2), (3, 3), (8, 8), (4, 1), (2, 5)])
+def test_upload_deal_out_keeps_the_order_inside_a_slab(built, world, threads):
+    """The upload side of sph_simulation::devices: every particle lands in the slab
+    [cuts[r], cuts[r+1]) that holds its x (a particle exactly on a face belongs to the slab on its
+    right), in the order it had in the caller's array, with its id beside it — the host threads'
+    shared partition against a numpy stable argsort by slab."""
+    from libclsph_b200 import PARTICLE, host
+    rng = np.random.default_rng(10 * world + threads)
+    n = 30011
+    p = np.zeros(n, PARTICLE)
+    p["position"][:, :3] = rng.normal(size=(n, 3)).astype(np.float32)
+    p["velocity"][:, :3] = rng.normal(size=(n, 3)).astype(np.float32)
+    ids = rng.permutation(n).astype(np.uint32)
+    cuts = host.equal_count_cuts(p, world)
+    if world > 1:
+        p["position"][:17, 0] = cuts[1]  # on a face
+    p["position"][17, 0], p["position"][18, 0] = np.float32(-1e30), np.float32(1e30)
+    stage, stage_ids, start = host.deal_out(p, ids, cuts, threads)
+    x = p["position"][:, 0]
+    slab = np.clip(np.searchsorted(cuts[1:-1], x, side="right"), 0, world - 1)
+    order = np.argsort(slab, kind="stable")
+    assert np.array_equal(start, np.concatenate([[0], np.cumsum(np.bincount(slab, minlength=world))]).astype(np.uint32))
+    assert stage.tobytes() == p[order].tobytes()
+    assert np.array_equal(stage_ids, ids[order])
+    for r in range(world):
+        xs = stage["position"][start[r]:start[r + 1], 0]
+        assert np.all((xs >= cuts[r]) & (xs < cuts[r + 1]))
