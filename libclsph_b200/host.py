@@ -18,7 +18,8 @@ _lib = None
 
 
 def lib_path():
-    return os.path.join(HERE, "libclsph_host.so")
+    # CLSPH_HOST_LIB: another build of the same library (tools/sanitize_cpu.sh: ASan / UBSan)
+    return os.environ.get("CLSPH_HOST_LIB") or os.path.join(HERE, "libclsph_host.so")
 
 
 def lib():

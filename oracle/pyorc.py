@@ -97,8 +97,8 @@ def _ptr(a):
 def lib_path(kind):
     if kind == "reference":
         return os.path.join(HERE, "_ref", "libsphref.so")
-    if kind == "port":
-        return os.path.join(HERE, "liboracle.so")
+    if kind == "port":  # SPHB_ORACLE_LIB: another build of it (tools/sanitize_cpu.sh)
+        return os.environ.get("SPHB_ORACLE_LIB") or os.path.join(HERE, "liboracle.so")
     raise ValueError(kind)
 
 
