@@ -3,7 +3,7 @@
 # (libclsph_b200/host/ -> libclsph_host.so) under tests/test_host.py, and the plain-C oracle
 # (oracle/sph_oracle.c) under tests/test_oracle_golden.py.  Instrumented copies are built under
 # libclsph_b200/build/asan/ and selected with CLSPH_HOST_LIB / SPHB_ORACLE_LIB; the product
-# libraries are not touched.  Prints the number of sanitizer reports (0 = clean).
+# libraries are not touched.  Then ThreadSanitizer over the threaded host code.  Prints the number of sanitizer reports (0 = clean).
 #   tools/sanitize_cpu.sh            (needs libclsph_b200/libsphb.so: python -m libclsph_b200.build)
 set -e
 cd "$(dirname "$0")/.."
@@ -32,6 +32,20 @@ CLSPH_HOST_LIB="$PWD/$OUT/libclsph_host.so" python -m pytest tests/test_host.py 
 SPHB_ORACLE_LIB="$PWD/$OUT/liboracle.so" python -m pytest tests/test_oracle_golden.py -q -s -p no:cacheprovider \
     > gpurun_out/asan_oracle.log 2>&1 || true
 unset LD_PRELOAD
+# ThreadSanitizer over the threaded host code (frame gather, deal-out, .geo / .bgeo formatting):
+# a stand-alone driver, tools/tsan_host.cpp, linked with the host sources
+mkdir -p libclsph_b200/build/tsan
+python - <<'PY'
+import os, subprocess
+from libclsph_b200 import build as B
+out = os.path.join(B.OBJDIR, "tsan")
+flags = [f for f in B.HOST_FLAGS if f not in ("-O2", "-fPIC")] + ["-fsanitize=thread", "-g", "-O1", "-fPIE"]
+srcs = [os.path.join(B.HOST, s) for s in B.HOST_SOURCES] + [os.path.join(B.HERE, "..", "tools", "tsan_host.cpp")]
+subprocess.check_call(["g++"] + flags + srcs + ["-o", os.path.join(out, "tsan_host"), "-L", B.HERE, "-lsphb",
+                                                "-Wl,-rpath," + B.HERE, "-pthread"])
+PY
+TSAN_OPTIONS=halt_on_error=0 libclsph_b200/build/tsan/tsan_host > gpurun_out/tsan_host.log 2>&1 || true
+echo "gpurun_out/tsan_host.log: $(tail -1 gpurun_out/tsan_host.log) | data races: $(grep -c 'WARNING: ThreadSanitizer' gpurun_out/tsan_host.log || true)"
 for f in gpurun_out/asan_host.log gpurun_out/asan_oracle.log; do
   echo "$f: $(tail -1 $f) | sanitizer reports: $(grep -c 'AddressSanitizer\|runtime error' $f || true)"
 done
