@@ -281,6 +281,9 @@ void* sphb_stream(sphb_engine* e);
  *   "sort"             0 (default) = counting sort by search cell (the scan of the counts is the
  *                      cell table), made stable by a per-cell canonical order; 1 = LSD radix
  *                      sort of (key, index) pairs.  Both give the same order.
+ *   "scan"             1 (default) = the prefix scans of the cell tables are one pass over the
+ *                      table (decoupled look-back); 0 = three kernels (tile scans, scan of the
+ *                      tile totals, add).  Same tables.  PROCESS-wide: applies to every engine.
  *   "triangle_bin"     1 (default) = scenes of 17+ faces get a uniform-grid triangle bin for the
  *                      collision pass; 0 = every particle tests every face (set before
  *                      sphb_set_scene)

@@ -285,6 +285,7 @@ int launch_sort_pairs(const SortBuffers& b, uint32_t n, int key_bits, int* resul
 // In-place exclusive scans of `len` u32 entries (sum, or running maximum with identity 0).
 // scratch must hold scan_scratch_entries(len) entries.
 size_t scan_scratch_entries(size_t len);
+void set_scan_variant(int one_pass);  // process-wide: 1 = one-pass (decoupled look-back), 0 = three kernels
 int launch_exclusive_sum(uint32_t* data, uint32_t len, uint32_t* scratch, cudaStream_t s);
 int launch_exclusive_max(uint32_t* data, uint32_t len, uint32_t* scratch, cudaStream_t s);
 

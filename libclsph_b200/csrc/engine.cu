@@ -906,6 +906,16 @@ int sphb_set_option(sphb_engine* e, const char* name, int value) {
     e->sort_variant = value ? 1 : 0;
     return 0;
   }
+  if (!strcmp(name, "scan")) {  // the cell tables' prefix scans: 1 = one pass, 0 = three kernels
+    CUDA_TRY(e, cudaSetDevice(e->device));
+    CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    if (e->qgraph) {  // a captured step holds the other variant's launches
+      cudaGraphExecDestroy(e->qgraph);
+      e->qgraph = nullptr;
+    }
+    set_scan_variant(value);  // (process-wide: every engine of this process)
+    return 0;
+  }
   if (!strcmp(name, "neighbor_kernel")) {
     e->neighbor_variant = value;
     return 0;

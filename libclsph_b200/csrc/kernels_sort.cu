@@ -273,21 +273,159 @@ int exclusive_scan(uint32_t* data, uint32_t len, uint32_t* scratch, cudaStream_t
   return 3;
 }
 
+// ---- the same scans in ONE pass over the data (decoupled look-back) ------------------------
+// A CTA takes the next tile by ticket (so every tile before it has been started), scans its
+// kLookTile entries in registers, publishes the tile's aggregate as one 64-bit word (flag, value),
+// and its first warp walks back over the preceding tiles' words — 32 at a time — until it meets
+// one that already carries an inclusive prefix.  One read and one write of the table instead of
+// two reads and two writes, one launch instead of three.  status[] and the ticket are zeroed by
+// the launcher.  A predecessor that does not answer within ~2 s is a bug: the kernel traps (the
+// next CUDA call fails) rather than spinning for ever.
+constexpr int kLookPer = 16;                       // entries per thread: 4 x uint4, warp-striped
+constexpr int kLookTile = kThreads * kLookPer;     // 4096 entries per CTA
+constexpr uint32_t kFlagAggregate = 1u, kFlagInclusive = 2u;
+
+__device__ __forceinline__ unsigned long long look_pack(uint32_t flag, uint32_t value) {
+  return ((unsigned long long)flag << 32) | value;
+}
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+template <typename Op>
+__global__ void __launch_bounds__(kThreads)
+    k_scan_lookback(uint32_t* __restrict__ data, uint32_t len, volatile unsigned long long* status,
+                    uint32_t* ticket) {
+  __shared__ uint32_t tile_s, prefix_s;
+  __shared__ uint32_t warp_tot[kWarps];
+  if (threadIdx.x == 0) tile_s = atomicAdd(ticket, 1u);
+  __syncthreads();
+  const uint32_t tile = tile_s;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  // warp w owns 512 consecutive entries: 4 chunks of 128, lane l holds entries 4l .. 4l+3 of each
+  const uint32_t wbase = tile * (uint32_t)kLookTile + (uint32_t)warp * (32u * kLookPer);
+  uint4 v[4];
+  uint32_t excl[4], chunk_tot[4];
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    const uint32_t i = wbase + r * 128u + lane * 4u;
+    if (i + 3u < len) {
+      v[r] = *reinterpret_cast<const uint4*>(data + i);
+    } else {
+      v[r].x = i < len ? data[i] : 0u;
+      v[r].y = i + 1u < len ? data[i + 1u] : 0u;
+      v[r].z = i + 2u < len ? data[i + 2u] : 0u;
+      v[r].w = 0u;
+    }
+    const uint32_t t = Op::apply(Op::apply(v[r].x, v[r].y), Op::apply(v[r].z, v[r].w));
+    const uint32_t incl = warp_inclusive<Op>(t, lane);
+    const uint32_t up = __shfl_up_sync(0xffffffffu, incl, 1);
+    excl[r] = lane ? up : 0u;
+    chunk_tot[r] = __shfl_sync(0xffffffffu, incl, 31);
+  }
+  uint32_t chunk_off[4];
+  chunk_off[0] = 0u;
+#pragma unroll
+  for (int r = 1; r < 4; ++r) chunk_off[r] = Op::apply(chunk_off[r - 1], chunk_tot[r - 1]);
+  if (lane == 0) warp_tot[warp] = Op::apply(chunk_off[3], chunk_tot[3]);
+  __syncthreads();
+  uint32_t warp_off = 0u, aggregate = 0u;
+#pragma unroll
+  for (int w = 0; w < kWarps; ++w) {
+    if (w < warp) warp_off = Op::apply(warp_off, warp_tot[w]);
+    aggregate = Op::apply(aggregate, warp_tot[w]);
+  }
+  if (warp == 0) {
+    uint32_t prefix = 0u;
+    if (tile == 0u) {
+      if (lane == 0) status[0] = look_pack(kFlagInclusive, aggregate);
+    } else {
+      if (lane == 0) status[tile] = look_pack(kFlagAggregate, aggregate);
+      const unsigned long long t0 = globaltimer_ns();
+      long long first = (long long)tile - 1;  // nearest tile of the window looked at
+      for (;;) {
+        const long long mine = first - lane;
+        unsigned long long word = look_pack(kFlagInclusive, 0u);  // before tile 0: nothing
+        if (mine >= 0) {
+          word = status[mine];
+          while ((uint32_t)(word >> 32) == 0u) {
+            if (globaltimer_ns() - t0 > 2000000000ull) __trap();
+            __nanosleep(40);
+            word = status[mine];
+          }
+        }
+        const uint32_t has_incl = __ballot_sync(0xffffffffu, (uint32_t)(word >> 32) == kFlagInclusive);
+        // lanes up to and including the nearest inclusive one contribute
+        const int stop = has_incl ? __ffs((int)has_incl) - 1 : 31;
+        uint32_t part = lane <= stop ? (uint32_t)word : 0u;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) part = Op::apply(part, __shfl_xor_sync(0xffffffffu, part, o));
+        prefix = Op::apply(prefix, part);
+        if (has_incl) break;
+        first -= 32;
+      }
+      if (lane == 0) status[tile] = look_pack(kFlagInclusive, Op::apply(prefix, aggregate));
+    }
+    if (lane == 0) prefix_s = prefix;
+  }
+  __syncthreads();
+  const uint32_t base_off = Op::apply(prefix_s, warp_off);
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    const uint32_t i = wbase + r * 128u + lane * 4u;
+    uint4 o;
+    o.x = Op::apply(base_off, Op::apply(chunk_off[r], excl[r]));
+    o.y = Op::apply(o.x, v[r].x);
+    o.z = Op::apply(o.y, v[r].y);
+    o.w = Op::apply(o.z, v[r].z);
+    if (i + 3u < len) {
+      *reinterpret_cast<uint4*>(data + i) = o;
+    } else {
+      if (i < len) data[i] = o.x;
+      if (i + 1u < len) data[i + 1u] = o.y;
+      if (i + 2u < len) data[i + 2u] = o.z;
+    }
+  }
+}
+
+int g_scan_one_pass = 1;  // process-wide: sphb_set_option("scan", 0) selects the three-kernel scan
+
+template <typename Op>
+int scan_in_place(uint32_t* data, uint32_t len, uint32_t* scratch, cudaStream_t s) {
+  // (the one-pass kernel wants 16-byte aligned data and 8-byte aligned scratch: cudaMalloc'ed bases are)
+  if (!g_scan_one_pass || len <= (uint32_t)kLookTile || ((uintptr_t)data & 15u) || ((uintptr_t)scratch & 7u))
+    return exclusive_scan<Op>(data, len, scratch, s);
+  const uint32_t tiles = (len + kLookTile - 1) / kLookTile;
+  cudaMemsetAsync(scratch, 0, sizeof(unsigned long long) * ((size_t)tiles + 1), s);
+  unsigned long long* status = reinterpret_cast<unsigned long long*>(scratch);
+  k_scan_lookback<Op><<<tiles, kThreads, 0, s>>>(data, len, status, reinterpret_cast<uint32_t*>(status + tiles));
+  return 1;
+}
+
 inline uint32_t tiles_for(uint32_t n) { return (n + kTile - 1) / kTile; }
 
 }  // namespace
+
+void set_scan_variant(int one_pass) { g_scan_one_pass = one_pass != 0; }
 
 size_t sort_hist_entries(uint32_t n) { return (size_t)256 * (tiles_for(n) ? tiles_for(n) : 1); }
 size_t sort_block_sum_entries(uint32_t n) {
   return (sort_hist_entries(n) + kScanTile - 1) / kScanTile;
 }
 
-size_t scan_scratch_entries(size_t len) { return (len + kScanTile - 1) / kScanTile + 1; }
+// the three-kernel scan's CTA totals, or the one-pass scan's 64-bit status words + ticket
+size_t scan_scratch_entries(size_t len) {
+  const size_t three = (len + kScanTile - 1) / kScanTile + 1;
+  const size_t one = 2 * ((len + kLookTile - 1) / kLookTile + 2);
+  return three > one ? three : one;
+}
 int launch_exclusive_sum(uint32_t* data, uint32_t len, uint32_t* scratch, cudaStream_t s) {
-  return exclusive_scan<OpSum>(data, len, scratch, s);
+  return scan_in_place<OpSum>(data, len, scratch, s);
 }
 int launch_exclusive_max(uint32_t* data, uint32_t len, uint32_t* scratch, cudaStream_t s) {
-  return exclusive_scan<OpMax>(data, len, scratch, s);
+  return scan_in_place<OpMax>(data, len, scratch, s);
 }
 
 int launch_sort_pairs(const SortBuffers& b, uint32_t n, int key_bits, int* result, cudaStream_t s) {

@@ -72,6 +72,34 @@ def test_dam_break_1m_one_step(port_oracle, tmp_path):
     run_reseeded(port_oracle, case, 1, "1M dam break")
 
 
+@pytest.mark.parametrize("mode", ["step", "frame"])
+def test_scan_variants_are_bit_identical(tmp_path, mode):
+    """The cell tables' prefix scans — one pass with decoupled look-back (default) and the
+    three-kernel scan (`sphb_set_option("scan", 0)`) — over tables of some hundred tiles: the same
+    permutation, cell table and particles, bit for bit, stepping from the host and from the device
+    (captured graph), where the whole table capacity is scanned."""
+    case = make_case(tmp_path, "water", 262144)
+    got = []
+    for scan in (1, 0):
+        with new_engine(case) as e:
+            e.set_option("scan", scan)
+            e.upload(case["particles"])
+            dt = 1.0 / 600.0
+            if mode == "step":
+                for _ in range(3):
+                    dt = e.step(dt)
+            else:
+                e.set_option("device_loop", 1)
+                e.set_option("graph", 1)
+                dt, _, done = e.run_frame(dt, 1.0, 3)
+                assert done == 3
+            dbg = e.debug()
+            got.append((np.float32(dt).tobytes(), e.download().tobytes(), dbg["perm"].tobytes(),
+                        dbg["cell_table"].tobytes(), dbg["keys"].tobytes()))
+            e.set_option("scan", 1)
+    assert got[0] == got[1]
+
+
 def sample_density(pos, keys, table, ncell, h, mass, poly6, idx):
     """float64 density of particles idx from the 27 cells around each (cell side 2h)."""
     from libclsph_b200 import engine  # noqa: F401  (layout only)

@@ -18,7 +18,10 @@ def main():
     legs = [("host", dict(device_loop=0, side_stream=1)), ("host_noside", dict(device_loop=0, side_stream=0)),
             ("queue", dict(device_loop=1, graph=0, side_stream=1)),
             ("graph", dict(device_loop=1, graph=1, side_stream=1)),
-            ("graph_noside", dict(device_loop=1, graph=1, side_stream=0))]
+            ("graph_noside", dict(device_loop=1, graph=1, side_stream=0)),
+            ("host_scan3", dict(device_loop=0, side_stream=1, scan=0)),
+            ("graph_scan3", dict(device_loop=1, graph=1, side_stream=1, scan=0))]
+    legs = [(k, dict(dict(scan=1), **v)) for k, v in legs]  # (scan: process-wide, so every leg sets it)
     if os.environ.get("AB_LEGS"):
         legs = [(k, v) for k, v in legs if k in os.environ["AB_LEGS"].split(",")]
     out = {}
