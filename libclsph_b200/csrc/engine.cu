@@ -297,6 +297,15 @@ int sphb_set_scene(sphb_engine* e, const sphb_bb* bbs, uint32_t face_count, cons
   float* d_rv = nullptr;
   uint32_t* d_cs = nullptr;
   uint32_t* d_cf = nullptr;
+  cudaEvent_t t0 = nullptr, t1 = nullptr;
+  struct Temporaries {  // released on every way out, the error returns of CUDA_TRY included
+    float*& tr; float*& rv; uint32_t*& cs; uint32_t*& cf; cudaEvent_t& a; cudaEvent_t& b;
+    ~Temporaries() {
+      cudaFree(tr); cudaFree(rv); cudaFree(cs); cudaFree(cf);
+      if (a) cudaEventDestroy(a);
+      if (b) cudaEventDestroy(b);
+    }
+  } temporaries = {d_tr, d_rv, d_cs, d_cf, t0, t1};
   e->df_build_ms = 0.f;
   if (face_count) {
     CUDA_TRY(e, cudaMemcpyAsync(e->faces, faces.data(), sizeof(Face) * face_count,
@@ -314,7 +323,9 @@ int sphb_set_scene(sphb_engine* e, const sphb_bb* bbs, uint32_t face_count, cons
     // can land a few ulps outside [min, max]; the margin covers that, and a face let in by it
     // merely fails the per-point test the kernel still makes.  Ascending order = the
     // reference's loop order (:70), so ties resolve as they do there.
-    if (e->df_face_lists && face_count > 1) {
+    // (built on the host by comparing every pair of boxes: 1.6 M pairs for the reference's
+    // largest scene; past 32 768 faces — 10^9 pairs — the kernel walks all faces instead)
+    if (e->df_face_lists && face_count > 1 && face_count <= 32768u) {
       std::vector<uint32_t> cstart(face_count + 1, 0), cfaces;
       for (uint32_t o = 0; o < face_count; ++o) {
         const sphb_bb& a = bbs[o];
@@ -337,7 +348,6 @@ int sphb_set_scene(sphb_engine* e, const sphb_bb* bbs, uint32_t face_count, cons
                                   cudaMemcpyHostToDevice, e->stream));
       // (pageable sources: both copies have been staged when the calls return)
     }
-    cudaEvent_t t0 = nullptr, t1 = nullptr;
     CUDA_TRY(e, cudaEventCreate(&t0));
     CUDA_TRY(e, cudaEventCreate(&t1));
     CUDA_TRY(e, cudaEventRecord(t0, e->stream));
@@ -347,14 +357,8 @@ int sphb_set_scene(sphb_engine* e, const sphb_bb* bbs, uint32_t face_count, cons
     CUDA_TRY(e, cudaEventRecord(t1, e->stream));
     CUDA_TRY(e, cudaEventSynchronize(t1));
     CUDA_TRY(e, cudaEventElapsedTime(&e->df_build_ms, t0, t1));
-    cudaEventDestroy(t0);
-    cudaEventDestroy(t1);
   }
   CUDA_TRY(e, cudaStreamSynchronize(e->stream));
-  cudaFree(d_tr);
-  cudaFree(d_rv);
-  cudaFree(d_cs);
-  cudaFree(d_cf);
   if (int rc = build_face_bin(e, bbs, face_count)) return rc;
   e->have_scene = true;
   return 0;
