@@ -291,16 +291,19 @@ int launch_exclusive_max(uint32_t* data, uint32_t len, uint32_t* scratch, cudaSt
 
 // kernels_neighbors.cu (compiled with FMA contraction on; tolerance-checked)
 // keys = compute-ordered fine keys, ftable = fine cell table (nfine + 1 entries).
-// variant 0: the density pass records a neighbour list (nlist: neighbor_list_entries(n) u16,
-// ncount: n u8) that the forces pass consumes; variant 1: both passes search on their own.
-size_t neighbor_list_entries(uint32_t n);
+// variant 0: the density pass records ONE neighbour list per pair of consecutive particles in
+// `pool` (neighbor_pool_words(n, cap) 32-bit words, cap = neighbor_list_cap(...) entries per
+// pair) that the forces pass consumes; variant 1: the forces pass searches on its own;
+// variant 2: the round-1 kernels (one list per particle), kept for A/B.
+size_t neighbor_pool_words(uint32_t n, uint32_t cap);
+uint32_t neighbor_list_cap(float h, float rho0, float mass);
 int launch_density(float4* pos, float4* vel, const uint32_t* keys, const uint32_t* ftable,
-                   float* rho, float* prs, uint16_t* nlist, uint8_t* ncount, const StepConsts& c,
+                   float* rho, float* prs, uint32_t* pool, uint32_t cap, const StepConsts& c,
                    int variant, cudaStream_t s, bool queued = false);
 int launch_forces(const float4* pos, const float4* vel, const uint32_t* keys,
-                  const uint32_t* ftable, const float* rho, const uint16_t* nlist,
-                  const uint8_t* ncount, float4* acc, const StepConsts& c, int variant,
-                  cudaStream_t s, const uint32_t* ghost_ids = nullptr, bool queued = false);
+                  const uint32_t* ftable, const float* rho, const uint32_t* pool, float4* acc,
+                  const StepConsts& c, int variant, cudaStream_t s,
+                  const uint32_t* ghost_ids = nullptr, bool queued = false);
 
 // kernels_slab.cu — the slab-decomposed (multi-GPU) step
 size_t slab_message_bytes(uint32_t record_capacity);

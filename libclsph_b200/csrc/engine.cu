@@ -54,7 +54,7 @@ int sphb_destroy(sphb_engine* e) {
   cudaFree(e->acc); cudaFree(e->rho); cudaFree(e->prs);
   cudaFree(e->sortb.hist); cudaFree(e->sortb.block_sums);
   cudaFree(e->rank_cur); cudaFree(e->rank_prev); cudaFree(e->ckey);
-  cudaFree(e->nlist); cudaFree(e->ncount);
+  cudaFree(e->npool);
   cudaFree(e->n_owned_dev); cudaFree(e->counters); cudaFree(e->src_of);
   if (e->host_counts) cudaFreeHost(e->host_counts);
   cudaFree(e->ftable); cudaFree(e->ref_table); cudaFree(e->scan_scratch); cudaFree(e->aos_stage);
@@ -151,8 +151,8 @@ int sphb_create_with_capacity(const sphb_params* params, const sphb_terms* terms
   TRY_OR_DESTROY(dev_alloc(&e->rank_cur, n));
   TRY_OR_DESTROY(dev_alloc(&e->rank_prev, n));
   TRY_OR_DESTROY(dev_alloc(&e->ckey, n));
-  TRY_OR_DESTROY(dev_alloc(&e->nlist, neighbor_list_entries(n)));
-  TRY_OR_DESTROY(dev_alloc(&e->ncount, n));
+  e->list_cap = neighbor_list_cap(params->h, params->fluid_density, params->particle_mass);
+  TRY_OR_DESTROY(dev_alloc(&e->npool, neighbor_pool_words(n, e->list_cap)));
   TRY_OR_DESTROY(dev_alloc(&e->acc, n));
   TRY_OR_DESTROY(dev_alloc(&e->rho, n));
   TRY_OR_DESTROY(dev_alloc(&e->prs, n));
@@ -492,9 +492,9 @@ int enqueue_queued_step(sphb_engine* e) {
   l += launch_reference_rank(skeys, e->ftable, e->rank_prev, e->ref_table, e->ckey, e->rank_cur, c,
                              e->scan_scratch, rs, true, e->ref_table_cap);
   if (e->use_side_stream) CUDA_TRY(e, cudaEventRecord(e->ev_join, e->side));
-  l += launch_density(e->pos[mid], e->vel[mid], skeys, e->ftable, e->rho, e->prs, e->nlist, e->ncount, c,
+  l += launch_density(e->pos[mid], e->vel[mid], skeys, e->ftable, e->rho, e->prs, e->npool, e->list_cap, c,
                       e->neighbor_variant, s, true);
-  l += launch_forces(e->pos[mid], e->vel[mid], skeys, e->ftable, e->rho, e->nlist, e->ncount, e->acc, c,
+  l += launch_forces(e->pos[mid], e->vel[mid], skeys, e->ftable, e->rho, e->npool, e->acc, c,
                      e->neighbor_variant, s, nullptr, true);
   if (e->use_side_stream) CUDA_TRY(e, cudaStreamWaitEvent(s, e->ev_join, 0));
   for (int a = 0; a < e->queued_attempts; ++a) {
@@ -713,12 +713,12 @@ int sphb_step(sphb_engine* e, float dt_in, float* dt_out) {
   {
     PassTimer t(e, SPHB_PASS_DENSITY);
     t.done(launch_density(e->pos[e->cur], e->vel[e->cur], skeys, e->ftable, e->rho,
-                          e->prs, e->nlist, e->ncount, c, e->neighbor_variant, s));
+                          e->prs, e->npool, e->list_cap, c, e->neighbor_variant, s));
   }
   {
     PassTimer t(e, SPHB_PASS_FORCES);
     t.done(launch_forces(e->pos[e->cur], e->vel[e->cur], skeys, e->ftable, e->rho,
-                         e->nlist, e->ncount, e->acc, c, e->neighbor_variant, s));
+                         e->npool, e->acc, c, e->neighbor_variant, s));
   }
   if (e->use_side_stream) CUDA_TRY(e, cudaStreamWaitEvent(s, e->ev_join, 0));
   CUDA_TRY(e, cudaGetLastError());

@@ -90,8 +90,8 @@ struct sphb_engine {
   uint32_t* rank_cur = nullptr;
   uint32_t* rank_prev = nullptr;
   uint32_t* ckey = nullptr;
-  uint16_t* nlist = nullptr;  // neighbour codes recorded by the density pass, k-major
-  uint8_t* ncount = nullptr;
+  uint32_t* npool = nullptr;  // neighbour lists recorded by the density pass (kernels_neighbors.cu)
+  uint32_t list_cap = 64;     // entries a pair's list has room for
   uint32_t* ftable = nullptr;     // fine cell table, nfine + 1 entries
   size_t ftable_cap = 0;
   uint32_t* ref_table = nullptr;  // the reference's cell table, grid_cell_count (+1) entries

@@ -5,14 +5,26 @@
 // every particle, the 27 cells of side 2h around its own cell, although the smoothing
 // kernels vanish beyond h: ~1000 candidate pairs per particle for ~20-40 true neighbours.
 // A pair with r >= h contributes exactly zero to every sum, so the kernels here (a) search a
-// grid of side h instead — 27 cells of side h hold ~130 candidates — and (b) skip pairs with
-// r >= h before doing any work on them; results are unchanged up to summation order.
+// grid of side h instead and (b) skip pairs with r >= h before doing any work on them; results
+// are unchanged up to summation order.
 //
 // Particles are sorted by the row-major index of their fine cell — side h in y and z, h / kXSub
 // along x (common.cuh) — so the x-adjacent cells of each of the 9 (dy, dz) rows are ONE contiguous
 // run [ftable[row + first], ftable[row + last + 1]), and that run is trimmed to the chord of the
-// support sphere at the row (row_reach below): ~70 candidates per particle at kXSub = 4 instead
-// of the ~100 of whole cells of side h.
+// support sphere at the row (row_reach): ~70 candidates per particle at kXSub = 4.
+//
+// BOTH passes give one thread a PAIR of consecutive particles (2t, 2t + 1).  Two particles that
+// are neighbours in the sorted array sit in the same row of cells a few sub-cells apart, so their
+// candidate runs and their neighbour sets largely coincide:
+//   * the density pass walks the UNION of the two particles' runs once — every 16-byte candidate
+//     load serves two distance tests, done together in packed fp32x2 arithmetic — and records
+//     ONE list per pair: the candidates that are inside h of either particle;
+//   * the forces pass evaluates every listed neighbour against both particles at once, again in
+//     packed fp32x2 arithmetic, with (h - r) and (h^2 - r^2) clamped at zero so that a neighbour
+//     of only one of the two contributes exactly nothing to the other.
+// A pair that straddles two rows (or sits far apart in one) is "split": the thread walks each
+// particle's own rows in turn (row ids 0-8, then 9-17), and the list says where the second part
+// begins.
 //
 // This translation unit is compiled with FMA contraction ON and uses rsqrt for 1/r; it is
 // checked against the CPU oracle to a stated tolerance (tests/test_gpu_parity.py), unlike
@@ -27,175 +39,86 @@ namespace sphb {
 
 namespace {
 
-constexpr int kBlock = 128;
+#include "neighbors_common.cuh"
+#include "neighbors_v1.cuh"
 
-// device-driven stepping (common.cuh: QueueCtl): see kernels_exact.cu
-__constant__ QueueHot g_hot;
+// ---- the pair list --------------------------------------------------------------------------
+// One pool of 32-bit words per engine, addressed by pair index t = i / 2 with np = ceil(n / 2):
+//   meta[t]                  bits 0-7 entries of the first part, 8-15 entries in all, bit 31 =
+//                            "list unusable" (it overflowed: the forces pass searches itself)
+//   start[r * np + t]        first particle of the run walked for row id r (0-8; 9-17 for the
+//                            second part of a split pair — written only then)
+//   codes[(k / 2) * np + t]  entries k and k + 1 as two 16-bit codes: row id << 11 | offset in
+//                            that row's run; kNullCode pads every part to a multiple of 4
+// Everything is laid out pair-minor, so the warp's stores and the forces pass's loads coalesce.
+constexpr int kUB = 64;                              // threads per CTA (128 particles)
+constexpr uint32_t kRowShift = 11;
+constexpr uint32_t kOffMask = (1u << kRowShift) - 1u;
+constexpr uint32_t kNullCode = kOffMask;             // row 0, offset 2047: never recorded
+constexpr uint32_t kMaxRun = kOffMask;               // a longer run cannot be coded: unusable
+constexpr uint32_t kSpanTogether = 2u * kXSub;       // sub-cells two particles may be apart (2h)
+constexpr uint32_t kUDump = 8;                       // rows past the capacity that absorb hits
+constexpr uint32_t kUStride = 2u * kUB;              // bytes between two rows of the hit columns
+constexpr uint32_t kMetaUnusable = 0x80000000u;
+constexpr uint32_t kStartRows = 18;
 
-// Tait equation, sphb.cl:32-34: K * ((rho/rho0)^7 - 1), pown as repeated multiplication
-__device__ __forceinline__ float tait_pressure(float rho, const StepConsts& c) {
-  const float q = rho / c.rho0;
-  float q7 = q;
-#pragma unroll
-  for (int k = 1; k < 7; ++k) q7 = q7 * q;
-  return c.K * (q7 - 1.f);
-}
-
-__device__ __forceinline__ void fine_coords_of(uint32_t key, const StepConsts& c, uint32_t& fx,
-                                               uint32_t& fy, uint32_t& fz) {
-  fx = key % c.fnx;
-  const uint32_t t = key / c.fnx;
-  fy = t % c.fny;
-  fz = t / c.fny;
-}
-
-// Where a particle sits inside its fine cell in y and z, in units of h: lo = distance to the
-// cell's lower face, hi = distance to its upper face (both clamped to [0, 1]); ux = its x
-// coordinate in units of the x sub-cell (h / kXSub), from the grid origin.
-struct CellFrac {
-  float lo[3], hi[3];
-  float ux;
+struct PairLists {
+  uint32_t* meta;
+  uint32_t* start;
+  uint32_t* codes;
+  uint32_t np;
 };
-__device__ __forceinline__ CellFrac cell_frac(const float4& p, uint32_t fx, uint32_t fy, uint32_t fz,
-                                              const StepConsts& c) {
-  CellFrac f;
-  const float inv_h = 1.f / c.h;
-  (void)fx;
-  const float u[3] = {0.f, (p.y - c.miny) * inv_h - (float)fy, (p.z - c.minz) * inv_h - (float)fz};
-#pragma unroll
-  for (int a = 0; a < 3; ++a) {
-    f.lo[a] = fminf(fmaxf(u[a], 0.f), 1.f);
-    f.hi[a] = 1.f - f.lo[a];
-  }
-  f.ux = (p.x - c.minx) * (inv_h * (float)kXSub);
-  return f;
+__host__ __device__ inline PairLists pair_lists(uint32_t* pool, uint32_t n) {
+  PairLists L;
+  L.np = (n + 1u) >> 1;
+  L.meta = pool;
+  L.start = pool + L.np;
+  L.codes = L.start + (size_t)kStartRows * L.np;
+  return L;
 }
 
-// Which x sub-cells of row (fy + dy, fz + dz) can hold a neighbour of a particle at `f` inside
-// cell (fx, fy, fz): the row is visited only if its nearest line is closer than h, and then only
-// over the chord of the support sphere at that distance, [x - w, x + w] with
-// w = sqrt(h^2 - gy^2 - gz^2), rounded out to whole sub-cells.  The radius carries a slack, so
-// that rounding in this arithmetic (or in the sub-cell a candidate was sorted into) can only add
-// candidates, never lose a pair with r < h.
-constexpr float kReach2 = 1.0f + 1.0e-3f;  // (h * (1 + slack))^2 in units of h^2
-struct Reach {
-  bool on;
-  uint32_t lo, hi;  // first / last sub-cell (inclusive); always lo <= fx <= hi
-};
-__device__ __forceinline__ Reach row_reach(const StepConsts& c, uint32_t fx, const CellFrac& f, int dy,
-                                           int dz) {
-  const float gy = dy < 0 ? f.lo[1] : (dy > 0 ? f.hi[1] : 0.f);
-  const float gz = dz < 0 ? f.lo[2] : (dz > 0 ? f.hi[2] : 0.f);
-  const float q = gy * gy + gz * gz;
-  Reach r;
-  r.on = q < kReach2;
-  const float w = sqrtf(fmaxf(kReach2 - q, 0.f)) * (float)kXSub;
-  // float -> unsigned conversion saturates at 0 for negatives and NaN
-  r.lo = min((uint32_t)fmaxf(f.ux - w, 0.f), fx);
-  r.hi = min(max((uint32_t)fmaxf(f.ux + w, 0.f), fx), c.fnx - 1u);
-  return r;
-}
+__device__ __forceinline__ float2 bcast2(float v) { return make_float2(v, v); }
 
-// First / one-past-last particle of that run; an empty range when nothing in the row can be.
-__device__ __forceinline__ void row_range(const uint32_t* __restrict__ ftable, const StepConsts& c,
-                                          uint32_t fx, uint32_t fy, uint32_t fz, const CellFrac& f,
-                                          int dy, int dz, uint32_t& s, uint32_t& e) {
-  s = e = 0;
-  const uint32_t y = fy + dy, z = fz + dz;  // wraps to a huge value below 0
-  if (y >= c.fny || z >= c.fnz) return;
-  const Reach r = row_reach(c, fx, f, dy, dz);
-  if (!r.on) return;
-  const uint32_t row = (z * c.fny + y) * c.fnx;
-  s = __ldg(ftable + row + r.lo);
-  e = __ldg(ftable + row + r.hi + 1u);
-}
-
-// ---- density + pressure: one thread per PAIR of consecutive particles, walking the 9 rows ----
-// Two particles that are neighbours in the sorted array sit in the same or in x-adjacent cells
-// four times out of five, so their candidate runs coincide: one thread tests every candidate
-// against both, which halves the 16-byte candidate loads (the pass is bound by L1 wavefronts
-// and issue slots, not by HBM).  A pair that is NOT in the same row / adjacent cells is walked
-// in two passes, one particle at a time (the idle one is given a NaN position, which fails
-// every distance test).
-//
-// Besides the density sum, the pass RECORDS which candidates were inside h, so that the forces
-// pass does not have to search again: a neighbour is stored as a 16-bit code
-// (row 0..8) << 12 | (offset of the neighbour inside the run that was walked for that row),
-// staged per particle in a shared-memory column and flushed k-major (nlist[k * n + i]) so that
-// the stores — and the forces pass's loads — are coalesced across the warp.  Where the walked
-// run began is recorded as kBackBits bits per row (nback: own sub-cell x - first sub-cell x).  count 255 =
-// "list unusable" (more than kListCap neighbours, or a run longer than 4096): the forces pass
-// then searches itself.
-// Where a walked run began is recorded per row as (own sub-cell - first sub-cell) in kBackBits
-// bits: at most kTogether (the partner's lead) + kXSub + 1 (the chord, rounded out).
-constexpr uint32_t kTogether = kXSub >= 2 ? 2u : 1u;  // sub-cells two particles of a thread may be apart
-constexpr uint32_t kBackBits = 3;
-static_assert(kTogether + kXSub + 1u < (1u << kBackBits), "run starts do not fit their bit field");
-constexpr int kListCap = 64;
-constexpr uint32_t kListOverflow = 255;
-constexpr int kPairBlock = 64;                  // threads per CTA; 2 particles each
-constexpr int kPairCols = 2 * kPairBlock;       // shared-memory columns (one per particle)
-constexpr int kDumpRows = 4;                    // rows past the capacity that absorb a group's hits
-constexpr uint32_t kColStride = 2u * kPairCols; // bytes between two entries of a column
-
-__device__ __forceinline__ uint32_t* nback_of(const uint16_t* nlist, uint32_t n) {
-  return reinterpret_cast<uint32_t*>(const_cast<uint16_t*>(nlist) + (size_t)kListCap * n);
-}
-
-// One candidate against the thread's TWO particles at once, in packed fp32x2 arithmetic (FADD2 /
-// FFMA2 / FMUL2: Blackwell's fp32 pipe retires two lanes per instruction only in this form; the
-// candidate's coordinates enter as broadcast scalar operands).  u = r^2 - h^2 per particle, then,
-// where u < 0: sum += u^3 (the caller negates the total), a predicated store of the code and the
-// cursor's advance — one predicate per particle drives all three (NaN compares false).
-__device__ __forceinline__ uint64_t pack2(float lo, float hi) {
-  uint64_t r;
-  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
-  return r;
-}
-__device__ __forceinline__ void density_test2(uint64_t qx, uint64_t qy, uint64_t qz, uint64_t neg_h2,
-                                              const float4& pj, float& sum_a, float& sum_b,
-                                              uint32_t& cur_a, uint32_t& cur_b, uint32_t code) {
+// One candidate against the thread's TWO particles at once (FADD2 / FFMA2 / FMUL2 with the
+// candidate's coordinates as broadcast operands).  u = r^2 - h^2 per particle; where u < 0 the
+// particle's sum takes u^3 (the caller negates the total), and where either is, the candidate's
+// code goes to the pair's list: a predicated store at a cursor that advances only on hits.
+__device__ __forceinline__ void density_test_union(const float2& qx, const float2& qy, const float2& qz,
+                                                   float neg_h2, const float4& pj, float& sum_a, float& sum_b,
+                                                   uint32_t& cur, uint32_t code) {
+  const float2 dx = __fadd2_rn(qx, bcast2(-pj.x));
+  const float2 dy = __fadd2_rn(qy, bcast2(-pj.y));
+  const float2 dz = __fadd2_rn(qz, bcast2(-pj.z));
+  float2 u = __ffma2_rn(dx, dx, bcast2(neg_h2));
+  u = __ffma2_rn(dy, dy, u);
+  u = __ffma2_rn(dz, dz, u);
+  const float2 u2 = __fmul2_rn(u, u);
   asm volatile(
-      "{ .reg .b64 bx, by, bz, dx, dy, dz, u, u2;\n"
-      "  .reg .f32 ua, ub, va, vb;\n"
-      "  .reg .pred pa, pb;\n"
-      "  mov.b64 bx, {%9, %9};\n"
-      "  mov.b64 by, {%10, %10};\n"
-      "  mov.b64 bz, {%11, %11};\n"
-      "  sub.rn.f32x2 dx, %5, bx;\n"
-      "  sub.rn.f32x2 dy, %6, by;\n"
-      "  sub.rn.f32x2 dz, %7, bz;\n"
-      "  fma.rn.f32x2 u, dx, dx, %8;\n"
-      "  fma.rn.f32x2 u, dy, dy, u;\n"
-      "  fma.rn.f32x2 u, dz, dz, u;\n"
-      "  mul.rn.f32x2 u2, u, u;\n"
-      "  mov.b64 {ua, ub}, u;\n"
-      "  mov.b64 {va, vb}, u2;\n"
-      "  setp.lt.f32 pa, ua, 0f00000000;\n"
-      "  setp.lt.f32 pb, ub, 0f00000000;\n"
-      "  @pa fma.rn.f32 %0, va, ua, %0;\n"
-      "  @pb fma.rn.f32 %1, vb, ub, %1;\n"
-      "  @pa st.shared.u16 [%2], %4;\n"
-      "  @pb st.shared.u16 [%3], %4;\n"
-      "  @pa add.u32 %2, %2, %12;\n"
-      "  @pb add.u32 %3, %3, %12; }"
-      : "+f"(sum_a), "+f"(sum_b), "+r"(cur_a), "+r"(cur_b)
-      : "h"((uint16_t)code), "l"(qx), "l"(qy), "l"(qz), "l"(neg_h2), "f"(pj.x), "f"(pj.y), "f"(pj.z),
-        "n"(kColStride)
+      "{ .reg .pred pa, pb, pc;\n"
+      "  setp.lt.f32 pa, %3, 0f00000000;\n"
+      "  setp.lt.f32 pb, %4, 0f00000000;\n"
+      "  @pa fma.rn.f32 %0, %5, %3, %0;\n"
+      "  @pb fma.rn.f32 %1, %6, %4, %1;\n"
+      "  or.pred pc, pa, pb;\n"
+      "  @pc st.shared.u16 [%2], %7;\n"
+      "  @pc add.u32 %2, %2, %8; }"
+      : "+f"(sum_a), "+f"(sum_b), "+r"(cur)
+      : "f"(u.x), "f"(u.y), "f"(u2.x), "f"(u2.y), "h"((uint16_t)code), "n"(kUStride)
       : "memory");
 }
 
 template <bool Q>
-__global__ void __launch_bounds__(kPairBlock)
-    k_density_pair(float4* pos, float4* vel, const uint32_t* __restrict__ keys,
-                   const uint32_t* __restrict__ ftable, float* __restrict__ rho,
-                   float* __restrict__ prs, uint16_t* __restrict__ nlist,
-                   uint8_t* __restrict__ ncount, StepConsts c_arg) {
+__global__ void __launch_bounds__(kUB)
+    k_density_union(float4* pos, float4* vel, const uint32_t* __restrict__ keys,
+                    const uint32_t* __restrict__ ftable, float* __restrict__ rho, float* __restrict__ prs,
+                    uint32_t* __restrict__ pool, uint32_t cap, StepConsts c_arg) {
   if (Q && !g_hot.active) return;
   const StepConsts& c = Q ? g_hot.c : c_arg;
-  __shared__ uint16_t hit[(kListCap + kDumpRows) * kPairCols];
-  const uint32_t ia = 2u * (blockIdx.x * kPairBlock + threadIdx.x);
+  extern __shared__ uint16_t hit[];  // (cap + kUDump) rows of kUB columns
+  const uint32_t t = blockIdx.x * kUB + threadIdx.x;
+  const uint32_t ia = 2u * t;
   if (ia >= c.n) return;
+  const PairLists L = pair_lists(pool, c.n);
   const bool has_b = ia + 1 < c.n;
   const uint32_t ib = has_b ? ia + 1 : ia;
   const float4 pa = pos[ia], pb = pos[ib];
@@ -204,28 +127,27 @@ __global__ void __launch_bounds__(kPairBlock)
   fine_coords_of(__ldg(keys + ib), c, fxb, fyb, fzb);
   const CellFrac fa = cell_frac(pa, fxa, fya, fza, c), fb = cell_frac(pb, fxb, fyb, fzb, c);
   // sorted by row-major cell: inside a row, b's cell is never left of a's
-  const bool together = has_b && fya == fyb && fza == fzb && fxb - fxa <= kTogether;
-  const int npass = (has_b && !together) ? 2 : 1;
+  const bool split = has_b && !(fya == fyb && fza == fzb && fxb - fxa <= kSpanTogether);
+  const int npass = split ? 2 : 1;
   const float nan = __int_as_float(0x7fc00000);
-  const float4 nowhere = make_float4(nan, nan, nan, 0.f);
+  const float4 nowhere = make_float4(nan, nan, nan, 0.f);  // fails every distance test
 
   // (shared-window byte addresses, so that a store is one predicated STS)
-  const uint32_t base_a = (uint32_t)__cvta_generic_to_shared(hit) + 4u * threadIdx.x, base_b = base_a + 2u;
-  const uint32_t end_a = base_a + kListCap * kColStride, end_b = base_b + kListCap * kColStride;
-  uint32_t cur_a = base_a, cur_b = base_b, back_a = 0, back_b = 0;
+  const uint32_t base = (uint32_t)__cvta_generic_to_shared(hit) + 2u * threadIdx.x;
+  const uint32_t end = base + cap * kUStride;
+  uint32_t cur = base, cnt_a = 0;
   float sum_a = 0.f, sum_b = 0.f;
-  bool overflow = false;
+  bool unusable = false;
   const float4* cand = reinterpret_cast<const float4*>(pos);
 #pragma unroll 1
   for (int pass = 0; pass < npass; ++pass) {
-    const bool la = pass == 0, lb = together || pass == 1;
+    const bool la = pass == 0, lb = has_b && (split ? pass == 1 : true);
     const float4 qa = la ? pa : nowhere, qb = lb ? pb : nowhere;
-    const uint64_t qx = pack2(qa.x, qb.x), qy = pack2(qa.y, qb.y), qz = pack2(qa.z, qb.z);
-    const uint64_t neg_h2 = pack2(-c.h2, -c.h2);
+    const float2 qx = make_float2(qa.x, qb.x), qy = make_float2(qa.y, qb.y), qz = make_float2(qa.z, qb.z);
     const uint32_t ry = la ? fya : fyb, rz = la ? fza : fzb;
-    uint32_t tag = 0, shift = 0;
+    uint32_t rowid = 9u * pass;
 #pragma unroll 1
-    for (int dz = -1; dz <= 1; ++dz, tag += 3u * 4096u, shift += 3u * kBackBits) {
+    for (int dz = -1; dz <= 1; ++dz, rowid += 3u) {
       const uint32_t z = rz + dz;  // wraps to a huge value below 0
       if (z >= c.fnz) continue;
       // the three rows of this plane are planned together, so that their six table loads
@@ -244,44 +166,44 @@ __global__ void __launch_bounds__(kPairBlock)
           const uint32_t rowbase = (z * c.fny + y) * c.fnx;
           rs[k] = __ldg(ftable + rowbase + x_lo);
           re[k] = __ldg(ftable + rowbase + x_hi);
-          // (a particle that cannot reach the row records nothing there: the union's start may
-          // lie beyond its own sub-cell)
-          if (ona) back_a |= (fxa - x_lo) << (shift + kBackBits * k);
-          if (onb) back_b |= (fxb - x_lo) << (shift + kBackBits * k);
         }
       }
 #pragma unroll
       for (int k = 0; k < 3; ++k) {
         const uint32_t e = re[k];
-        uint32_t j = rs[k], code = tag + 4096u * k;
-        if (e - j > 4096u) overflow = true;
-        // The loop body is branch-free: the cubic term is clamped instead of skipped, and a hit
-        // (the particle itself included — the forces pass skips it) is recorded with a
-        // predicated store at a cursor that advances only on hits; the cursors are pulled
-        // back into the dump rows once per group of four candidates.
+        uint32_t j = rs[k], code = (rowid + k) << kRowShift;
+        L.start[(size_t)(rowid + k) * L.np + t] = j;
+        if (e - j > kMaxRun) unusable = true;
+        // The loop body is branch-free; the cursor is pulled back into the dump rows once per
+        // group of four candidates.
         for (; j + 4u <= e; j += 4u, code += 4u) {
           const float4 p0 = __ldg(cand + j), p1 = __ldg(cand + j + 1), p2 = __ldg(cand + j + 2),
                        p3 = __ldg(cand + j + 3);
-          density_test2(qx, qy, qz, neg_h2, p0, sum_a, sum_b, cur_a, cur_b, code);
-          density_test2(qx, qy, qz, neg_h2, p1, sum_a, sum_b, cur_a, cur_b, code + 1u);
-          density_test2(qx, qy, qz, neg_h2, p2, sum_a, sum_b, cur_a, cur_b, code + 2u);
-          density_test2(qx, qy, qz, neg_h2, p3, sum_a, sum_b, cur_a, cur_b, code + 3u);
-          cur_a = min(cur_a, end_a);
-          cur_b = min(cur_b, end_b);
+          density_test_union(qx, qy, qz, -c.h2, p0, sum_a, sum_b, cur, code);
+          density_test_union(qx, qy, qz, -c.h2, p1, sum_a, sum_b, cur, code + 1u);
+          density_test_union(qx, qy, qz, -c.h2, p2, sum_a, sum_b, cur, code + 2u);
+          density_test_union(qx, qy, qz, -c.h2, p3, sum_a, sum_b, cur, code + 3u);
+          cur = min(cur, end);
         }
         for (; j < e; ++j, ++code) {
           const float4 p0 = __ldg(cand + j);
-          density_test2(qx, qy, qz, neg_h2, p0, sum_a, sum_b, cur_a, cur_b, code);
-          cur_a = min(cur_a, end_a);
-          cur_b = min(cur_b, end_b);
+          density_test_union(qx, qy, qz, -c.h2, p0, sum_a, sum_b, cur, code);
         }
+        cur = min(cur, end);
       }
     }
+    // every part ends on a multiple of four entries (the forces pass takes four per trip)
+#pragma unroll
+    for (int u = 0; u < 3; ++u)
+      if (((cur - base) / kUStride) & 3u) {
+        asm volatile("st.shared.u16 [%0], %1;" ::"r"(cur), "h"((uint16_t)kNullCode) : "memory");
+        cur += kUStride;
+      }
+    cur = min(cur, end);
+    if (pass == 0) cnt_a = (cur - base) / kUStride;
   }
-  uint32_t* const nback = nback_of(nlist, c.n);
-  const uint16_t* col = hit + 2 * threadIdx.x;
-  uint32_t cnt2[2];
-  bool over2[2];
+  const uint32_t cnt = (cur - base) / kUStride;
+  unusable = unusable || cnt >= cap;  // the dump rows were reached
 #pragma unroll
   for (int w = 0; w < 2; ++w) {
     if (w == 1 && !has_b) break;
@@ -293,244 +215,239 @@ __global__ void __launch_bounds__(kPairBlock)
     // derived per-particle factors for the forces pass (only the w lanes are written)
     reinterpret_cast<float*>(pos + i)[3] = pressure / (density * density);
     reinterpret_cast<float*>(vel + i)[3] = c.mass / density;
-    cnt2[w] = ((w ? cur_b : cur_a) - (w ? base_b : base_a)) / kColStride;
-    over2[w] = overflow || cnt2[w] >= (uint32_t)kListCap;  // the dump rows were reached
-    ncount[i] = over2[w] ? (uint8_t)kListOverflow : (uint8_t)cnt2[w];
-    nback[i] = w ? back_b : back_a;
   }
-  if (has_b && !over2[0] && !over2[1] && (c.n & 1u) == 0u) {
-    // both columns of the thread leave as one aligned 32-bit store per entry (entries past the
-    // shorter list's count are never read)
-    const uint32_t m = max(cnt2[0], cnt2[1]);
-    const uint32_t* col32 = reinterpret_cast<const uint32_t*>(col);
-    uint32_t* out = reinterpret_cast<uint32_t*>(nlist + ia);
-    for (uint32_t k = 0; k < m; ++k) out[(size_t)k * (c.n / 2u)] = col32[k * (kPairCols / 2)];
-  } else {
-#pragma unroll
-    for (int w = 0; w < 2; ++w) {
-      if ((w == 1 && !has_b) || over2[w]) continue;
-      const uint32_t i = w ? ib : ia;
-      for (uint32_t k = 0; k < cnt2[w]; ++k) nlist[(size_t)k * c.n + i] = col[k * kPairCols + w];
-    }
+  L.meta[t] = unusable ? kMetaUnusable : (cnt_a | (cnt << 8));
+  if (!unusable) {
+    const uint16_t* col = hit + threadIdx.x;
+    uint32_t* out = L.codes + t;
+    for (uint32_t k = 0; k < cnt; k += 2u)
+      out[(size_t)(k >> 1) * L.np] = (uint32_t)col[k * kUB] | ((uint32_t)col[(k + 1u) * kUB] << 16);
   }
 }
 
-struct ForceAcc {
-  float px, py, pz;  // sum (p_j/rho_j^2 + p_i/rho_i^2) (h-r)^2 (x_i-x_j)/r
-  float vx, vy, vz;  // sum (v_j - v_i) (m/rho_j) (h-r)
-  float nx, ny, nz;  // sum (m/rho_j) (h^2-r^2)^2 (x_i-x_j)
-  float lap;         // sum (m/rho_j) (h^2-r^2)(3h^2-7r^2)
-  float quirk;       // sum (p_j/rho_j^2 + p_i/rho_i^2) over pairs with r < 1e-7
+// ---- forces from the pair list ---------------------------------------------------------------
+struct ForceAcc2 {
+  float2 px, py, pz;  // lane x: particle a, lane y: particle b (sums as in ForceAcc)
+  float2 vx, vy, vz;
+  float2 nx, ny, nz;
+  float2 lap;
+  float quirk_a, quirk_b;
 };
 
-// One (i, j) pair with j != i and r^2 < h^2.
-__device__ __forceinline__ void force_pair(ForceAcc& A, const float4& pi, const float4& vi,
-                                           const float4& pj, const float4& vj, float dx, float dy,
-                                           float dz, float r2, const StepConsts& c) {
-  float r, inv_r;
-  bool quirk = false;
-  if (r2 < 2.0e-14f) {
-    // smoothing.cl:21-25: for |x_i - x_j| < 1e-7 spiky_gradient returns the SCALAR
-    // -45/(pi h^6) broadcast to xyz, ungated.  Decide with the reference's own test.
-    r = sqrtf(r2);
-    quirk = (r - 1.0e-7f < 0.f) && (0.f < r + 1.0e-7f);
-    inv_r = quirk ? 0.f : 1.f / r;
-  } else {
-    inv_r = rsqrtf(r2);
-    r = r2 * inv_r;
-  }
-  const float hr = c.h - r;
-  const float pp = pj.w + pi.w;
-  if (quirk) {
-    A.quirk += pp;
-  } else {
-    const float sp = pp * hr * hr * inv_r;
-    A.px += sp * dx; A.py += sp * dy; A.pz += sp * dz;
-  }
-  const float vw = vj.w * hr;
-  A.vx += (vj.x - vi.x) * vw; A.vy += (vj.y - vi.y) * vw; A.vz += (vj.z - vi.z) * vw;
-  const float t = c.h2 - r2;
-  const float nw = vj.w * t * t;
-  A.nx += nw * dx; A.ny += nw * dy; A.nz += nw * dz;
-  A.lap += vj.w * t * (3.f * c.h2 - 7.f * r2);
+__device__ __forceinline__ float rsqrt_fast(float x) {
+  float r;
+  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
 }
 
-// sphb.cl:108-122: combine the four sums into the acceleration.
-__device__ __forceinline__ float4 force_finish(const ForceAcc& A, float rho_i, float mrho_i,
-                                               const StepConsts& c) {
-  // the self pair contributes only to the colour-field laplacian (r = 0)
-  const float lap = c.c_poly6_lap * (A.lap + mrho_i * c.h2 * (3.f * c.h2));
-  const float ms = c.mass * c.c_spiky, mq = c.mass * c.spiky_eps * A.quirk;
-  const float prx = ms * A.px + mq, pry = ms * A.py + mq, prz = ms * A.pz + mq;
-  const float nx = c.c_poly6_grad * A.nx, ny = c.c_poly6_grad * A.ny, nz = c.c_poly6_grad * A.nz;
-  const float mv = c.mu * c.c_visc;
-  float sx = -rho_i * prx + mv * A.vx, sy = -rho_i * pry + mv * A.vy, sz = -rho_i * prz + mv * A.vz;
-  const float nl = sqrtf(nx * nx + ny * ny + nz * nz);
-  if (nl > c.st_threshold) {
-    const float k = -c.st * lap / nl;
-    sx += k * nx; sy += k * ny; sz += k * nz;
-  }
-  return make_float4(sx / rho_i + c.gx, sy / rho_i + c.gy, sz / rho_i + c.gz, 0.f);
-}
+struct PairQuery {
+  float2 x, y, z, w;     // positions, p/rho^2
+  float2 vx, vy, vz;     // velocities
+};
 
-// Forces in two loops per particle.  Loop A tests the ~100 candidates and only RECORDS the
-// ~20-40 with r < h in a per-thread column of shared memory; loop B then evaluates the pair
-// terms for recorded neighbours only.  In a single loop nearly every iteration has at least
-// one of the 32 lanes inside h, so the whole warp would pay for the ~45-instruction pair
-// evaluation on every candidate.
-constexpr int kHitCap = 40;
-__global__ void __launch_bounds__(kBlock)
-    k_forces_list(const float4* __restrict__ pos, const float4* __restrict__ vel,
-                  const uint32_t* __restrict__ keys, const uint32_t* __restrict__ ftable,
-                  const float* __restrict__ rho, float4* __restrict__ acc, StepConsts c) {
-  __shared__ uint32_t hit[kHitCap][kBlock];
-  const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
-  if (i >= c.n) return;
-  const float4 pi = __ldg(pos + i), vi = __ldg(vel + i);
-  uint32_t fx, fy, fz;
-  fine_coords_of(__ldg(keys + i), c, fx, fy, fz);
-  const CellFrac f = cell_frac(pi, fx, fy, fz, c);
-  ForceAcc A = {};
-  int cnt = 0;
-  auto drain = [&]() {
-    for (int k = 0; k < cnt; ++k) {
-      const uint32_t j = hit[k][threadIdx.x];
-      const float4 pj = __ldg(pos + j);
-      const float4 vj = __ldg(vel + j);
-      const float dx = pi.x - pj.x, dy_ = pi.y - pj.y, dz_ = pi.z - pj.z;
-      const float r2 = dx * dx + dy_ * dy_ + dz_ * dz_;
-      force_pair(A, pi, vi, pj, vj, dx, dy_, dz_, r2, c);
+// One listed neighbour j against both particles of the thread.  Nothing is skipped: a particle
+// with r >= h (and a masked one, parked at 1e18) gets (h - r) = (h^2 - r^2) = 0 and so exactly
+// zero from every term; the particle itself (r = 0) gets zero from the pressure, viscosity and
+// normal terms (x_i - x_j = v_j - v_i = 0) and its own term of the colour-field laplacian, which
+// the reference also sums (sphb.cl:95-106).
+__device__ __forceinline__ void force_pair2(ForceAcc2& A, const PairQuery& q, const float4& pj,
+                                            const float4& vj, uint32_t j, uint32_t ia, uint32_t ib,
+                                            const StepConsts& c) {
+  const float2 dx = __fadd2_rn(q.x, bcast2(-pj.x));
+  const float2 dy = __fadd2_rn(q.y, bcast2(-pj.y));
+  const float2 dz = __fadd2_rn(q.z, bcast2(-pj.z));
+  float2 r2 = __fmul2_rn(dx, dx);
+  r2 = __ffma2_rn(dy, dy, r2);
+  r2 = __ffma2_rn(dz, dz, r2);
+  const float2 r2c = make_float2(fmaxf(r2.x, 1.0e-30f), fmaxf(r2.y, 1.0e-30f));
+  float2 inv_r = make_float2(rsqrt_fast(r2c.x), rsqrt_fast(r2c.y));
+  const float2 pp = __fadd2_rn(q.w, bcast2(pj.w));
+  if (fminf(r2.x, r2.y) < 2.0e-14f) {
+    // smoothing.cl:21-25: for |x_i - x_j| < 1e-7 (and j != i) spiky_gradient returns the SCALAR
+    // -45/(pi h^6) broadcast to xyz, ungated.  Decided with the reference's own test; reached
+    // for the two self pairs of the thread and for coincident particles only.
+    if (r2.x < 2.0e-14f && j != ia) {
+      const float r = sqrtf(r2.x);
+      if ((r - 1.0e-7f < 0.f) && (0.f < r + 1.0e-7f)) { A.quirk_a += pp.x; inv_r.x = 0.f; }
     }
-    cnt = 0;
-  };
-#pragma unroll 1
-  for (int dz = -1; dz <= 1; ++dz)
-#pragma unroll 1
-    for (int dy = -1; dy <= 1; ++dy) {
-      uint32_t s, e;
-      row_range(ftable, c, fx, fy, fz, f, dy, dz, s, e);
-      for (uint32_t j = s; j < e; ++j) {
-        const float4 pj = __ldg(pos + j);
-        const float dx = pi.x - pj.x, dy_ = pi.y - pj.y, dz_ = pi.z - pj.z;
-        const float r2 = dx * dx + dy_ * dy_ + dz_ * dz_;
-        if (r2 < c.h2 && j != i) {
-          hit[cnt][threadIdx.x] = j;
-          if (++cnt == kHitCap) drain();
-        }
-      }
+    if (r2.y < 2.0e-14f && j != ib) {
+      const float r = sqrtf(r2.y);
+      if ((r - 1.0e-7f < 0.f) && (0.f < r + 1.0e-7f)) { A.quirk_b += pp.y; inv_r.y = 0.f; }
     }
-  drain();
-  acc[i] = force_finish(A, __ldg(rho + i), vi.w, c);
+  }
+  const float2 r = __fmul2_rn(r2c, inv_r);
+  float2 hr = __fadd2_rn(bcast2(c.h), make_float2(-r.x, -r.y));
+  hr = make_float2(fmaxf(hr.x, 0.f), fmaxf(hr.y, 0.f));
+  // pressure: (p_j/rho_j^2 + p_i/rho_i^2) (h - r)^2 (x_i - x_j) / r
+  const float2 sp = __fmul2_rn(__fmul2_rn(pp, hr), __fmul2_rn(hr, inv_r));
+  A.px = __ffma2_rn(sp, dx, A.px);
+  A.py = __ffma2_rn(sp, dy, A.py);
+  A.pz = __ffma2_rn(sp, dz, A.pz);
+  // viscosity: (v_j - v_i) (m/rho_j) (h - r)
+  const float2 vw = __fmul2_rn(bcast2(vj.w), hr);
+  A.vx = __ffma2_rn(__fadd2_rn(bcast2(vj.x), make_float2(-q.vx.x, -q.vx.y)), vw, A.vx);
+  A.vy = __ffma2_rn(__fadd2_rn(bcast2(vj.y), make_float2(-q.vy.x, -q.vy.y)), vw, A.vy);
+  A.vz = __ffma2_rn(__fadd2_rn(bcast2(vj.z), make_float2(-q.vz.x, -q.vz.y)), vw, A.vz);
+  // colour field: normal (m/rho_j)(h^2 - r^2)^2 (x_i - x_j), laplacian (m/rho_j)(h^2 - r^2)(3h^2 - 7r^2)
+  float2 tt = __fadd2_rn(bcast2(c.h2), make_float2(-r2.x, -r2.y));
+  tt = make_float2(fmaxf(tt.x, 0.f), fmaxf(tt.y, 0.f));
+  const float2 mt = __fmul2_rn(bcast2(vj.w), tt);
+  const float2 nw = __fmul2_rn(mt, tt);
+  A.nx = __ffma2_rn(nw, dx, A.nx);
+  A.ny = __ffma2_rn(nw, dy, A.ny);
+  A.nz = __ffma2_rn(nw, dz, A.nz);
+  A.lap = __ffma2_rn(mt, __ffma2_rn(r2, bcast2(-7.f), bcast2(3.f * c.h2)), A.lap);
 }
 
-// Forces from the neighbour list the density pass recorded.
-// (experiments: -DSPHB_FORCES_MINBLOCKS=<n> asks for n resident CTAs per SM)
-#ifdef SPHB_FORCES_MINBLOCKS
-#define SPHB_FORCES_BOUNDS __launch_bounds__(kBlock, SPHB_FORCES_MINBLOCKS)
-#else
-#define SPHB_FORCES_BOUNDS __launch_bounds__(kBlock)
+#ifndef SPHB_FORCES_TRIP
+#define SPHB_FORCES_TRIP 4
 #endif
+constexpr int kTrip = SPHB_FORCES_TRIP;  // neighbours per trip (2 or 4): their gathers are issued together
+static_assert(kTrip == 2 || kTrip == 4, "a trip is one or two words of codes");
+constexpr float kFar = 1.0e18f;
+
 template <bool Q>
-__global__ void SPHB_FORCES_BOUNDS
-    k_forces_nlist(const float4* __restrict__ pos, const float4* __restrict__ vel,
+__global__ void __launch_bounds__(kUB)
+    k_forces_union(const float4* __restrict__ pos, const float4* __restrict__ vel,
                    const uint32_t* __restrict__ keys, const uint32_t* __restrict__ ftable,
-                   const float* __restrict__ rho, const uint16_t* __restrict__ nlist,
-                   const uint8_t* __restrict__ ncount, float4* __restrict__ acc, StepConsts c_arg,
-                   const uint32_t* __restrict__ ghost_ids) {
+                   const float* __restrict__ rho, const uint32_t* __restrict__ pool,
+                   float4* __restrict__ acc, StepConsts c_arg, const uint32_t* __restrict__ ghost_ids) {
   if (Q && !g_hot.active) return;
   const StepConsts& c = Q ? g_hot.c : c_arg;
-  __shared__ uint32_t row_start[9][kBlock];
-  const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
-  if (i >= c.n) return;
-  if (ghost_ids && (__ldg(ghost_ids + i) & 0x80000000u)) {  // slab mode: another rank's particle
-    acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  __shared__ uint32_t start[kStartRows][kUB];
+  const uint32_t t = blockIdx.x * kUB + threadIdx.x;
+  const uint32_t ia = 2u * t;
+  if (ia >= c.n) return;
+  const PairLists L = pair_lists(const_cast<uint32_t*>(pool), c.n);
+  const bool has_b = ia + 1 < c.n;
+  const uint32_t ib = has_b ? ia + 1 : ia;
+  // slab mode: another rank's particles get no forces
+  const bool ghost_a = ghost_ids && (__ldg(ghost_ids + ia) & 0x80000000u);
+  const bool ghost_b = ghost_ids && (__ldg(ghost_ids + ib) & 0x80000000u);
+  const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+  const uint32_t meta = __ldg(L.meta + t);
+  if (meta & kMetaUnusable) {  // no list: each particle searches on its own
+    acc[ia] = ghost_a ? zero4 : forces_by_search(ia, pos, vel, keys, ftable, rho, c);
+    if (has_b) acc[ib] = ghost_b ? zero4 : forces_by_search(ib, pos, vel, keys, ftable, rho, c);
     return;
   }
-  const float4 pi = __ldg(pos + i), vi = __ldg(vel + i);
-  uint32_t fx, fy, fz;
-  fine_coords_of(__ldg(keys + i), c, fx, fy, fz);
-  const uint32_t cnt = ncount[i];
-  ForceAcc A = {};
-  if (cnt != kListOverflow) {
-    // where the run the density pass walked for each row began: kBackBits bits per row
-    uint32_t back = __ldg(nback_of(nlist, c.n) + i);
+  const uint32_t cnt_a = meta & 255u, cnt = (meta >> 8) & 255u;
+  const bool split = cnt > cnt_a;
 #pragma unroll
-    for (int dz = -1; dz <= 1; ++dz)
+  for (int r = 0; r < 9; ++r) start[r][threadIdx.x] = __ldg(L.start + (size_t)r * L.np + t);
+  if (split) {
 #pragma unroll
-      for (int dy = -1; dy <= 1; ++dy, back >>= kBackBits) {
-        const uint32_t y = fy + dy, z = fz + dz;
-        uint32_t s = 0;
-        if (y < c.fny && z < c.fnz)
-          s = __ldg(ftable + ((z * c.fny + y) * c.fnx + fx - (back & ((1u << kBackBits) - 1u))));
-        row_start[(dz + 1) * 3 + (dy + 1)][threadIdx.x] = s;
+    for (int r = 9; r < 18; ++r) start[r][threadIdx.x] = __ldg(L.start + (size_t)r * L.np + t);
+  }
+  const float4 pa = __ldg(pos + ia), va = __ldg(vel + ia);
+  const float4 pb = __ldg(pos + ib), vb = __ldg(vel + ib);
+  PairQuery q;
+  q.w = make_float2(pa.w, pb.w);
+  q.vx = make_float2(va.x, vb.x); q.vy = make_float2(va.y, vb.y); q.vz = make_float2(va.z, vb.z);
+  ForceAcc2 A = {};
+  const uint32_t* mine = L.codes + t;
+#pragma unroll 1
+  for (int part = 0; part < 2; ++part) {
+    const uint32_t k0 = part ? cnt_a : 0u, k1 = part ? cnt : cnt_a;
+    if (k0 >= k1) continue;
+    // a particle that is not part of this walk is parked far away: it collects exact zeros
+    const bool on_a = part == 0, on_b = has_b && (split ? part == 1 : true);
+    q.x = make_float2(on_a ? pa.x : kFar, on_b ? pb.x : kFar);
+    q.y = make_float2(on_a ? pa.y : kFar, on_b ? pb.y : kFar);
+    q.z = make_float2(on_a ? pa.z : kFar, on_b ? pb.z : kFar);
+    constexpr int W = kTrip / 2;  // words of codes per trip
+    uint32_t next[W];
+#pragma unroll
+    for (int u = 0; u < W; ++u) next[u] = __ldg(mine + (size_t)((k0 >> 1) + u) * L.np);
+    for (uint32_t k = k0; k < k1; k += kTrip) {
+      uint32_t word[W];
+#pragma unroll
+      for (int u = 0; u < W; ++u) {
+        // the next trip's codes are requested before this trip's gathers are
+        word[u] = next[u];
+        const uint32_t kn = k + kTrip + 2u * u;
+        next[u] = kn < k1 ? __ldg(mine + (size_t)(kn >> 1) * L.np) : (kNullCode | (kNullCode << 16));
       }
-    // four neighbours per trip: their codes, then their eight float4 loads, are issued together
-    // (each is a dependent chain code -> row start -> position / velocity -> ~45 flops)
-    const uint16_t* mine = nlist + i;
-    uint32_t code[4], next[4];
+      uint32_t j[kTrip];
+      bool dead[kTrip];
 #pragma unroll
-    for (int u = 0; u < 4; ++u) next[u] = (uint32_t)u < cnt ? mine[(size_t)u * c.n] : 0u;
-    for (uint32_t k = 0; k < cnt; k += 4) {
-      uint32_t j[4];
-      // the next trip's codes are requested before this trip's gathers are
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        code[u] = next[u];
-        next[u] = k + 4 + u < cnt ? mine[(size_t)(k + 4 + u) * c.n] : 0u;
+      for (int u = 0; u < kTrip; ++u) {
+        const uint32_t code = (word[u >> 1] >> (16 * (u & 1))) & 0xffffu;
+        dead[u] = code == kNullCode;  // (kTrip == 2 can end a part of 4n entries on a null pair)
+        j[u] = dead[u] ? ia : start[code >> kRowShift][threadIdx.x] + (code & kOffMask);
       }
+      float4 pj[kTrip], vj[kTrip];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        // a dead slot points at the particle itself, which is skipped like its own list entry
-        j[u] = k + u < cnt ? row_start[code[u] >> 12][threadIdx.x] + (code[u] & 4095u) : i;
-      }
-      float4 pj[4], vj[4];
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {
+      for (int u = 0; u < kTrip; ++u) {
         pj[u] = __ldg(pos + j[u]);
         vj[u] = __ldg(vel + j[u]);
       }
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        if (j[u] == i) continue;  // the list holds the particle itself
-        const float dx = pi.x - pj[u].x, dy_ = pi.y - pj[u].y, dz_ = pi.z - pj[u].z;
-        const float r2 = dx * dx + dy_ * dy_ + dz_ * dz_;
-        force_pair(A, pi, vi, pj[u], vj[u], dx, dy_, dz_, r2, c);
+      for (int u = 0; u < kTrip; ++u) {
+        if (dead[u]) pj[u].x = -kFar;  // out of reach of both, parked or not
+        force_pair2(A, q, pj[u], vj[u], dead[u] ? 0xffffffffu : j[u], ia, has_b ? ib : 0xfffffffeu, c);
       }
     }
-  } else {  // the list overflowed: search again
-    const CellFrac f = cell_frac(pi, fx, fy, fz, c);
-#pragma unroll 1
-    for (int dz = -1; dz <= 1; ++dz)
-#pragma unroll 1
-      for (int dy = -1; dy <= 1; ++dy) {
-        uint32_t s, e;
-        row_range(ftable, c, fx, fy, fz, f, dy, dz, s, e);
-        for (uint32_t j = s; j < e; ++j) {
-          const float4 pj = __ldg(pos + j);
-          const float dx = pi.x - pj.x, dy_ = pi.y - pj.y, dz_ = pi.z - pj.z;
-          const float r2 = dx * dx + dy_ * dy_ + dz_ * dz_;
-          if (r2 < c.h2 && j != i) force_pair(A, pi, vi, pj, __ldg(vel + j), dx, dy_, dz_, r2, c);
-        }
-      }
   }
-  acc[i] = force_finish(A, __ldg(rho + i), vi.w, c);
+  ForceAcc Aa, Ab;
+  Aa.px = A.px.x; Aa.py = A.py.x; Aa.pz = A.pz.x; Aa.vx = A.vx.x; Aa.vy = A.vy.x; Aa.vz = A.vz.x;
+  Aa.nx = A.nx.x; Aa.ny = A.ny.x; Aa.nz = A.nz.x; Aa.lap = A.lap.x; Aa.quirk = A.quirk_a;
+  Ab.px = A.px.y; Ab.py = A.py.y; Ab.pz = A.pz.y; Ab.vx = A.vx.y; Ab.vy = A.vy.y; Ab.vz = A.vz.y;
+  Ab.nx = A.nx.y; Ab.ny = A.ny.y; Ab.nz = A.nz.y; Ab.lap = A.lap.y; Ab.quirk = A.quirk_b;
+  acc[ia] = ghost_a ? zero4 : force_finish(Aa, __ldg(rho + ia), va.w, c, true);
+  if (has_b) acc[ib] = ghost_b ? zero4 : force_finish(Ab, __ldg(rho + ib), vb.w, c, true);
 }
 
-
 inline unsigned blocks_for(uint32_t n) { return (n + kBlock - 1) / kBlock; }
+inline unsigned pair_blocks(uint32_t n) { return ((n + 1u) / 2u + kUB - 1) / kUB; }
+inline size_t union_smem(uint32_t cap) { return (size_t)(cap + kUDump) * kUB * sizeof(uint16_t); }
+
+// round-1 layout inside the same pool: 64 + 2 u16 per particle, then one count byte per particle
+inline uint16_t* v1_list(uint32_t* pool) { return reinterpret_cast<uint16_t*>(pool); }
+inline uint8_t* v1_count(uint32_t* pool, uint32_t n) {
+  return reinterpret_cast<uint8_t*>(reinterpret_cast<uint16_t*>(pool) + (size_t)(kListCap + 2) * n);
+}
 
 }  // namespace
 
-// kListCap codes per particle + one 32-bit nback word (stored behind the codes)
-size_t neighbor_list_entries(uint32_t n) { return (size_t)(kListCap + 2) * n; }
+// 32-bit words of the list pool for n particles with room for `cap` entries per pair
+// (also enough for the round-1 kernels' per-particle lists)
+size_t neighbor_pool_words(uint32_t n, uint32_t cap) {
+  const size_t np = ((size_t)n + 1) / 2;
+  const size_t pairs = np * (1 + kStartRows + cap / 2);
+  const size_t v1 = ((size_t)(kListCap + 2) * n * 2 + n + 3) / 4;
+  return (pairs > v1 ? pairs : v1) + 4;
+}
+
+// Entries a pair's list should have room for, from the particles expected inside one support
+// sphere at rest density (4/3 pi h^3 rho0 / m): a pair's union is ~1.5 spheres; the margin absorbs
+// compression.  64 keeps the hit columns at 9 KB per CTA; denser fluids (mucus) take 128.
+uint32_t neighbor_list_cap(float h, float rho0, float mass) {
+  const float in_sphere = 4.18879f * h * h * h * rho0 / mass;
+  return 1.5f * in_sphere * 1.6f <= 64.f ? 64u : 128u;
+}
+
+int neighbor_kernels_init() {
+  // the 128-entry columns need 17 KB of dynamic shared memory: below the 48 KB default, nothing to opt into
+  return 0;
+}
 
 int launch_density(float4* pos, float4* vel, const uint32_t* keys, const uint32_t* ftable,
-                   float* rho, float* prs, uint16_t* nlist, uint8_t* ncount, const StepConsts& c,
+                   float* rho, float* prs, uint32_t* pool, uint32_t cap, const StepConsts& c,
                    int variant, cudaStream_t s, bool queued) {
-  const unsigned pairs = (c.n + 1u) / 2u, grid = (pairs + kPairBlock - 1) / kPairBlock;
-  (void)variant;  // the list is recorded either way; variant 1 just does not use it
-  if (queued) k_density_pair<true><<<grid, kPairBlock, 0, s>>>(pos, vel, keys, ftable, rho, prs, nlist, ncount, c);
-  else k_density_pair<false><<<grid, kPairBlock, 0, s>>>(pos, vel, keys, ftable, rho, prs, nlist, ncount, c);
+  if (variant == 2) {  // round-1 kernel (A/B)
+    const unsigned pairs = (c.n + 1u) / 2u, grid = (pairs + kPairBlock - 1) / kPairBlock;
+    uint16_t* nlist = v1_list(pool);
+    uint8_t* ncount = v1_count(pool, c.n);
+    if (queued) k_density_pair<true><<<grid, kPairBlock, 0, s>>>(pos, vel, keys, ftable, rho, prs, nlist, ncount, c);
+    else k_density_pair<false><<<grid, kPairBlock, 0, s>>>(pos, vel, keys, ftable, rho, prs, nlist, ncount, c);
+    return 1;
+  }
+  // variant 1 records the list too; its forces pass just does not use it
+  if (queued)
+    k_density_union<true><<<pair_blocks(c.n), kUB, union_smem(cap), s>>>(pos, vel, keys, ftable, rho, prs, pool, cap, c);
+  else
+    k_density_union<false><<<pair_blocks(c.n), kUB, union_smem(cap), s>>>(pos, vel, keys, ftable, rho, prs, pool, cap, c);
   return 1;
 }
 
@@ -550,17 +467,24 @@ int queue_refresh_neighbors(const QueueCtl* ctl, cudaStream_t s) {
 }
 
 int launch_forces(const float4* pos, const float4* vel, const uint32_t* keys,
-                  const uint32_t* ftable, const float* rho, const uint16_t* nlist,
-                  const uint8_t* ncount, float4* acc, const StepConsts& c, int variant,
-                  cudaStream_t s, const uint32_t* ghost_ids, bool queued) {
+                  const uint32_t* ftable, const float* rho, const uint32_t* pool, float4* acc,
+                  const StepConsts& c, int variant, cudaStream_t s, const uint32_t* ghost_ids,
+                  bool queued) {
+  if (variant == 2) {
+    const uint16_t* nlist = v1_list(const_cast<uint32_t*>(pool));
+    const uint8_t* ncount = v1_count(const_cast<uint32_t*>(pool), c.n);
+    if (queued)
+      k_forces_nlist<true><<<blocks_for(c.n), kBlock, 0, s>>>(pos, vel, keys, ftable, rho, nlist, ncount, acc, c, ghost_ids);
+    else
+      k_forces_nlist<false><<<blocks_for(c.n), kBlock, 0, s>>>(pos, vel, keys, ftable, rho, nlist, ncount, acc, c, ghost_ids);
+    return 1;
+  }
   if (queued)  // always from the recorded list (sphb_run_frame steps one at a time under variant 1)
-    k_forces_nlist<true><<<blocks_for(c.n), kBlock, 0, s>>>(pos, vel, keys, ftable, rho, nlist, ncount, acc, c,
-                                                            ghost_ids);
+    k_forces_union<true><<<pair_blocks(c.n), kUB, 0, s>>>(pos, vel, keys, ftable, rho, pool, acc, c, ghost_ids);
   else if (variant == 1 && !ghost_ids)
     k_forces_list<<<blocks_for(c.n), kBlock, 0, s>>>(pos, vel, keys, ftable, rho, acc, c);
   else
-    k_forces_nlist<false><<<blocks_for(c.n), kBlock, 0, s>>>(pos, vel, keys, ftable, rho, nlist, ncount, acc, c,
-                                                             ghost_ids);
+    k_forces_union<false><<<pair_blocks(c.n), kUB, 0, s>>>(pos, vel, keys, ftable, rho, pool, acc, c, ghost_ids);
   return 1;
 }
 

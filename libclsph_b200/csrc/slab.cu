@@ -222,12 +222,12 @@ int sphb_slab_forces(sphb_engine* e, const float gmin[3], const float gmax[3]) {
   {
     PassTimer t(e, SPHB_PASS_DENSITY);
     t.done(launch_density(e->pos[e->cur], e->vel[e->cur], skeys, e->ftable, e->rho, e->prs,
-                          e->nlist, e->ncount, c, 0, s));
+                          e->npool, e->list_cap, c, 0, s));
   }
   {
     PassTimer t(e, SPHB_PASS_FORCES);
-    t.done(launch_forces(e->pos[e->cur], e->vel[e->cur], skeys, e->ftable, e->rho, e->nlist,
-                         e->ncount, e->acc, c, 0, s, e->rank_cur));
+    t.done(launch_forces(e->pos[e->cur], e->vel[e->cur], skeys, e->ftable, e->rho, e->npool,
+                         e->acc, c, 0, s, e->rank_cur));
   }
   // every owned particle's dense slot in the advected arrays (ghosts are dropped there)
   e->launches += launch_slab_owned_scan(e->rank_cur, n, e->free_keys, e->scan_scratch, e->n_owned_dev, s);
