@@ -136,8 +136,36 @@ def build_host(force=False, verbose=False):
     return HOST_OUT
 
 
+REFERENCE = "/root/reference"
+REF_CALLER_OUT = os.path.join(HERE, "build", "reference_caller", "particles")
+
+
+def build_reference_caller(force=False, verbose=False):
+    """The REFERENCE's own command-line caller — /root/reference/example/particles.cpp, compiled
+    where it lies, unchanged — against this repository's headers (host/, include/) and libraries:
+    the check that the C++ surface of libclsph/sph_simulation.h:10-27 is kept.
+    Only cereal's headers come from the reference tree (-I /root/reference finds util/cereal; every
+    other include resolves in host/ first).  The binary lands under build/ (git-ignored; it travels
+    to the GPU box, where the reference tree does not exist).  Returns None without the tree."""
+    src = os.path.join(REFERENCE, "example", "particles.cpp")
+    if not os.path.exists(src):
+        return REF_CALLER_OUT if os.path.exists(REF_CALLER_OUT) else None
+    gxx = shutil.which("g++") or "/usr/bin/g++"
+    os.makedirs(os.path.dirname(REF_CALLER_OUT), exist_ok=True)
+    if force or _stale(REF_CALLER_OUT, [src, HOST_OUT, OUT]):
+        cmd = [gxx, "-std=c++11", "-O2", "-I", HOST, "-I", os.path.join(HERE, "..", "include"), "-I", REFERENCE,
+               src, "-o", REF_CALLER_OUT, "-L", HERE, "-lclsph_host", "-lsphb", "-Wl,-rpath,$ORIGIN/../..",
+               "-pthread"]
+        if verbose:
+            print(" ".join(cmd), flush=True)
+        subprocess.check_call(cmd)
+    return REF_CALLER_OUT
+
+
 def build_all(force=False, verbose=False):
-    return build(force, verbose), build_host(force, verbose)
+    out = build(force, verbose), build_host(force, verbose)
+    build_reference_caller(force, verbose)
+    return out
 
 
 if __name__ == "__main__":

@@ -233,7 +233,8 @@ int launch_cell_sort(const float4* pos, const StepConsts& c, uint32_t* keys_tmp,
                      uint32_t* perm, cudaStream_t s, bool queued = false, size_t table_entries = 0);
 int launch_reorder(const uint32_t* perm, uint32_t n, const float4* pos_in, const float4* vel_in,
                    const float4* vhf_in, const uint32_t* rank_in, float4* pos_out, float4* vel_out,
-                   float4* vhf_out, uint32_t* rank_out, cudaStream_t s, bool queued = false);
+                   float4* vhf_out, uint32_t* rank_out, cudaStream_t s, bool queued = false,
+                   float4* pairs_out = nullptr);
 // fine cell table: ftable[f] = index of the first sorted particle whose fine key is >= f,
 // for f in [0, nfine]; ftable must hold nfine + 1 entries.  scratch: scan_scratch_entries().
 int launch_fine_table(const uint32_t* sorted_keys, uint32_t n, uint32_t* ftable, uint32_t nfine,
@@ -293,14 +294,17 @@ int launch_exclusive_max(uint32_t* data, uint32_t len, uint32_t* scratch, cudaSt
 // keys = compute-ordered fine keys, ftable = fine cell table (nfine + 1 entries).
 // variant 0: the density pass records ONE neighbour list per pair of consecutive particles in
 // `pool` (neighbor_pool_words(n, cap) 32-bit words, cap = neighbor_list_cap(...) entries per
-// pair) that the forces pass consumes; variant 1: the forces pass searches on its own;
-// variant 2: the round-1 kernels (one list per particle), kept for A/B.
+// pair) that the forces pass consumes; variant 1: the round-1 density pass + forces by their own
+// search; variant 2: the round-1 kernels (one list per particle); 4 / 5 / 6: the sub-warp-cooperative
+// density pass with 4 / 8 / 16 lanes per particle + forces by their own search.  1, 2, 4-6 are kept
+// for A/B measurements.
 size_t neighbor_pool_words(uint32_t n, uint32_t cap);
 uint32_t neighbor_list_cap(float h, float rho0, float mass);
-int launch_density(float4* pos, float4* vel, const uint32_t* keys, const uint32_t* ftable,
-                   float* rho, float* prs, uint32_t* pool, uint32_t cap, const StepConsts& c,
-                   int variant, cudaStream_t s, bool queued = false);
-int launch_forces(const float4* pos, const float4* vel, const uint32_t* keys,
+// pairs = the reorder pass's pair records (n + 2 float4), pv = the forces pass's records (2 n float4)
+int launch_density(float4* pos, float4* vel, const float4* pairs, float4* pv, const uint32_t* keys,
+                   const uint32_t* ftable, float* rho, float* prs, uint32_t* pool, uint32_t cap,
+                   const StepConsts& c, int variant, cudaStream_t s, bool queued = false);
+int launch_forces(const float4* pos, const float4* vel, const float4* pv, const uint32_t* keys,
                   const uint32_t* ftable, const float* rho, const uint32_t* pool, float4* acc,
                   const StepConsts& c, int variant, cudaStream_t s,
                   const uint32_t* ghost_ids = nullptr, bool queued = false);

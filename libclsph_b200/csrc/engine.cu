@@ -54,7 +54,7 @@ int sphb_destroy(sphb_engine* e) {
   cudaFree(e->acc); cudaFree(e->rho); cudaFree(e->prs);
   cudaFree(e->sortb.hist); cudaFree(e->sortb.block_sums);
   cudaFree(e->rank_cur); cudaFree(e->rank_prev); cudaFree(e->ckey);
-  cudaFree(e->npool);
+  cudaFree(e->npool); cudaFree(e->pairs); cudaFree(e->pv);
   cudaFree(e->n_owned_dev); cudaFree(e->counters); cudaFree(e->src_of);
   if (e->host_counts) cudaFreeHost(e->host_counts);
   cudaFree(e->ftable); cudaFree(e->ref_table); cudaFree(e->scan_scratch); cudaFree(e->aos_stage);
@@ -153,6 +153,8 @@ int sphb_create_with_capacity(const sphb_params* params, const sphb_terms* terms
   TRY_OR_DESTROY(dev_alloc(&e->ckey, n));
   e->list_cap = neighbor_list_cap(params->h, params->fluid_density, params->particle_mass);
   TRY_OR_DESTROY(dev_alloc(&e->npool, neighbor_pool_words(n, e->list_cap)));
+  TRY_OR_DESTROY(dev_alloc(&e->pairs, (size_t)n + 4));
+  TRY_OR_DESTROY(dev_alloc(&e->pv, 2 * (size_t)n + 2));
   TRY_OR_DESTROY(dev_alloc(&e->acc, n));
   TRY_OR_DESTROY(dev_alloc(&e->rho, n));
   TRY_OR_DESTROY(dev_alloc(&e->prs, n));
@@ -483,7 +485,7 @@ int enqueue_queued_step(sphb_engine* e) {
   const uint32_t* skeys = b.keys[1];
   const uint32_t* perm = b.vals[0];
   l += launch_reorder(perm, e->n, e->pos[in], e->vel[in], e->vhf[in], e->rank_cur, e->pos[mid], e->vel[mid],
-                      e->vhf[mid], e->rank_prev, s, true);
+                      e->vhf[mid], e->rank_prev, s, true, e->pairs);
   cudaStream_t rs = e->use_side_stream ? e->side : s;
   if (e->use_side_stream) {
     CUDA_TRY(e, cudaEventRecord(e->ev_fork, s));
@@ -492,9 +494,9 @@ int enqueue_queued_step(sphb_engine* e) {
   l += launch_reference_rank(skeys, e->ftable, e->rank_prev, e->ref_table, e->ckey, e->rank_cur, c,
                              e->scan_scratch, rs, true, e->ref_table_cap);
   if (e->use_side_stream) CUDA_TRY(e, cudaEventRecord(e->ev_join, e->side));
-  l += launch_density(e->pos[mid], e->vel[mid], skeys, e->ftable, e->rho, e->prs, e->npool, e->list_cap, c,
+  l += launch_density(e->pos[mid], e->vel[mid], e->pairs, e->pv, skeys, e->ftable, e->rho, e->prs, e->npool, e->list_cap, c,
                       e->neighbor_variant, s, true);
-  l += launch_forces(e->pos[mid], e->vel[mid], skeys, e->ftable, e->rho, e->npool, e->acc, c,
+  l += launch_forces(e->pos[mid], e->vel[mid], e->pv, skeys, e->ftable, e->rho, e->npool, e->acc, c,
                      e->neighbor_variant, s, nullptr, true);
   if (e->use_side_stream) CUDA_TRY(e, cudaStreamWaitEvent(s, e->ev_join, 0));
   for (int a = 0; a < e->queued_attempts; ++a) {
@@ -569,7 +571,7 @@ int sphb_run_frame(sphb_engine* e, float dt_in, float frame_time, uint64_t max_s
   while (timeleft > 0.0) {
     if (max_steps && steps >= max_steps) break;
     const bool want_queue = e->use_queue == 1 || (e->use_queue == 2 && e->n <= kQueueAutoMax);
-    const bool can_queue = want_queue && e->bbox_valid && e->sort_variant == 0 && e->neighbor_variant != 1 &&
+    const bool can_queue = want_queue && e->bbox_valid && e->sort_variant == 0 && (e->neighbor_variant == 0 || e->neighbor_variant == 2) &&
                            !e->profile && e->ftable_cap && e->ref_table_cap && e->scan_scratch;
     if (!can_queue) {  // the first step after an upload (its bbox needs a pass of its own), or an option
       float computed = dt;
@@ -690,7 +692,7 @@ int sphb_step(sphb_engine* e, float dt_in, float* dt_out) {
     PassTimer t(e, SPHB_PASS_REORDER);
     const int in = e->cur, out = in ^ 1;
     t.done(launch_reorder(perm, n, e->pos[in], e->vel[in], e->vhf[in], e->rank_cur,
-                          e->pos[out], e->vel[out], e->vhf[out], e->rank_prev, s));
+                          e->pos[out], e->vel[out], e->vhf[out], e->rank_prev, s, false, e->pairs));
     e->cur = out;
   }
   // the reference's cell table (kernels/sort.cl:61-78) and every particle's place in the
@@ -712,12 +714,12 @@ int sphb_step(sphb_engine* e, float dt_in, float* dt_out) {
   // 4. density_pressure (kernels/sphb.cl:3-35), 5. forces (:37-126)
   {
     PassTimer t(e, SPHB_PASS_DENSITY);
-    t.done(launch_density(e->pos[e->cur], e->vel[e->cur], skeys, e->ftable, e->rho,
+    t.done(launch_density(e->pos[e->cur], e->vel[e->cur], e->pairs, e->pv, skeys, e->ftable, e->rho,
                           e->prs, e->npool, e->list_cap, c, e->neighbor_variant, s));
   }
   {
     PassTimer t(e, SPHB_PASS_FORCES);
-    t.done(launch_forces(e->pos[e->cur], e->vel[e->cur], skeys, e->ftable, e->rho,
+    t.done(launch_forces(e->pos[e->cur], e->vel[e->cur], e->pv, skeys, e->ftable, e->rho,
                          e->npool, e->acc, c, e->neighbor_variant, s));
   }
   if (e->use_side_stream) CUDA_TRY(e, cudaStreamWaitEvent(s, e->ev_join, 0));

@@ -92,6 +92,8 @@ struct sphb_engine {
   uint32_t* ckey = nullptr;
   uint32_t* npool = nullptr;  // neighbour lists recorded by the density pass (kernels_neighbors.cu)
   uint32_t list_cap = 64;     // entries a pair's list has room for
+  float4* pairs = nullptr;    // positions as one record per pair of particles (reorder -> density)
+  float4* pv = nullptr;       // position + velocity + pair factors per particle (density -> forces)
   uint32_t* ftable = nullptr;     // fine cell table, nfine + 1 entries
   size_t ftable_cap = 0;
   uint32_t* ref_table = nullptr;  // the reference's cell table, grid_cell_count (+1) entries

@@ -193,17 +193,32 @@ __global__ void __launch_bounds__(kBlock)
               const float4* __restrict__ vel_in, const float4* __restrict__ vhf_in,
               const uint32_t* __restrict__ rank_in, float4* __restrict__ pos_out,
               float4* __restrict__ vel_out, float4* __restrict__ vhf_out,
-              uint32_t* __restrict__ rank_out) {
+              uint32_t* __restrict__ rank_out, float4* __restrict__ pairs_out) {
   if (Q && !g_hot.active) return;
   const uint32_t k = blockIdx.x * kBlock + threadIdx.x;
-  if (k >= n) return;
-  const uint32_t src = __ldg(perm + k);
-  float4 p = __ldg(pos_in + src), v = __ldg(vel_in + src), w = __ldg(vhf_in + src);
-  p.w = 0.f; v.w = 0.f; w.w = 0.f;
-  pos_out[k] = p;
-  vel_out[k] = v;
-  vhf_out[k] = w;
-  rank_out[k] = __ldg(rank_in + src);
+  const bool live = k < n;
+  float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (live) {
+    const uint32_t src = __ldg(perm + k);
+    p = __ldg(pos_in + src);
+    float4 v = __ldg(vel_in + src), w = __ldg(vhf_in + src);
+    p.w = 0.f; v.w = 0.f; w.w = 0.f;
+    pos_out[k] = p;
+    vel_out[k] = v;
+    vhf_out[k] = w;
+    rank_out[k] = __ldg(rank_in + src);
+  }
+  // the positions once more as one 32-byte record per PAIR of consecutive particles,
+  // {x0, x1, y0, y1 | z0, z1, 0, 0}: what the density pass walks (kernels_neighbors.cu) — one
+  // 256-bit load brings two candidates with their coordinates already paired for fp32x2
+  if (pairs_out) {  // (kernel argument: uniform; every lane of the warp reaches the shuffles)
+    const float x1 = __shfl_down_sync(0xffffffffu, p.x, 1), y1 = __shfl_down_sync(0xffffffffu, p.y, 1),
+                z1 = __shfl_down_sync(0xffffffffu, p.z, 1);
+    if (live && !(k & 1u)) {
+      pairs_out[k] = make_float4(p.x, x1, p.y, y1);   // record k / 2 = float4s k and k + 1
+      pairs_out[k + 1] = make_float4(p.z, z1, 0.f, 0.f);
+    }
+  }
 }
 
 // Fine cell table, step 1: ends[f] = (index of the last particle of fine cell f) + 1 (else 0).
@@ -711,13 +726,13 @@ int launch_cell_sort(const float4* pos, const StepConsts& c, uint32_t* keys_tmp,
 
 int launch_reorder(const uint32_t* perm, uint32_t n, const float4* pos_in, const float4* vel_in,
                    const float4* vhf_in, const uint32_t* rank_in, float4* pos_out, float4* vel_out,
-                   float4* vhf_out, uint32_t* rank_out, cudaStream_t s, bool queued) {
+                   float4* vhf_out, uint32_t* rank_out, cudaStream_t s, bool queued, float4* pairs_out) {
   if (queued)
     k_reorder<true><<<blocks_for(n), kBlock, 0, s>>>(perm, n, pos_in, vel_in, vhf_in, rank_in, pos_out,
-                                                     vel_out, vhf_out, rank_out);
+                                                     vel_out, vhf_out, rank_out, pairs_out);
   else
     k_reorder<false><<<blocks_for(n), kBlock, 0, s>>>(perm, n, pos_in, vel_in, vhf_in, rank_in, pos_out,
-                                                      vel_out, vhf_out, rank_out);
+                                                      vel_out, vhf_out, rank_out, pairs_out);
   return 1;
 }
 

@@ -30,9 +30,14 @@
 // checked against the CPU oracle to a stated tolerance (tests/test_gpu_parity.py), unlike
 // kernels_exact.cu which is bit-exact.
 //
-// Data layout (sorted SoA): pos = (x, y, z, p/rho^2), vel = (vx, vy, vz, m/rho).  The two
-// w lanes are written by the density pass for the forces pass: the reference recomputes
-// p_j/rho_j^2 and m/rho_j for every PAIR (sphb.cl:80-106); they depend only on j.
+// Data the two passes exchange (both are bound by L1 data-pipe wavefronts — one per 128-byte
+// line a warp-wide load touches — so both read 32-byte records with ONE 256-bit load):
+//   pairs[t]  {x0, x1, y0, y1 | z0, z1, -, -} of particles 2t, 2t + 1, written by the reorder
+//             pass: the density pass's candidates, two per load, coordinates already paired
+//             for fp32x2 arithmetic;
+//   pv[i]     {x, y, z, p/rho^2 | vx, vy, vz, m/rho}, written by the density pass: everything
+//             the forces pass needs of a neighbour in one gather.  The reference recomputes
+//             p_j/rho_j^2 and m/rho_j for every PAIR (sphb.cl:80-106); they depend only on j.
 #include "common.cuh"
 
 namespace sphb {
@@ -79,38 +84,70 @@ __host__ __device__ inline PairLists pair_lists(uint32_t* pool, uint32_t n) {
 
 __device__ __forceinline__ float2 bcast2(float v) { return make_float2(v, v); }
 
-// One candidate against the thread's TWO particles at once (FADD2 / FFMA2 / FMUL2 with the
-// candidate's coordinates as broadcast operands).  u = r^2 - h^2 per particle; where u < 0 the
-// particle's sum takes u^3 (the caller negates the total), and where either is, the candidate's
-// code goes to the pair's list: a predicated store at a cursor that advances only on hits.
-__device__ __forceinline__ void density_test_union(const float2& qx, const float2& qy, const float2& qz,
-                                                   float neg_h2, const float4& pj, float& sum_a, float& sum_b,
-                                                   uint32_t& cur, uint32_t code) {
-  const float2 dx = __fadd2_rn(qx, bcast2(-pj.x));
-  const float2 dy = __fadd2_rn(qy, bcast2(-pj.y));
-  const float2 dz = __fadd2_rn(qz, bcast2(-pj.z));
-  float2 u = __ffma2_rn(dx, dx, bcast2(neg_h2));
-  u = __ffma2_rn(dy, dy, u);
-  u = __ffma2_rn(dz, dz, u);
-  const float2 u2 = __fmul2_rn(u, u);
+// 32 bytes with one load (LDG.E.256): a, b the first float4, c, d the second
+struct Rec8 {
+  float2 a, b, c, d;
+};
+__device__ __forceinline__ Rec8 ldg256(const float4* p) {
+  Rec8 r;
+  asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=f"(r.a.x), "=f"(r.a.y), "=f"(r.b.x), "=f"(r.b.y), "=f"(r.c.x), "=f"(r.c.y), "=f"(r.d.x),
+                 "=f"(r.d.y)
+               : "l"(p));
+  return r;
+}
+
+// TWO candidates (one record of `pairs`) against the thread's TWO particles: per particle
+// u = r^2 - h^2 for both candidates in packed fp32x2 arithmetic (FADD2 / FFMA2 / FMUL2, the
+// particle's coordinates as broadcast operands); where u < 0 the particle's sum takes u^3 (the
+// caller negates the total), and where either particle's is, the candidate's code goes to the
+// pair's list: a predicated store at a cursor that advances only on hits.
+__device__ __forceinline__ void density_test_record(const float2& qx, const float2& qy, const float2& qz,
+                                                    float neg_h2, const float2& X, const float2& Y,
+                                                    const float2& Z, float& sum_a, float& sum_b,
+                                                    uint32_t& cur, uint32_t code) {
+  float2 d = __fadd2_rn(X, bcast2(-qx.x));
+  float2 ua = __ffma2_rn(d, d, bcast2(neg_h2));
+  d = __fadd2_rn(Y, bcast2(-qy.x));
+  ua = __ffma2_rn(d, d, ua);
+  d = __fadd2_rn(Z, bcast2(-qz.x));
+  ua = __ffma2_rn(d, d, ua);
+  d = __fadd2_rn(X, bcast2(-qx.y));
+  float2 ub = __ffma2_rn(d, d, bcast2(neg_h2));
+  d = __fadd2_rn(Y, bcast2(-qy.y));
+  ub = __ffma2_rn(d, d, ub);
+  d = __fadd2_rn(Z, bcast2(-qz.y));
+  ub = __ffma2_rn(d, d, ub);
+  const float2 ua2 = __fmul2_rn(ua, ua), ub2 = __fmul2_rn(ub, ub);
   asm volatile(
       "{ .reg .pred pa, pb, pc;\n"
+      "  .reg .b16 c1;\n"
       "  setp.lt.f32 pa, %3, 0f00000000;\n"
-      "  setp.lt.f32 pb, %4, 0f00000000;\n"
-      "  @pa fma.rn.f32 %0, %5, %3, %0;\n"
-      "  @pb fma.rn.f32 %1, %6, %4, %1;\n"
+      "  setp.lt.f32 pb, %5, 0f00000000;\n"
+      "  @pa fma.rn.f32 %0, %7, %3, %0;\n"
+      "  @pb fma.rn.f32 %1, %9, %5, %1;\n"
       "  or.pred pc, pa, pb;\n"
-      "  @pc st.shared.u16 [%2], %7;\n"
-      "  @pc add.u32 %2, %2, %8; }"
+      "  @pc st.shared.u16 [%2], %11;\n"
+      "  @pc add.u32 %2, %2, %12;\n"
+      "  setp.lt.f32 pa, %4, 0f00000000;\n"
+      "  setp.lt.f32 pb, %6, 0f00000000;\n"
+      "  @pa fma.rn.f32 %0, %8, %4, %0;\n"
+      "  @pb fma.rn.f32 %1, %10, %6, %1;\n"
+      "  or.pred pc, pa, pb;\n"
+      "  add.u16 c1, %11, 1;\n"
+      "  @pc st.shared.u16 [%2], c1;\n"
+      "  @pc add.u32 %2, %2, %12; }"
       : "+f"(sum_a), "+f"(sum_b), "+r"(cur)
-      : "f"(u.x), "f"(u.y), "f"(u2.x), "f"(u2.y), "h"((uint16_t)code), "n"(kUStride)
+      : "f"(ua.x), "f"(ua.y), "f"(ub.x), "f"(ub.y), "f"(ua2.x), "f"(ua2.y), "f"(ub2.x), "f"(ub2.y),
+        "h"((uint16_t)code), "n"(kUStride)
       : "memory");
 }
 
 template <bool Q>
 __global__ void __launch_bounds__(kUB)
-    k_density_union(float4* pos, float4* vel, const uint32_t* __restrict__ keys,
-                    const uint32_t* __restrict__ ftable, float* __restrict__ rho, float* __restrict__ prs,
+    k_density_union(const float4* __restrict__ pairs, const float4* __restrict__ vel,
+                    const uint32_t* __restrict__ keys, const uint32_t* __restrict__ ftable,
+                    float* __restrict__ rho, float* __restrict__ prs, float4* __restrict__ pv,
                     uint32_t* __restrict__ pool, uint32_t cap, StepConsts c_arg) {
   if (Q && !g_hot.active) return;
   const StepConsts& c = Q ? g_hot.c : c_arg;
@@ -121,7 +158,9 @@ __global__ void __launch_bounds__(kUB)
   const PairLists L = pair_lists(pool, c.n);
   const bool has_b = ia + 1 < c.n;
   const uint32_t ib = has_b ? ia + 1 : ia;
-  const float4 pa = pos[ia], pb = pos[ib];
+  const Rec8 own = ldg256(pairs + ia);  // {xa, xb, ya, yb | za, zb, -, -}
+  const float4 pa = make_float4(own.a.x, own.b.x, own.c.x, 0.f);
+  const float4 pb = has_b ? make_float4(own.a.y, own.b.y, own.c.y, 0.f) : pa;
   uint32_t fxa, fya, fza, fxb, fyb, fzb;
   fine_coords_of(__ldg(keys + ia), c, fxa, fya, fza);
   fine_coords_of(__ldg(keys + ib), c, fxb, fyb, fzb);
@@ -138,7 +177,6 @@ __global__ void __launch_bounds__(kUB)
   uint32_t cur = base, cnt_a = 0;
   float sum_a = 0.f, sum_b = 0.f;
   bool unusable = false;
-  const float4* cand = reinterpret_cast<const float4*>(pos);
 #pragma unroll 1
   for (int pass = 0; pass < npass; ++pass) {
     const bool la = pass == 0, lb = has_b && (split ? pass == 1 : true);
@@ -170,26 +208,24 @@ __global__ void __launch_bounds__(kUB)
       }
 #pragma unroll
       for (int k = 0; k < 3; ++k) {
-        const uint32_t e = re[k];
-        uint32_t j = rs[k], code = (rowid + k) << kRowShift;
-        L.start[(size_t)(rowid + k) * L.np + t] = j;
-        if (e - j > kMaxRun) unusable = true;
-        // The loop body is branch-free; the cursor is pulled back into the dump rows once per
-        // group of four candidates.
-        for (; j + 4u <= e; j += 4u, code += 4u) {
-          const float4 p0 = __ldg(cand + j), p1 = __ldg(cand + j + 1), p2 = __ldg(cand + j + 2),
-                       p3 = __ldg(cand + j + 3);
-          density_test_union(qx, qy, qz, -c.h2, p0, sum_a, sum_b, cur, code);
-          density_test_union(qx, qy, qz, -c.h2, p1, sum_a, sum_b, cur, code + 1u);
-          density_test_union(qx, qy, qz, -c.h2, p2, sum_a, sum_b, cur, code + 2u);
-          density_test_union(qx, qy, qz, -c.h2, p3, sum_a, sum_b, cur, code + 3u);
+        const uint32_t s = rs[k], e = re[k];
+        L.start[(size_t)(rowid + k) * L.np + t] = s;
+        if (e - s > kMaxRun) unusable = true;
+        // The run [s, e) is walked as whole records — candidates 2r, 2r + 1 — from the record
+        // that holds s to the one that holds e - 1; a candidate outside the run (only the first
+        // record's first, when s is odd, and the last record's second, when e is odd) is moved
+        // out of reach.  code = row id << 11 | (candidate - s).  The body is branch-free; the
+        // cursor is pulled back into the dump rows once per record.
+        const uint32_t j_end = s < e ? e : s & ~1u;  // (an empty run walks nothing)
+        uint32_t code = ((rowid + k) << kRowShift) - (s & 1u);
+#pragma unroll 2
+        for (uint32_t j = s & ~1u; j < j_end; j += 2u, code += 2u) {
+          Rec8 r = ldg256(pairs + j);
+          if (j < s) r.a.x = nan;
+          if (j + 1u >= e) r.a.y = nan;
+          density_test_record(qx, qy, qz, -c.h2, r.a, r.b, r.c, sum_a, sum_b, cur, code);
           cur = min(cur, end);
         }
-        for (; j < e; ++j, ++code) {
-          const float4 p0 = __ldg(cand + j);
-          density_test_union(qx, qy, qz, -c.h2, p0, sum_a, sum_b, cur, code);
-        }
-        cur = min(cur, end);
       }
     }
     // every part ends on a multiple of four entries (the forces pass takes four per trip)
@@ -212,9 +248,10 @@ __global__ void __launch_bounds__(kUB)
     const float pressure = tait_pressure(density, c);
     rho[i] = density;
     prs[i] = pressure;
-    // derived per-particle factors for the forces pass (only the w lanes are written)
-    reinterpret_cast<float*>(pos + i)[3] = pressure / (density * density);
-    reinterpret_cast<float*>(vel + i)[3] = c.mass / density;
+    // the forces pass's record of this particle, with the two per-particle factors of its pair terms
+    const float4 p = w ? pb : pa, v = __ldg(vel + i);
+    pv[2u * i] = make_float4(p.x, p.y, p.z, pressure / (density * density));
+    pv[2u * i + 1u] = make_float4(v.x, v.y, v.z, c.mass / density);
   }
   L.meta[t] = unusable ? kMetaUnusable : (cnt_a | (cnt << 8));
   if (!unusable) {
@@ -299,23 +336,35 @@ __device__ __forceinline__ void force_pair2(ForceAcc2& A, const PairQuery& q, co
   A.lap = __ffma2_rn(mt, __ffma2_rn(r2, bcast2(-7.f), bcast2(3.f * c.h2)), A.lap);
 }
 
+// Tuning of the forces pass, measured on the B200 at 16.7 M particles:
+// two neighbours per trip and 80 registers (12 CTAs of 64 threads per SM) 1.18 ms; four per trip
+// at 123 registers 1.23 ms, at 96 registers (spills) 1.44 ms; a double-buffered software pipeline
+// of the gathers 1.31 ms at best (the register copies, or the second register set, cost more than
+// the latency they hide); CTAs of 128 threads 1.43-1.53 ms.
 #ifndef SPHB_FORCES_TRIP
-#define SPHB_FORCES_TRIP 4
+#define SPHB_FORCES_TRIP 2
+#endif
+#ifndef SPHB_FORCES_BLOCK
+#define SPHB_FORCES_BLOCK 64
+#endif
+#ifndef SPHB_FORCES_MINB
+#define SPHB_FORCES_MINB 12
 #endif
 constexpr int kTrip = SPHB_FORCES_TRIP;  // neighbours per trip (2 or 4): their gathers are issued together
 static_assert(kTrip == 2 || kTrip == 4, "a trip is one or two words of codes");
+constexpr int kFB = SPHB_FORCES_BLOCK;   // threads per CTA
 constexpr float kFar = 1.0e18f;
 
 template <bool Q>
-__global__ void __launch_bounds__(kUB)
-    k_forces_union(const float4* __restrict__ pos, const float4* __restrict__ vel,
-                   const uint32_t* __restrict__ keys, const uint32_t* __restrict__ ftable,
-                   const float* __restrict__ rho, const uint32_t* __restrict__ pool,
-                   float4* __restrict__ acc, StepConsts c_arg, const uint32_t* __restrict__ ghost_ids) {
+__global__ void __launch_bounds__(kFB, SPHB_FORCES_MINB)
+    k_forces_union(const float4* __restrict__ pv, const uint32_t* __restrict__ keys,
+                   const uint32_t* __restrict__ ftable, const float* __restrict__ rho,
+                   const uint32_t* __restrict__ pool, float4* __restrict__ acc, StepConsts c_arg,
+                   const uint32_t* __restrict__ ghost_ids) {
   if (Q && !g_hot.active) return;
   const StepConsts& c = Q ? g_hot.c : c_arg;
-  __shared__ uint32_t start[kStartRows][kUB];
-  const uint32_t t = blockIdx.x * kUB + threadIdx.x;
+  __shared__ uint32_t start[kStartRows][kFB];
+  const uint32_t t = blockIdx.x * kFB + threadIdx.x;
   const uint32_t ia = 2u * t;
   if (ia >= c.n) return;
   const PairLists L = pair_lists(const_cast<uint32_t*>(pool), c.n);
@@ -327,8 +376,8 @@ __global__ void __launch_bounds__(kUB)
   const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
   const uint32_t meta = __ldg(L.meta + t);
   if (meta & kMetaUnusable) {  // no list: each particle searches on its own
-    acc[ia] = ghost_a ? zero4 : forces_by_search(ia, pos, vel, keys, ftable, rho, c);
-    if (has_b) acc[ib] = ghost_b ? zero4 : forces_by_search(ib, pos, vel, keys, ftable, rho, c);
+    acc[ia] = ghost_a ? zero4 : forces_by_search<2>(ia, pv, pv + 1, keys, ftable, rho, c);
+    if (has_b) acc[ib] = ghost_b ? zero4 : forces_by_search<2>(ib, pv, pv + 1, keys, ftable, rho, c);
     return;
   }
   const uint32_t cnt_a = meta & 255u, cnt = (meta >> 8) & 255u;
@@ -339,8 +388,8 @@ __global__ void __launch_bounds__(kUB)
 #pragma unroll
     for (int r = 9; r < 18; ++r) start[r][threadIdx.x] = __ldg(L.start + (size_t)r * L.np + t);
   }
-  const float4 pa = __ldg(pos + ia), va = __ldg(vel + ia);
-  const float4 pb = __ldg(pos + ib), vb = __ldg(vel + ib);
+  const float4 pa = __ldg(pv + 2u * ia), va = __ldg(pv + 2u * ia + 1u);
+  const float4 pb = __ldg(pv + 2u * ib), vb = __ldg(pv + 2u * ib + 1u);
   PairQuery q;
   q.w = make_float2(pa.w, pb.w);
   q.vx = make_float2(va.x, vb.x); q.vy = make_float2(va.y, vb.y); q.vz = make_float2(va.z, vb.z);
@@ -356,36 +405,35 @@ __global__ void __launch_bounds__(kUB)
     q.y = make_float2(on_a ? pa.y : kFar, on_b ? pb.y : kFar);
     q.z = make_float2(on_a ? pa.z : kFar, on_b ? pb.z : kFar);
     constexpr int W = kTrip / 2;  // words of codes per trip
+    const uint32_t null_word = kNullCode | (kNullCode << 16);
     uint32_t next[W];
 #pragma unroll
     for (int u = 0; u < W; ++u) next[u] = __ldg(mine + (size_t)((k0 >> 1) + u) * L.np);
-    for (uint32_t k = k0; k < k1; k += kTrip) {
+    for (uint32_t k = k0; k < k1; k += kTrip) {  // (every part holds a multiple of 4 entries)
       uint32_t word[W];
 #pragma unroll
       for (int u = 0; u < W; ++u) {
         // the next trip's codes are requested before this trip's gathers are
         word[u] = next[u];
         const uint32_t kn = k + kTrip + 2u * u;
-        next[u] = kn < k1 ? __ldg(mine + (size_t)(kn >> 1) * L.np) : (kNullCode | (kNullCode << 16));
+        next[u] = kn < k1 ? __ldg(mine + (size_t)(kn >> 1) * L.np) : null_word;
       }
       uint32_t j[kTrip];
-      bool dead[kTrip];
-#pragma unroll
-      for (int u = 0; u < kTrip; ++u) {
-        const uint32_t code = (word[u >> 1] >> (16 * (u & 1))) & 0xffffu;
-        dead[u] = code == kNullCode;  // (kTrip == 2 can end a part of 4n entries on a null pair)
-        j[u] = dead[u] ? ia : start[code >> kRowShift][threadIdx.x] + (code & kOffMask);
-      }
       float4 pj[kTrip], vj[kTrip];
 #pragma unroll
       for (int u = 0; u < kTrip; ++u) {
-        pj[u] = __ldg(pos + j[u]);
-        vj[u] = __ldg(vel + j[u]);
+        const uint32_t code = (word[u >> 1] >> (16 * (u & 1))) & 0xffffu;
+        // a null entry (padding) reads the thread's own particle and is moved out of reach below
+        j[u] = code == kNullCode ? 0xffffffffu : start[code >> kRowShift][threadIdx.x] + (code & kOffMask);
+        const uint32_t jj = j[u] == 0xffffffffu ? ia : j[u];
+        const Rec8 r = ldg256(pv + 2u * (size_t)jj);  // one gather per neighbour
+        pj[u] = make_float4(r.a.x, r.a.y, r.b.x, r.b.y);
+        vj[u] = make_float4(r.c.x, r.c.y, r.d.x, r.d.y);
       }
 #pragma unroll
       for (int u = 0; u < kTrip; ++u) {
-        if (dead[u]) pj[u].x = -kFar;  // out of reach of both, parked or not
-        force_pair2(A, q, pj[u], vj[u], dead[u] ? 0xffffffffu : j[u], ia, has_b ? ib : 0xfffffffeu, c);
+        if (j[u] == 0xffffffffu) pj[u].x = -kFar;  // out of reach of both, parked or not
+        force_pair2(A, q, pj[u], vj[u], j[u], ia, has_b ? ib : 0xfffffffeu, c);
       }
     }
   }
@@ -398,8 +446,75 @@ __global__ void __launch_bounds__(kUB)
   if (has_b) acc[ib] = ghost_b ? zero4 : force_finish(Ab, __ldg(rho + ib), vb.w, c, true);
 }
 
+// ---- experiment (sphb_set_option("neighbor_kernel", 2 + log2 G): 4, 5, 6 for G = 4, 8, 16) ----------
+// Sub-warp-cooperative density: G lanes share ONE particle (a warp = 32 / G consecutive particles).
+// Lane g plans rows g, g + G, ...; the G lanes stride each row's run with consecutive 16-byte
+// loads (8 lanes = one 128-byte line), the row's hits come out of __ballot_sync as a bit mask per
+// (particle, row) — stored as the neighbour list, 9 words per particle — and the partial sums are
+// reduced with __shfl_xor_sync.  Built to be MEASURED against the pair kernels above (DESIGN.md
+// section 3): every candidate load serves ONE distance test instead of four, nothing is packed, and
+// a run of ~8 candidates fills a group's lanes only partly.  The forces pass that goes with it
+// searches on its own (k_forces_list).
+template <int G>
+__global__ void __launch_bounds__(128)
+    k_density_coop(float4* pos, float4* vel, const uint32_t* __restrict__ keys,
+                   const uint32_t* __restrict__ ftable, float* __restrict__ rho, float* __restrict__ prs,
+                   uint32_t* __restrict__ masks, StepConsts c) {
+  constexpr uint32_t kPer = 32 / G;  // particles per warp
+  constexpr int kOwn = (9 + G - 1) / G;
+  const uint32_t lane = threadIdx.x & 31u, g = lane % G, grp = lane / G;
+  const uint32_t warp = (blockIdx.x * 128u + threadIdx.x) >> 5;
+  const uint32_t i_raw = warp * kPer + grp;
+  const bool live = i_raw < c.n;
+  const uint32_t i = live ? i_raw : c.n - 1u;  // (idle groups shadow the last particle; nothing is written)
+  const float4 pi = pos[i];
+  uint32_t fx, fy, fz;
+  fine_coords_of(__ldg(keys + i), c, fx, fy, fz);
+  const CellFrac f = cell_frac(pi, fx, fy, fz, c);
+  uint32_t my_s[kOwn], my_e[kOwn];
+#pragma unroll
+  for (int q = 0; q < kOwn; ++q) {
+    const int row = q * G + (int)g;
+    my_s[q] = my_e[q] = 0;
+    if (row < 9) row_range(ftable, c, fx, fy, fz, f, row % 3 - 1, row / 3 - 1, my_s[q], my_e[q]);
+  }
+  float sum = 0.f;
+  const uint32_t gshift = grp * G;
+#pragma unroll
+  for (int row = 0; row < 9; ++row) {
+    const int owner = (int)(grp * G) + row % G;
+    const uint32_t s = __shfl_sync(0xffffffffu, my_s[row / G], owner),
+                   e = __shfl_sync(0xffffffffu, my_e[row / G], owner);
+    uint32_t rowmask = 0, shift = 0;
+    for (uint32_t j0 = s; __any_sync(0xffffffffu, j0 < e); j0 += G, shift += G) {
+      const uint32_t j = j0 + g;
+      bool hit = false;
+      if (j < e) {
+        const float4 pj = __ldg(reinterpret_cast<const float4*>(pos) + j);
+        const float dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
+        const float u = c.h2 - (dx * dx + dy * dy + dz * dz);
+        hit = u > 0.f;
+        if (hit) sum += u * u * u;
+      }
+      const uint32_t b = __ballot_sync(0xffffffffu, hit);
+      if (shift < 32u) rowmask |= ((b >> gshift) & ((1u << G) - 1u)) << shift;
+    }
+    if (live && g == 0) masks[(size_t)row * c.n + i] = rowmask;
+  }
+#pragma unroll
+  for (int o = G / 2; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+  if (live && g == 0) {
+    const float density = (c.mass * c.c_poly6) * sum;
+    const float pressure = tait_pressure(density, c);
+    rho[i] = density;
+    prs[i] = pressure;
+    reinterpret_cast<float*>(pos + i)[3] = pressure / (density * density);
+    reinterpret_cast<float*>(vel + i)[3] = c.mass / density;
+  }
+}
+
 inline unsigned blocks_for(uint32_t n) { return (n + kBlock - 1) / kBlock; }
-inline unsigned pair_blocks(uint32_t n) { return ((n + 1u) / 2u + kUB - 1) / kUB; }
+inline unsigned pair_blocks(uint32_t n, int block = kUB) { return ((n + 1u) / 2u + block - 1) / block; }
 inline size_t union_smem(uint32_t cap) { return (size_t)(cap + kUDump) * kUB * sizeof(uint16_t); }
 
 // round-1 layout inside the same pool: 64 + 2 u16 per particle, then one count byte per particle
@@ -432,22 +547,29 @@ int neighbor_kernels_init() {
   return 0;
 }
 
-int launch_density(float4* pos, float4* vel, const uint32_t* keys, const uint32_t* ftable,
-                   float* rho, float* prs, uint32_t* pool, uint32_t cap, const StepConsts& c,
-                   int variant, cudaStream_t s, bool queued) {
-  if (variant == 2) {  // round-1 kernel (A/B)
-    const unsigned pairs = (c.n + 1u) / 2u, grid = (pairs + kPairBlock - 1) / kPairBlock;
+int launch_density(float4* pos, float4* vel, const float4* pairs, float4* pv, const uint32_t* keys,
+                   const uint32_t* ftable, float* rho, float* prs, uint32_t* pool, uint32_t cap,
+                   const StepConsts& c, int variant, cudaStream_t s, bool queued) {
+  if (variant >= 4 && variant <= 6 && !queued) {  // experiment: G = 4 / 8 / 16 lanes per particle
+    const int G = 1 << (variant - 2);
+    const unsigned grid = (unsigned)(((size_t)c.n * G + 127) / 128);
+    if (G == 4) k_density_coop<4><<<grid, 128, 0, s>>>(pos, vel, keys, ftable, rho, prs, pool, c);
+    else if (G == 8) k_density_coop<8><<<grid, 128, 0, s>>>(pos, vel, keys, ftable, rho, prs, pool, c);
+    else k_density_coop<16><<<grid, 128, 0, s>>>(pos, vel, keys, ftable, rho, prs, pool, c);
+    return 1;
+  }
+  if (variant != 0) {  // round-1 kernel (A/B; it leaves p/rho^2 and m/rho in the w lanes of pos / vel)
+    const unsigned pairs_n = (c.n + 1u) / 2u, grid = (pairs_n + kPairBlock - 1) / kPairBlock;
     uint16_t* nlist = v1_list(pool);
     uint8_t* ncount = v1_count(pool, c.n);
     if (queued) k_density_pair<true><<<grid, kPairBlock, 0, s>>>(pos, vel, keys, ftable, rho, prs, nlist, ncount, c);
     else k_density_pair<false><<<grid, kPairBlock, 0, s>>>(pos, vel, keys, ftable, rho, prs, nlist, ncount, c);
     return 1;
   }
-  // variant 1 records the list too; its forces pass just does not use it
   if (queued)
-    k_density_union<true><<<pair_blocks(c.n), kUB, union_smem(cap), s>>>(pos, vel, keys, ftable, rho, prs, pool, cap, c);
+    k_density_union<true><<<pair_blocks(c.n), kUB, union_smem(cap), s>>>(pairs, vel, keys, ftable, rho, prs, pv, pool, cap, c);
   else
-    k_density_union<false><<<pair_blocks(c.n), kUB, union_smem(cap), s>>>(pos, vel, keys, ftable, rho, prs, pool, cap, c);
+    k_density_union<false><<<pair_blocks(c.n), kUB, union_smem(cap), s>>>(pairs, vel, keys, ftable, rho, prs, pv, pool, cap, c);
   return 1;
 }
 
@@ -466,11 +588,15 @@ int queue_refresh_neighbors(const QueueCtl* ctl, cudaStream_t s) {
   return (int)cudaMemcpyAsync(slot, &ctl->hot, sizeof(QueueHot), cudaMemcpyDeviceToDevice, s);
 }
 
-int launch_forces(const float4* pos, const float4* vel, const uint32_t* keys,
+int launch_forces(const float4* pos, const float4* vel, const float4* pv, const uint32_t* keys,
                   const uint32_t* ftable, const float* rho, const uint32_t* pool, float4* acc,
                   const StepConsts& c, int variant, cudaStream_t s, const uint32_t* ghost_ids,
                   bool queued) {
-  if (variant == 2) {
+  if ((variant == 1 || variant >= 4) && !ghost_ids && !queued) {  // forces by their own search
+    k_forces_list<<<blocks_for(c.n), kBlock, 0, s>>>(pos, vel, keys, ftable, rho, acc, c);
+    return 1;
+  }
+  if (variant != 0) {  // round-1 kernel, from the round-1 density pass's per-particle lists
     const uint16_t* nlist = v1_list(const_cast<uint32_t*>(pool));
     const uint8_t* ncount = v1_count(const_cast<uint32_t*>(pool), c.n);
     if (queued)
@@ -479,12 +605,10 @@ int launch_forces(const float4* pos, const float4* vel, const uint32_t* keys,
       k_forces_nlist<false><<<blocks_for(c.n), kBlock, 0, s>>>(pos, vel, keys, ftable, rho, nlist, ncount, acc, c, ghost_ids);
     return 1;
   }
-  if (queued)  // always from the recorded list (sphb_run_frame steps one at a time under variant 1)
-    k_forces_union<true><<<pair_blocks(c.n), kUB, 0, s>>>(pos, vel, keys, ftable, rho, pool, acc, c, ghost_ids);
-  else if (variant == 1 && !ghost_ids)
-    k_forces_list<<<blocks_for(c.n), kBlock, 0, s>>>(pos, vel, keys, ftable, rho, acc, c);
+  if (queued)
+    k_forces_union<true><<<pair_blocks(c.n, kFB), kFB, 0, s>>>(pv, keys, ftable, rho, pool, acc, c, ghost_ids);
   else
-    k_forces_union<false><<<pair_blocks(c.n), kUB, 0, s>>>(pos, vel, keys, ftable, rho, pool, acc, c, ghost_ids);
+    k_forces_union<false><<<pair_blocks(c.n, kFB), kFB, 0, s>>>(pv, keys, ftable, rho, pool, acc, c, ghost_ids);
   return 1;
 }
 

@@ -148,12 +148,14 @@ __device__ __forceinline__ float4 force_finish(const ForceAcc& A, float rho_i, f
 
 // Forces of one particle by its own search of the 9 row runs (no recorded list): what a thread
 // falls back to when the density pass could not record its neighbours.
+// (S = 1: separate position / velocity arrays; S = 2: the interleaved records pv, pos = pv, vel = pv + 1)
+template <int S>
 __device__ __noinline__ float4 forces_by_search(uint32_t i, const float4* __restrict__ pos,
                                                 const float4* __restrict__ vel,
                                                 const uint32_t* __restrict__ keys,
                                                 const uint32_t* __restrict__ ftable,
                                                 const float* __restrict__ rho, const StepConsts& c) {
-  const float4 pi = __ldg(pos + i), vi = __ldg(vel + i);
+  const float4 pi = __ldg(pos + (size_t)S * i), vi = __ldg(vel + (size_t)S * i);
   uint32_t fx, fy, fz;
   fine_coords_of(__ldg(keys + i), c, fx, fy, fz);
   const CellFrac f = cell_frac(pi, fx, fy, fz, c);
@@ -165,10 +167,10 @@ __device__ __noinline__ float4 forces_by_search(uint32_t i, const float4* __rest
       uint32_t s, e;
       row_range(ftable, c, fx, fy, fz, f, dy, dz, s, e);
       for (uint32_t j = s; j < e; ++j) {
-        const float4 pj = __ldg(pos + j);
+        const float4 pj = __ldg(pos + (size_t)S * j);
         const float dx = pi.x - pj.x, dy_ = pi.y - pj.y, dz_ = pi.z - pj.z;
         const float r2 = dx * dx + dy_ * dy_ + dz_ * dz_;
-        if (r2 < c.h2 && j != i) force_pair(A, pi, vi, pj, __ldg(vel + j), dx, dy_, dz_, r2, c);
+        if (r2 < c.h2 && j != i) force_pair(A, pi, vi, pj, __ldg(vel + (size_t)S * j), dx, dy_, dz_, r2, c);
       }
     }
   return force_finish(A, __ldg(rho + i), vi.w, c);

@@ -214,19 +214,19 @@ int sphb_slab_forces(sphb_engine* e, const float gmin[3], const float gmax[3]) {
     PassTimer t(e, SPHB_PASS_REORDER);
     const int in = e->cur, out = in ^ 1;
     int l = launch_reorder(perm, n, e->pos[in], e->vel[in], e->vhf[in], e->rank_cur, e->pos[out],
-                           e->vel[out], e->vhf[out], e->rank_prev, s);
+                           e->vel[out], e->vhf[out], e->rank_prev, s, false, e->pairs);
     std::swap(e->rank_cur, e->rank_prev);  // ids (+ ghost bit) now in compute order
     e->cur = out;
     t.done(l);
   }
   {
     PassTimer t(e, SPHB_PASS_DENSITY);
-    t.done(launch_density(e->pos[e->cur], e->vel[e->cur], skeys, e->ftable, e->rho, e->prs,
+    t.done(launch_density(e->pos[e->cur], e->vel[e->cur], e->pairs, e->pv, skeys, e->ftable, e->rho, e->prs,
                           e->npool, e->list_cap, c, 0, s));
   }
   {
     PassTimer t(e, SPHB_PASS_FORCES);
-    t.done(launch_forces(e->pos[e->cur], e->vel[e->cur], skeys, e->ftable, e->rho, e->npool,
+    t.done(launch_forces(e->pos[e->cur], e->vel[e->cur], e->pv, skeys, e->ftable, e->rho, e->npool,
                          e->acc, c, 0, s, e->rank_cur));
   }
   // every owned particle's dense slot in the advected arrays (ghosts are dropped there)

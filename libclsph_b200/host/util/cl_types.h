@@ -8,6 +8,17 @@
 
 #include <stdint.h>
 
+// The reference's common/structures.h reaches <iostream>, <string>, <vector>, <fstream> and
+// <sstream> through util/cl_boilerplate.h:4-8, and its callers rely on that (example/particles.cpp
+// uses std::ofstream / std::filebuf without including <fstream>): the same headers come along here.
+#ifdef __cplusplus
+#include <fstream>
+#include <iostream>
+#include <sstream>
+#include <string>
+#include <vector>
+#endif
+
 typedef int32_t cl_int;
 typedef uint32_t cl_uint;
 typedef float cl_float;

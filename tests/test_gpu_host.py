@@ -70,6 +70,31 @@ def test_command_line_driver(tmp_path):
     assert head.startswith("PGEOMETRY V5\nNPoints 512 NPrims 1")
 
 
+def test_reference_caller_runs(tmp_path):
+    """The reference's OWN example/particles.cpp, compiled unchanged against this repository's
+    headers and libraries (libclsph_b200.build.build_reference_caller; built where the reference
+    tree exists, the binary travels): `echo y |` 2 frames of 4 096 particles, as its README runs it."""
+    from libclsph_b200 import build as b
+    exe = b.build_reference_caller()
+    if not exe or not os.path.exists(exe):
+        pytest.skip("the reference caller was not built (no reference tree at build time)")
+    for d in ("fluid_properties", "simulation_properties", "scenes", "frames"):
+        os.makedirs(tmp_path / d)
+    write_json(str(tmp_path / "fluid_properties" / "water.json"), FLUIDS["water"])
+    write_json(str(tmp_path / "simulation_properties" / "small.json"),
+               dict(DEFAULT_SIM, particles_count=4096, simulation_time=0.03, serialize=True))
+    v, f = box_mesh(-1, 1, -2, 0, -1, 1)
+    write_obj(str(tmp_path / "scenes" / "box.obj"), [(v, f)])
+    r = subprocess.run([exe, "water", "small", "box.obj", ""], cwd=tmp_path, input="y\n", capture_output=True,
+                       text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "Simulating frame 2" in r.stdout and "Duration :" in r.stdout
+    geo = sorted(os.listdir(tmp_path / "frames"))
+    assert geo[0] == "frame0000001.geo" and len(geo) == 3  # initial + 2 frames of 1/60 s
+    assert os.path.getsize(tmp_path / "last_frame.bin") == 4096 * 80
+    assert open(tmp_path / "frames" / geo[-1]).read(40).startswith("PGEOMETRY V5\nNPoints 4096 NPrims 1")
+
+
 def _features(state, scales=None):
     """one row per particle: position, velocity, v_half, acceleration, density, each scaled by its
     largest magnitude"""

@@ -175,9 +175,12 @@ def test_free_run_matches_reference(port_oracle):
             assert abs(dt - float(g[f"s{s}_dt"])) <= 50 * TOL * float(g[f"s{s}_dt"])
 
 
-@pytest.mark.parametrize("variant", [0, 1])
+@pytest.mark.parametrize("variant", [0, 1, 2, 4, 5, 6])
 def test_neighbor_kernel_variants(variant):
-    """Both neighbour-pass variants (recorded list / independent search) against the fixture."""
+    """Every neighbour-pass variant against the fixture: 0 = the pair-list kernels (default),
+    1 = round-1 density + forces by their own search, 2 = the round-1 kernels (one list per
+    particle), 4 / 5 / 6 = the sub-warp-cooperative density pass with 4 / 8 / 16 lanes per particle
+    (kept as measured evidence)."""
     from libclsph_b200 import Engine
     g = np.load(os.path.join(GOLDEN, "steps_monkeybox_mucus.npz"))
     sc = np.load(os.path.join(GOLDEN, "scene_monkeybox_mucus.npz"))

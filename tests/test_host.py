@@ -293,3 +293,18 @@ def test_upload_deal_out_keeps_the_order_inside_a_slab(built, world, threads):
     for r in range(world):
         xs = stage["position"][start[r]:start[r + 1], 0]
         assert np.all((xs >= cuts[r]) & (xs < cuts[r + 1]))
+
+
+def test_reference_caller_compiles_unchanged():
+    """The reference's own example/particles.cpp (the boundary's caller) compiles
+    UNCHANGED against libclsph_b200/host + include/ and links against the two product libraries
+    (INTEGRATION.md section A).  Needs the reference tree: skipped where it is absent (GPU box)."""
+    import subprocess
+    from libclsph_b200 import build as b
+    if not os.path.exists(os.path.join(b.REFERENCE, "example", "particles.cpp")):
+        pytest.skip("no reference tree here")
+    exe = b.build_reference_caller(force=True)
+    assert exe and os.path.exists(exe)
+    # too few arguments: the reference's usage text and its exit code (-1 -> 255); no engine is made
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=60)
+    assert r.returncode == 255 and "Usage: ./sph <fluid_name>" in r.stdout
