@@ -308,6 +308,25 @@ int sphb_set_option(sphb_engine* e, const char* name, int value);
 int sphb_host_alloc(void** out, size_t bytes);
 int sphb_host_free(void* p);
 
+/* ---- entry points that allocate nothing ---------------------------------------------------
+ * No counterpart in the reference: added for callers
+ * that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  sphb_cell_table_noalloc computes the reference's cell table — cell_table[c] = number
+ * of particles whose Morton key (grid_index) is < c, c in [0, params->grid_cell_count): what
+ * sphb_download_debug returns as `cell_table`, without the c >= N quirk of kernels/sort.cl:61-78 —
+ * from DEVICE-resident positions (n x {x, y, z, -} floats, 16-byte aligned) under the grid in
+ * `params` (h, min_point, grid_size_*, grid_cell_count, e.g. from sphb_get_parameters), into the
+ * DEVICE array cell_table_dev (cell_table_entries >= grid_cell_count), enqueued on `stream` (a
+ * cudaStream_t, NULL = the default stream) of the CURRENT device; it does not synchronise.
+ * It calls no cudaMalloc / cudaFree / allocating routine: the scan's scratch (one partial sum per
+ * 2048 cells) is a static device array of SPHB_NOALLOC_MAX_CELLS / 2048 words = 8 KB that every
+ * GPU which loads the library holds until exit.  grid_cell_count > SPHB_NOALLOC_MAX_CELLS returns
+ * SPHB_ERR_CAPACITY (text from sphb_last_error(NULL)).  Every call shares that array: calls that
+ * overlap on one GPU (two streams, two threads) race; calls on one stream are ordered. */
+#define SPHB_NOALLOC_MAX_CELLS 4194304u
+int sphb_cell_table_noalloc(const float* positions_dev, uint32_t n, const sphb_params* params,
+                            uint32_t* cell_table_dev, uint32_t cell_table_entries, void* stream);
+
 const char* sphb_last_error(sphb_engine* e);
 /* text for a return code when no engine exists (sphb_create failed) */
 const char* sphb_error_string(int code);

@@ -44,6 +44,7 @@ SOURCES = {
     "kernels_slab.cu": ["-fmad=false"],
     "slab.cu": [],
     "slab_nccl.cu": [],
+    "noalloc.cu": ["-fmad=false"],
 }
 
 

@@ -82,7 +82,7 @@ SYMBOLS = [
     "sphb_slab_pack", "sphb_slab_unpack", "sphb_slab_forces", "sphb_slab_advect", "sphb_slab_commit",
     "sphb_slab_download", "sphb_compute_dt", "sphb_scene_build_ms", "sphb_upload_begin", "sphb_upload_commit",
     "sphb_nccl_unique_id", "sphb_slab_comm_init", "sphb_slab_start", "sphb_slab_step", "sphb_slab_bytes_sent",
-    "sphb_slab_phase_ms", "sphb_slab_resends", "sphb_slab_p2p_active",
+    "sphb_slab_phase_ms", "sphb_slab_resends", "sphb_slab_p2p_active", "sphb_cell_table_noalloc",
 ]
 
 
@@ -170,6 +170,7 @@ def lib():
         L.sphb_event_elapsed_ms.argtypes = [vp, i32, i32, C.POINTER(f32)]
         L.sphb_host_alloc.argtypes = [C.POINTER(vp), C.c_size_t]
         L.sphb_host_free.argtypes = [vp]
+        L.sphb_cell_table_noalloc.argtypes = [vp, u32, vp, vp, u32, vp]
         _lib = L
     return _lib
 
