@@ -388,6 +388,7 @@ def main():
                     help="N > 1: the library's own NCCL step driver, or the Python protocol driver")
     ap.add_argument("--p2p", type=int, default=1, help="N > 1, native driver: 1 = halo exchange over peer "
                     "memory when it can be mapped, 0 = ncclSend / ncclRecv")
+    ap.add_argument("--no-parity", action="store_true", help="N > 1: skip the parity check that precedes the timing")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-secondary", action="store_true", help="skip the 1 M dam-break leg")
     args = ap.parse_args()

@@ -15,6 +15,87 @@ import time
 import numpy as np
 
 
+def parity_check(B, dist, rank, world, local, n=262144, steps=3):
+    """Correctness BEFORE timing: an n-particle water block stepped `steps` times by the `world`
+    slab engines — once with the halo over NVLink peer memory (where it can be mapped), once over
+    ncclSend / ncclRecv — against ONE whole-domain engine on rank 0, per particle id.  Bar, as in
+    tests/test_gpu_slab.py: step 0 within 1e-5 with bit-exact grid_index and the same number of
+    advection attempts, later steps within 5e-4 (free-running trajectories), no particle lost or
+    owned twice, the same dt on every rank.  Returns a dict for the JSON line (rank 0) or None."""
+    from libclsph_b200 import Engine, host
+    from libclsph_b200.slab import CudaSlab, SlabDriver, equal_count_cuts
+
+    def rel(a, b):
+        a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+        return float(np.max(np.abs(a - b)) / max(float(np.max(np.abs(b))), 1e-30))
+
+    fields = dict(pos="position", vel="velocity", vhf="intermediate_velocity", acc="acceleration")
+    with tempfile.TemporaryDirectory() as tmp:
+        case = B.build_case(tmp, n, "dam_break")
+    params, terms, sc = case["params"], case["terms"], case["scene"]
+    p = host.lattice(n, case["volume"])
+    ids = np.arange(n, dtype=np.uint32)
+    ref = []
+    if rank == 0:  # the whole-domain engine; states re-ordered to id (= upload) order
+        e = Engine(params, terms, local)
+        e.set_scene(sc["bbs"], sc["transforms"], sc["rvertices"], sc["total_gridpoints"])
+        e.upload(p)
+        dt, order = 1.0 / 600.0, np.arange(n)
+        for _ in range(steps):
+            dt = e.step(dt)
+            st, dbg = e.download(), e.debug()
+            order = order[dbg["perm"]]
+            inv = np.empty(n, np.int64)
+            inv[order] = np.arange(n)
+            ref.append((st[inv], dt, dbg["attempts"]))
+        e.close()
+    x = p["position"][:, 0]
+    cuts = equal_count_cuts(x, world)
+    mine = (x >= np.float32(cuts[rank])) & (x < np.float32(cuts[rank + 1]))
+    result = dict(particles=n, steps=steps, tolerance=dict(step0=1e-5, later=5e-4), modes={})
+    ok_all = True
+    for p2p in (1, 0):
+        loc = CudaSlab(params, terms, sc, local, int(1.5 * n / world) + 65536, max(65536, n // 4))
+        loc.e.set_option("p2p_halo", p2p)
+        loc.comm_init(rank, world, dist)
+        drv = SlabDriver(loc, cuts, rank, world, dist)
+        drv.start(p[mine], ids[mine])
+        dt, worst, ok = 1.0 / 600.0, {}, True
+        for s in range(steps):
+            dt = drv.step(dt)
+            part, pid = loc.download()
+            gathered = [None] * world if rank == 0 else None
+            dist.gather_object((part, pid, dt, drv.attempts), gathered, dst=0)
+            if rank == 0:
+                allp = np.concatenate([g[0] for g in gathered])
+                allid = np.concatenate([g[1] for g in gathered])
+                ok &= len(allid) == n and len(np.unique(allid)) == n
+                if not ok:  # (keep taking part in the collectives of the remaining steps)
+                    continue
+                got = allp[np.argsort(allid)]
+                want, want_dt, want_attempts = ref[s]
+                tol = 1e-5 if s == 0 else 5e-4
+                errs = {k: rel(got[f][:, :3], want[f][:, :3]) for k, f in fields.items()}
+                errs["rho"] = rel(got["density"], want["density"])
+                errs["dt"] = abs(dt - want_dt) / want_dt
+                for k, v in errs.items():
+                    worst[k] = max(worst.get(k, 0.0), v)
+                ok &= all(v <= tol for v in errs.values()) and all(g[2] == gathered[0][2] for g in gathered)
+                if s == 0:
+                    ok &= bool(np.array_equal(got["grid_index"], want["grid_index"])) and gathered[0][3] == want_attempts
+        name = "peer_memory" if loc.p2p_active() else ("nccl_send_recv" if p2p == 0 else "nccl_send_recv(peer memory not mapped)")
+        loc.close()
+        dist.barrier()
+        if rank == 0:
+            result["modes"][name] = dict(ok=bool(ok), worst_relative_error={k: float(f"{v:.3g}") for k, v in worst.items()},
+                                         grid_index_step0="bit-exact" if ok else "see ok")
+            ok_all &= ok
+    flag = [ok_all]
+    dist.broadcast_object_list(flag, src=0)
+    result["ok"] = bool(flag[0])
+    return result
+
+
 def main_multi(args, rank, world, local, workload):
     import torch
     import torch.distributed as dist
@@ -29,6 +110,15 @@ def main_multi(args, rank, world, local, workload):
     if rank == 0:
         build.build_all()
     dist.barrier()
+    parity = None
+    if not getattr(args, "no_parity", False):
+        parity = parity_check(B, dist, rank, world, local)
+        if not parity["ok"]:  # a wrong answer is not timed
+            if rank == 0:
+                B.emit(dict(metric="SPH particle-steps/sec", value=None, n_gpus=world, error="parity_check failed",
+                            parity_check=parity))
+            dist.destroy_process_group()
+            return 1
     strong = getattr(args, "scaling", "weak") == "strong"
     n0 = int(args.particles)
     n_total = n0 if strong else n0 * world
@@ -188,6 +278,7 @@ def main_multi(args, rank, world, local, workload):
             ranks=per_rank)
         if e2e:
             line["e2e"] = e2e
+        line["parity_check"] = parity
         B.emit(line)
     loc.close()
     dist.barrier()

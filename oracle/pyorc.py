@@ -146,6 +146,13 @@ class Oracle:
         sizes = (C.c_uint32 * 4)()
         L.orc_sizes(sizes)
         assert list(sizes) == [80, 128, 20, 56], list(sizes)
+        # every host core this process may run on — NOT omp_get_max_threads(), which follows
+        # OMP_NUM_THREADS, and torch.distributed.run sets that to 1 for every rank
+        try:
+            self.cores = len(os.sched_getaffinity(0))
+        except AttributeError:
+            self.cores = os.cpu_count() or 1
+        L.orc_set_threads(self.cores)
 
     # ---- settings -------------------------------------------------------------------
     def settings(self, fluid, sim, particles_count=None, particle_mass=None):

@@ -11,6 +11,8 @@ Fixtures (all produced by the "reference" checker, never by the port or the CUDA
                      soup they came from, and a strided sample + checksum of the distance field
   steps_<name>.npz   k successive simulate_single_frame results from the reference lattice:
                      per step keys, permutation, cell table, rho, p, a, x, v, v_half, dt, attempts
+                     (steps_labyrinth_water / steps_river_water: a block thrown at the mesh —
+                     collisions on every step, advection retries on the first ones)
   advect_random.npz  one advection_collision over a seeded random state inside monkeybox
 """
 import hashlib
@@ -60,9 +62,11 @@ def scene_fixture(orc, name, root_dir, filename, threshold, soup, out):
     return sc, df
 
 
-def steps_fixture(orc, fluid, n, sc, df, nsteps, out):
+def steps_fixture(orc, fluid, n, sc, df, nsteps, out, prepare=None):
     params, terms, vol = orc.settings(FLUIDS[fluid], DEFAULT_SIM, particles_count=n)
     front = orc.init_particles(params, vol)
+    if prepare:
+        prepare(front)
     dt = np.float32(1.0) / params["target_fps"][0] * params["simulation_scale"][0]
     rec = dict(n=np.uint32(n), fluid=np.array(fluid), initial=front.copy(), params0=params.copy(),
                terms=terms.copy(), dt0=np.float32(dt))
@@ -146,6 +150,37 @@ def extra_scenes(orc):
         scene_fixture(orc, name, REF, fn, np.float32(hw) * 2, soup, os.path.join(HERE, f"scene_{name}.npz"))
 
 
+def collision_steps(orc):
+    """Step sequences INSIDE the collision-heavy meshes of SURVEY.md 8(d) config 5 (labyrinth.obj,
+    river.obj): the reference lattice of 2 744 water particles is moved to just above a face near
+    the middle of the mesh and thrown at it (seeded velocities, ~60 m/s downwards), so that
+    handle_collisions (kernels/collisionsv2.cl:249-336) fires for ~1/3 of the particles on every
+    step and the advection retry of sph_simulation.cpp:246-260 (attempts > 1) fires on the first
+    steps.  12 steps each."""
+    hw = float(orc.settings(FLUIDS["water"], DEFAULT_SIM)[0]["h"][0])
+    for name, fn, face in [("labyrinth_water", "labyrinth.obj", 81), ("river_water", "river.obj", 85)]:
+        soup = parse_obj_triangles(os.path.join(REF, "scenes", fn))
+        sc = orc.ref_scene(REF, fn, np.float32(hw) * 2)
+        df = orc.compute_df(sc["bbs"], sc["transforms"], sc["rvertices"], sc["total_gridpoints"])
+        c = soup.mean(axis=1)[face]
+
+        def prepare(front, c=c):
+            n = len(front)
+            rng = np.random.default_rng(5)
+            front["position"][:, 0] += np.float32(c[0])
+            front["position"][:, 1] += np.float32(c[1] + 0.03)
+            front["position"][:, 2] += np.float32(c[2])
+            v = np.zeros((n, 3), np.float32)
+            v[:, 1] = (-60 + rng.normal(0, 5, n)).astype(np.float32)
+            v[:, 0] = rng.normal(0, 3, n).astype(np.float32)
+            v[:, 2] = rng.normal(0, 3, n).astype(np.float32)
+            front["velocity"][:, :3] = v
+            front["intermediate_velocity"][:, :3] = v
+
+        print("steps", name)
+        steps_fixture(orc, "water", 2744, sc, df, 12, os.path.join(HERE, f"steps_{name}.npz"), prepare)
+
+
 def geo_fixture(orc):
     """One frame written by the reference's own houdini_file_saver (+ HoudiniFileDumpHelper)."""
     import ctypes as C
@@ -175,10 +210,14 @@ if __name__ == "__main__":
     if "--extra-scenes" in sys.argv:
         pyorc.build("reference")
         extra_scenes(pyorc.load("reference"))
+    elif "--collision-steps" in sys.argv:
+        pyorc.build("reference")
+        collision_steps(pyorc.load("reference"))
     elif "--geo-only" in sys.argv:
         pyorc.build("reference")
         geo_fixture(pyorc.load("reference"))
     else:
         main()
         extra_scenes(pyorc.load("reference"))
+        collision_steps(pyorc.load("reference"))
         geo_fixture(pyorc.load("reference"))

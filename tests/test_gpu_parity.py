@@ -63,7 +63,10 @@ def check_exact(dbg, state_key, want_perm, want_table, want_key, where=""):
 
 
 FIXTURES = [("steps_box_water", "scene_box_water"), ("steps_dambreak_water", "scene_dambreak_water"),
-            ("steps_monkeybox_mucus", "scene_monkeybox_mucus")]
+            ("steps_monkeybox_mucus", "scene_monkeybox_mucus"),
+            # a block thrown INTO the collision-heavy meshes: collisions on every step, advection
+            # retries (attempts > 1) on several (tests/golden/make_golden.py: collision_steps)
+            ("steps_labyrinth_water", "scene_labyrinth_water"), ("steps_river_water", "scene_river_water")]
 
 
 @pytest.mark.parametrize("steps,scene", FIXTURES)

@@ -3,7 +3,8 @@
   * 64 000 (default.json) water-in-box and mucus-in-monkeybox: live CPU oracle, re-seeded steps,
     same bar as tests/test_gpu_parity.py;
   * 1 000 000 dam break: one oracle step (the oracle needs ~10 s of all host cores for it);
-  * 16 777 216 water box: size-independent properties — sorted keys, the permutation is a
+  * 16 777 216 water box: one oracle step (all host cores, under a minute), and
+    size-independent properties — sorted keys, the permutation is a
     permutation and carries the keys, the cell table equals searchsorted(keys), densities of a
     random sample recomputed in float64 from the 27 cells, idempotent re-upload.
 """
@@ -49,10 +50,41 @@ def run_reseeded(orc, case, steps, where):
     print(where, "worst relative errors:", {k: f"{v:.2e}" for k, v in worst.items()})
 
 
+def run_free(orc, case, steps, where):
+    """`steps` FREE-RUNNING engine steps (no re-upload).  Every step is checked twice: strictly,
+    against the oracle stepped from the engine's own previous state (order bit-exact, floats to
+    TOL), and loosely (50 TOL: trajectories are chaotic) against the oracle's own free run."""
+    params, terms, sc = case["params"], case["terms"], case["scene"]
+    K, rho0 = float(params["K"][0]), float(params["fluid_density"][0])
+    df = oracle_df(orc, sc)
+    free, pf = case["particles"].copy(), params.copy()
+    dt_free = dt = float(np.float32(1.0) / params["target_fps"][0] * params["simulation_scale"][0])
+    with new_engine(case) as e:
+        e.upload(case["particles"])
+        for s in range(steps):
+            prev, prev_dt = e.download(), dt
+            dt = e.step(dt)
+            out, dbg = e.download(), e.debug()
+            p = e.parameters().copy()
+            r = orc.step(prev, p, terms.copy(), df, sc["bbs"], prev_dt)
+            check_exact(dbg, out["grid_index"], r["perm"], r["cell_table"], prev["grid_index"], f"{where} free step {s}")
+            assert e.parameters().tobytes() == p.tobytes()
+            check_floats(state_arrays(out), state_arrays(prev), K, rho0, f"{where} free step {s}")
+            assert abs(dt - r["dt"]) <= TOL * r["dt"] and dbg["attempts"] == r["attempts"]
+            dt_free = orc.step(free, pf, terms.copy(), df, sc["bbs"], dt_free)["dt"]
+            got, want = state_arrays(out), state_arrays(free)
+            for k in ("pos", "vel", "vhf", "acc", "rho"):
+                assert rel_err(got[k], want[k]) <= 50 * TOL, (where, s, k)
+            assert abs(dt - dt_free) <= 50 * TOL * dt_free
+
+
 def test_default_config_64000_water_box(port_oracle, tmp_path):
-    """BASELINE.json configs[0]: default.json + water.json in (a generated copy of) box.obj."""
+    """BASELINE.json configs[0]: default.json + water.json in (a generated copy of) box.obj, to the
+    horizon SURVEY.md 8(d) names: 10 sub-steps free-running, and the per-step re-seeded check
+    over 100 steps (the block falls ~2 cm and compresses against the floor in that time)."""
     case = make_case(tmp_path, "water", 64000, box=(-1, 1, -2, 0, -1, 1))
-    run_reseeded(port_oracle, case, 3, "64000 water box")
+    run_free(port_oracle, case, 10, "64000 water box")
+    run_reseeded(port_oracle, case, 100, "64000 water box")
 
 
 def test_mucus_64000_monkeybox(port_oracle, tmp_path):
@@ -70,6 +102,18 @@ def test_dam_break_1m_one_step(port_oracle, tmp_path):
     """BASELINE.json configs[2]: 1 M particle dam break, one step against the oracle."""
     case = make_case(tmp_path, "water", 1000000)
     run_reseeded(port_oracle, case, 1, "1M dam break")
+
+
+def test_water_box_16m_one_oracle_step(port_oracle, tmp_path):
+    """BASELINE.json configs[3] at its full size on one GPU, against the ORACLE (not only against
+    properties): 16 777 216 particles, one step — keys, permutation and cell table bit-exact;
+    rho, p, a, x, v, v_half and dt to 1e-5; same number of advection attempts.  The oracle step
+    takes all host cores for ~30-60 s."""
+    n = 16777216
+    side = float(np.cbrt(n * 0.05 / 998.29))
+    half = side / 2 + 0.082  # the bench's water box: x, z in [-4.8, 4.8], y in [-0.06, 12]
+    case = make_case(tmp_path, "water", n, box=(-half, half, -0.06, 1.27 * side, -half, half))
+    run_reseeded(port_oracle, case, 1, "16.7M water box")
 
 
 @pytest.mark.parametrize("mode", ["step", "frame"])

@@ -10,7 +10,9 @@ import pytest
 from common import GOLDEN, state_arrays
 
 STEP_FIXTURES = [("steps_box_water", "scene_box_water"), ("steps_dambreak_water", "scene_dambreak_water"),
-                 ("steps_monkeybox_mucus", "scene_monkeybox_mucus")]
+                 ("steps_monkeybox_mucus", "scene_monkeybox_mucus"),
+                 # a block thrown INTO the collision-heavy meshes (make_golden.py: collision_steps)
+                 ("steps_labyrinth_water", "scene_labyrinth_water"), ("steps_river_water", "scene_river_water")]
 
 
 def load_scene(name):
@@ -67,6 +69,25 @@ def test_steps_match_reference(port_oracle, steps, scene):
         st = state_arrays(front)
         for k, v in st.items():
             assert np.array_equal(bits(v), bits(g[f"s{s}_{k}"])), (s, k)
+
+
+@pytest.mark.parametrize("steps", ["steps_labyrinth_water", "steps_river_water"])
+def test_collision_fixtures_do_collide_and_retry(steps):
+    """The in-mesh fixtures are worth having only if handle_collisions fires DURING the run
+    (kernels/collisionsv2.cl:249-336) and the advection is retried (sph_simulation.cpp:246-260)."""
+    g = np.load(os.path.join(GOLDEN, steps + ".npz"))
+    attempts = [int(g[f"s{s}_attempts"]) for s in range(int(g["nsteps"]))]
+    assert int(g["nsteps"]) >= 10 and max(attempts) > 1
+    collided = []
+    vh = g["initial"]["intermediate_velocity"][:, :3]
+    for s in range(int(g["nsteps"])):
+        free = vh[g[f"s{s}_perm"]] + g[f"s{s}_acc"] * g[f"s{s}_dt"]  # v' = v_half + a dt without a response
+        if attempts[s] == 1:  # (after a retry the dt of the last attempt is not the step's output dt)
+            dt_used = np.float32(g["dt0"]) if s == 0 else g[f"s{s-1}_dt"]
+            free = vh[g[f"s{s}_perm"]] + g[f"s{s}_acc"] * np.float32(dt_used)
+            collided.append(int(np.any(free != g[f"s{s}_vhf"], axis=1).sum()))
+        vh = g[f"s{s}_vhf"]
+    assert len(collided) >= 8 and min(collided) > 200, collided
 
 
 def test_settings_match_reference(port_oracle):
