@@ -163,6 +163,45 @@ def physical_device(local_index):
     return local_index
 
 
+def kernel_source_hash():
+    """sha256 (16 hex digits) of the sources the two neighbour passes are built from: what an ncu
+    capture under profiles/ was taken on, and what this run executes."""
+    import hashlib
+    h = hashlib.sha256()
+    for f in ("kernels_neighbors.cu", "neighbors_common.cuh", "neighbors_v1.cuh", "common.cuh"):
+        h.update(open(os.path.join(ROOT, "libclsph_b200", "csrc", f), "rb").read())
+    return h.hexdigest()[:16]
+
+
+def ncu_counters(which, n):
+    """(record, reason): the committed ncu counters of neighbour pass `which` at n particles, or
+    (None, why not) when there is none for the sources this run executes."""
+    path = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    try:
+        doc = json.load(open(path))
+    except Exception as ex:
+        return None, f"profiles/ncu_traffic.json unreadable ({ex})"
+    if doc.get("source_hash") != kernel_source_hash():
+        return None, (f"stale: profiles/ncu_traffic.json was captured on kernel sources {doc.get('source_hash')} "
+                      f"(commit {doc.get('commit')}), this run executes {kernel_source_hash()}")
+    rec = doc.get(which, {}).get(str(n))
+    return (rec, None) if rec else (None, f"no capture at {n} particles")
+
+
+def opencl_cpu_runtime():
+    """BASELINE.md section 1 / SURVEY 8(d): probe for an OpenCL CPU runtime the reference's own host
+    path could run on (it is timed beside the GPU only if one exists)."""
+    import glob
+    found = []
+    for pat in ("/etc/OpenCL/vendors/*.icd", "/usr/lib/x86_64-linux-gnu/libpocl*", "/usr/lib*/libpocl*",
+                "/usr/local/lib/libpocl*", "/usr/include/CL/cl.h", "/usr/lib/x86_64-linux-gnu/libOpenCL.so*"):
+        found += glob.glob(pat)
+    cpu = [f for f in found if "pocl" in f.lower() or "intel" in f.lower()]
+    if not cpu:
+        return "none found" + (f" (only: {', '.join(sorted(found))})" if found else "")
+    return "found: " + ", ".join(sorted(found))
+
+
 def measured_peak():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(path):
@@ -185,13 +224,27 @@ def pinned_particles(n):
     return np.frombuffer(buf, dtype=PARTICLE), ptr
 
 
-def run_gpu_case(case, steps, warmup, device, e2e_steps, sampler=None, options=()):
+def jitter_lattice(stage, case, amount):
+    """SURVEY.md 8(d) config 4's non-lattice variant: every particle displaced by uniform
+    +-amount lattice spacings per axis, mt19937(seed = 12345)."""
+    n = case["n"]
+    spacing = float(np.float32(np.cbrt(np.float32(case["volume"]))) / np.float32(np.ceil(np.cbrt(np.float32(n)))))
+    rng = np.random.Generator(np.random.MT19937(12345))
+    for lo in range(0, n, 1 << 22):  # in pieces: 16.7 M x 3 doubles at once would be 400 MB
+        hi = min(n, lo + (1 << 22))
+        d = (rng.random((hi - lo, 3), dtype=np.float32) * np.float32(2) - np.float32(1)) * np.float32(amount * spacing)
+        stage["position"][lo:hi, :3] += d
+
+
+def run_gpu_case(case, steps, warmup, device, e2e_steps, sampler=None, options=(), jitter=0.0):
     """Times `steps` resident steps (after `warmup`), then `e2e_steps` host-buffer steps."""
     from libclsph_b200 import Engine, PASS_NAMES, host
     n = case["n"]
     sc = case["scene"]
     stage, stage_ptr = pinned_particles(n)
     host.lattice(n, case["volume"], out=stage)
+    if jitter:
+        jitter_lattice(stage, case, jitter)
     e = Engine(case["params"], case["terms"], device)
     for k, v in options:
         e.set_option(k, v)
@@ -227,7 +280,9 @@ def run_gpu_case(case, steps, warmup, device, e2e_steps, sampler=None, options=(
     e.profile(False)
     e.set_option("side_stream", 1)
     params_now = e.parameters()
+    list_stats = e.neighbor_list_stats() if not any(k == "neighbor_kernel" and v for k, v in options) else None
     res = dict(ms_total=ms, ms_profiled_serial=ms_serial, launches=launches, pass_ms=pass_ms, pass_launches=pass_launches,
+               list_stats=list_stats,
                clocks=clocks, dt=dt, grid=[int(params_now[k][0]) for k in ("grid_size_x", "grid_size_y", "grid_size_z")],
                grid_cell_count=int(params_now["grid_cell_count"][0]))
     # the frame loop as one engine call (sphb_run_frame): the same steps enqueued without a host
@@ -311,16 +366,65 @@ def run_gpu_case(case, steps, warmup, device, e2e_steps, sampler=None, options=(
     return res
 
 
-def cpu_arm(budget_s, steps, warmup, kind_pref="reference"):
+def list_summary(st, n):
+    """The neighbour lists of a step, per particle (sphb_neighbor_list_stats)."""
+    if not st:
+        return None
+    pairs = (n + 1) // 2
+    return dict(list_overflows=st["overflowed_pairs"], overflow_fraction=st["overflowed_pairs"] / pairs,
+                split_pairs_fraction=st["split_pairs"] / pairs, entries_per_pair=st["entries"] / pairs,
+                longest_list=st["longest"])
+
+
+def run_dam_break_horizon(case, device, warmup, horizon=200, window=20):
+    """the dam break over steps 0-`horizon`, the first and the last
+    `window` steps timed separately (the rest lattice, then the collapsing, splashing block).  The
+    engine is warmed up on the same state first, then the lattice is uploaded again."""
+    from libclsph_b200 import Engine, host
+    n, sc = case["n"], case["scene"]
+    stage, stage_ptr = pinned_particles(n)
+    host.lattice(n, case["volume"], out=stage)
+    e = Engine(case["params"], case["terms"], device)
+    e.set_scene(sc["bbs"], sc["transforms"], sc["rvertices"], sc["total_gridpoints"])
+    e.upload_ptr(stage_ptr.value, n)
+    e.run_frame(1.0 / 600.0, 1.0, warmup)
+    e.upload_ptr(stage_ptr.value, n)
+    out, dt, done_total = {}, 1.0 / 600.0, 0
+    for name, k, timed in ((f"steps_0_{window}", window, True), ("between", horizon - 2 * window, False),
+                           (f"steps_{horizon - window}_{horizon}", window, True)):
+        e.event_record(0)
+        dt, _, done = e.run_frame(dt, 1.0, k)
+        e.event_record(1)
+        done_total += done
+        if timed:
+            ms = e.event_elapsed_ms(0, 1)
+            out[name] = dict(ms_per_step=ms / max(1, done), value=n * done / (ms * 1e-3), steps=done,
+                             neighbor_lists=list_summary(e.neighbor_list_stats(), n), dt=dt)
+    p = e.parameters()
+    out["grid_after"] = [int(p[k][0]) for k in ("grid_size_x", "grid_size_y", "grid_size_z")]
+    out["steps_done"] = done_total
+    e.download_ptr(stage_ptr.value)
+    out["finite"] = bool(np.isfinite(stage["position"][:: max(1, n // 4096), :3]).all())
+    e.close()
+    del stage
+    from libclsph_b200 import lib
+    lib().sphb_host_free(stage_ptr)
+    return out
+
+
+def cpu_arm(budget_s, steps, warmup, kind_pref="reference", fixed_n=None):
     """The reference's CPU implementation of the step (oracle/_ref = its own kernels/sph.cl +
-    scene.cpp compiled as C++, OpenMP over work-items; else the plain-C port) on a bounded
-    water-box sample sized so that (steps + warmup) steps take about budget_s seconds."""
+    scene.cpp compiled as C++, OpenMP over work-items; else the plain-C port) on EVERY host core
+    this process may run on (its affinity mask — not OMP_NUM_THREADS, which torch.distributed.run
+    sets to 1).  fixed_n: time exactly that many particles (the headline configuration); else a
+    bounded water-box sample sized so that (steps + warmup) steps take about budget_s seconds."""
     from oracle import pyorc
     kind = kind_pref if pyorc.available(kind_pref) else "port"
     if kind == "port" and not pyorc.available("port"):
         pyorc.build("port")
     orc = pyorc.load(kind)
-    cores = orc.lib.orc_get_threads() or (os.cpu_count() or 1)
+    orc.lib.orc_set_threads(orc.cores)
+    cores = orc.lib.orc_get_threads()
 
     def prepare(n, tmp):
         p, t, vol = orc.settings(WATER, dict(SIM, particles_count=int(n)))
@@ -346,16 +450,20 @@ def cpu_arm(budget_s, steps, warmup, kind_pref="reference"):
         return time.perf_counter() - t0
 
     with tempfile.TemporaryDirectory() as tmp:
-        probe_n = 32 ** 3
-        rate = probe_n / max(run(probe_n, 1, 1, tmp), 1e-6)  # particle-steps/s, calibration
-        want = rate * budget_s / max(1, steps + warmup)
-        side = int(max(32, min(160, np.floor(np.cbrt(want)))))
-        n = side ** 3
+        if fixed_n:
+            n, side = int(fixed_n), None
+        else:
+            probe_n = 32 ** 3
+            rate = probe_n / max(run(probe_n, 1, 1, tmp), 1e-6)  # particle-steps/s, calibration
+            want = rate * budget_s / max(1, steps + warmup)
+            side = int(max(32, min(160, np.floor(np.cbrt(want)))))
+            n = side ** 3
         secs = run(n, steps, warmup, tmp)
+    shape = f" ({side}^3)" if side else ""
     return dict(value=n * steps / secs, unit="particle-steps/s", cores=int(cores), kind=kind,
-                sample=f"{n} particle ({side}^3) water box, {steps} steps after {warmup} warm-up, "
-                       f"{secs:.1f} s; same physics and scene family as the GPU workload",
-                n=n, seconds=secs)
+                sample=f"{n} particle{shape} water box, {steps} step(s) after {warmup} warm-up, "
+                       f"{secs:.1f} s on {cores} host threads; same physics and scene family as the GPU workload",
+                n=n, seconds=secs, steps=steps, warmup=warmup)
 
 
 def emit(line):
@@ -402,15 +510,27 @@ def main():
     if args.impl == "reference":
         if rank != 0:
             return 0
-        cb = cpu_arm(max(30.0, 12.0 * (args.steps + args.warmup)), args.steps, args.warmup)
-        line = dict(metric="SPH particle-steps/sec", value=cb["value"], unit="particle-steps/s", impl="reference",
-                    n_gpus=args.gpus, steps=args.steps, warmup=args.warmup,
-                    ms_per_step=1e3 * cb["seconds"] / args.steps, higher_is_better=True, scaling="weak",
+        # The headline configuration itself: ONE timed step at --particles after ONE warm-up step
+        # (16.7 M: ~25 s per step on 16 cores), whatever --steps / --warmup ask for — a CPU step is
+        # the same work every time, and K + W of them would take the better part of an hour.  At
+        # N > 1 the GPU arm's workload is N such blocks; the CPU arm still times one block (its
+        # particle-steps/s do not depend on how many blocks stand side by side) and says so.
+        full = cpu_arm(0.0, 1, 1, fixed_n=args.particles)
+        small = cpu_arm(0.0, 2, 1, fixed_n=160 ** 3) if args.particles > 160 ** 3 else None
+        same = args.gpus == 1
+        line = dict(metric="SPH particle-steps/sec", value=full["value"], unit="particle-steps/s", impl="reference",
+                    n_gpus=args.gpus, steps=full["steps"], warmup=full["warmup"],
+                    requested=dict(steps=args.steps, warmup=args.warmup),
+                    ms_per_step=1e3 * full["seconds"] / full["steps"], higher_is_better=True, scaling="weak",
                     vs_baseline=None, dtype="f32", data="synthetic",
-                    config=dict(workload=workload, timed_sample=cb["sample"]),
-                    cpu_baseline=dict(value=cb["value"], unit=cb["unit"], cores=cb["cores"], kind=cb["kind"],
-                                      sample=cb["sample"]),
-                    e2e=dict(value=cb["value"], unit="particle-steps/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0))
+                    config=dict(workload=workload, timed_sample=full["sample"], same_config=same,
+                                same_config_note=None if same else
+                                f"the GPU arm steps {args.gpus} such blocks side by side; the CPU arm times one",
+                                second_sample=small and dict(value=small["value"], sample=small["sample"])),
+                    cpu_baseline=dict(value=full["value"], unit=full["unit"], cores=full["cores"], kind=full["kind"],
+                                      sample=full["sample"]),
+                    opencl_cpu_runtime=opencl_cpu_runtime(),
+                    e2e=dict(value=full["value"], unit="particle-steps/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0))
         emit(line)
         return 0
 
@@ -432,7 +552,19 @@ def main():
                              value=c2["n"] * max(args.steps, 20) / (r2["ms_total"] * 1e-3), unit="particle-steps/s",
                              ms_per_step=r2["ms_total"] / max(args.steps, 20),
                              pass_ms_per_step={k: v / max(args.steps, 20) for k, v in r2["pass_ms"].items()},
-                             frame_loop_ms_per_step=r2["frame_loop_ms_per_step"])
+                             frame_loop_ms_per_step=r2["frame_loop_ms_per_step"],
+                             neighbor_lists=list_summary(r2["list_stats"], c2["n"]),
+                             horizon_0_200=run_dam_break_horizon(c2, local, warmup))
+            # SURVEY 8(d) config 4's non-lattice variant: the headline box with every particle
+            # displaced by +-0.1 spacings (mt19937(12345)) — irregular neighbour counts
+            rj = run_gpu_case(case, args.steps, warmup, local, 0, jitter=0.1)
+            secondary["jittered_16M"] = dict(
+                workload=f"the headline {case['n']}-particle box, every particle displaced by uniform +-0.1 lattice "
+                         "spacings per axis (mt19937 seed 12345), SURVEY.md 8(d) config 4",
+                value=case["n"] * args.steps / (rj["ms_total"] * 1e-3), unit="particle-steps/s",
+                ms_per_step=rj["ms_total"] / args.steps,
+                pass_ms_per_step={k: v / args.steps for k, v in rj["pass_ms"].items() if v},
+                neighbor_lists=list_summary(rj["list_stats"], case["n"]))
             # collision-heavy leg (SURVEY 8d config 5's size, config 2's fluid and mesh): the
             # advection pass with the triangle bin, and with the reference's all-faces scan
             c3 = build_case(tmp, 4096000, "mucus_monkeybox")
@@ -442,7 +574,8 @@ def main():
                 r3 = run_gpu_case(c3, k3, warmup, local, 0, options=(("triangle_bin", opt),))
                 legs[name] = dict(ms_per_step=r3["ms_total"] / k3, value=c3["n"] * k3 / (r3["ms_total"] * 1e-3),
                                   advect_ms_per_launch=r3["pass_ms"]["advect"] / max(1, r3["pass_launches"]["advect"]) * 2,
-                                  pass_ms_per_step={k: v / k3 for k, v in r3["pass_ms"].items() if v})
+                                  pass_ms_per_step={k: v / k3 for k, v in r3["pass_ms"].items() if v},
+                                  neighbor_lists=list_summary(r3["list_stats"], c3["n"]))
             secondary["collision_heavy"] = dict(
                 workload="synthetic 4096000-particle mucus.json lattice in the 978-face monkeybox scene "
                          "(BASELINE.json configs[1] physics and mesh at configs[4]'s particle count)",
@@ -455,11 +588,36 @@ def main():
     dom = max(("density", "forces"), key=lambda k: r["pass_ms"][k])
     f_ms = r["pass_ms"][dom] / max(1, r["pass_launches"][dom])
     achieved = ALGO_BYTES[dom] * n / (f_ms * 1e-3) / 1e9
-    traffic = None
+    # ncu counters of that kernel, taken on THESE sources (else null + why): DRAM traffic per launch,
+    # and the two other roofs — issue slots (one warp instruction per clock and SM sub-partition)
+    # and the L1 data pipe (one wavefront per clock and SM) — at the clock this run measured
+    counters, stale = ncu_counters(dom, n)
+    traffic = counters["dram_bytes"] if counters else None
+    clock_hz = 1e6 * float((r["clocks"] or {}).get("sm_mhz") or 0.0)
+    sms = 148
     try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))[dom].get(str(n))
+        import pynvml
+        pynvml.nvmlInit()
+        hdl = pynvml.nvmlDeviceGetHandleByIndex(physical_device(local))
+        sms = int(pynvml.nvmlDeviceGetNumGpuCores(hdl)) // 128 or 148
     except Exception:
         pass
+    other_roofs = {}
+    if counters and clock_hz > 0:
+        t = f_ms * 1e-3
+        other_roofs = dict(
+            issue_slots=dict(achieved=counters["warp_inst"] / t, peak=sms * 4 * clock_hz, unit="warp instructions/s",
+                             frac=counters["warp_inst"] / t / (sms * 4 * clock_hz),
+                             lane_efficiency=counters.get("lane_efficiency"),
+                             thread_instructions_per_particle=counters.get("thread_inst", 0.0) / n),
+            l1_data_pipe=dict(achieved=counters["l1_wavefronts"] / t, peak=sms * clock_hz, unit="wavefronts/s",
+                              frac=counters["l1_wavefronts"] / t / (sms * clock_hz)),
+            fp32=dict(note="thread instructions x 2 flop as an upper bound of the fp32 work", unit="TFLOP/s",
+                      achieved=2 * counters.get("thread_inst", 0.0) / t / 1e12, peak=sms * 128 * 2 * clock_hz / 1e12,
+                      frac=counters.get("thread_inst", 0.0) / t / (sms * 128 * clock_hz)))
+    binding = max(other_roofs, key=lambda k: other_roofs[k]["frac"]) if other_roofs else None
+    if binding and other_roofs[binding]["frac"] < achieved / peak:
+        binding = "hbm"
     radix_passes = (max(1, r["grid_cell_count"].bit_length()) + 7) // 8
     step_bytes = STEP_BYTES_FUSED.get(radix_passes, 301)
     per_pass = {}
@@ -483,27 +641,35 @@ def main():
         frame_loop=dict(ms_per_step=r["frame_loop_ms_per_step"], steps_without_host_round_trip=r["queued_steps"],
                         note="sphb_run_frame over %d steps per mode, each from the same state; `value` is "
                              "its default mode (device_loop_graph up to 6 M particles)" % args.steps),
-        roofline=dict(bound="hbm", kernel={"density": "density + pressure pass (k_density_pair)",
-                                           "forces": "forces pass (k_forces_nlist)"}[dom],
+        roofline=dict(bound="hbm", kernel={"density": "density + pressure pass (k_density_union)",
+                                           "forces": "forces pass (k_forces_union)"}[dom],
                       achieved=achieved, peak=peak, unit="GB/s", frac=achieved / peak, traffic=traffic,
+                      traffic_note=stale or "ncu dram__bytes_read.sum + dram__bytes_write.sum per launch, captured on "
+                                            "these kernel sources (profiles/ncu_traffic.json)",
                       peak_source=peak_src, algorithmic_bytes_per_particle=ALGO_BYTES[dom], launch_ms=f_ms,
-                      note="both neighbour passes are L1/issue-bound, not HBM-bound (DESIGN.md section 3); "
-                           "traffic = ncu dram bytes per launch, mostly the neighbour list handed to the forces pass",
+                      binding_bound=binding, other_roofs=other_roofs,
+                      both_passes={k: dict(launch_ms=r["pass_ms"][k] / max(1, r["pass_launches"][k]),
+                                           frac=ALGO_BYTES[k] * n / (r["pass_ms"][k] / max(1, r["pass_launches"][k]) * 1e-3)
+                                           / 1e9 / peak) for k in ("density", "forces")},
+                      note="`frac` is the HBM fraction the contract asks for (algorithmic bytes / time / measured "
+                           "copy peak); what BINDS the kernel is `binding_bound` (DESIGN.md section 3): the passes "
+                           "are bound by the L1 data pipe, not by HBM",
                       whole_step=dict(algorithmic_bytes_per_particle=step_bytes,
                                       achieved=step_bytes * n / (ms_step * 1e-3) / 1e9,
                                       frac=step_bytes * n / (ms_step * 1e-3) / 1e9 / peak)),
-        passes=per_pass)
+        passes=per_pass, neighbor_lists=list_summary(r["list_stats"], n), opencl_cpu_runtime=opencl_cpu_runtime())
     if "e2e_s" in r:
-        line["e2e"] = dict(value=n * r["e2e_steps"] / r["e2e_s"], unit="particle-steps/s",
+        line["e2e"] = dict(value=n * r["e2e_steps"] / r["e2e_serial_s"], unit="particle-steps/s",
                            h2d_bytes_per_step=80 * n, d2h_bytes_per_step=80 * n + 32, steps=r["e2e_steps"],
                            finite=r["finite"],
-                           note="every step: upload of all particles (80-byte AoS) from pinned host memory, one step, "
-                                "read-back of all particles, through the C ABI; independent batches, so the upload "
-                                "of the next batch and the read-back of the previous one overlap the step "
-                                "(sphb_upload_begin/_commit, sphb_download_begin/_wait)",
-                           serial=dict(value=n * r["e2e_steps"] / r["e2e_serial_s"], unit="particle-steps/s",
-                                       note="the same without overlap: upload, step, download, each waiting for the "
-                                            "one before (a chain of dependent steps through host memory)"),
+                           note="a chain of DEPENDENT steps through host memory, through the C ABI: every step uploads "
+                                "all particles (80-byte AoS) from pinned host memory, steps once, and reads all "
+                                "particles back, each waiting for the one before",
+                           pipelined=dict(value=n * r["e2e_steps"] / r["e2e_s"], unit="particle-steps/s",
+                                          note="the same three things per step over INDEPENDENT batches, so that the "
+                                               "upload of the next batch and the read-back of the previous one "
+                                               "overlap the step (sphb_upload_begin/_commit, "
+                                               "sphb_download_begin/_wait)"),
                            simulate_frames=dict(
                                value=n * r["frames"][0] * r["frames"][1] / r["frames_s"], unit="particle-steps/s",
                                note="the copy pattern of sph_simulation::simulate(): state resident, %d frames of %d "

@@ -96,33 +96,15 @@ def parity_check(B, dist, rank, world, local, n=262144, steps=3):
     return result
 
 
-def main_multi(args, rank, world, local, workload):
-    import torch
-    import torch.distributed as dist
-    import __main__ as B  # bench.py itself (it owns the real stdout)
-    if not hasattr(B, "emit"):
-        import bench as B
-    from libclsph_b200 import PARTICLE, build, host
+def run_config(a, B, torch, dist, rank, world, local, workload):
+    """One timed configuration (a.scaling, a.scene, a.particles, a.steps ...) -> the JSON line's
+    dict on rank 0, None elsewhere."""
+    from libclsph_b200 import PARTICLE, host
     from libclsph_b200.slab import CudaSlab, SlabDriver, equal_count_cuts
-
-    torch.cuda.set_device(local)
-    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    if rank == 0:
-        build.build_all()
-    dist.barrier()
-    parity = None
-    if not getattr(args, "no_parity", False):
-        parity = parity_check(B, dist, rank, world, local)
-        if not parity["ok"]:  # a wrong answer is not timed
-            if rank == 0:
-                B.emit(dict(metric="SPH particle-steps/sec", value=None, n_gpus=world, error="parity_check failed",
-                            parity_check=parity))
-            dist.destroy_process_group()
-            return 1
-    strong = getattr(args, "scaling", "weak") == "strong"
-    n0 = int(args.particles)
+    warmup = max(a.warmup, 3)
+    strong = getattr(a, "scaling", "weak") == "strong"
+    n0 = int(a.particles)
     n_total = n0 if strong else n0 * world
-    warmup = max(args.warmup, 3)
 
     with tempfile.TemporaryDirectory() as tmp:
         B.write_json(os.path.join(tmp, "fluid.json"), B.WATER)
@@ -150,7 +132,7 @@ def main_multi(args, rank, world, local, workload):
             cuts = [-np.inf] + [float(x0 + np.float32(r) * pitch - np.float32(spacing) / 2) for r in range(1, world)] + [np.inf]
             d = B.water_box_dims(n0)
             dims = (d[0], float(d[1] + np.float32(world - 1) * pitch), d[2], d[3], d[4], d[5])
-        scene_name = getattr(args, "scene", "box")
+        scene_name = getattr(a, "scene", "box")
         if scene_name != "box":
             if not strong:
                 raise SystemExit("--scene needs --scaling strong")
@@ -167,8 +149,8 @@ def main_multi(args, rank, world, local, workload):
     exch = int(1.5 * per_side * per_side * planes) + 65536
     cap = int(n_mine * 1.25) + 2 * exch
     loc = CudaSlab(params, terms, sc, local, cap, exch)
-    if getattr(args, "driver", "native") == "native":
-        loc.e.set_option("p2p_halo", int(getattr(args, "p2p", 1)))
+    if getattr(a, "driver", "native") == "native":
+        loc.e.set_option("p2p_halo", int(getattr(a, "p2p", 1)))
         loc.comm_init(rank, world, dist)  # the library drives exchange + all-reduce itself
     drv = SlabDriver(loc, cuts, rank, world, dist)
     drv.start(mine_p, ids)
@@ -187,7 +169,7 @@ def main_multi(args, rank, world, local, workload):
     bytes0 = drv.bytes_sent
     t0 = time.perf_counter()
     e.event_record(0)
-    for _ in range(args.steps):
+    for _ in range(a.steps):
         dt = drv.step(dt)
     e.event_record(1)
     ms = e.event_elapsed_ms(0, 1)
@@ -201,7 +183,7 @@ def main_multi(args, rank, world, local, workload):
     # profiling synchronises inside the step, which the timed region above must not
     e.profile(True)
     drv.profile = True
-    for _ in range(args.steps):
+    for _ in range(a.steps):
         dt = drv.step(dt)
     pass_ms, pass_launches, _ = e.pass_times()
     e.profile(False)
@@ -215,7 +197,7 @@ def main_multi(args, rank, world, local, workload):
     owned_total = sum(int(s[3]) for s in allstats)
     # end to end: every rank downloads its slab to the host and uploads it again, every step
     e2e = None
-    if args.e2e_steps > 0:
+    if a.e2e_steps > 0:
         # host buffers page-locked (sphb_host_alloc), as sph_simulation::simulate() holds its array
         stage, stage_ptr = B.pinned_particles(cap)
         ids_raw, ids_ptr = B.pinned_particles((cap * 4 + PARTICLE.itemsize - 1) // PARTICLE.itemsize)
@@ -226,7 +208,7 @@ def main_multi(args, rank, world, local, workload):
         torch.cuda.synchronize()
         dist.barrier()
         t0 = time.perf_counter()
-        for _ in range(args.e2e_steps):
+        for _ in range(a.e2e_steps):
             part, pid = loc.download(stage, ids_stage)
             drv.start(part, pid)
             dt = drv.step(dt)
@@ -234,29 +216,30 @@ def main_multi(args, rank, world, local, workload):
         e2e_s = time.perf_counter() - t0
         t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e = dict(value=n_total * args.e2e_steps / float(t[0]), unit="particle-steps/s",
+        e2e = dict(value=n_total * a.e2e_steps / float(t[0]), unit="particle-steps/s",
                    h2d_bytes_per_step=84 * n_total, d2h_bytes_per_step=84 * n_total + 32 * world,
-                   steps=args.e2e_steps)
+                   steps=a.e2e_steps)
+    line = None
     if rank == 0:
         ms_max = max(float(s[0]) for s in allstats)
-        ms_step = ms_max / args.steps
+        ms_step = ms_max / a.steps
         peak, peak_src = B.measured_peak()
         names = sorted(pass_ms)
         per_rank = []
         for r, s in enumerate(allstats):
-            per_rank.append(dict(rank=r, ms_per_step=float(s[0]) / args.steps, owned=int(s[3]), ghosts=int(s[4]),
-                                 halo_bytes_per_step=float(s[5]) / args.steps,
-                                 host_phase_ms_per_step=dict(pack_exchange_unpack=float(s[6]) / args.steps,
-                                                            sort_to_first_advect=float(s[7]) / args.steps,
-                                                            retries_commit=float(s[8]) / args.steps),
-                                 pass_ms_per_step={k: float(s[9 + i]) / args.steps for i, k in enumerate(names)}))
+            per_rank.append(dict(rank=r, ms_per_step=float(s[0]) / a.steps, owned=int(s[3]), ghosts=int(s[4]),
+                                 halo_bytes_per_step=float(s[5]) / a.steps,
+                                 host_phase_ms_per_step=dict(pack_exchange_unpack=float(s[6]) / a.steps,
+                                                            sort_to_first_advect=float(s[7]) / a.steps,
+                                                            retries_commit=float(s[8]) / a.steps),
+                                 pass_ms_per_step={k: float(s[9 + i]) / a.steps for i, k in enumerate(names)}))
         slow = max(per_rank, key=lambda d: d["ms_per_step"])
         f_ms = slow["pass_ms_per_step"]["forces"]
         n_loc = slow["owned"]
         achieved = B.ALGO_BYTES["forces"] * n_loc / (f_ms * 1e-3) / 1e9 if f_ms > 0 else 0.0
         line = dict(
-            metric="SPH particle-steps/sec", value=n_total * args.steps / (ms_max * 1e-3), unit="particle-steps/s",
-            n_gpus=world, steps=args.steps, warmup=warmup, ms_per_step=ms_step, higher_is_better=True,
+            metric="SPH particle-steps/sec", value=n_total * a.steps / (ms_max * 1e-3), unit="particle-steps/s",
+            n_gpus=world, steps=a.steps, warmup=warmup, ms_per_step=ms_step, higher_is_better=True,
             scaling="strong" if strong else "weak", vs_baseline=None, dtype="f32", data="synthetic",
             config=dict(workload=workload if strong else
                         f"{world} x ({n0}-particle reference lattice block) side by side along x in one open-top "
@@ -278,9 +261,59 @@ def main_multi(args, rank, world, local, workload):
             ranks=per_rank)
         if e2e:
             line["e2e"] = e2e
-        line["parity_check"] = parity
-        B.emit(line)
     loc.close()
+    dist.barrier()
+    return line
+
+
+def main_multi(args, rank, world, local, workload):
+    import torch
+    import torch.distributed as dist
+    import __main__ as B  # bench.py itself (it owns the real stdout)
+    if not hasattr(B, "emit"):
+        import bench as B
+    from libclsph_b200 import PARTICLE, build, host
+    from libclsph_b200.slab import CudaSlab, SlabDriver, equal_count_cuts
+
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    if rank == 0:
+        build.build_all()
+    dist.barrier()
+    parity = None
+    if not getattr(args, "no_parity", False):
+        parity = parity_check(B, dist, rank, world, local)
+        if not parity["ok"]:  # a wrong answer is not timed
+            if rank == 0:
+                B.emit(dict(metric="SPH particle-steps/sec", value=None, n_gpus=world, error="parity_check failed",
+                            parity_check=parity))
+            dist.destroy_process_group()
+            return 1
+    import argparse
+    line = run_config(args, B, torch, dist, rank, world, local, workload)
+    secondary = {}
+    if not getattr(args, "no_secondary", False) and getattr(args, "scaling", "weak") == "weak" \
+            and getattr(args, "scene", "box") == "box":
+        # what BASELINE.json configs[3] / configs[4] word, recorded by the driver's default command:
+        # the STRONG series (the 16.7 M box cut into N slabs) and the collision-heavy scenes
+        legs = [("strong_16M", dict(scaling="strong", scene="box", particles=args.particles))]
+        legs += [(f"strong_{sc}_4M", dict(scaling="strong", scene=sc, particles=4096000)) for sc in ("labyrinth", "river")]
+        for name, over in legs:
+            a2 = argparse.Namespace(**dict(vars(args), e2e_steps=0, **over))
+            l2 = run_config(a2, B, torch, dist, rank, world, local,
+                            f"synthetic {over['particles']}-particle water box (BASELINE.json configs[3]) cut into "
+                            f"{world} x-slabs")
+            if rank == 0:
+                secondary[name] = dict(workload=l2["config"]["workload"], scaling="strong", value=l2["value"],
+                                       unit=l2["unit"], ms_per_step=l2["ms_per_step"], particles=l2["config"]["particles"],
+                                       p2p_halo=l2["config"]["p2p_halo"],
+                                       ranks=[dict(rank=r["rank"], ms_per_step=r["ms_per_step"], owned=r["owned"],
+                                                   ghosts=r["ghosts"], host_phase_ms_per_step=r["host_phase_ms_per_step"])
+                                              for r in l2["ranks"]])
+    if rank == 0:
+        line["parity_check"] = parity
+        line["config"]["secondary"] = secondary or None
+        B.emit(line)
     dist.barrier()
     dist.destroy_process_group()
     return 0

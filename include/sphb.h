@@ -269,6 +269,11 @@ int sphb_event_record(sphb_engine* e, int slot);
 int sphb_event_elapsed_ms(sphb_engine* e, int from_slot, int to_slot, float* ms);
 /* number of kernel launches issued by this engine since creation */
 uint64_t sphb_launch_count(sphb_engine* e);
+/* What the last step's density pass handed to its forces pass (measurement only; new — the
+ * reference searches twice, kernels/sphb.cl:3-35 and :37-126): out[0] = pairs of particles whose
+ * neighbour list overflowed (their forces come from a second search), out[1] = pairs walked in
+ * two parts, out[2] = list entries over all pairs, out[3] = entries of the longest list. */
+int sphb_neighbor_list_stats(sphb_engine* e, uint64_t out[4]);
 /* the engine's cudaStream_t (as void*), so a caller can record its own events on it */
 void* sphb_stream(sphb_engine* e);
 /* named integer options; unknown names return SPHB_ERR_INVALID.

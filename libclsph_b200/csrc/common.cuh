@@ -309,6 +309,8 @@ int launch_forces(const float4* pos, const float4* vel, const float4* pv, const 
                   const StepConsts& c, int variant, cudaStream_t s,
                   const uint32_t* ghost_ids = nullptr, bool queued = false);
 
+int launch_list_stats(const uint32_t* pool, uint32_t n, unsigned long long* out_dev, cudaStream_t s);
+
 // kernels_slab.cu — the slab-decomposed (multi-GPU) step
 size_t slab_message_bytes(uint32_t record_capacity);
 int launch_slab_pack(const float4* pos, const float4* vel, const float4* vhf, uint32_t* ids,

@@ -738,6 +738,22 @@ int sphb_step(sphb_engine* e, float dt_in, float* dt_out) {
   return 0;
 }
 
+int sphb_neighbor_list_stats(sphb_engine* e, uint64_t out[4]) {
+  if (!e || !out) return SPHB_ERR_INVALID;
+  if (!e->stepped) SPHB_FAIL(e, SPHB_ERR_INVALID, "sphb_neighbor_list_stats before the first step");
+  if (e->neighbor_variant != 0) SPHB_FAIL(e, SPHB_ERR_INVALID, "sphb_neighbor_list_stats: option neighbor_kernel != 0");
+  CUDA_TRY(e, cudaSetDevice(e->device));
+  // (the four counters are staged in the free half of the sort buffers, as sphb_download_debug does)
+  unsigned long long* dev = reinterpret_cast<unsigned long long*>(e->free_keys);
+  if (!dev || e->cap < 8) SPHB_FAIL(e, SPHB_ERR_INVALID, "sphb_neighbor_list_stats: no scratch");
+  e->launches += launch_list_stats(e->npool, e->n, dev, e->stream);
+  unsigned long long host[4];
+  CUDA_TRY(e, cudaMemcpyAsync(host, dev, sizeof host, cudaMemcpyDeviceToHost, e->stream));
+  CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+  for (int k = 0; k < 4; ++k) out[k] = host[k];
+  return 0;
+}
+
 int sphb_get_parameters(sphb_engine* e, sphb_params* out) {
   if (!e || !out) return SPHB_ERR_INVALID;
   *out = e->params;

@@ -573,6 +573,38 @@ int launch_density(float4* pos, float4* vel, const float4* pairs, float4* pv, co
   return 1;
 }
 
+// What the density pass recorded, for measurement (sphb_neighbor_list_stats): out[0] = pairs whose
+// list is unusable (overflow: their particles search on their own in the forces pass), out[1] =
+// split pairs, out[2] = list entries over all pairs (padding included), out[3] = longest list.
+__global__ void __launch_bounds__(256) k_list_stats(const uint32_t* __restrict__ meta, uint32_t np,
+                                                    unsigned long long* __restrict__ out) {
+  const uint32_t t = blockIdx.x * 256u + threadIdx.x;
+  uint32_t bad = 0, split = 0, entries = 0;
+  if (t < np) {
+    const uint32_t m = __ldg(meta + t);
+    bad = (m & kMetaUnusable) ? 1u : 0u;
+    if (!bad) {
+      entries = (m >> 8) & 255u;
+      split = entries > (m & 255u) ? 1u : 0u;
+    }
+  }
+  const uint32_t nb = __reduce_add_sync(0xffffffffu, bad), ns = __reduce_add_sync(0xffffffffu, split),
+                 ne = __reduce_add_sync(0xffffffffu, entries), mx = __reduce_max_sync(0xffffffffu, entries);
+  if ((threadIdx.x & 31u) == 0) {
+    if (nb) atomicAdd(out + 0, (unsigned long long)nb);
+    if (ns) atomicAdd(out + 1, (unsigned long long)ns);
+    if (ne) atomicAdd(out + 2, (unsigned long long)ne);
+    atomicMax(out + 3, (unsigned long long)mx);
+  }
+}
+
+int launch_list_stats(const uint32_t* pool, uint32_t n, unsigned long long* out_dev, cudaStream_t s) {
+  const uint32_t np = (n + 1u) / 2u;
+  cudaMemsetAsync(out_dev, 0, 4 * sizeof(unsigned long long), s);
+  k_list_stats<<<(np + 255u) / 256u, 256, 0, s>>>(pool, np, out_dev);
+  return 1;
+}
+
 int queue_refresh_neighbors(const QueueCtl* ctl, cudaStream_t s) {
   // the symbol's address is looked up once per device: a plain device-to-device copy after that
   static thread_local void* addr[64] = {};

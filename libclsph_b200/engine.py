@@ -82,7 +82,7 @@ SYMBOLS = [
     "sphb_slab_pack", "sphb_slab_unpack", "sphb_slab_forces", "sphb_slab_advect", "sphb_slab_commit",
     "sphb_slab_download", "sphb_compute_dt", "sphb_scene_build_ms", "sphb_upload_begin", "sphb_upload_commit",
     "sphb_nccl_unique_id", "sphb_slab_comm_init", "sphb_slab_start", "sphb_slab_step", "sphb_slab_bytes_sent",
-    "sphb_slab_phase_ms", "sphb_slab_resends", "sphb_slab_p2p_active", "sphb_cell_table_noalloc",
+    "sphb_slab_phase_ms", "sphb_slab_resends", "sphb_slab_p2p_active", "sphb_cell_table_noalloc", "sphb_neighbor_list_stats",
 ]
 
 
@@ -171,6 +171,7 @@ def lib():
         L.sphb_host_alloc.argtypes = [C.POINTER(vp), C.c_size_t]
         L.sphb_host_free.argtypes = [vp]
         L.sphb_cell_table_noalloc.argtypes = [vp, u32, vp, vp, u32, vp]
+        L.sphb_neighbor_list_stats.argtypes = [vp, vp]
         _lib = L
     return _lib
 
@@ -324,6 +325,12 @@ class Engine:
         ms = C.c_float()
         self._check(self.L.sphb_event_elapsed_ms(self.h, a, b, C.byref(ms)))
         return ms.value
+
+    def neighbor_list_stats(self):
+        """dict(overflowed_pairs, split_pairs, entries, longest) of the last step's neighbour lists"""
+        out = (C.c_uint64 * 4)()
+        self._check(self.L.sphb_neighbor_list_stats(self.h, out))
+        return dict(overflowed_pairs=int(out[0]), split_pairs=int(out[1]), entries=int(out[2]), longest=int(out[3]))
 
     def launch_count(self):
         return int(self.L.sphb_launch_count(self.h))
