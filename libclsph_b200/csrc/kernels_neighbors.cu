@@ -38,6 +38,8 @@
 //   pv[i]     {x, y, z, p/rho^2 | vx, vy, vz, m/rho}, written by the density pass: everything
 //             the forces pass needs of a neighbour in one gather.  The reference recomputes
 //             p_j/rho_j^2 and m/rho_j for every PAIR (sphb.cl:80-106); they depend only on j.
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace sphb {
@@ -50,7 +52,10 @@ namespace {
 // ---- the pair list --------------------------------------------------------------------------
 // One pool of 32-bit words per engine, addressed by pair index t = i / 2 with np = ceil(n / 2):
 //   meta[t]                  bits 0-7 entries of the first part, 8-15 entries in all, bit 31 =
-//                            "list unusable" (it overflowed: the forces pass searches itself)
+//                            "list unusable" (it overflowed): the pair is queued instead
+//   qcount[0], queue[]       the pairs whose list is unusable, in no particular order: a follow-up
+//                            kernel (k_forces_overflow) lets their particles search on their own,
+//                            so that no warp of the forces pass mixes the two kinds of work
 //   start[r * np + t]        first particle of the run walked for row id r (0-8; 9-17 for the
 //                            second part of a split pair — written only then)
 //   codes[(k / 2) * np + t]  entries k and k + 1 as two 16-bit codes: row id << 11 | offset in
@@ -69,6 +74,8 @@ constexpr uint32_t kStartRows = 18;
 
 struct PairLists {
   uint32_t* meta;
+  uint32_t* qcount;  // 4 words (16-byte aligned rest)
+  uint32_t* queue;
   uint32_t* start;
   uint32_t* codes;
   uint32_t np;
@@ -77,7 +84,9 @@ __host__ __device__ inline PairLists pair_lists(uint32_t* pool, uint32_t n) {
   PairLists L;
   L.np = (n + 1u) >> 1;
   L.meta = pool;
-  L.start = pool + L.np;
+  L.qcount = pool + L.np;
+  L.queue = L.qcount + 4;
+  L.start = L.queue + L.np;
   L.codes = L.start + (size_t)kStartRows * L.np;
   return L;
 }
@@ -254,6 +263,7 @@ __global__ void __launch_bounds__(kUB)
     pv[2u * i + 1u] = make_float4(v.x, v.y, v.z, c.mass / density);
   }
   L.meta[t] = unusable ? kMetaUnusable : (cnt_a | (cnt << 8));
+  if (unusable) L.queue[atomicAdd(L.qcount, 1u)] = t;
   if (!unusable) {
     const uint16_t* col = hit + threadIdx.x;
     uint32_t* out = L.codes + t;
@@ -375,11 +385,7 @@ __global__ void __launch_bounds__(kFB, SPHB_FORCES_MINB)
   const bool ghost_b = ghost_ids && (__ldg(ghost_ids + ib) & 0x80000000u);
   const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
   const uint32_t meta = __ldg(L.meta + t);
-  if (meta & kMetaUnusable) {  // no list: each particle searches on its own
-    acc[ia] = ghost_a ? zero4 : forces_by_search<2>(ia, pv, pv + 1, keys, ftable, rho, c);
-    if (has_b) acc[ib] = ghost_b ? zero4 : forces_by_search<2>(ib, pv, pv + 1, keys, ftable, rho, c);
-    return;
-  }
+  if (meta & kMetaUnusable) return;  // no list: the pair is in the queue of k_forces_overflow
   const uint32_t cnt_a = meta & 255u, cnt = (meta >> 8) & 255u;
   const bool split = cnt > cnt_a;
 #pragma unroll
@@ -513,6 +519,28 @@ __global__ void __launch_bounds__(128)
   }
 }
 
+// The particles of the queued pairs (their lists overflowed: compressed fluid), each by its own
+// search of the 9 row runs; a fixed, small grid strides over the queue, whose length only the
+// device knows.
+constexpr int kOverflowBlocks = 592, kOverflowThreads = 64;
+template <bool Q>
+__global__ void __launch_bounds__(kOverflowThreads)
+    k_forces_overflow(const float4* __restrict__ pv, const uint32_t* __restrict__ keys,
+                      const uint32_t* __restrict__ ftable, const float* __restrict__ rho,
+                      const uint32_t* __restrict__ pool, float4* __restrict__ acc, StepConsts c_arg,
+                      const uint32_t* __restrict__ ghost_ids) {
+  if (Q && !g_hot.active) return;
+  const StepConsts& c = Q ? g_hot.c : c_arg;
+  const PairLists L = pair_lists(const_cast<uint32_t*>(pool), c.n);
+  const uint32_t total = 2u * min(__ldg(L.qcount), L.np);
+  for (uint32_t k = blockIdx.x * kOverflowThreads + threadIdx.x; k < total; k += kOverflowBlocks * kOverflowThreads) {
+    const uint32_t i = 2u * __ldg(L.queue + (k >> 1)) + (k & 1u);
+    if (i >= c.n) continue;
+    const bool ghost = ghost_ids && (__ldg(ghost_ids + i) & 0x80000000u);
+    acc[i] = ghost ? make_float4(0.f, 0.f, 0.f, 0.f) : forces_by_search<2>(i, pv, pv + 1, keys, ftable, rho, c);
+  }
+}
+
 inline unsigned blocks_for(uint32_t n) { return (n + kBlock - 1) / kBlock; }
 inline unsigned pair_blocks(uint32_t n, int block = kUB) { return ((n + 1u) / 2u + block - 1) / block; }
 inline size_t union_smem(uint32_t cap) { return (size_t)(cap + kUDump) * kUB * sizeof(uint16_t); }
@@ -529,7 +557,7 @@ inline uint8_t* v1_count(uint32_t* pool, uint32_t n) {
 // (also enough for the round-1 kernels' per-particle lists)
 size_t neighbor_pool_words(uint32_t n, uint32_t cap) {
   const size_t np = ((size_t)n + 1) / 2;
-  const size_t pairs = np * (1 + kStartRows + cap / 2);
+  const size_t pairs = np * (2 + kStartRows + cap / 2) + 4;
   const size_t v1 = ((size_t)(kListCap + 2) * n * 2 + n + 3) / 4;
   return (pairs > v1 ? pairs : v1) + 4;
 }
@@ -538,6 +566,10 @@ size_t neighbor_pool_words(uint32_t n, uint32_t cap) {
 // sphere at rest density (4/3 pi h^3 rho0 / m): a pair's union is ~1.5 spheres; the margin absorbs
 // compression.  64 keeps the hit columns at 9 KB per CTA; denser fluids (mucus) take 128.
 uint32_t neighbor_list_cap(float h, float rho0, float mass) {
+  if (const char* env = getenv("SPHB_LIST_CAP")) {  // experiments (tools/ab_neighbors.py): 8 ... 248, a multiple of 8
+    const int v = atoi(env);
+    if (v >= 8 && v <= 248) return (uint32_t)(v & ~7);
+  }
   const float in_sphere = 4.18879f * h * h * h * rho0 / mass;
   return 1.5f * in_sphere * 1.6f <= 64.f ? 64u : 128u;
 }
@@ -566,6 +598,7 @@ int launch_density(float4* pos, float4* vel, const float4* pairs, float4* pv, co
     else k_density_pair<false><<<grid, kPairBlock, 0, s>>>(pos, vel, keys, ftable, rho, prs, nlist, ncount, c);
     return 1;
   }
+  cudaMemsetAsync(pair_lists(pool, c.n).qcount, 0, 4 * sizeof(uint32_t), s);  // (c.n: the launch-time count, also when queued)
   if (queued)
     k_density_union<true><<<pair_blocks(c.n), kUB, union_smem(cap), s>>>(pairs, vel, keys, ftable, rho, prs, pv, pool, cap, c);
   else
@@ -637,11 +670,14 @@ int launch_forces(const float4* pos, const float4* vel, const float4* pv, const 
       k_forces_nlist<false><<<blocks_for(c.n), kBlock, 0, s>>>(pos, vel, keys, ftable, rho, nlist, ncount, acc, c, ghost_ids);
     return 1;
   }
-  if (queued)
+  if (queued) {
     k_forces_union<true><<<pair_blocks(c.n, kFB), kFB, 0, s>>>(pv, keys, ftable, rho, pool, acc, c, ghost_ids);
-  else
+    k_forces_overflow<true><<<kOverflowBlocks, kOverflowThreads, 0, s>>>(pv, keys, ftable, rho, pool, acc, c, ghost_ids);
+  } else {
     k_forces_union<false><<<pair_blocks(c.n, kFB), kFB, 0, s>>>(pv, keys, ftable, rho, pool, acc, c, ghost_ids);
-  return 1;
+    k_forces_overflow<false><<<kOverflowBlocks, kOverflowThreads, 0, s>>>(pv, keys, ftable, rho, pool, acc, c, ghost_ids);
+  }
+  return 2;
 }
 
 }  // namespace sphb

@@ -73,7 +73,8 @@ def main():
             diff = float(np.max(np.abs(acc - ref_acc)) / max(1e-30, np.max(np.abs(ref_acc))))
         line = dict(variant=v, n=n, kind=a.kind, jitter=a.jitter, evolve=a.evolve, ms_per_step=ms,
                     passes={k: v / max(1, psteps) for k, v in pass_ms.items() if v > 0},
-                    acc_rel_diff_vs_first=diff, finite=bool(np.isfinite(acc).all()), dt=dt)
+                    acc_rel_diff_vs_first=diff, finite=bool(np.isfinite(acc).all()), dt=dt,
+                    lists=e.neighbor_list_stats() if v == 0 else None, list_cap=os.environ.get("SPHB_LIST_CAP"))
         print(json.dumps(line), flush=True)
         e.close()
 

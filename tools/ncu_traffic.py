@@ -22,7 +22,7 @@ import bench  # noqa: E402
 WANT = dict(dram_read="dram__bytes_read.sum", dram_write="dram__bytes_write.sum",
             warp_inst="smsp__inst_executed.sum", thread_inst="smsp__thread_inst_executed.sum",
             lane_efficiency="smsp__thread_inst_executed_per_inst_executed.ratio",
-            l1_wavefronts="l1tex__data_pipe_lsu_wavefronts.sum", time="gpu__time_duration.sum",
+            l1_wavefronts_per_sm="l1tex__data_pipe_lsu_wavefronts.avg", time="gpu__time_duration.sum",
             issue_active_pct="smsp__issue_active.avg.pct_of_peak_sustained_active",
             l1_wavefronts_pct="l1tex__data_pipe_lsu_wavefronts.avg.pct_of_peak_sustained_elapsed",
             warps_active_pct="sm__warps_active.avg.pct_of_peak_sustained_active",
@@ -51,6 +51,9 @@ def main(path, n):
             if hit and d[hit[0]] != "":
                 rec[k] = float(d[hit[0]].replace(",", "")) * SCALE.get(units[head.index(hit[0])], 1.0)
         rec["dram_bytes"] = rec.get("dram_read", 0.0) + rec.get("dram_write", 0.0)
+        # (--set full has the per-SM average of the wavefront counter and the lane efficiency, not their sums)
+        rec["l1_wavefronts"] = rec.get("l1_wavefronts_per_sm", 0.0) * 148
+        rec["thread_inst"] = rec.get("thread_inst") or rec.get("warp_inst", 0.0) * rec.get("lane_efficiency", 32.0)
         doc[which][str(n)] = rec
     json.dump(doc, open(dest, "w"), indent=1)
     print(json.dumps(doc, indent=1))
