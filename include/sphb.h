@@ -195,6 +195,9 @@ int sphb_slab_create(const sphb_params* params /* particles_count = GLOBAL count
                      const sphb_terms* terms, int device, uint32_t capacity /* local particle slots */,
                      uint32_t exchange_capacity /* records per message */, sphb_engine** out);
 size_t sphb_slab_message_bytes(sphb_engine* e); /* 16 + 48 * exchange_capacity */
+/* A slab with a neighbour on both sides must be at least 3 h wide (the 2 h ghost layer + one
+ * step's motion): ranks exchange with their two neighbours only.  A thinner one is refused
+ * (SPHB_ERR_INVALID) — use fewer GPUs, or cut elsewhere. */
 int sphb_slab_configure(sphb_engine* e, float xlo, float xhi, int has_left, int has_right);
 int sphb_slab_upload(sphb_engine* e, const sphb_particle* aos, const uint32_t* ids, uint32_t n_owned);
 int sphb_slab_bbox(sphb_engine* e, float* red8_dev); /* bbox of the owned positions only */

@@ -218,7 +218,23 @@ int queue_refresh_neighbors(const QueueCtl* ctl, cudaStream_t s);
 int launch_queue_plan(QueueCtl* ctl, const Reduce* red, cudaStream_t s);
 int launch_queue_attempt(QueueCtl* ctl, const Reduce* red, float* timeleft_log, int last, cudaStream_t s);
 
+// Streaming multiprocessors of the CURRENT device (cudaDevAttrMultiProcessorCount, looked up once
+// per device): grid-stride kernels size their grids as a multiple of it.
+inline int sm_count() {
+  static int cached[64] = {};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  if (!cached[dev]) {
+    int v = 0;
+    cached[dev] = (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && v > 0) ? v : 148;
+  }
+  return cached[dev];
+}
+
 // ---- launchers (each enqueues on `s` and returns the number of kernels launched) -------
+// A launcher does not return CUDA errors itself: an enqueue-time failure of a kernel launch or of a
+// cudaMemsetAsync inside it is recorded by the runtime and surfaces in the cudaGetLastError() that
+// every caller issues after its launches (CUDA_TRY(e, cudaGetLastError()) in engine.cu / slab.cu).
 // kernels_exact.cu  (compiled with -fmad=false: results are those of the literal
 // expression trees, bit-identical to the CPU checker)
 int launch_reduce_init(Reduce* red, cudaStream_t s, const QueueCtl* q = nullptr);

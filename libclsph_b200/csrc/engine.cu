@@ -681,6 +681,7 @@ int sphb_step(sphb_engine* e, float dt_in, float* dt_out) {
   }
   const uint32_t ncell = e->params.grid_cell_count;
   const StepConsts c = make_consts(e);
+  if (int rc = check_search_grid(e, c)) return rc;
   if (int rc = ensure_tables(e, (size_t)c.nfine + 1, (size_t)ncell + 1)) return rc;
 
   // 2. locate_in_grid (kernels/grid.cl:40-64) + 3. sort_particles (sph_simulation.cpp:110-198):

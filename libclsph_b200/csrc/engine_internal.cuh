@@ -241,6 +241,18 @@ void accumulate_pass(sphb_engine* e, int pass) {
   if (cudaEventElapsedTime(&ms, e->ev[pass][0], e->ev[pass][1]) == cudaSuccess) e->pass_ms[pass] += ms;
 }
 
+// The search grid's cell count is kept in 32 bits (keys, table indices): fnx * fny * fnz is
+// computed in 64 bits here and refused when it does not fit, BEFORE any table is sized from the
+// wrapped product (the reference allows up to 1023 cells per axis; 32 x 512^3 search cells already
+// exceed 2^32).
+int check_search_grid(sphb_engine* e, const StepConsts& c) {
+  const unsigned long long cells = (unsigned long long)c.fnx * c.fny * c.fnz;
+  if (cells + 1ull > 0xFFFFFFFFull || cells != (unsigned long long)c.nfine)
+    SPHB_FAIL(e, SPHB_ERR_GRID, "search grid %u x %u x %u = %llu cells does not fit 32-bit cell keys (grid %d x %d x %d)",
+              c.fnx, c.fny, c.fnz, cells, e->params.grid_size_x, e->params.grid_size_y, e->params.grid_size_z);
+  return 0;
+}
+
 int ensure_tables(sphb_engine* e, size_t fine_entries, size_t ref_entries) {
   // grow rarely: capacities are kept with 1.5x headroom
   const bool grow_f = fine_entries > e->ftable_cap, grow_r = ref_entries > e->ref_table_cap;

@@ -693,7 +693,7 @@ int queue_refresh_exact(const QueueCtl* ctl, cudaStream_t s) {
 
 int launch_bbox(const float4* pos, uint32_t n, Reduce* red, cudaStream_t s) {
   unsigned grid = blocks_for(n);
-  if (grid > 148 * 8) grid = 148 * 8;  // grid-stride: 8 resident CTAs of 256 on each of 148 SMs
+  if (grid > (unsigned)sm_count() * 8u) grid = (unsigned)sm_count() * 8u;  // grid-stride: 8 resident CTAs of 256 threads per SM
   k_bbox<<<grid, kBlock, 0, s>>>(pos, n, red);
   return 1;
 }
@@ -775,7 +775,7 @@ int launch_advect(const float4* pos, const float4* vhf, const float4* acc, float
   SlabAdvect sa = {};
   if (slab) sa = *slab;
   unsigned grid = blocks_for(n);
-  if (grid > 148 * 8) grid = 148 * 8;  // 8 resident CTAs of 256 threads on each of 148 SMs
+  if (grid > (unsigned)sm_count() * 8u) grid = (unsigned)sm_count() * 8u;  // grid-stride: 8 resident CTAs of 256 threads per SM
   if (q)
     k_advect<true><<<grid, kBlock, 0, s>>>(pos, vhf, acc, pos_out, vel_out, vhf_out, n, dt, restitution, faces,
                                            face_count, df, red, sa, b, q);

@@ -305,7 +305,7 @@ int launch_slab_reduce_floats(const Reduce* red, float* out, cudaStream_t s) {
 int launch_slab_bbox(const float4* pos, const uint32_t* n_owned_dev, uint32_t n_upper, Reduce* red,
                      cudaStream_t s) {
   unsigned grid = blocks_for(n_upper ? n_upper : 1);
-  if (grid > 148 * 8) grid = 148 * 8;
+  if (grid > (unsigned)sm_count() * 8u) grid = (unsigned)sm_count() * 8u;  // grid-stride: 8 resident CTAs of 256 threads per SM
   k_slab_bbox<<<grid, kBlock, 0, s>>>(pos, n_owned_dev, red);
   return 1;
 }

@@ -63,6 +63,15 @@ size_t sphb_slab_message_bytes(sphb_engine* e) { return e ? slab_message_bytes(e
 int sphb_slab_configure(sphb_engine* e, float xlo, float xhi, int has_left, int has_right) {
   if (int rc = require_slab(e)) return rc;
   if (!(xlo < xhi)) SPHB_FAIL(e, SPHB_ERR_INVALID, "slab bounds [%g, %g)", xlo, xhi);
+  // A slab with a neighbour on BOTH sides must be wider than the ghost layer (2h) plus what a
+  // particle can move in one step (< h: the time step keeps v dt below h): a rank exchanges only
+  // with its two neighbours and sends only particles it OWNS, so across a thinner slab the
+  // particles its neighbours need — and a migrant's new owner — would lie two ranks away and
+  // ghost densities would be silently wrong.
+  const float min_width = (kHaloCells + 1.f) * e->params.h;
+  if (has_left && has_right && !(xhi - xlo >= min_width))
+    SPHB_FAIL(e, SPHB_ERR_INVALID, "slab [%g, %g) is %g wide: an inner slab must be at least %g (3 h) — use fewer "
+              "GPUs for this fluid, or re-cut", xlo, xhi, xhi - xlo, min_width);
   e->xlo = xlo; e->xhi = xhi;
   e->has_left = has_left ? 1 : 0;
   e->has_right = has_right ? 1 : 0;
@@ -202,6 +211,7 @@ int sphb_slab_forces(sphb_engine* e, const float gmin[3], const float gmax[3]) {
   c.minx = lo;
   c.fnx = kXPerRef * ((uint32_t)((hi - lo) / c.cell) + 1u);
   c.nfine = c.fnx * c.fny * c.fnz;
+  if (int rc = check_search_grid(e, c)) return rc;
   if (int rc = ensure_tables(e, (size_t)c.nfine + 1, 1)) return rc;
   if (n == 0) {
     e->slab_in = e->cur;

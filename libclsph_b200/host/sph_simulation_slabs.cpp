@@ -41,9 +41,16 @@ class worker_team {
     go_.notify_all();
     for (size_t r = 0; r < threads_.size(); ++r) threads_[r].join();
   }
+  // Called ON THE WORKER THREAD the moment its job returns non-zero, before anything waits for the
+  // other ranks: a rank that fails between two collectives (capacity, a CUDA error, the 20 s halo
+  // time-out) leaves its peers inside an all-reduce that can never complete, so run() itself
+  // would never return.  The slab driver prints the engine's message there and ends the process.
+  std::function<void(int /*rank*/, int /*rc*/, const char* /*what*/)> on_failure;
+
   // the first non-zero result in rank order (and which rank it came from), else 0
-  int run(const std::function<int(int)>& f, int* failed_rank = 0) {
+  int run(const std::function<int(int)>& f, int* failed_rank = 0, const char* what = "slab call") {
     std::unique_lock<std::mutex> lock(m_);
+    what_ = what;
     job_ = &f;
     pending_ = (int)threads_.size();
     ++generation_;
@@ -71,6 +78,7 @@ class worker_team {
         job = job_;
       }
       const int rc = (*job)(rank);
+      if (rc != 0 && on_failure) on_failure(rank, rc, what_);
       {
         std::lock_guard<std::mutex> lock(m_);
         rc_[rank] = rc;
@@ -82,6 +90,7 @@ class worker_team {
   std::mutex m_;
   std::condition_variable go_, done_;
   const std::function<int(int)>* job_;
+  const char* what_ = "slab call";
   unsigned long generation_;
   int pending_;
   bool quit_;
@@ -293,7 +302,12 @@ void sph_simulation::slabs_fail(int rc, int rank, const char* what) {
   std::cerr << "A CUDA engine error occured (" << what << ", GPU rank " << rank << ")-> "
             << ((team_ && team_->engines[rank]) ? sphb_last_error(team_->engines[rank]) : sphb_error_string(rc))
             << std::endl;
-  std::exit(-1);
+  std::cerr.flush();
+  std::cout.flush();
+  // The reference's convention is a message and exit(-1) (util/cl_boilerplate.h:32-34).  _Exit and
+  // not exit: the other ranks' threads may sit inside a collective that will never complete, and a
+  // normal exit would wait for them while tearing down the CUDA runtime.
+  std::_Exit(255);
 }
 
 // Engines, scene, communicator.  Every rank gets room for 1.6 x its fair share plus two ghost
@@ -339,9 +353,12 @@ void sph_simulation::slabs_begin() {
                           current_scene.rvertices.data(), current_scene.totalGridpoints);
   }, &bad);
   if (rc != 0) slabs_fail(rc, bad, "slab set-up");
+  // from here on the ranks meet in collectives: a rank that fails reports and ends the process at once
+  T.workers.on_failure = [this](int r, int c, const char* what) { slabs_fail(c, r, what); };
   // (collective: entered only once every rank has an engine, so a missing GPU is an error
   // message above and not a rendezvous that never completes)
-  rc = T.workers.run([&](int r) -> int { return sphb_slab_comm_init(T.engines[r], id, r, world); }, &bad);
+  rc = T.workers.run([&](int r) -> int { return sphb_slab_comm_init(T.engines[r], id, r, world); }, &bad,
+                     "NCCL communicator");
   if (rc != 0) slabs_fail(rc, bad, "NCCL communicator");
 }
 
@@ -419,7 +436,7 @@ float sph_simulation::slabs_step(float dt) {
     int attempts = 0;
     uint32_t ghosts = 0;
     return sphb_slab_step(T.engines[r], dt, &out[r], &attempts, &T.owned[r], &ghosts);
-  }, &bad);
+  }, &bad, "slab step");
   if (rc != 0) slabs_fail(rc, bad, "slab step");
   for (int r = 1; r < T.world; ++r)
     if (std::memcmp(&out[r], &out[0], sizeof(float)) != 0) {

@@ -6,7 +6,7 @@
  *
  * Parity status: the reference ships no tests, golden vectors or fixtures for this
  * path, so it is PINNED AGAINST THE REFERENCE ITSELF RUN HERE:
- * tests/test_oracle_vs_reference.py requires this file to agree bit-for-bit with
+ * tests/test_oracle_golden.py requires this file to agree bit-for-bit with
  * oracle/_ref/libsphref.so (the reference's own kernels/sph.cl compiled as C++),
  * and tests/golden/ holds vectors generated from that library.  What remains
  * unpinned is only the arithmetic of the OpenCL built-ins (pown, length, '/',

@@ -73,6 +73,23 @@ def slab_world(case, world):
     return lw
 
 
+def test_inner_slab_narrower_than_the_halo_is_refused(tmp_path):
+    """Ranks exchange with their two neighbours only, so an inner slab thinner than the 2 h ghost
+    layer (+ h of motion) would silently lose ghosts: sphb_slab_configure refuses it."""
+    from libclsph_b200 import SphbError
+    from libclsph_b200.slab import CudaSlab
+    case = make_case(tmp_path, "water", 4096)
+    h = float(case["params"]["h"][0])
+    loc = CudaSlab(case["params"], case["terms"], case["scene"], 0, 4096, 4096)
+    try:
+        with pytest.raises(SphbError, match="inner slab"):
+            loc.configure(0.0, 2.9 * h, True, True)
+        loc.configure(0.0, 3.1 * h, True, True)    # wide enough
+        loc.configure(0.0, 0.5 * h, True, False)   # an edge slab may be thin: its one neighbour owns the rest
+    finally:
+        loc.close()
+
+
 @pytest.mark.parametrize("world", [1, 2, 3])
 def test_slabs_on_one_gpu_match_whole_domain(tmp_path, world):
     case = make_case(tmp_path, "water", 32768)
