@@ -242,8 +242,8 @@ int launch_bbox(const float4* pos, uint32_t n, Reduce* red, cudaStream_t s);
 int launch_locate(const float4* pos, uint32_t* keys, const StepConsts& c, cudaStream_t s);
 // Counting sort by search cell (locate fused in): on return keys_sorted[d] = cell key of the
 // particle at sorted position d, perm[d] = its index before the sort (stable: ascending inside a
-// cell), ftable[f] = first sorted position of cell f (nfine + 1 entries).  keys_tmp, slot_tmp,
-// src_tmp: n-entry scratch.
+// cell), ftable[f] = first sorted position of cell f (nfine + 1 entries).  keys_tmp, src_tmp:
+// n-entry scratch; slot_tmp may alias perm (it is not used any more); src_tmp must not.
 int launch_cell_sort(const float4* pos, const StepConsts& c, uint32_t* keys_tmp, uint32_t* slot_tmp,
                      uint32_t* ftable, uint32_t* scan_scratch, uint32_t* keys_sorted, uint32_t* src_tmp,
                      uint32_t* perm, cudaStream_t s, bool queued = false, size_t table_entries = 0);

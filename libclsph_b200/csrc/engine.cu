@@ -14,10 +14,11 @@
 
 namespace {
 constexpr uint32_t kQueueLog = 4096;  // timeleft log entries = most steps one batch may hold
-// Device-driven stepping pays where a step is short enough for the host round trip to show:
-// measured on a B200 (tools/ab_frame.py, ms per step, host round trip per step -> graph per step)
-// 0.355 -> 0.324 at 1 M particles, 1.169 -> 1.147 at 4.1 M, 4.716 -> 4.74 at 16.7 M.
-constexpr uint32_t kQueueAutoMax = 6000000;
+// Device-driven stepping (option "device_loop" = 2: automatic) is used up to this many particles.
+// Measured on a B200 (tools/ab_options.py, ms per step, host round trip per step -> device loop):
+// 0.355 -> 0.324 at 1 M particles, 1.169 -> 1.147 at 4.1 M, and with the round-2 kernels 3.86 -> 3.80
+// at 16.7 M (round 1 measured a small loss there, when the whole table capacity was scanned in three passes).
+constexpr uint32_t kQueueAutoMax = 1u << 26;
 }  // namespace
 
 std::string& sphb_create_error_slot() {

@@ -134,53 +134,109 @@ __global__ void __launch_bounds__(kBlock) k_locate(const float4* __restrict__ po
 // canonicalisation that orders each cell's members by their previous index, so that the
 // result is exactly the stable sort a radix sort would give (atomics decide the slots, so
 // without it the order inside a cell would vary from run to run).
+constexpr int kLocPer = 4;  // particles per thread of k_locate_count: four atomic round trips in flight
 template <bool Q>
 __global__ void __launch_bounds__(kBlock)
     k_locate_count(const float4* __restrict__ pos, uint32_t* __restrict__ keys, uint32_t* __restrict__ slot,
                    uint32_t* __restrict__ count, StepConsts c) {
   SPHB_Q_PROLOGUE(c);
-  const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
-  const bool valid = i < cc.n;
-  const uint32_t key = valid ? fine_key_of(__ldg(pos + i), cc) : 0xFFFFFFFFu;
-  const unsigned peers = __match_any_sync(0xffffffffu, key);
+  // the kernel is bound by the latency of the atomic's round trip to L2 (ncu: long-scoreboard 16
+  // cycles per issue at 85 % occupancy), so every thread carries kLocPer independent particles,
+  // kBlock apart (coalesced), through it at once
+  const uint32_t i0 = blockIdx.x * (kBlock * kLocPer) + threadIdx.x;
   const int lane = threadIdx.x & 31;
-  const int leader = __ffs(peers) - 1;
-  uint32_t base = 0;
-  if (valid && lane == leader) base = atomicAdd(count + key, __popc(peers));
-  base = __shfl_sync(0xffffffffu, base, leader);
-  if (valid) {
-    keys[i] = key;
-    slot[i] = base + __popc(peers & ((1u << lane) - 1u));
+  uint32_t key[kLocPer], base[kLocPer];
+  unsigned peers[kLocPer];
+#pragma unroll
+  for (int u = 0; u < kLocPer; ++u) {
+    const uint32_t i = i0 + u * kBlock;
+    key[u] = i < cc.n ? fine_key_of(__ldg(pos + i), cc) : 0xFFFFFFFFu;
+  }
+#pragma unroll
+  for (int u = 0; u < kLocPer; ++u) {
+    peers[u] = __match_any_sync(0xffffffffu, key[u]);
+    base[u] = 0;
+    if (key[u] != 0xFFFFFFFFu && lane == __ffs(peers[u]) - 1) base[u] = atomicAdd(count + key[u], __popc(peers[u]));
+  }
+#pragma unroll
+  for (int u = 0; u < kLocPer; ++u) {
+    const uint32_t i = i0 + u * kBlock;
+    const uint32_t b = __shfl_sync(0xffffffffu, base[u], __ffs(peers[u]) - 1);
+    if (i < cc.n) {
+      keys[i] = key[u];
+      slot[i] = b + __popc(peers[u] & ((1u << lane) - 1u));
+    }
   }
 }
 
+// Placement: sorted position = first position of the particle's cell + its slot inside the cell.
+// The slots came from atomics, so the order INSIDE a cell is arbitrary here; k_order_cells fixes it.
 template <bool Q>
 __global__ void __launch_bounds__(kBlock)
     k_place(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ slot,
             const uint32_t* __restrict__ start, uint32_t n, uint32_t* __restrict__ keys_sorted,
-            uint32_t* __restrict__ src_tmp) {
+            uint32_t* __restrict__ perm) {
   if (Q && !g_hot.active) return;
   const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
   if (i >= n) return;
   const uint32_t key = __ldg(keys + i);
   const uint32_t d = __ldg(start + key) + __ldg(slot + i);
   keys_sorted[d] = key;
-  src_tmp[d] = i;
+  perm[d] = i;
 }
 
+// One thread per CELL: the members of a cell that holds two or more particles are put in
+// ascending order of their previous index, which makes the result exactly the stable sort (and
+// run-to-run deterministic).  A search cell holds ~1.2 particles, so most threads read two table
+// entries and leave; small cells are insertion-sorted, a pile-up (hundreds of particles pressed
+// into one cell) is heap-sorted: O(m log m) whatever the occupancy.
+__device__ void order_members(uint32_t* __restrict__ a, uint32_t m) {
+  if (m <= 4u) {  // the common cases: all loads issued together, a 5-comparator network, stores only if needed
+    uint32_t v0 = a[0], v1 = a[1], v2 = m > 2u ? a[2] : 0xFFFFFFFFu, v3 = m > 3u ? a[3] : 0xFFFFFFFFu;
+    const uint32_t o0 = v0, o1 = v1, o2 = v2, o3 = v3;
+#define SPHB_CSWAP(x, y) { const uint32_t lo = min(x, y), hi = max(x, y); x = lo; y = hi; }
+    SPHB_CSWAP(v0, v1) SPHB_CSWAP(v2, v3) SPHB_CSWAP(v0, v2) SPHB_CSWAP(v1, v3) SPHB_CSWAP(v1, v2)
+#undef SPHB_CSWAP
+    if (v0 != o0) a[0] = v0;
+    if (v1 != o1) a[1] = v1;
+    if (m > 2u && v2 != o2) a[2] = v2;
+    if (m > 3u && v3 != o3) a[3] = v3;
+    return;
+  }
+  if (m <= 16u) {
+    for (uint32_t k = 1; k < m; ++k) {
+      const uint32_t v = a[k];
+      uint32_t j = k;
+      for (; j > 0 && a[j - 1] > v; --j) a[j] = a[j - 1];
+      a[j] = v;
+    }
+    return;
+  }
+  auto sift = [&](uint32_t root, uint32_t end) {
+    for (;;) {
+      uint32_t child = 2u * root + 1u;
+      if (child >= end) return;
+      if (child + 1u < end && a[child] < a[child + 1u]) ++child;
+      if (a[root] >= a[child]) return;
+      const uint32_t t = a[root]; a[root] = a[child]; a[child] = t;
+      root = child;
+    }
+  };
+  for (uint32_t k = m / 2u; k-- > 0;) sift(k, m);
+  for (uint32_t end = m; end-- > 1;) {
+    const uint32_t t = a[0]; a[0] = a[end]; a[end] = t;
+    sift(0, end);
+  }
+}
 template <bool Q>
 __global__ void __launch_bounds__(kBlock)
-    k_canonical_order(const uint32_t* __restrict__ keys_sorted, const uint32_t* __restrict__ src_tmp,
-                      const uint32_t* __restrict__ start, uint32_t n, uint32_t* __restrict__ perm) {
+    k_order_cells(const uint32_t* __restrict__ start, uint32_t cells_arg, uint32_t* __restrict__ perm) {
   if (Q && !g_hot.active) return;
-  const uint32_t d = blockIdx.x * kBlock + threadIdx.x;
-  if (d >= n) return;
-  const uint32_t key = __ldg(keys_sorted + d);
-  const uint32_t s = __ldg(start + key), e = __ldg(start + key + 1);
-  const uint32_t mine = __ldg(src_tmp + d);
-  uint32_t before = 0;
-  for (uint32_t j = s; j < e; ++j) before += (__ldg(src_tmp + j) < mine) ? 1u : 0u;
-  perm[s + before] = mine;
+  const uint32_t cells = Q ? g_hot.c.nfine : cells_arg;
+  const uint32_t cell = blockIdx.x * kBlock + threadIdx.x;
+  if (cell >= cells) return;
+  const uint32_t s = __ldg(start + cell), e = __ldg(start + cell + 1u);
+  if (e - s >= 2u) order_members(perm + s, e - s);
 }
 
 // The reference moves whole 80-byte structs in each of its 4 radix passes
@@ -711,15 +767,22 @@ int launch_cell_sort(const float4* pos, const StepConsts& c, uint32_t* keys_tmp,
                      uint32_t* perm, cudaStream_t s, bool queued, size_t table_entries) {
   if (!queued) table_entries = (size_t)c.nfine + 1;
   cudaMemsetAsync(ftable, 0, sizeof(uint32_t) * table_entries, s);
-  if (queued) k_locate_count<true><<<blocks_for(c.n), kBlock, 0, s>>>(pos, keys_tmp, slot_tmp, ftable, c);
-  else k_locate_count<false><<<blocks_for(c.n), kBlock, 0, s>>>(pos, keys_tmp, slot_tmp, ftable, c);
+  const unsigned loc_grid = (c.n + kBlock * kLocPer - 1) / (kBlock * kLocPer);
+  // The slots live in src_tmp, NOT in slot_tmp: the callers hand the same buffer as slot_tmp and as
+  // perm, and the placement writes perm while other threads still read their slots.
+  (void)slot_tmp;
+  uint32_t* const slots = src_tmp;
+  if (queued) k_locate_count<true><<<loc_grid, kBlock, 0, s>>>(pos, keys_tmp, slots, ftable, c);
+  else k_locate_count<false><<<loc_grid, kBlock, 0, s>>>(pos, keys_tmp, slots, ftable, c);
   int l = 1 + launch_exclusive_sum(ftable, (uint32_t)table_entries, scan_scratch, s);
+  // (the placement writes the permutation directly; k_order_cells then orders each cell in place)
+  const unsigned cell_grid = (unsigned)((table_entries - 1 + kBlock - 1) / kBlock);
   if (queued) {
-    k_place<true><<<blocks_for(c.n), kBlock, 0, s>>>(keys_tmp, slot_tmp, ftable, c.n, keys_sorted, src_tmp);
-    k_canonical_order<true><<<blocks_for(c.n), kBlock, 0, s>>>(keys_sorted, src_tmp, ftable, c.n, perm);
+    k_place<true><<<blocks_for(c.n), kBlock, 0, s>>>(keys_tmp, slots, ftable, c.n, keys_sorted, perm);
+    k_order_cells<true><<<cell_grid, kBlock, 0, s>>>(ftable, 0u, perm);
   } else {
-    k_place<false><<<blocks_for(c.n), kBlock, 0, s>>>(keys_tmp, slot_tmp, ftable, c.n, keys_sorted, src_tmp);
-    k_canonical_order<false><<<blocks_for(c.n), kBlock, 0, s>>>(keys_sorted, src_tmp, ftable, c.n, perm);
+    k_place<false><<<blocks_for(c.n), kBlock, 0, s>>>(keys_tmp, slots, ftable, c.n, keys_sorted, perm);
+    k_order_cells<false><<<cell_grid, kBlock, 0, s>>>(ftable, c.nfine, perm);
   }
   return l + 2;
 }
