@@ -183,14 +183,18 @@ def run_config(a, B, torch, dist, rank, world, local, workload):
     # profiling synchronises inside the step, which the timed region above must not
     e.profile(True)
     drv.profile = True
+    if drv.native:
+        loc.native_gpu_segments(reset=True)
     for _ in range(a.steps):
         dt = drv.step(dt)
+    segments = loc.native_gpu_segments() if drv.native else {}
     pass_ms, pass_launches, _ = e.pass_times()
     e.profile(False)
     drv.profile = False
     stats = torch.tensor([ms, wall * 1e3, float(launches), float(drv.n_owned), float(drv.n_ghost),
                           float(bytes_timed), drv.phase_s["exchange"] * 1e3, drv.phase_s["forces_advect"] * 1e3,
-                          drv.phase_s["retries_commit"] * 1e3] + [pass_ms[k] for k in sorted(pass_ms)],
+                          drv.phase_s["retries_commit"] * 1e3] + [pass_ms[k] for k in sorted(pass_ms)]
+                         + [segments.get(k, 0.0) for k in CudaSlab.SEGMENTS],
                          dtype=torch.float64, device="cuda")
     allstats = [torch.zeros_like(stats) for _ in range(world)]
     dist.all_gather(allstats, stats)
@@ -232,7 +236,9 @@ def run_config(a, B, torch, dist, rank, world, local, workload):
                                  host_phase_ms_per_step=dict(pack_exchange_unpack=float(s[6]) / a.steps,
                                                             sort_to_first_advect=float(s[7]) / a.steps,
                                                             retries_commit=float(s[8]) / a.steps),
-                                 pass_ms_per_step={k: float(s[9 + i]) / a.steps for i, k in enumerate(names)}))
+                                 pass_ms_per_step={k: float(s[9 + i]) / a.steps for i, k in enumerate(names)},
+                                 gpu_segments_ms_per_step={k: float(s[9 + len(names) + i])
+                                                           for i, k in enumerate(CudaSlab.SEGMENTS)}))
         slow = max(per_rank, key=lambda d: d["ms_per_step"])
         f_ms = slow["pass_ms_per_step"]["forces"]
         n_loc = slow["owned"]
@@ -308,7 +314,8 @@ def main_multi(args, rank, world, local, workload):
                                        unit=l2["unit"], ms_per_step=l2["ms_per_step"], particles=l2["config"]["particles"],
                                        p2p_halo=l2["config"]["p2p_halo"],
                                        ranks=[dict(rank=r["rank"], ms_per_step=r["ms_per_step"], owned=r["owned"],
-                                                   ghosts=r["ghosts"], host_phase_ms_per_step=r["host_phase_ms_per_step"])
+                                                   ghosts=r["ghosts"], host_phase_ms_per_step=r["host_phase_ms_per_step"],
+                                                   gpu_segments_ms_per_step=r["gpu_segments_ms_per_step"])
                                               for r in l2["ranks"]])
     if rank == 0:
         line["parity_check"] = parity

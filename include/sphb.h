@@ -245,6 +245,13 @@ uint64_t sphb_slab_resends(sphb_engine* e);
  * pack + exchange + unpack | sort .. forces + first advection attempt + all-reduce | further
  * attempts + commit */
 int sphb_slab_phase_ms(sphb_engine* e, double out3[3], int reset);
+/* GPU-side time (CUDA events on the engine's stream, ms, accumulated over `*steps` steps taken with
+ * sphb_profile_enable on) of the segments of sphb_slab_step: [0] pack, [1] waiting for the neighbours'
+ * halos (peer memory) / send + receive (NCCL), [2] the count read-back — a host round trip during
+ * which the GPU idles — and the unpack, [3] sort ... forces, [4] the first advection, [5] its
+ * reduction + the all-reduce, [6] the read-back of the all-reduce and any further attempts, [7] idle
+ * between the end of a step and the start of the next (host).  Measurement only. */
+int sphb_slab_gpu_segments(sphb_engine* e, double out8[8], uint64_t* steps, int reset);
 
 /* ---- measurement ------------------------------------------------------------------ */
 enum {

@@ -67,6 +67,8 @@ int sphb_destroy(sphb_engine* e) {
   cudaFree(e->qctl); cudaFree(e->qlog);
   if (e->qctl_host) cudaFreeHost(e->qctl_host);
   if (e->qlog_host) cudaFreeHost(e->qlog_host);
+  if (e->seg_created)
+    for (int k = 0; k < 9; ++k) cudaEventDestroy(e->seg_ev[k]);
   if (e->ev_created)
     for (int p = 0; p <= SPHB_PASS_COUNT; ++p) {
       cudaEventDestroy(e->ev[p][0]);

@@ -52,6 +52,13 @@ struct sphb_engine {
   bool p2p_ipc[2] = {false, false};  // opened with cudaIpcOpenMemHandle (to be closed)
   uint32_t p2p_seq = 0;
   double phase_ms[3] = {0.0, 0.0, 0.0};  // pack..unpack | sort..first reduction | retries + commit
+  // GPU-side segments of a slab step (sphb_slab_gpu_segments; recorded while profiling is on):
+  // pack | wait for the halos | count read-back (host) + unpack | sort..forces + owned scan |
+  // first advection | reduction + all-reduce | later attempts | (idle between steps)
+  cudaEvent_t seg_ev[9] = {};
+  bool seg_created = false;
+  double seg_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  uint64_t seg_steps = 0;
   uint32_t n = 0;    // particles the kernels run over (slab mode: owned + ghosts of this step)
   uint32_t cap = 0;  // allocated particle slots (== n outside slab mode)
   // slab mode (multi-GPU, slab.cu): this engine owns the particles with x in [xlo, xhi)

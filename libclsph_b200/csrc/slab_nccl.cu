@@ -91,11 +91,12 @@ int require_comm(sphb_engine* e) {
 }
 
 // all-reduce MAX of the 8 floats at e->red8_dev, then bring them to the host
-int reduce8(sphb_engine* e) {
+int reduce8(sphb_engine* e, cudaEvent_t after_allreduce = nullptr) {
   NcclApi& a = nccl();
   if (e->comm_world > 1)
     NCCL_TRY(e, a.AllReduce(e->red8_dev, e->red8_dev, 8, kNcclFloat32, kNcclMax,
                             static_cast<ncclComm_t>(e->comm), e->stream));
+  if (after_allreduce) cudaEventRecord(after_allreduce, e->stream);
   CUDA_TRY(e, cudaMemcpyAsync(e->red8_host, e->red8_dev, 8 * sizeof(float), cudaMemcpyDeviceToHost, e->stream));
   CUDA_TRY(e, cudaStreamSynchronize(e->stream));
   return 0;
@@ -297,15 +298,26 @@ int sphb_slab_step(sphb_engine* e, float dt_in, float* dt_out, int* attempts_out
   clk::time_point t1 = t0, t2 = t0;
   void* send_l = e->msg[0]; void* recv_l = e->msg[1]; void* send_r = e->msg[2]; void* recv_r = e->msg[3];
   uint32_t n_owned = 0, n_ghost = 0;
+  // GPU-side segment marks (only while profiling: an event record is cheap but not free)
+  const bool seg = e->profile;
+  if (seg && !e->seg_created) {
+    for (int k = 0; k < 9; ++k) CUDA_TRY(e, cudaEventCreate(&e->seg_ev[k]));
+    e->seg_created = true;
+  }
+  bool seg_prev = seg && e->seg_steps > 0;  // seg_ev[8]: the end of the previous profiled step
+  auto mark = [&](int k) { if (seg) cudaEventRecord(e->seg_ev[k], e->stream); };
+  mark(0);
   if (e->p2p_active) {
     // The exchange over peer memory: the pack kernel writes its records into the neighbours'
     // inboxes over NVLink and publishes this step's number behind them; this stream waits for
     // the same number in its own inboxes.  No send, no receive, no message sizing.
     const uint32_t seq = ++e->p2p_seq;
     if (int rc = slab_pack_to(e, e->p2p_remote[0], e->p2p_remote[1], seq)) return rc;
+    mark(1);
     e->launches += launch_slab_wait(e->has_left ? recv_l : nullptr, e->has_right ? recv_r : nullptr, seq,
                                     e->counters + 4, 20ull * 1000ull * 1000ull * 1000ull, e->stream);
     CUDA_TRY(e, cudaGetLastError());
+    mark(2);
     if (int rc = slab_read_counts(e, recv_l, recv_r)) return rc;  // host sync
     const uint32_t* hc = e->host_counts;
     if (hc[13]) SPHB_FAIL(e, SPHB_ERR_INVALID, "the %s neighbour's halo did not arrive within 20 s",
@@ -315,6 +327,7 @@ int sphb_slab_step(sphb_engine* e, float dt_in, float* dt_out, int* attempts_out
     if (int rc = slab_apply_unpack(e, recv_l, recv_r, &n_owned, &n_ghost)) return rc;
   } else {
   if (int rc = sphb_slab_pack(e, send_l, send_r)) return rc;
+  mark(1);
   // A message carries the records its predecessor carried one step ago plus a margin, not the
   // full capacity: both ends of a pair know that count (the sender counted it, the receiver
   // read it from the header), so both post the same size.  A message that outgrew its size is
@@ -344,6 +357,7 @@ int sphb_slab_step(sphb_engine* e, float dt_in, float* dt_out, int* attempts_out
     return 0;
   };
   if (int rc = exchange(e->has_left, e->has_right, rec)) return rc;
+  mark(2);
   if (int rc = slab_read_counts(e, recv_l, recv_r)) return rc;  // host sync
   {
     const uint32_t* hc = e->host_counts;
@@ -361,19 +375,32 @@ int sphb_slab_step(sphb_engine* e, float dt_in, float* dt_out, int* attempts_out
   if (int rc = slab_apply_unpack(e, recv_l, recv_r, &n_owned, &n_ghost)) return rc;
   }
   t1 = clk::now();
+  mark(3);
   if (int rc = sphb_slab_forces(e, e->gmin, e->gmax)) return rc;
+  mark(4);
   float dt = dt_in, computed = dt_in;
   int attempts = 0;
   do {
     dt = computed;
     if (int rc = sphb_slab_advect(e, dt, e->red8_dev)) return rc;
-    if (int rc = reduce8(e)) return rc;  // host sync
+    if (attempts == 0) mark(5);
+    if (int rc = reduce8(e, seg && attempts == 0 ? e->seg_ev[6] : nullptr)) return rc;  // host sync
     if (attempts == 0) t2 = clk::now();
     computed = dt_from_maxima(e->params, e->red8_host[6], e->red8_host[7]);
     ++attempts;
   } while (dt - computed > 0.00001);  // sph_simulation.cpp:260
   if (int rc = sphb_slab_commit(e)) return rc;
   bbox_from_red8(e);
+  if (seg) {
+    cudaEventRecord(e->seg_ev[7], e->stream);  // after the last attempt's reduction
+    CUDA_TRY(e, cudaEventSynchronize(e->seg_ev[7]));
+    float ms = 0.f;
+    if (seg_prev && cudaEventElapsedTime(&ms, e->seg_ev[8], e->seg_ev[0]) == cudaSuccess) e->seg_ms[7] += ms;
+    for (int k = 0; k < 7; ++k)
+      if (cudaEventElapsedTime(&ms, e->seg_ev[k], e->seg_ev[k + 1]) == cudaSuccess) e->seg_ms[k] += ms;
+    cudaEventRecord(e->seg_ev[8], e->stream);
+    ++e->seg_steps;
+  }
   // wall-clock per phase, split at the step's host synchronisation points
   const clk::time_point t3 = clk::now();
   e->phase_ms[0] += std::chrono::duration<double, std::milli>(t1 - t0).count();
@@ -389,6 +416,17 @@ int sphb_slab_step(sphb_engine* e, float dt_in, float* dt_out, int* attempts_out
 uint64_t sphb_slab_bytes_sent(sphb_engine* e) { return e ? e->bytes_sent : 0; }
 int sphb_slab_p2p_active(sphb_engine* e) { return e && e->p2p_active ? 1 : 0; }
 uint64_t sphb_slab_resends(sphb_engine* e) { return e ? e->resends : 0; }
+
+int sphb_slab_gpu_segments(sphb_engine* e, double out8[8], uint64_t* steps, int reset) {
+  if (!e || !out8) return SPHB_ERR_INVALID;
+  for (int k = 0; k < 8; ++k) {
+    out8[k] = e->seg_ms[k];
+    if (reset) e->seg_ms[k] = 0.0;
+  }
+  if (steps) *steps = e->seg_steps;
+  if (reset) e->seg_steps = 0;
+  return 0;
+}
 
 int sphb_slab_phase_ms(sphb_engine* e, double out3[3], int reset) {
   if (!e || !out3) return SPHB_ERR_INVALID;

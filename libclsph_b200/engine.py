@@ -82,7 +82,7 @@ SYMBOLS = [
     "sphb_slab_pack", "sphb_slab_unpack", "sphb_slab_forces", "sphb_slab_advect", "sphb_slab_commit",
     "sphb_slab_download", "sphb_compute_dt", "sphb_scene_build_ms", "sphb_upload_begin", "sphb_upload_commit",
     "sphb_nccl_unique_id", "sphb_slab_comm_init", "sphb_slab_start", "sphb_slab_step", "sphb_slab_bytes_sent",
-    "sphb_slab_phase_ms", "sphb_slab_resends", "sphb_slab_p2p_active", "sphb_cell_table_noalloc", "sphb_neighbor_list_stats",
+    "sphb_slab_phase_ms", "sphb_slab_resends", "sphb_slab_p2p_active", "sphb_cell_table_noalloc", "sphb_neighbor_list_stats", "sphb_slab_gpu_segments",
 ]
 
 
@@ -158,6 +158,7 @@ def lib():
         L.sphb_slab_bytes_sent.argtypes = [vp]
         L.sphb_slab_bytes_sent.restype = C.c_uint64
         L.sphb_slab_phase_ms.argtypes = [vp, vp, i32]
+        L.sphb_slab_gpu_segments.argtypes = [vp, vp, vp, i32]
         L.sphb_slab_p2p_active.argtypes = [vp]
         L.sphb_slab_resends.argtypes = [vp]
         L.sphb_slab_resends.restype = C.c_uint64

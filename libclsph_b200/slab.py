@@ -145,6 +145,18 @@ class CudaSlab:
         self._chk(self.e.L.sphb_slab_phase_ms(self.e.h, out.ctypes.data, int(reset)))
         return out
 
+    SEGMENTS = ["pack", "halo_wait", "count_readback_unpack", "sort_to_forces", "first_advect",
+                "reduce_allreduce", "readback_and_retries", "idle_between_steps"]
+
+    def native_gpu_segments(self, reset=False):
+        """GPU-side ms per segment of sphb_slab_step, averaged over the profiled steps"""
+        import ctypes as C
+        out = np.zeros(8, np.float64)
+        steps = C.c_uint64()
+        self._chk(self.e.L.sphb_slab_gpu_segments(self.e.h, out.ctypes.data, C.byref(steps), int(reset)))
+        k = max(1, int(steps.value))
+        return {name: float(v) / k for name, v in zip(self.SEGMENTS, out)}
+
     def p2p_active(self):
         """the halo exchange runs over peer memory (no ncclSend / ncclRecv)"""
         return bool(self.e.L.sphb_slab_p2p_active(self.e.h))
