@@ -134,7 +134,10 @@ int sphb_step(sphb_engine* e, float dt_in, float* dt_out);
  * needs more than two advection attempts, and for the first step after an upload.
  * max_steps > 0 stops after that many steps.  *dt_out = the loop's dt afterwards; *steps_out =
  * steps run; timeleft_log[k] (k < log_cap) = timeleft after step k — what the reference prints
- * per step.  One engine per device at a time may be inside this call. */
+ * per step.  Several engines of one process may be inside this call on the same device at once:
+ * the device-driven steps share per-process constants, so one engine at a time per device runs
+ * them and any other engine steps from the host for that batch (same results, one host round
+ * trip per step). */
 int sphb_run_frame(sphb_engine* e, float dt_in, float frame_time, uint64_t max_steps, float* dt_out,
                    uint32_t* steps_out, float* timeleft_log, uint32_t log_cap);
 /* Steps that sphb_run_frame ran without a host round trip since the engine was created. */

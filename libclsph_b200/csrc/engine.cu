@@ -10,6 +10,8 @@
 
 
 
+#include <atomic>
+
 #include "engine_internal.cuh"
 
 namespace {
@@ -19,6 +21,27 @@ constexpr uint32_t kQueueLog = 4096;  // timeleft log entries = most steps one b
 // 0.355 -> 0.324 at 1 M particles, 1.169 -> 1.147 at 4.1 M, and with the round-2 kernels 3.86 -> 3.80
 // at 16.7 M (round 1 measured a small loss there, when the whole table capacity was scanned in three passes).
 constexpr uint32_t kQueueAutoMax = 1u << 26;
+
+// Device-driven steps read their per-step constants from ONE __constant__ copy per translation
+// unit (g_hot in kernels_exact.cu / kernels_neighbors.cu), refreshed on the engine's stream: two
+// engines of one process stepping device-driven on the same GPU at the same time would overwrite
+// each other's grid.  So one engine at a time per device holds this lease for the length of a
+// batch (which ends in a stream synchronisation); an engine that finds it taken steps from the host
+// for that batch (sphb_step passes its constants as kernel arguments and is not affected).
+std::atomic<sphb_engine*> g_queue_owner[64];
+struct QueueLease {
+  std::atomic<sphb_engine*>* slot = nullptr;
+  bool held = false;
+  QueueLease(sphb_engine* e, bool want) {
+    if (!want || e->device < 0 || e->device >= 64) return;
+    slot = &g_queue_owner[e->device];
+    sphb_engine* nobody = nullptr;
+    held = slot->compare_exchange_strong(nobody, e);
+  }
+  ~QueueLease() {
+    if (held) slot->store(nullptr);
+  }
+};
 }  // namespace
 
 std::string& sphb_create_error_slot() {
@@ -574,8 +597,10 @@ int sphb_run_frame(sphb_engine* e, float dt_in, float frame_time, uint64_t max_s
   while (timeleft > 0.0) {
     if (max_steps && steps >= max_steps) break;
     const bool want_queue = e->use_queue == 1 || (e->use_queue == 2 && e->n <= kQueueAutoMax);
-    const bool can_queue = want_queue && e->bbox_valid && e->sort_variant == 0 && (e->neighbor_variant == 0 || e->neighbor_variant == 2) &&
+    const bool may_queue = want_queue && e->bbox_valid && e->sort_variant == 0 && (e->neighbor_variant == 0 || e->neighbor_variant == 2) &&
                            !e->profile && e->ftable_cap && e->ref_table_cap && e->scan_scratch;
+    const QueueLease lease(e, may_queue);  // (released at the end of this iteration, after the batch's sync)
+    const bool can_queue = may_queue && lease.held;
     if (!can_queue) {  // the first step after an upload (its bbox needs a pass of its own), or an option
       float computed = dt;
       if (int rc = sphb_step(e, dt, &computed)) return rc;

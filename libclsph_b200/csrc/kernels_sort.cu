@@ -279,7 +279,7 @@ int exclusive_scan(uint32_t* data, uint32_t len, uint32_t* scratch, cudaStream_t
 // and its first warp walks back over the preceding tiles' words — 32 at a time — until it meets
 // one that already carries an inclusive prefix.  One read and one write of the table instead of
 // two reads and two writes, one launch instead of three.  status[] and the ticket are zeroed by
-// the launcher.  A predecessor that does not answer within ~2 s is a bug: the kernel traps (the
+// the launcher.  A predecessor that does not answer within 60 s is a bug: the kernel traps (the
 // next CUDA call fails) rather than spinning for ever.
 constexpr int kLookPer = 16;                       // entries per thread: 4 x uint4, warp-striped
 constexpr int kLookTile = kThreads * kLookPer;     // 4096 entries per CTA
@@ -351,7 +351,10 @@ __global__ void __launch_bounds__(kThreads)
         if (mine >= 0) {
           word = status[mine];
           while ((uint32_t)(word >> 32) == 0u) {
-            if (globaltimer_ns() - t0 > 2000000000ull) __trap();
+            // %globaltimer is wall clock: it keeps running while the context is time-sliced out
+            // (other processes on the GPU, a profiler's replay), so the bound is generous — a
+            // predecessor silent for a whole minute is a bug, and a trap beats a hung device
+            if (globaltimer_ns() - t0 > 60000000000ull) __trap();
             __nanosleep(40);
             word = status[mine];
           }

@@ -124,3 +124,45 @@ def test_run_frame_mucus_monkeybox_fixture_scene():
                            total_gridpoints=int(sc["total_gridpoints"])))
     for graph in (0, 1):
         _compare(case, case["particles"], 2, {"graph": graph})
+
+
+def test_two_engines_in_run_frame_at_once(tmp_path):
+    """Two engines on ONE device inside sphb_run_frame at the same time, from two threads: the
+    device-driven steps share per-process constants, so one engine at a time holds the device's
+    lease and the other steps from the host for that batch — both must give exactly what each
+    gives alone (different particle counts, so a leaked grid would be visible at once)."""
+    import threading
+    for d in ("a", "b"):
+        os.makedirs(tmp_path / d)
+    cases = [make_case(tmp_path / "a", "water", 32768), make_case(tmp_path / "b", "water", 46656)]
+    alone = []
+    for c in cases:
+        with new_engine(c) as e:
+            e.set_option("device_loop", 1)
+            e.upload(c["particles"])
+            e.step(1.0 / 600.0)
+            for _ in range(4):
+                e.run_frame(1.0 / 600.0, 1.0, 3)
+            alone.append(e.download())
+    for attempt in range(3):
+        engines = [new_engine(c) for c in cases]
+        got = [None, None]
+
+        def work(k):
+            e = engines[k]
+            e.set_option("device_loop", 1)
+            e.upload(cases[k]["particles"])
+            e.step(1.0 / 600.0)
+            for _ in range(4):  # four calls of three steps: the lease changes hands between them
+                e.run_frame(1.0 / 600.0, 1.0, 3)
+            got[k] = e.download()
+
+        threads = [threading.Thread(target=work, args=(k,)) for k in range(2)]
+        for t in threads:
+            t.start()
+        for t in threads:
+            t.join()
+        for e in engines:
+            e.close()
+        for k in range(2):
+            assert got[k].tobytes() == alone[k].tobytes(), (attempt, k)
