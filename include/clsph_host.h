@@ -44,6 +44,11 @@ void clsph_lattice(sphb_particle* out, uint32_t count, float initial_volume);
 size_t clsph_geo_text(const sphb_particle* particles, uint32_t count, float particle_mass,
                       uint32_t threads, char* out, size_t cap);
 
+/* The .geo writer's float formatter on its own (tests): each value as the reference's
+ * `stream << float` prints it (printf "%g"; util/houdini_geo/HoudiniFileDumpHelper.cpp:56-75),
+ * followed by '\n'.  Same return convention as clsph_geo_text. */
+size_t clsph_format_floats(const float* values, size_t count, char* out, size_t cap);
+
 /* The Bgeo-V5 bytes of the reference's USE_PARTIO build for the same frame
  * (util/partio/PartioFunctions.h:5-65 + Partio::write, libclsph/file_save_delegates/
  * houdini_file_saver.cpp:78-89; partio itself is not vendored in the reference).  Same return

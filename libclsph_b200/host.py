@@ -9,7 +9,7 @@ from .engine import BB, PARAMS, PARTICLE, TERMS, HERE, _ptr, lib as _engine_lib
 
 SYMBOLS = [
     "clsph_scene_load", "clsph_scene_face_count", "clsph_scene_total_grid_points", "clsph_scene_copy",
-    "clsph_scene_free", "clsph_load_settings", "clsph_lattice", "clsph_geo_text", "clsph_bgeo_bytes",
+    "clsph_scene_free", "clsph_load_settings", "clsph_lattice", "clsph_geo_text", "clsph_bgeo_bytes", "clsph_format_floats",
     "clsph_save_frame", "clsph_simulate", "clsph_simulate_devices", "clsph_equal_count_cuts", "clsph_gather_sort",
     "clsph_deal_out",
 ]
@@ -107,6 +107,18 @@ def geo_text(particles, particle_mass, threads=0):
     n = L.clsph_geo_text(_ptr(particles), len(particles), particle_mass, threads, None, 0)
     buf = C.create_string_buffer(n)
     L.clsph_geo_text(_ptr(particles), len(particles), particle_mass, threads, buf, n)
+    return buf.raw[:n]
+
+
+def format_floats(values):
+    """the .geo writer's formatter: b"<value>\\n" per float32, as `ostream << float` prints it"""
+    values = np.ascontiguousarray(values, np.float32)
+    L = lib()
+    L.clsph_format_floats.restype = C.c_size_t
+    L.clsph_format_floats.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]
+    n = L.clsph_format_floats(_ptr(values), len(values), None, 0)
+    buf = C.create_string_buffer(n)
+    L.clsph_format_floats(_ptr(values), len(values), buf, n)
     return buf.raw[:n]
 
 

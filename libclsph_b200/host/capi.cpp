@@ -114,6 +114,13 @@ size_t clsph_geo_text(const sphb_particle* particles, uint32_t count, float part
   return text.size();
 }
 
+size_t clsph_format_floats(const float* values, size_t count, char* out, size_t cap) {
+  if (!values) return 0;
+  const std::string text = sphb_host::format_floats_like_ostream(values, count);
+  if (out && cap >= text.size()) std::memcpy(out, text.data(), text.size());
+  return text.size();
+}
+
 size_t clsph_bgeo_bytes(const sphb_particle* particles, const sphb_params* params, uint32_t threads,
                         char* out, size_t cap) {
   if (!particles || !params) return 0;

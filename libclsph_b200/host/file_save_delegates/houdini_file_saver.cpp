@@ -1,7 +1,9 @@
 #include "file_save_delegates/houdini_file_saver.h"
 
+#include <cmath>
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <fstream>
 #include <iostream>
@@ -11,8 +13,72 @@
 namespace sphb_host {
 namespace {
 
-// operator<<(ostream&, float) with default flags is printf("%g") (precision 6).
-inline char* put_float(char* p, float f) { return p + std::sprintf(p, "%g", (double)f); }
+// operator<<(ostream&, float) with default flags is printf("%g") (precision 6).  put_float writes
+// exactly those bytes without going through printf for almost every value: the 6 significant
+// digits come from one multiplication by a power of ten and one rounding, and whenever that
+// rounding could be a close call (the scaled value within 1e-6 of a tie — the multiplication is
+// good to ~1e-10 there), or the value is not an ordinary finite number, printf itself is asked.
+inline char* put_float_slow(char* p, float f) { return p + std::sprintf(p, "%g", (double)f); }
+
+struct Pow10Table {
+  double v[121];  // 10^-60 ... 10^60
+  Pow10Table() {
+    for (int k = 0; k <= 120; ++k) {
+      char lit[16];
+      std::snprintf(lit, sizeof lit, "1e%d", k - 60);
+      v[k] = std::strtod(lit, nullptr);  // correctly rounded
+    }
+  }
+  double operator()(int e) const { return v[e + 60]; }
+};
+const Pow10Table kPow10;
+
+inline char* put_float(char* p, float f) {
+  uint32_t bits;
+  std::memcpy(&bits, &f, 4);
+  const uint32_t mag = bits & 0x7fffffffu;
+  if (mag == 0u) {  // "0" / "-0"
+    if (bits) *p++ = '-';
+    *p++ = '0';
+    return p;
+  }
+  if (mag < 0x00800000u || mag >= 0x7f800000u) return put_float_slow(p, f);  // denormal, inf, nan
+  const double a = std::fabs((double)f);
+  // decimal exponent: from the binary one (log10(2) = 0.30103), corrected by the scaled value itself
+  int e10 = (int)(((int)(mag >> 23) - 127) * 0.30102999566398120);
+  if ((int)(mag >> 23) - 127 < 0) --e10;
+  double scaled = a * kPow10(5 - e10);
+  if (scaled < 1e5) { --e10; scaled = a * kPow10(5 - e10); }
+  else if (scaled >= 1e6) { ++e10; scaled = a * kPow10(5 - e10); }
+  if (!(scaled >= 1e5 && scaled < 1e6)) return put_float_slow(p, f);
+  const double fl = std::floor(scaled), frac = scaled - fl;
+  if (std::fabs(frac - 0.5) < 1e-6) return put_float_slow(p, f);  // a tie, or too close to call here
+  uint32_t digits = (uint32_t)fl + (frac > 0.5 ? 1u : 0u);
+  if (digits == 1000000u) { digits = 100000u; ++e10; }
+  if (bits >> 31) *p++ = '-';
+  char d[6];
+  for (int k = 5; k >= 0; --k) { d[k] = (char)('0' + digits % 10u); digits /= 10u; }
+  int nd = 6;
+  while (nd > 1 && d[nd - 1] == '0') --nd;  // %g drops trailing zeros
+  if (e10 < -4 || e10 >= 6) {  // d.ddddde+XX
+    *p++ = d[0];
+    if (nd > 1) { *p++ = '.'; for (int k = 1; k < nd; ++k) *p++ = d[k]; }
+    *p++ = 'e';
+    int e = e10;
+    if (e < 0) { *p++ = '-'; e = -e; } else *p++ = '+';
+    if (e >= 100) { *p++ = (char)('0' + e / 100); e %= 100; }
+    *p++ = (char)('0' + e / 10);
+    *p++ = (char)('0' + e % 10);
+  } else if (e10 >= 0) {  // ddd.ddd
+    for (int k = 0; k <= e10; ++k) *p++ = k < nd ? d[k] : '0';
+    if (nd > e10 + 1) { *p++ = '.'; for (int k = e10 + 1; k < nd; ++k) *p++ = d[k]; }
+  } else {  // 0.000ddd
+    *p++ = '0'; *p++ = '.';
+    for (int k = -1; k > e10; --k) *p++ = '0';
+    for (int k = 0; k < nd; ++k) *p++ = d[k];
+  }
+  return p;
+}
 inline char* put_char(char* p, char c) { *p = c; return p + 1; }
 
 // density -> colour ramp of houdini_file_saver.cpp:47-61
@@ -53,8 +119,11 @@ void format_ids(unsigned int lo, unsigned int hi, std::string* out) {
   char buf[16];
   out->reserve((size_t)(hi - lo) * 9);
   for (unsigned int i = lo; i < hi; ++i) {
-    const int n = std::sprintf(buf, " %d", (int)i);
-    out->append(buf, (size_t)n);
+    char* q = buf + sizeof buf;  // " %d", digits written backwards
+    unsigned int v = i;
+    do { *--q = (char)('0' + v % 10u); v /= 10u; } while (v);
+    *--q = ' ';
+    out->append(q, (size_t)(buf + sizeof buf - q));
   }
 }
 
@@ -160,6 +229,18 @@ void bgeo_indices(unsigned int lo, unsigned int hi, bool wide, char* out) {
 }
 
 }  // namespace
+
+std::string format_floats_like_ostream(const float* values, size_t count) {
+  std::string out;
+  out.reserve(count * 12);
+  char buf[32];
+  for (size_t k = 0; k < count; ++k) {
+    char* p = put_float(buf, values[k]);
+    *p++ = '\n';
+    out.append(buf, (size_t)(p - buf));
+  }
+  return out;
+}
 
 std::string houdini_bgeo_bytes(const particle* particles, const simulation_parameters& parameters,
                                unsigned int threads) {

@@ -40,6 +40,10 @@ class houdini_file_saver {
 
 namespace sphb_host {
 // The .geo text of `count` particles (what writeFrameToFile writes), for tests.
+// The writer's float formatter on its own (tests): every value as operator<<(ostream&, float)
+// prints it, each followed by '\n'.
+std::string format_floats_like_ostream(const float* values, size_t count);
+
 std::string houdini_geo_text(const particle* particles, unsigned int count, float particle_mass,
                              unsigned int threads = 0);
 // The Bgeo-V5 bytes the reference's USE_PARTIO build writes for the same frame: makeData
