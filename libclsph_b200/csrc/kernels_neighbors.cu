@@ -111,6 +111,7 @@ __device__ __forceinline__ Rec8 ldg256(const float4* p) {
 // particle's coordinates as broadcast operands); where u < 0 the particle's sum takes u^3 (the
 // caller negates the total), and where either particle's is, the candidate's code goes to the
 // pair's list: a predicated store at a cursor that advances only on hits.
+template <uint32_t STRIDE>  // bytes between two entries of a hit column
 __device__ __forceinline__ void density_test_record(const float2& qx, const float2& qy, const float2& qz,
                                                     float neg_h2, const float2& X, const float2& Y,
                                                     const float2& Z, float& sum_a, float& sum_b,
@@ -148,23 +149,21 @@ __device__ __forceinline__ void density_test_record(const float2& qx, const floa
       "  @pc add.u32 %2, %2, %12; }"
       : "+f"(sum_a), "+f"(sum_b), "+r"(cur)
       : "f"(ua.x), "f"(ua.y), "f"(ub.x), "f"(ub.y), "f"(ua2.x), "f"(ua2.y), "f"(ub2.x), "f"(ub2.y),
-        "h"((uint16_t)code), "n"(kUStride)
+        "h"((uint16_t)code), "n"(STRIDE)
       : "memory");
 }
 
-template <bool Q>
-__global__ void __launch_bounds__(kUB)
-    k_density_union(const float4* __restrict__ pairs, const float4* __restrict__ vel,
-                    const uint32_t* __restrict__ keys, const uint32_t* __restrict__ ftable,
-                    float* __restrict__ rho, float* __restrict__ prs, float4* __restrict__ pv,
-                    uint32_t* __restrict__ pool, uint32_t cap, StepConsts c_arg) {
-  if (Q && !g_hot.active) return;
-  const StepConsts& c = Q ? g_hot.c : c_arg;
-  extern __shared__ uint16_t hit[];  // (cap + kUDump) rows of kUB columns
-  const uint32_t t = blockIdx.x * kUB + threadIdx.x;
+// The density pass of ONE pair of particles (2t, 2t + 1): walks the union of their runs, sums both
+// densities, records the pair's list (staged in the shared-memory column `col`, entries STRIDE
+// bytes apart) and writes rho, p and the pv records.
+template <uint32_t STRIDE>
+__device__ __forceinline__ void density_pair(uint32_t t, uint16_t* col, const float4* __restrict__ pairs,
+                                             const float4* __restrict__ vel, const uint32_t* __restrict__ keys,
+                                             const uint32_t* __restrict__ ftable, float* __restrict__ rho,
+                                             float* __restrict__ prs, float4* __restrict__ pv, const PairLists& L,
+                                             uint32_t cap, const StepConsts& c) {
   const uint32_t ia = 2u * t;
   if (ia >= c.n) return;
-  const PairLists L = pair_lists(pool, c.n);
   const bool has_b = ia + 1 < c.n;
   const uint32_t ib = has_b ? ia + 1 : ia;
   const Rec8 own = ldg256(pairs + ia);  // {xa, xb, ya, yb | za, zb, -, -}
@@ -181,8 +180,8 @@ __global__ void __launch_bounds__(kUB)
   const float4 nowhere = make_float4(nan, nan, nan, 0.f);  // fails every distance test
 
   // (shared-window byte addresses, so that a store is one predicated STS)
-  const uint32_t base = (uint32_t)__cvta_generic_to_shared(hit) + 2u * threadIdx.x;
-  const uint32_t end = base + cap * kUStride;
+  const uint32_t base = (uint32_t)__cvta_generic_to_shared(col);
+  const uint32_t end = base + cap * STRIDE;
   uint32_t cur = base, cnt_a = 0;
   float sum_a = 0.f, sum_b = 0.f;
   bool unusable = false;
@@ -232,7 +231,7 @@ __global__ void __launch_bounds__(kUB)
           Rec8 r = ldg256(pairs + j);
           if (j < s) r.a.x = nan;
           if (j + 1u >= e) r.a.y = nan;
-          density_test_record(qx, qy, qz, -c.h2, r.a, r.b, r.c, sum_a, sum_b, cur, code);
+          density_test_record<STRIDE>(qx, qy, qz, -c.h2, r.a, r.b, r.c, sum_a, sum_b, cur, code);
           cur = min(cur, end);
         }
       }
@@ -240,14 +239,14 @@ __global__ void __launch_bounds__(kUB)
     // every part ends on a multiple of four entries (the forces pass takes four per trip)
 #pragma unroll
     for (int u = 0; u < 3; ++u)
-      if (((cur - base) / kUStride) & 3u) {
+      if (((cur - base) / STRIDE) & 3u) {
         asm volatile("st.shared.u16 [%0], %1;" ::"r"(cur), "h"((uint16_t)kNullCode) : "memory");
-        cur += kUStride;
+        cur += STRIDE;
       }
     cur = min(cur, end);
-    if (pass == 0) cnt_a = (cur - base) / kUStride;
+    if (pass == 0) cnt_a = (cur - base) / STRIDE;
   }
-  const uint32_t cnt = (cur - base) / kUStride;
+  const uint32_t cnt = (cur - base) / STRIDE;
   unusable = unusable || cnt >= cap;  // the dump rows were reached
 #pragma unroll
   for (int w = 0; w < 2; ++w) {
@@ -265,10 +264,234 @@ __global__ void __launch_bounds__(kUB)
   L.meta[t] = unusable ? kMetaUnusable : (cnt_a | (cnt << 8));
   if (unusable) L.queue[atomicAdd(L.qcount, 1u)] = t;
   if (!unusable) {
-    const uint16_t* col = hit + threadIdx.x;
     uint32_t* out = L.codes + t;
     for (uint32_t k = 0; k < cnt; k += 2u)
-      out[(size_t)(k >> 1) * L.np] = (uint32_t)col[k * kUB] | ((uint32_t)col[(k + 1u) * kUB] << 16);
+      out[(size_t)(k >> 1) * L.np] = (uint32_t)col[k * (STRIDE / 2u)] | ((uint32_t)col[(k + 1u) * (STRIDE / 2u)] << 16);
+  }
+}
+
+template <bool Q>
+__global__ void __launch_bounds__(kUB)
+    k_density_union(const float4* __restrict__ pairs, const float4* __restrict__ vel,
+                    const uint32_t* __restrict__ keys, const uint32_t* __restrict__ ftable,
+                    float* __restrict__ rho, float* __restrict__ prs, float4* __restrict__ pv,
+                    uint32_t* __restrict__ pool, uint32_t cap, StepConsts c_arg) {
+  if (Q && !g_hot.active) return;
+  const StepConsts& c = Q ? g_hot.c : c_arg;
+  extern __shared__ uint16_t hit[];  // (cap + kUDump) rows of kUB columns
+  const PairLists L = pair_lists(pool, c.n);
+  density_pair<kUStride>(blockIdx.x * kUB + threadIdx.x, hit + threadIdx.x, pairs, vel, keys, ftable, rho, prs, pv, L,
+                         cap, c);
+}
+
+// ---- experiment (sphb_set_option("neighbor_kernel", 7)): four particles per thread -----------------
+// The passes are bound by bytes delivered from L1 to registers; a 32-byte record serves 4 distance
+// tests in k_density_union.  Here a thread owns FOUR consecutive particles (two pairs): when all
+// four sit in one row of cells within 2 h of each other it walks the union of their runs ONCE and
+// every record serves 8 tests; it still records one list per PAIR (two shared-memory columns), so
+// the forces pass is unchanged.  Any other quad (row ends, n not a multiple of 4) is done as two
+// pair walks.
+constexpr int kQB = 64;                          // threads per CTA (256 particles)
+constexpr uint32_t kQStride = 2u * 2u * kQB;     // bytes between two entries of a column (2 columns per thread)
+
+template <uint32_t STRIDE>
+__device__ __forceinline__ void density_test_record_quad(const float2 (&qx)[2], const float2 (&qy)[2],
+                                                         const float2 (&qz)[2], float neg_h2, const float2& X,
+                                                         const float2& Y, const float2& Z, float (&sum)[4],
+                                                         uint32_t& cur0, uint32_t& cur1, uint32_t code) {
+  float2 u[4], u2[4];  // per particle: (candidate 0, candidate 1)
+#pragma unroll
+  for (int w = 0; w < 4; ++w) {
+    const float px = (w & 1) ? qx[w >> 1].y : qx[w >> 1].x, py = (w & 1) ? qy[w >> 1].y : qy[w >> 1].x,
+                pz = (w & 1) ? qz[w >> 1].y : qz[w >> 1].x;
+    float2 d = __fadd2_rn(X, bcast2(-px));
+    u[w] = __ffma2_rn(d, d, bcast2(neg_h2));
+    d = __fadd2_rn(Y, bcast2(-py));
+    u[w] = __ffma2_rn(d, d, u[w]);
+    d = __fadd2_rn(Z, bcast2(-pz));
+    u[w] = __ffma2_rn(d, d, u[w]);
+    u2[w] = __fmul2_rn(u[w], u[w]);
+  }
+  asm volatile(
+      "{ .reg .pred pa, pb, pc, pd, p0, p1;\n"
+      "  .reg .b16 c1;\n"
+      "  setp.lt.f32 pa, %6, 0f00000000;\n"
+      "  setp.lt.f32 pb, %8, 0f00000000;\n"
+      "  setp.lt.f32 pc, %10, 0f00000000;\n"
+      "  setp.lt.f32 pd, %12, 0f00000000;\n"
+      "  @pa fma.rn.f32 %0, %14, %6, %0;\n"
+      "  @pb fma.rn.f32 %1, %16, %8, %1;\n"
+      "  @pc fma.rn.f32 %2, %18, %10, %2;\n"
+      "  @pd fma.rn.f32 %3, %20, %12, %3;\n"
+      "  or.pred p0, pa, pb;\n"
+      "  or.pred p1, pc, pd;\n"
+      "  @p0 st.shared.u16 [%4], %22;\n"
+      "  @p0 add.u32 %4, %4, %23;\n"
+      "  @p1 st.shared.u16 [%5], %22;\n"
+      "  @p1 add.u32 %5, %5, %23;\n"
+      "  setp.lt.f32 pa, %7, 0f00000000;\n"
+      "  setp.lt.f32 pb, %9, 0f00000000;\n"
+      "  setp.lt.f32 pc, %11, 0f00000000;\n"
+      "  setp.lt.f32 pd, %13, 0f00000000;\n"
+      "  @pa fma.rn.f32 %0, %15, %7, %0;\n"
+      "  @pb fma.rn.f32 %1, %17, %9, %1;\n"
+      "  @pc fma.rn.f32 %2, %19, %11, %2;\n"
+      "  @pd fma.rn.f32 %3, %21, %13, %3;\n"
+      "  or.pred p0, pa, pb;\n"
+      "  or.pred p1, pc, pd;\n"
+      "  add.u16 c1, %22, 1;\n"
+      "  @p0 st.shared.u16 [%4], c1;\n"
+      "  @p0 add.u32 %4, %4, %23;\n"
+      "  @p1 st.shared.u16 [%5], c1;\n"
+      "  @p1 add.u32 %5, %5, %23; }"
+      : "+f"(sum[0]), "+f"(sum[1]), "+f"(sum[2]), "+f"(sum[3]), "+r"(cur0), "+r"(cur1)
+      : "f"(u[0].x), "f"(u[0].y), "f"(u[1].x), "f"(u[1].y), "f"(u[2].x), "f"(u[2].y), "f"(u[3].x), "f"(u[3].y),
+        "f"(u2[0].x), "f"(u2[0].y), "f"(u2[1].x), "f"(u2[1].y), "f"(u2[2].x), "f"(u2[2].y), "f"(u2[3].x),
+        "f"(u2[3].y), "h"((uint16_t)code), "n"(STRIDE)
+      : "memory");
+}
+
+__device__ __noinline__ void density_pair_outlined(uint32_t t, uint16_t* col, const float4* __restrict__ pairs,
+                                                  const float4* __restrict__ vel, const uint32_t* __restrict__ keys,
+                                                  const uint32_t* __restrict__ ftable, float* __restrict__ rho,
+                                                  float* __restrict__ prs, float4* __restrict__ pv, const PairLists& L,
+                                                  uint32_t cap, const StepConsts& c) {
+  density_pair<kQStride>(t, col, pairs, vel, keys, ftable, rho, prs, pv, L, cap, c);
+}
+
+#ifndef SPHB_QUAD_MINB
+#define SPHB_QUAD_MINB 10
+#endif
+__global__ void __launch_bounds__(kQB, SPHB_QUAD_MINB)
+    k_density_quad(const float4* __restrict__ pairs, const float4* __restrict__ vel,
+                   const uint32_t* __restrict__ keys, const uint32_t* __restrict__ ftable,
+                   float* __restrict__ rho, float* __restrict__ prs, float4* __restrict__ pv,
+                   uint32_t* __restrict__ pool, uint32_t cap, StepConsts c) {
+  extern __shared__ uint16_t hit[];  // (cap + kUDump) rows of 2 * kQB columns
+  const uint32_t q = blockIdx.x * kQB + threadIdx.x;
+  const uint32_t i0 = 4u * q;
+  if (i0 >= c.n) return;
+  const PairLists L = pair_lists(pool, c.n);
+  uint16_t* const col0 = hit + 2u * threadIdx.x;
+  uint32_t fx[4], fy[4], fz[4];
+  bool quad = i0 + 3u < c.n;
+  if (quad) {
+#pragma unroll
+    for (int w = 0; w < 4; ++w) fine_coords_of(__ldg(keys + i0 + w), c, fx[w], fy[w], fz[w]);
+    quad = fy[0] == fy[3] && fz[0] == fz[3] && fy[1] == fy[0] && fy[2] == fy[0] && fz[1] == fz[0] && fz[2] == fz[0] &&
+           fx[3] - fx[0] <= kSpanTogether;
+  }
+  if (!quad) {  // two pair walks (rare: out of line, one copy)
+#pragma unroll 1
+    for (uint32_t pr = 0; pr < 2u; ++pr)
+      density_pair_outlined(2u * q + pr, col0 + pr, pairs, vel, keys, ftable, rho, prs, pv, L, cap, c);
+    return;
+  }
+  const Rec8 o0 = ldg256(pairs + i0), o1 = ldg256(pairs + i0 + 2u);
+  const float2 qx[2] = {o0.a, o1.a}, qy[2] = {o0.b, o1.b}, qz[2] = {o0.c, o1.c};
+  CellFrac f[4];
+#pragma unroll
+  for (int w = 0; w < 4; ++w) {
+    const float4 p = make_float4((w & 1) ? qx[w >> 1].y : qx[w >> 1].x, (w & 1) ? qy[w >> 1].y : qy[w >> 1].x,
+                                 (w & 1) ? qz[w >> 1].y : qz[w >> 1].x, 0.f);
+    f[w] = cell_frac(p, fx[w], fy[w], fz[w], c);
+  }
+  const float nan = __int_as_float(0x7fc00000);
+  const uint32_t base0 = (uint32_t)__cvta_generic_to_shared(col0), base1 = base0 + 2u;
+  const uint32_t end0 = base0 + cap * kQStride, end1 = base1 + cap * kQStride;
+  uint32_t cur0 = base0, cur1 = base1;
+  float sum[4] = {0.f, 0.f, 0.f, 0.f};
+  bool unusable = false;
+  const uint32_t t0 = 2u * q, t1 = t0 + 1u;
+  uint32_t rowid = 0;
+#pragma unroll 1
+  for (int dz = -1; dz <= 1; ++dz, rowid += 3u) {
+    const uint32_t z = fz[0] + dz;
+    if (z >= c.fnz) {
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        L.start[(size_t)(rowid + k) * L.np + t0] = 0;
+        L.start[(size_t)(rowid + k) * L.np + t1] = 0;
+      }
+      continue;
+    }
+    uint32_t rs[3], re[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      const int dy = k - 1;
+      const uint32_t y = fy[0] + dy;
+      uint32_t x_lo = 0xFFFFFFFFu, x_hi = 0;
+      bool any = false;
+#pragma unroll
+      for (int w = 0; w < 4; ++w) {
+        const Reach R = row_reach(c, fx[w], f[w], dy, dz);
+        if (R.on) { any = true; x_lo = min(x_lo, R.lo); x_hi = max(x_hi, R.hi); }
+      }
+      rs[k] = re[k] = 0;
+      if (y < c.fny && any) {
+        const uint32_t rowbase = (z * c.fny + y) * c.fnx;
+        rs[k] = __ldg(ftable + rowbase + x_lo);
+        re[k] = __ldg(ftable + rowbase + x_hi + 1u);
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      const uint32_t s = rs[k], e = re[k];
+      L.start[(size_t)(rowid + k) * L.np + t0] = s;
+      L.start[(size_t)(rowid + k) * L.np + t1] = s;
+      if (e - s > kMaxRun) unusable = true;
+      const uint32_t j_end = s < e ? e : s & ~1u;
+      uint32_t code = ((rowid + k) << kRowShift) - (s & 1u);
+#pragma unroll 1
+      for (uint32_t j = s & ~1u; j < j_end; j += 2u, code += 2u) {
+        Rec8 r = ldg256(pairs + j);
+        if (j < s) r.a.x = nan;
+        if (j + 1u >= e) r.a.y = nan;
+        density_test_record_quad<kQStride>(qx, qy, qz, -c.h2, r.a, r.b, r.c, sum, cur0, cur1, code);
+        cur0 = min(cur0, end0);
+        cur1 = min(cur1, end1);
+      }
+    }
+  }
+#pragma unroll
+  for (int u = 0; u < 3; ++u) {  // both lists end on a multiple of four entries
+    if (((cur0 - base0) / kQStride) & 3u) {
+      asm volatile("st.shared.u16 [%0], %1;" ::"r"(cur0), "h"((uint16_t)kNullCode) : "memory");
+      cur0 += kQStride;
+    }
+    if (((cur1 - base1) / kQStride) & 3u) {
+      asm volatile("st.shared.u16 [%0], %1;" ::"r"(cur1), "h"((uint16_t)kNullCode) : "memory");
+      cur1 += kQStride;
+    }
+  }
+  cur0 = min(cur0, end0);
+  cur1 = min(cur1, end1);
+#pragma unroll
+  for (int w = 0; w < 4; ++w) {
+    const uint32_t i = i0 + w;
+    const float density = (c.mass * c.c_poly6) * -sum[w];
+    const float pressure = tait_pressure(density, c);
+    rho[i] = density;
+    prs[i] = pressure;
+    const float4 v = __ldg(vel + i);
+    pv[2u * i] = make_float4((w & 1) ? qx[w >> 1].y : qx[w >> 1].x, (w & 1) ? qy[w >> 1].y : qy[w >> 1].x,
+                             (w & 1) ? qz[w >> 1].y : qz[w >> 1].x, pressure / (density * density));
+    pv[2u * i + 1u] = make_float4(v.x, v.y, v.z, c.mass / density);
+  }
+#pragma unroll
+  for (int pr = 0; pr < 2; ++pr) {
+    const uint32_t t = pr ? t1 : t0;
+    const uint32_t cnt = ((pr ? cur1 : cur0) - (pr ? base1 : base0)) / kQStride;
+    const bool bad = unusable || cnt >= cap;
+    L.meta[t] = bad ? kMetaUnusable : (cnt | (cnt << 8));
+    if (bad) {
+      L.queue[atomicAdd(L.qcount, 1u)] = t;
+    } else {
+      const uint16_t* col = col0 + pr;
+      uint32_t* out = L.codes + t;
+      for (uint32_t k = 0; k < cnt; k += 2u)
+        out[(size_t)(k >> 1) * L.np] = (uint32_t)col[k * (kQStride / 2u)] | ((uint32_t)col[(k + 1u) * (kQStride / 2u)] << 16);
+    }
   }
 }
 
@@ -574,11 +797,6 @@ uint32_t neighbor_list_cap(float h, float rho0, float mass) {
   return 1.5f * in_sphere * 1.6f <= 64.f ? 64u : 128u;
 }
 
-int neighbor_kernels_init() {
-  // the 128-entry columns need 17 KB of dynamic shared memory: below the 48 KB default, nothing to opt into
-  return 0;
-}
-
 int launch_density(float4* pos, float4* vel, const float4* pairs, float4* pv, const uint32_t* keys,
                    const uint32_t* ftable, float* rho, float* prs, uint32_t* pool, uint32_t cap,
                    const StepConsts& c, int variant, cudaStream_t s, bool queued) {
@@ -588,6 +806,13 @@ int launch_density(float4* pos, float4* vel, const float4* pairs, float4* pv, co
     if (G == 4) k_density_coop<4><<<grid, 128, 0, s>>>(pos, vel, keys, ftable, rho, prs, pool, c);
     else if (G == 8) k_density_coop<8><<<grid, 128, 0, s>>>(pos, vel, keys, ftable, rho, prs, pool, c);
     else k_density_coop<16><<<grid, 128, 0, s>>>(pos, vel, keys, ftable, rho, prs, pool, c);
+    return 1;
+  }
+  if (variant == 7 && !queued) {  // experiment: four particles per thread, the same pair lists
+    const unsigned quads = (c.n + 3u) / 4u;
+    cudaMemsetAsync(pair_lists(pool, c.n).qcount, 0, 4 * sizeof(uint32_t), s);
+    k_density_quad<<<(quads + kQB - 1) / kQB, kQB, (size_t)(cap + kUDump) * 2 * kQB * sizeof(uint16_t), s>>>(
+        pairs, vel, keys, ftable, rho, prs, pv, pool, cap, c);
     return 1;
   }
   if (variant != 0) {  // round-1 kernel (A/B; it leaves p/rho^2 and m/rho in the w lanes of pos / vel)
@@ -657,11 +882,11 @@ int launch_forces(const float4* pos, const float4* vel, const float4* pv, const 
                   const uint32_t* ftable, const float* rho, const uint32_t* pool, float4* acc,
                   const StepConsts& c, int variant, cudaStream_t s, const uint32_t* ghost_ids,
                   bool queued) {
-  if ((variant == 1 || variant >= 4) && !ghost_ids && !queued) {  // forces by their own search
+  if ((variant == 1 || (variant >= 4 && variant <= 6)) && !ghost_ids && !queued) {  // forces by their own search
     k_forces_list<<<blocks_for(c.n), kBlock, 0, s>>>(pos, vel, keys, ftable, rho, acc, c);
     return 1;
   }
-  if (variant != 0) {  // round-1 kernel, from the round-1 density pass's per-particle lists
+  if (variant != 0 && variant != 7) {  // round-1 kernel, from the round-1 density pass's per-particle lists
     const uint16_t* nlist = v1_list(const_cast<uint32_t*>(pool));
     const uint8_t* ncount = v1_count(const_cast<uint32_t*>(pool), c.n);
     if (queued)

@@ -178,7 +178,7 @@ def test_free_run_matches_reference(port_oracle):
             assert abs(dt - float(g[f"s{s}_dt"])) <= 50 * TOL * float(g[f"s{s}_dt"])
 
 
-@pytest.mark.parametrize("variant", [0, 1, 2, 4, 5, 6])
+@pytest.mark.parametrize("variant", [0, 1, 2, 4, 5, 6, 7])
 def test_neighbor_kernel_variants(variant):
     """Every neighbour-pass variant against the fixture: 0 = the pair-list kernels (default),
     1 = round-1 density + forces by their own search, 2 = the round-1 kernels (one list per
@@ -211,9 +211,11 @@ def test_neighbor_list_overflow_falls_back(tmp_path, port_oracle):
     with new_engine(case) as e:
         e.upload(p)
         e.step(1.0 / 600.0)
+        stats = e.neighbor_list_stats()  # the compressed block overflows its lists: the overflow queue is used
         out = e.download()
         dbg = e.debug()
     r = orc.step(front, params, case["terms"].copy(), df, sc["bbs"], 1.0 / 600.0)
+    assert stats["overflowed_pairs"] > 0 and stats["overflowed_pairs"] <= len(p) // 2, stats
     check_exact(dbg, out["grid_index"], r["perm"], r["cell_table"], front["grid_index"], "overflow")
     got, want = state_arrays(out), state_arrays(front)
     assert rel_err(got["rho"], want["rho"]) <= TOL
@@ -353,3 +355,16 @@ def test_split_upload_overlaps_and_replaces_the_state():
     finally:
         for p in ptrs:
             lib().sphb_host_free(p)
+
+
+def test_neighbor_list_stats_on_the_rest_lattice(tmp_path):
+    """sphb_neighbor_list_stats: no list overflows on the rest lattice; every pair has a list of
+    at least its own two particles, padded to a multiple of four, below the capacity."""
+    case = make_case(tmp_path, "water", 32768)
+    with new_engine(case) as e:
+        e.upload(case["particles"])
+        e.step(1.0 / 600.0)
+        st = e.neighbor_list_stats()
+    pairs = 32768 // 2
+    assert st["overflowed_pairs"] == 0 and st["longest"] < 64 and st["longest"] % 4 == 0
+    assert 4 * pairs <= st["entries"] <= 64 * pairs and st["split_pairs"] < pairs // 10
