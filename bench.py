@@ -626,6 +626,21 @@ def main():
         ab = ALGO_BYTES.get(k) if k != "sort" else 16 * radix_passes + 4
         if ab and v > 0:
             per_pass[k]["algo_gbs"] = ab * n / (v / args.steps * 1e-3) / 1e9
+    # ncu's DRAM traffic of every captured kernel of a pass (same staleness rule as `traffic`)
+    pass_kernels = dict(sort=("k_locate_count", "k_place", "k_order_cells"), reorder=("k_reorder",),
+                        density=("k_density_union",), forces=("k_forces_union",), advect=("k_advect",),
+                        refrank=("k_morton_hist", "k_reference_rank"))
+    try:
+        doc = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+        if doc.get("source_hash") == kernel_source_hash():
+            for k, names in pass_kernels.items():
+                recs = {nm: doc["kernels"][nm] for nm in names if nm in doc.get("kernels", {}) and
+                        doc["kernels"][nm].get("particles") == n}
+                if recs and k in per_pass:
+                    per_pass[k]["ncu_dram"] = {nm: dict(gb_per_launch=r_["dram_bytes"] / 1e9, gbs=r_["dram_gbs"],
+                                                        frac_of_peak=r_["dram_gbs"] / peak) for nm, r_ in recs.items()}
+    except Exception:
+        pass
     line = dict(
         metric="SPH particle-steps/sec", value=value, unit="particle-steps/s", n_gpus=1, steps=args.steps,
         warmup=warmup, ms_per_step=ms_step, higher_is_better=True, scaling="weak", vs_baseline=None,

@@ -261,7 +261,7 @@ def run_config(a, B, torch, dist, rank, world, local, workload):
                         driver="sphb_slab_step (C, NCCL by dlopen)" if drv.native else "SlabDriver (Python, torch.distributed)",
                         l2="inputs exceed L2", exchange_capacity_records=exch, owned_total=owned_total),
             clocks=clocks, gpu_launches=int(sum(float(s[2]) for s in allstats)),
-            roofline=dict(bound="hbm", kernel="forces pass (k_forces_nlist), slowest rank", achieved=achieved,
+            roofline=dict(bound="hbm", kernel="forces pass (k_forces_union), slowest rank", achieved=achieved,
                           peak=peak, unit="GB/s", frac=achieved / peak, traffic=None, peak_source=peak_src,
                           algorithmic_bytes_per_particle=B.ALGO_BYTES["forces"], launch_ms=f_ms),
             ranks=per_rank)

@@ -39,10 +39,21 @@ def main(path, n):
                commit=subprocess.run(["git", "rev-parse", "--short", "HEAD"], capture_output=True, text=True,
                                      cwd=ROOT).stdout.strip(),
                how="ncu --set full --clock-control none, one launch each (tools/round_gpu.sh)", density={}, forces={})
+    doc["kernels"] = {}  # every captured kernel (first launch of each): DRAM bytes and duration under ncu
     for r in rows[2:]:
         d = dict(zip(head, r))
         name = d.get("Kernel Name", "")
-        which = "density" if "k_density" in name else ("forces" if "k_forces" in name else None)
+        short = name.split("(")[0].split("::")[-1].replace("unnamed>", "").strip().split("<")[0]
+        if short and short not in doc["kernels"]:
+            vals = {}
+            for k in ("dram_read", "dram_write", "time"):
+                hit = [h for h in head if h == WANT[k] or h.endswith("." + WANT[k])]
+                if hit and d[hit[0]] != "":
+                    vals[k] = float(d[hit[0]].replace(",", "")) * SCALE.get(units[head.index(hit[0])], 1.0)
+            if "time" in vals:
+                b = vals.get("dram_read", 0.0) + vals.get("dram_write", 0.0)
+                doc["kernels"][short] = dict(particles=n, dram_bytes=b, seconds=vals["time"], dram_gbs=b / vals["time"] / 1e9)
+        which = "density" if "k_density" in name else ("forces" if "k_forces_union" in name else None)
         if not which or str(n) in doc[which]:
             continue
         rec = dict(kernel=name.split("(")[0].split("::")[-1].replace("unnamed>", "").strip())

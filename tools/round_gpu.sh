@@ -16,7 +16,7 @@ short="python bench.py --steps 2 --warmup 3 --no-cpu --no-secondary --e2e-steps 
 $short > $o/plain_$tag.log 2>&1 &&
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $o/launches_$tag.csv \
   $short > $o/ncu_launch_$tag.log 2>&1; echo "ncu launches rc=$?"
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:'k_density_union|k_forces_union|k_advect|k_reorder|k_reference_rank|k_place|k_locate_count|k_canonical_order' \
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:'k_density_union|k_forces_union|k_advect|k_reorder|k_reference_rank|k_morton_hist|k_place|k_locate_count|k_order_cells' \
   --launch-skip 24 --launch-count 10 -o $o/prof_$tag -f \
   $short > $o/ncu_full_$tag.log 2>&1; echo "ncu full rc=$?"
 ls -la $o | tail -20
