@@ -290,8 +290,13 @@ int sphb_neighbor_list_stats(sphb_engine* e, uint64_t out[4]);
 /* the engine's cudaStream_t (as void*), so a caller can record its own events on it */
 void* sphb_stream(sphb_engine* e);
 /* named integer options; unknown names return SPHB_ERR_INVALID.
- *   "neighbor_kernel"  0 (default) = the density pass records a neighbour list that the forces
- *                      pass consumes; 1 = both passes search the grid on their own
+ *   "neighbor_kernel"  0 (default) = the density pass records ONE neighbour list per pair of
+ *                      consecutive particles that the forces pass consumes.  The others are kept
+ *                      for measurement (same results within the tolerance): 1 = round-1 density +
+ *                      forces by their own search; 2 = the round-1 kernels (one list per
+ *                      particle); 4 / 5 / 6 = sub-warp-cooperative density with 4 / 8 / 16 lanes
+ *                      per particle + forces by their own search; 7 = density with four
+ *                      particles per thread (the default's lists and forces)
  *   "df_face_lists"    1 (default) = the distance-field build tests, per grid point, only the
  *                      faces whose box meets the box of the face that owns the point; 0 = all
  *                      faces, as kernels/collisionsv2.cl:70-76 does (set before sphb_set_scene).

@@ -368,3 +368,33 @@ def test_neighbor_list_stats_on_the_rest_lattice(tmp_path):
     pairs = 32768 // 2
     assert st["overflowed_pairs"] == 0 and st["longest"] < 64 and st["longest"] % 4 == 0
     assert 4 * pairs <= st["entries"] <= 64 * pairs and st["split_pairs"] < pairs // 10
+
+
+@pytest.mark.parametrize("scale", [0.2, 0.05])
+def test_pile_up_many_particles_per_cell(tmp_path, port_oracle, scale):
+    """A block squeezed to 1/5 and 1/20 of its size: hundreds to thousands of particles per search
+    cell.  Exercises the per-cell ordering beyond its sorting-network / insertion-sort sizes (heap
+    sort), runs too long to be coded in a neighbour list (> 2047 candidates: the pair is queued and
+    searched), and the overflow queue — the sorted order must still be the reference's, bit for bit."""
+    case = make_case(tmp_path, "water", 4096)
+    p = case["particles"]
+    p["position"][:, :3] *= np.float32(scale)
+    orc = port_oracle
+    sc = case["scene"]
+    df = orc.compute_df(sc["bbs"], sc["transforms"], sc["rvertices"], int(sc["total_gridpoints"]))
+    front, params = p.copy(), case["params"].copy()
+    with new_engine(case) as e:
+        e.upload(p)
+        e.step(1.0 / 600.0)
+        stats = e.neighbor_list_stats()
+        out = e.download()
+        dbg = e.debug()
+    r = orc.step(front, params, case["terms"].copy(), df, sc["bbs"], 1.0 / 600.0)
+    assert stats["overflowed_pairs"] > 1000, stats
+    check_exact(dbg, out["grid_index"], r["perm"], r["cell_table"], front["grid_index"], f"pile-up {scale}")
+    got, want = state_arrays(out), state_arrays(front)
+    assert rel_err(got["rho"], want["rho"]) <= TOL
+    # Every particle has thousands of neighbours here and rho ~ 100 rho0: a density that differs by a few
+    # 1e-6 (fp32 summation order over ~4 000 terms) moves the Tait pressure K (rho/rho0)^7 by 7 times
+    # that, and the accelerations (~1e11 m/s^2, all pressure) with it.  Hence 10 TOL for this state only.
+    assert rel_err(got["acc"], want["acc"]) <= 10 * TOL
