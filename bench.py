@@ -585,8 +585,9 @@ def main():
     value = n * args.steps / (r["ms_total"] * 1e-3)
     peak, peak_src = measured_peak()
     # dominant kernel: whichever of the two neighbour passes takes longer (one launch per step each)
+    # (time per STEP: the forces pass is two launches, k_forces_union and the few-microsecond k_forces_overflow)
     dom = max(("density", "forces"), key=lambda k: r["pass_ms"][k])
-    f_ms = r["pass_ms"][dom] / max(1, r["pass_launches"][dom])
+    f_ms = r["pass_ms"][dom] / args.steps
     achieved = ALGO_BYTES[dom] * n / (f_ms * 1e-3) / 1e9
     # ncu counters of that kernel, taken on THESE sources (else null + why): DRAM traffic per launch,
     # and the two other roofs — issue slots (one warp instruction per clock and SM sub-partition)
@@ -663,9 +664,9 @@ def main():
                                             "these kernel sources (profiles/ncu_traffic.json)",
                       peak_source=peak_src, algorithmic_bytes_per_particle=ALGO_BYTES[dom], launch_ms=f_ms,
                       binding_bound=binding, other_roofs=other_roofs,
-                      both_passes={k: dict(launch_ms=r["pass_ms"][k] / max(1, r["pass_launches"][k]),
-                                           frac=ALGO_BYTES[k] * n / (r["pass_ms"][k] / max(1, r["pass_launches"][k]) * 1e-3)
-                                           / 1e9 / peak) for k in ("density", "forces")},
+                      both_passes={k: dict(launch_ms=r["pass_ms"][k] / args.steps,
+                                           frac=ALGO_BYTES[k] * n / (r["pass_ms"][k] / args.steps * 1e-3) / 1e9 / peak)
+                                   for k in ("density", "forces")},
                       note="`frac` is the HBM fraction the contract asks for (algorithmic bytes / time / measured "
                            "copy peak); what BINDS the kernel is `binding_bound` (DESIGN.md section 3): the passes "
                            "are bound by the L1 data pipe, not by HBM",
