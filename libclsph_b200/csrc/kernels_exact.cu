@@ -406,8 +406,11 @@ __device__ __forceinline__ float len3(float x, float y, float z) {
 // collisionsv2.cl:249-336 (handle_collisions) + :9-22 (respond), with the reductions of
 // computeTimeStep (reduction.cl:66-124) and of the NEXT step's findMinMaxPosition
 // (reduction.cl:2-64) fused in, so that a step ends with one 32-byte read-back.
+#ifndef SPHB_ADVECT_MINB
+#define SPHB_ADVECT_MINB 4  // 64 registers: 4 CTAs of 256 threads per SM (72 registers uncapped: 0.38 ms; capped: 0.328; no prefetch: 0.342)
+#endif
 template <bool Q>
-__global__ void __launch_bounds__(kBlock)
+__global__ void __launch_bounds__(kBlock, SPHB_ADVECT_MINB)
     k_advect(const float4* __restrict__ pos, const float4* __restrict__ vhf,
              const float4* __restrict__ acc, float4* __restrict__ pos_out,
              float4* __restrict__ vel_out, float4* __restrict__ vhf_out, uint32_t n, float dt,
@@ -421,8 +424,16 @@ __global__ void __launch_bounds__(kBlock)
   // grid-stride over a grid sized to the machine: one set of 8 atomics per CTA, not per 256
   // particles (65 536 CTAs hammering the same 8 words serialise in L2)
   float rv[8] = {INFINITY, INFINITY, INFINITY, -INFINITY, -INFINITY, -INFINITY, -INFINITY, -INFINITY};
-  for (uint32_t i = blockIdx.x * kBlock + threadIdx.x; i < n; i += gridDim.x * kBlock) {
-    const float4 x0 = __ldg(pos + i), vh = __ldg(vhf + i), a = __ldg(acc + i);
+  // (the pass is bound by load latency, not by issue slots: the NEXT particle's three loads are
+  // requested before this one is worked on — six 16-byte loads in flight per thread instead of three)
+  const uint32_t stride = gridDim.x * kBlock;
+  uint32_t i_next = blockIdx.x * kBlock + threadIdx.x;
+  float4 x0_n = make_float4(0.f, 0.f, 0.f, 0.f), vh_n = x0_n, a_n = x0_n;
+  if (i_next < n) { x0_n = __ldg(pos + i_next); vh_n = __ldg(vhf + i_next); a_n = __ldg(acc + i_next); }
+  for (uint32_t i = i_next; i < n; i = i_next) {
+    const float4 x0 = x0_n, vh = vh_n, a = a_n;
+    i_next = i + stride;
+    if (i_next < n) { x0_n = __ldg(pos + i_next); vh_n = __ldg(vhf + i_next); a_n = __ldg(acc + i_next); }
     uint32_t o = i;  // where the result goes
     if (slab.ids) {
       // slab mode: a ghost belongs to another rank, which advects it; owned particles are
