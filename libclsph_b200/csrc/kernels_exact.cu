@@ -358,15 +358,18 @@ __global__ void __launch_bounds__(kBlock)
 #pragma unroll
     for (uint32_t k = 0; k < 4; ++k) {
       const uint32_t e = re[k];
-      // four independent loads in flight; a slot past the run reads its last element as "huge"
+      // four independent loads in flight; a slot past the run is not loaded and counts as "huge"
       for (uint32_t j = rs[k]; j < e; j += 4) {
-        const uint32_t last = e - 1;
+        uint32_t r[4];
 #pragma unroll
         for (uint32_t u = 0; u < 4; ++u) {
-          uint32_t r = __ldg(rank_prev + min(j + u, last));
-          if (j + u > last) r = 0xFFFFFFFFu;
-          before_a += r < qa ? 1u : 0u;
-          before_b += r < qb ? 1u : 0u;
+          r[u] = 0xFFFFFFFFu;
+          if (j + u < e) r[u] = __ldg(rank_prev + j + u);  // (one predicated load)
+        }
+#pragma unroll
+        for (uint32_t u = 0; u < 4; ++u) {
+          before_a += r[u] < qa ? 1u : 0u;
+          before_b += r[u] < qb ? 1u : 0u;
         }
       }
     }
