@@ -270,8 +270,14 @@ __device__ __forceinline__ void density_pair(uint32_t t, uint16_t* col, const fl
   }
 }
 
+// Residency of the density pass, measured at 16.7 M (tools/ab_builds.sh): 16 CTAs of 64 threads per
+// SM = 64 registers: 1.20 ms; 12 CTAs (80 registers) 1.23; 20 CTAs (48 registers, spills) 1.53; left
+// to the compiler with a minimum of 1 (94 registers) 1.33.
+#ifndef SPHB_DENSITY_MINB
+#define SPHB_DENSITY_MINB 16
+#endif
 template <bool Q>
-__global__ void __launch_bounds__(kUB)
+__global__ void __launch_bounds__(kUB, SPHB_DENSITY_MINB)
     k_density_union(const float4* __restrict__ pairs, const float4* __restrict__ vel,
                     const uint32_t* __restrict__ keys, const uint32_t* __restrict__ ftable,
                     float* __restrict__ rho, float* __restrict__ prs, float4* __restrict__ pv,
