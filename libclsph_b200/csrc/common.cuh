@@ -246,7 +246,8 @@ int launch_locate(const float4* pos, uint32_t* keys, const StepConsts& c, cudaSt
 // n-entry scratch; slot_tmp may alias perm (it is not used any more); src_tmp must not.
 int launch_cell_sort(const float4* pos, const StepConsts& c, uint32_t* keys_tmp, uint32_t* slot_tmp,
                      uint32_t* ftable, uint32_t* scan_scratch, uint32_t* keys_sorted, uint32_t* src_tmp,
-                     uint32_t* perm, cudaStream_t s, bool queued = false, size_t table_entries = 0);
+                     uint32_t* perm, cudaStream_t s, bool queued = false, size_t table_entries = 0,
+                     uint8_t* cell_flags = nullptr);  // one byte per cell (table_entries of them), or nullptr
 int launch_reorder(const uint32_t* perm, uint32_t n, const float4* pos_in, const float4* vel_in,
                    const float4* vhf_in, const uint32_t* rank_in, float4* pos_out, float4* vel_out,
                    float4* vhf_out, uint32_t* rank_out, cudaStream_t s, bool queued = false,

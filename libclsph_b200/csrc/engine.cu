@@ -507,7 +507,7 @@ int enqueue_queued_step(sphb_engine* e) {
   CUDA_TRY(e, (cudaError_t)queue_refresh_exact(e->qctl, s));
   CUDA_TRY(e, (cudaError_t)queue_refresh_neighbors(e->qctl, s));
   l += launch_cell_sort(e->pos[in], c, b.keys[0], b.vals[0], e->ftable, e->scan_scratch, b.keys[1], b.vals[1],
-                        b.vals[0], s, true, e->ftable_cap);
+                        b.vals[0], s, true, e->ftable_cap, e->cell_flags);
   const uint32_t* skeys = b.keys[1];
   const uint32_t* perm = b.vals[0];
   l += launch_reorder(perm, e->n, e->pos[in], e->vel[in], e->vhf[in], e->rank_cur, e->pos[mid], e->vel[mid],

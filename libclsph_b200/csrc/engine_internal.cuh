@@ -102,6 +102,7 @@ struct sphb_engine {
   float4* pairs = nullptr;    // positions as one record per pair of particles (reorder -> density)
   float4* pv = nullptr;       // position + velocity + pair factors per particle (density -> forces)
   uint32_t* ftable = nullptr;     // fine cell table, nfine + 1 entries
+  uint8_t* cell_flags = nullptr;  // one byte per fine cell, inside ftable's allocation (behind ftable_cap entries)
   size_t ftable_cap = 0;
   uint32_t* ref_table = nullptr;  // the reference's cell table, grid_cell_count (+1) entries
   size_t ref_table_cap = 0;
@@ -269,7 +270,9 @@ int ensure_tables(sphb_engine* e, size_t fine_entries, size_t ref_entries) {
     cudaFree(e->ftable);
     e->ftable = nullptr;
     e->ftable_cap = e->table_headroom ? fine_entries + fine_entries / 2 + 1024 : fine_entries;
-    CUDA_TRY(e, dev_alloc(&e->ftable, e->ftable_cap));
+    // (+ one byte per cell behind the table: the counting sort's "this cell needs ordering" flags)
+    CUDA_TRY(e, dev_alloc(&e->ftable, e->ftable_cap + e->ftable_cap / 4 + 4));
+    e->cell_flags = reinterpret_cast<uint8_t*>(e->ftable + e->ftable_cap);
   }
   if (grow_r) {
     cudaFree(e->ref_table);
@@ -299,7 +302,7 @@ int order_by_cell(sphb_engine* e, const StepConsts& c, const uint32_t** skeys, c
   if (e->sort_variant == 0) {
     PassTimer t(e, SPHB_PASS_SORT);
     t.done(launch_cell_sort(e->pos[e->cur], c, b.keys[0], b.vals[0], e->ftable, e->scan_scratch, b.keys[1],
-                            b.vals[1], b.vals[0], s));
+                            b.vals[1], b.vals[0], s, false, 0, e->cell_flags));
     e->sorted = 1;
     *skeys = b.keys[1];
     *perm = b.vals[0];

@@ -164,7 +164,10 @@ __global__ void __launch_bounds__(kBlock)
     const uint32_t b = __shfl_sync(0xffffffffu, base[u], __ffs(peers[u]) - 1);
     if (i < cc.n) {
       keys[i] = key[u];
-      slot[i] = b + __popc(peers[u] & ((1u << lane) - 1u));
+      // bits 24-31: how many particles of the cell this warp instruction ranked together (their slots
+      // ascend with their index); k_place compares it with the cell's final count.  0 = unknown.
+      const uint32_t together = cc.n <= (1u << 24) ? min((uint32_t)__popc(peers[u]), 255u) : 0u;
+      slot[i] = (b + __popc(peers[u] & ((1u << lane) - 1u))) | (together << 24);
     }
   }
 }
@@ -175,14 +178,22 @@ template <bool Q>
 __global__ void __launch_bounds__(kBlock)
     k_place(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ slot,
             const uint32_t* __restrict__ start, uint32_t n, uint32_t* __restrict__ keys_sorted,
-            uint32_t* __restrict__ perm) {
+            uint32_t* __restrict__ perm, uint8_t* __restrict__ cell_flags) {
   if (Q && !g_hot.active) return;
   const uint32_t i = blockIdx.x * kBlock + threadIdx.x;
   if (i >= n) return;
   const uint32_t key = __ldg(keys + i);
-  const uint32_t d = __ldg(start + key) + __ldg(slot + i);
+  const uint32_t w = __ldg(slot + i);
+  const bool packed = n <= (1u << 24);
+  const uint32_t s = __ldg(start + key), d = s + (packed ? (w & 0xFFFFFFu) : w);
   keys_sorted[d] = key;
   perm[d] = i;
+  if (cell_flags) {
+    // A cell whose members were ALL ranked by one warp instruction is already in ascending order
+    // of their index; any other cell with two or more members is flagged for k_order_cells.
+    const uint32_t cnt = __ldg(start + key + 1u) - s, together = packed ? (w >> 24) : 0u;
+    if (cnt > 1u && !(cnt < 255u && together == cnt)) cell_flags[key] = 1;
+  }
 }
 
 // One thread per CELL: the members of a cell that holds two or more particles are put in
@@ -230,11 +241,13 @@ __device__ void order_members(uint32_t* __restrict__ a, uint32_t m) {
 }
 template <bool Q>
 __global__ void __launch_bounds__(kBlock)
-    k_order_cells(const uint32_t* __restrict__ start, uint32_t cells_arg, uint32_t* __restrict__ perm) {
+    k_order_cells(const uint32_t* __restrict__ start, uint32_t cells_arg, uint32_t* __restrict__ perm,
+                  const uint8_t* __restrict__ cell_flags) {
   if (Q && !g_hot.active) return;
   const uint32_t cells = Q ? g_hot.c.nfine : cells_arg;
   const uint32_t cell = blockIdx.x * kBlock + threadIdx.x;
   if (cell >= cells) return;
+  if (cell_flags && !cell_flags[cell]) return;  // single member, or ranked in order already (k_place)
   const uint32_t s = __ldg(start + cell), e = __ldg(start + cell + 1u);
   if (e - s >= 2u) order_members(perm + s, e - s);
 }
@@ -778,9 +791,10 @@ int launch_locate(const float4* pos, uint32_t* keys, const StepConsts& c, cudaSt
 // on the device (entries past it scan to n and are never read).
 int launch_cell_sort(const float4* pos, const StepConsts& c, uint32_t* keys_tmp, uint32_t* slot_tmp,
                      uint32_t* ftable, uint32_t* scan_scratch, uint32_t* keys_sorted, uint32_t* src_tmp,
-                     uint32_t* perm, cudaStream_t s, bool queued, size_t table_entries) {
+                     uint32_t* perm, cudaStream_t s, bool queued, size_t table_entries, uint8_t* cell_flags) {
   if (!queued) table_entries = (size_t)c.nfine + 1;
   cudaMemsetAsync(ftable, 0, sizeof(uint32_t) * table_entries, s);
+  if (cell_flags) cudaMemsetAsync(cell_flags, 0, table_entries, s);
   const unsigned loc_grid = (c.n + kBlock * kLocPer - 1) / (kBlock * kLocPer);
   // The slots live in src_tmp, NOT in slot_tmp: the callers hand the same buffer as slot_tmp and as
   // perm, and the placement writes perm while other threads still read their slots.
@@ -792,11 +806,11 @@ int launch_cell_sort(const float4* pos, const StepConsts& c, uint32_t* keys_tmp,
   // (the placement writes the permutation directly; k_order_cells then orders each cell in place)
   const unsigned cell_grid = (unsigned)((table_entries - 1 + kBlock - 1) / kBlock);
   if (queued) {
-    k_place<true><<<blocks_for(c.n), kBlock, 0, s>>>(keys_tmp, slots, ftable, c.n, keys_sorted, perm);
-    k_order_cells<true><<<cell_grid, kBlock, 0, s>>>(ftable, 0u, perm);
+    k_place<true><<<blocks_for(c.n), kBlock, 0, s>>>(keys_tmp, slots, ftable, c.n, keys_sorted, perm, cell_flags);
+    k_order_cells<true><<<cell_grid, kBlock, 0, s>>>(ftable, 0u, perm, cell_flags);
   } else {
-    k_place<false><<<blocks_for(c.n), kBlock, 0, s>>>(keys_tmp, slots, ftable, c.n, keys_sorted, perm);
-    k_order_cells<false><<<cell_grid, kBlock, 0, s>>>(ftable, c.nfine, perm);
+    k_place<false><<<blocks_for(c.n), kBlock, 0, s>>>(keys_tmp, slots, ftable, c.n, keys_sorted, perm, cell_flags);
+    k_order_cells<false><<<cell_grid, kBlock, 0, s>>>(ftable, c.nfine, perm, cell_flags);
   }
   return l + 2;
 }
