@@ -168,7 +168,8 @@ def kernel_source_hash():
     capture under profiles/ was taken on, and what this run executes."""
     import hashlib
     h = hashlib.sha256()
-    for f in ("kernels_neighbors.cu", "neighbors_common.cuh", "neighbors_v1.cuh", "common.cuh"):
+    for f in ("kernels_neighbors.cu", "neighbors_common.cuh", "neighbors_v1.cuh", "common.cuh", "kernels_exact.cu",
+              "kernels_sort.cu"):
         h.update(open(os.path.join(ROOT, "libclsph_b200", "csrc", f), "rb").read())
     return h.hexdigest()[:16]
 
