@@ -270,8 +270,9 @@ int ensure_tables(sphb_engine* e, size_t fine_entries, size_t ref_entries) {
     cudaFree(e->ftable);
     e->ftable = nullptr;
     e->ftable_cap = e->table_headroom ? fine_entries + fine_entries / 2 + 1024 : fine_entries;
-    // (+ one byte per cell behind the table: the counting sort's "this cell needs ordering" flags)
-    CUDA_TRY(e, dev_alloc(&e->ftable, e->ftable_cap + e->ftable_cap / 4 + 4));
+    e->ftable_cap = (e->ftable_cap + 3) & ~(size_t)3;  // the flags behind the table start 16-byte aligned
+    // (+ one byte per cell behind the table, padded to 16: the counting sort's "this cell needs ordering" flags)
+    CUDA_TRY(e, dev_alloc(&e->ftable, e->ftable_cap + e->ftable_cap / 4 + 8));
     e->cell_flags = reinterpret_cast<uint8_t*>(e->ftable + e->ftable_cap);
   }
   if (grow_r) {

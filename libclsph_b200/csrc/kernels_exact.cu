@@ -239,15 +239,32 @@ __device__ void order_members(uint32_t* __restrict__ a, uint32_t m) {
     sift(0, end);
   }
 }
+constexpr uint32_t kCellsPerThread = 16;  // with flags: one 16-byte load decides for 16 cells
 template <bool Q>
 __global__ void __launch_bounds__(kBlock)
     k_order_cells(const uint32_t* __restrict__ start, uint32_t cells_arg, uint32_t* __restrict__ perm,
                   const uint8_t* __restrict__ cell_flags) {
   if (Q && !g_hot.active) return;
   const uint32_t cells = Q ? g_hot.c.nfine : cells_arg;
+  if (cell_flags) {
+    // (one thread per cell would be bound by launching 17 M threads that read one byte each)
+    const uint32_t first = (blockIdx.x * kBlock + threadIdx.x) * kCellsPerThread;
+    if (first >= cells) return;
+    const uint4 f = __ldg(reinterpret_cast<const uint4*>(cell_flags + first));  // (the flags are padded to 16)
+    if (!(f.x | f.y | f.z | f.w)) return;  // nothing to order: single members, or ranked in order already
+    const uint32_t w[4] = {f.x, f.y, f.z, f.w};
+#pragma unroll
+    for (uint32_t k = 0; k < kCellsPerThread; ++k) {
+      const uint32_t cell = first + k;
+      if (((w[k >> 2] >> (8u * (k & 3u))) & 0xffu) && cell < cells) {
+        const uint32_t s = __ldg(start + cell), e = __ldg(start + cell + 1u);
+        if (e - s >= 2u) order_members(perm + s, e - s);
+      }
+    }
+    return;
+  }
   const uint32_t cell = blockIdx.x * kBlock + threadIdx.x;
   if (cell >= cells) return;
-  if (cell_flags && !cell_flags[cell]) return;  // single member, or ranked in order already (k_place)
   const uint32_t s = __ldg(start + cell), e = __ldg(start + cell + 1u);
   if (e - s >= 2u) order_members(perm + s, e - s);
 }
@@ -794,7 +811,7 @@ int launch_cell_sort(const float4* pos, const StepConsts& c, uint32_t* keys_tmp,
                      uint32_t* perm, cudaStream_t s, bool queued, size_t table_entries, uint8_t* cell_flags) {
   if (!queued) table_entries = (size_t)c.nfine + 1;
   cudaMemsetAsync(ftable, 0, sizeof(uint32_t) * table_entries, s);
-  if (cell_flags) cudaMemsetAsync(cell_flags, 0, table_entries, s);
+  if (cell_flags) cudaMemsetAsync(cell_flags, 0, (table_entries + 15) & ~(size_t)15, s);
   const unsigned loc_grid = (c.n + kBlock * kLocPer - 1) / (kBlock * kLocPer);
   // The slots live in src_tmp, NOT in slot_tmp: the callers hand the same buffer as slot_tmp and as
   // perm, and the placement writes perm while other threads still read their slots.
@@ -804,7 +821,8 @@ int launch_cell_sort(const float4* pos, const StepConsts& c, uint32_t* keys_tmp,
   else k_locate_count<false><<<loc_grid, kBlock, 0, s>>>(pos, keys_tmp, slots, ftable, c);
   int l = 1 + launch_exclusive_sum(ftable, (uint32_t)table_entries, scan_scratch, s);
   // (the placement writes the permutation directly; k_order_cells then orders each cell in place)
-  const unsigned cell_grid = (unsigned)((table_entries - 1 + kBlock - 1) / kBlock);
+  const size_t cell_threads = cell_flags ? (table_entries - 1 + kCellsPerThread - 1) / kCellsPerThread : table_entries - 1;
+  const unsigned cell_grid = (unsigned)((cell_threads + kBlock - 1) / kBlock);
   if (queued) {
     k_place<true><<<blocks_for(c.n), kBlock, 0, s>>>(keys_tmp, slots, ftable, c.n, keys_sorted, perm, cell_flags);
     k_order_cells<true><<<cell_grid, kBlock, 0, s>>>(ftable, 0u, perm, cell_flags);
